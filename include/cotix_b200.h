@@ -1,0 +1,273 @@
+/*
+ * cotix_b200.h — C-ABI of the B200-native batched rigid-body step engine for cotix.
+ *
+ * This is the drop-in boundary. The reference (the `cotix` Python/JAX package) has no
+ * FFI of its own: its hot path is a set of pure Python callables on JAX pytrees. Each
+ * entry point below replaces one of those callables for a whole batch and cites the
+ * reference interface it stands in for (paths relative to the reference root).
+ *
+ * Conventions (all entry points):
+ *   - extern "C", plain pointers and sizes; no torch / jax types.
+ *   - return 0 on success, a negative COTIX_E* code on error; cotix_last_error()
+ *     returns a thread-local message for the last failure.
+ *   - "device" entry points only ENQUEUE work on the given stream (cudaStream_t passed as
+ *     void*); they never synchronise, never allocate, and are CUDA-Graph capturable.
+ *   - "host" entry points (suffix _host) take HOST buffers, copy in, run, copy out and
+ *     synchronise; they are the reference-facing convenience path and what bench.py's
+ *     `e2e` number times.
+ *   - "no value" is NaN, never an error (reference: cotix/_contacts.py:19-24).
+ *   - There is no CPU fallback anywhere in this library.
+ */
+#ifndef COTIX_B200_H
+#define COTIX_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define COTIX_ABI_VERSION 1
+
+/* error codes */
+#define COTIX_OK 0
+#define COTIX_EINVAL (-1)   /* bad argument (null pointer, bad size, bad enum)            */
+#define COTIX_ECUDA (-2)    /* a CUDA runtime call failed; see cotix_last_error()          */
+#define COTIX_ESHAPE (-3)   /* shape-type pair not in the reference dispatch table         */
+#define COTIX_ENODEV (-4)   /* no usable sm_100 device                                     */
+
+/* ------------------------------------------------------------------------------------ */
+/* Shapes (reference: cotix/_convex_shapes.py Circle :10-47, AABB :50-133,               */
+/* AbstractPolygon :136-194).  One record = 16 floats = 64 B, so a warp reads 2 KB of     */
+/* contiguous records.                                                                    */
+/*   rec[0] type   0 = Circle, 1 = AABB, 2 = Polygon (value stored as a float)            */
+/*   rec[1] n      polygon vertex count 3..6 (float); ignored otherwise                   */
+/*   rec[2] radius circle radius; ignored otherwise                                       */
+/*   rec[3] pad                                                                           */
+/*   rec[4..15]    Circle: position = rec[4..5];  AABB: lower = rec[4..5], upper =        */
+/*                 rec[6..7];  Polygon: vertices k = rec[4+2k .. 5+2k], ALREADY in the    */
+/*                 order Polygon.__init__ leaves them (order_clockwise,                   */
+/*                 cotix/_geometry_utils.py:60-67) — use cotix_order_clockwise().         */
+/* ------------------------------------------------------------------------------------ */
+#define COTIX_SHAPE_CIRCLE 0
+#define COTIX_SHAPE_AABB 1
+#define COTIX_SHAPE_POLYGON 2
+#define COTIX_SHAPE_REC_FLOATS 16
+#define COTIX_MAX_POLY 6
+
+typedef struct CotixNarrowParams {
+  float init_dir[2];     /* GJK start direction = random_direction(PRNGKey(1)),          */
+                         /* cotix/_collisions.py:287-298 (a global constant there)       */
+  int32_t gjk_max_iters; /* 32, cotix/_collisions.py:101                                 */
+  int32_t epa_iters_circle_poly; /* 128, cotix/_contacts.py:163                           */
+} CotixNarrowParams;
+
+/* status bits written per pair / per env */
+#define COTIX_ST_GJK_CAP 0x1u      /* GJK hit gjk_max_iters                               */
+#define COTIX_ST_EPA_CAP 0x2u      /* EPA used every allowed iteration                    */
+#define COTIX_ST_NAN 0x4u          /* a NaN reached the dynamic state                     */
+#define COTIX_ST_GROUND_NAN 0x8u   /* a non-finite impulse hit the static ground body     */
+#define COTIX_ST_CCP_ERR 0x10u     /* circle_vs_aabb eqx.error_if condition               */
+                                   /* (cotix/_contacts.py:105-107) was true               */
+#define COTIX_ST_ANGLE_RANGE 0x20u /* |angle| >= 1e9: sin/cos defined as NaN              */
+
+/*
+ * Narrowphase sweep: one contact query per pair (a[k], b[k]).
+ * Replaces cotix/_contacts.py: circle_vs_circle :30-58, aabb_vs_aabb :61-96,
+ * circle_vs_aabb :99-154, circle_vs_polygon :157-202, aabb_vs_polygon :270-291,
+ * polygon_vs_polygon :294-315 (which call GJK cotix/_collisions.py:20-112,277-310 and
+ * EPA :115-273,313-329).  Dispatch follows the key order of `_contact_funcs`
+ * (cotix/_colliders.py:21-35): type(a) <= type(b) in the order Circle < AABB < Polygon;
+ * any other order makes the pair's result NaN and sets bit 0x80 in its status byte.
+ *   exists[k]  1 iff the ContactInfo is not NaN (ContactInfo.isnan(), _contacts.py:26)
+ *   pen[2k..]  penetration_vector (zeros when no contact, as ContactInfo.nan())
+ *   cp[2k..]   contact_point (NaN, NaN when no contact)
+ *   status[k]  COTIX_ST_* bits; may be NULL
+ * All pointers are DEVICE pointers; a, b are [n][16] floats.
+ */
+int cotix_narrowphase(void* stream, int64_t n, const float* a, const float* b,
+                      uint8_t* exists, float* pen, float* cp, uint8_t* status,
+                      const CotixNarrowParams* params);
+
+/* Same query with HOST buffers: copies in, runs, copies out, synchronises. */
+int cotix_narrowphase_host(int device, int64_t n, const float* a, const float* b,
+                           uint8_t* exists, float* pen, float* cp, uint8_t* status,
+                           const CotixNarrowParams* params);
+
+/*
+ * order_clockwise (cotix/_geometry_utils.py:60-67) for a batch of polygons, in place on
+ * DEVICE records (non-polygon records are left untouched).  This is what
+ * Polygon.__init__ (cotix/_convex_shapes.py:143-144,197-229) does to its vertices.
+ */
+int cotix_order_clockwise(void* stream, int64_t n, float* recs);
+
+/* ------------------------------------------------------------------------------------ */
+/* LunarLander (reference: cotix/_lunar_lander.py, examples/test_viz.py:25-44).           */
+/*                                                                                        */
+/* State = struct-of-arrays over the env axis: one float/uint32 buffer `state[f*ld + e]`  */
+/* for field f < COTIX_LUNAR_NF and env e < B, ld >= B.  Bodies follow the reference      */
+/* order (cotix/_lunar_lander.py:143): 0 lander, 1 right_leg, 2 left_leg.  The ground     */
+/* (body 3) is static — mass = inertia = inf, position = angle = 0 — so only its terrain  */
+/* is stored.  Per body the 6 evolving DynamicBody leaves (cotix/_bodies.py:189-206).     */
+/* ------------------------------------------------------------------------------------ */
+#define COTIX_LUNAR_NBODY 3
+#define COTIX_F_PX 0
+#define COTIX_F_PY 1
+#define COTIX_F_VX 2
+#define COTIX_F_VY 3
+#define COTIX_F_ANG 4
+#define COTIX_F_ANGVEL 5
+#define COTIX_F_BODY(b, f) ((b) * 6 + (f)) /* 0..17                                        */
+#define COTIX_F_HEIGHT0 18 /* 18..25: terrain heights[0..7], _lunar_lander.py:110-114       */
+#define COTIX_F_KNOT0 26   /* 26..29: random x-knots positions[1],[2],[5],[6], :116-125     */
+#define COTIX_F_KEY0 30    /* uint32: PRNG key word 0                                       */
+#define COTIX_F_KEY1 31    /* uint32: PRNG key word 1                                       */
+#define COTIX_F_STEPS 32   /* uint32: steps taken in this episode                           */
+#define COTIX_F_STATUS 33  /* uint32: sticky COTIX_ST_* bits of this episode                */
+#define COTIX_F_RETURN 34  /* float : undiscounted return of this episode so far            */
+#define COTIX_F_SHAPING 35 /* float : previous shaping potential (NaN = none yet)           */
+#define COTIX_LUNAR_NF 36
+#define COTIX_LUNAR_NOBS 8
+
+#define COTIX_RNG_THREEFRY 0 /* jax.random default (threefry2x32), bit-exact key chain      */
+#define COTIX_RNG_PHILOX 1   /* Philox4x32-10 counter mode, same distributions              */
+
+/* done[] codes */
+#define COTIX_DONE_NO 0
+#define COTIX_DONE_CRASH 1    /* lander body touched the ground                             */
+#define COTIX_DONE_OOB 2      /* left the arena                                             */
+#define COTIX_DONE_LANDED 3   /* both legs on the ground and at rest                        */
+#define COTIX_DONE_TIMEOUT 4  /* max_episode_steps reached                                  */
+#define COTIX_DONE_NAN 5      /* non-finite state                                           */
+
+typedef struct CotixLunarParams {
+  /* ---- literals of the reference step; defaults reproduce it exactly --------------- */
+  float dt;               /* 1e-2   examples/test_viz.py:26                               */
+  float gravity_dv[2];    /* (0,-0.002) added to the lander velocity each step, :27-31    */
+  float init_dir[2];      /* GJK start direction, cotix/_collisions.py:287-298            */
+  float baumgarte;        /* 0.3    cotix/_collision_resolution.py:105                    */
+  float baumgarte_dt;     /* 0.01   cotix/_collision_resolution.py:115                    */
+  float coin_p;           /* 0.5    cotix/_colliders.py:220                               */
+  float spring_kp;        /* 1.0    cotix/_lunar_lander.py:189                            */
+  float spring_kv0;       /* 0.1                                                          */
+  float spring_kv;        /* 0.05                                                         */
+  float leg_damping;      /* 0.95   cotix/_lunar_lander.py:208,211                        */
+  float body_props[4][4]; /* per body: mass, inertia, elasticity, friction (:78-141)      */
+  float lander_local[6][2];   /* Polygon6 local vertices in stored order (:30)            */
+  float leg_local[2][4][2];   /* [0] right_leg (body 1), [1] left_leg (body 2) (:32-72)   */
+  float joint_local[4][2];    /* lander-side anchors: left j1, left j2, right j1, right j2 */
+  float leg_joint2_local[2];  /* (0, 0.4)  (:158,173)                                      */
+  float lander_start[3];      /* x, y, angle = 0, 5, 0.01 (:74,78-87)                      */
+  float leg_offset[2][2];     /* [0] right (-1.2,-0.4), [1] left (+1.2,-0.4) (:75-76)      */
+  float ground_floor;         /* -10  (:129,131)                                           */
+  float terrain_x_outer;      /* 100  (:117,124)                                           */
+  float pad_half_width;       /* 2    (:120-121)                                           */
+  float pad_y;                /* -2   (:112-113)                                           */
+  int32_t gjk_max_iters;      /* 32                                                        */
+  int32_t rng_mode;           /* COTIX_RNG_*                                               */
+  /* ---- new env logic the north_star asks for; the reference has none of it ---------- */
+  int32_t substeps;           /* K physics sub-steps per call with the same action (>=1)   */
+  int32_t auto_reset;         /* 1: a finished env is reset inside the same launch          */
+  int32_t judge_enabled;      /* 0: reward = 0, done only on NaN/timeout (parity runs)      */
+  int32_t max_episode_steps;  /* 0 = no limit                                               */
+  int32_t reset_perturb;      /* 1: randomise the lander pose at reset                      */
+  float main_engine_dv;       /* lander dv per step at full main throttle                   */
+  float side_engine_dv;       /* lateral dv per step at full side throttle                  */
+  float side_engine_dw;       /* angular-velocity change per step at full side throttle     */
+  float x_limit, y_limit;     /* arena: |x| < x_limit, y < y_limit                          */
+  float land_speed, land_angvel; /* "at rest" thresholds for COTIX_DONE_LANDED             */
+  float reset_x[2], reset_y[2], reset_angle[2]; /* uniform ranges (reset_perturb)           */
+  float reset_v, reset_w;     /* uniform half-ranges for velocity / angular velocity        */
+  uint32_t philox_seed[2];    /* stream seed for COTIX_RNG_PHILOX                           */
+} CotixLunarParams;
+
+/* Fill *p with the reference literals (leaving the new env logic disabled). */
+int cotix_lunar_default_params(CotixLunarParams* p);
+
+/*
+ * reset(key): replaces the LunarLander constructor cotix/_lunar_lander.py:29-143.
+ * keys: DEVICE uint32 [B][2]; state: DEVICE [COTIX_LUNAR_NF][ld].
+ */
+int cotix_lunar_reset(void* stream, int64_t B, const uint32_t* keys, float* state,
+                      int64_t ld, const CotixLunarParams* p);
+
+/*
+ * step(state, action): replaces the composed step f(env, key) of
+ * examples/test_viz.py:25-44 = ExplicitEulerPhysics.step (cotix/_physics_solvers.py:16-33)
+ * -> gravity -> RandomizedCollider.resolve (cotix/_colliders.py:74-351) -> key split ->
+ * LunarLander.step (cotix/_lunar_lander.py:145-218), `substeps` times, plus the judge /
+ * auto-reset logic (template: cotix/_envs.py:37-132).
+ *   state_in / state_out  DEVICE [NF][ld]; may alias
+ *   action   DEVICE [2][ld] (main, side) or NULL for zero action
+ *   reward   DEVICE [B] float or NULL;  done DEVICE [B] uint8 or NULL
+ *   obs      DEVICE [COTIX_LUNAR_NOBS][ld] float or NULL
+ *            (x, y, vx, vy, angle, angvel, right-leg contact, left-leg contact)
+ */
+int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* state_out,
+                     int64_t ld, const float* action, float* reward, uint8_t* done,
+                     float* obs, const CotixLunarParams* p);
+
+/*
+ * Host-facing env handle: owns the device state of B envs on `device`, keeps it
+ * resident, and exposes reset/step with HOST buffers (pinned or pageable).  One step =
+ * H2D(action) -> kernel -> D2H(obs, reward, done), on the handle's own stream.
+ */
+typedef struct CotixLunarEnv CotixLunarEnv;
+int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B,
+                           const CotixLunarParams* p);
+int cotix_lunar_env_destroy(CotixLunarEnv* env);
+int cotix_lunar_env_reset_host(CotixLunarEnv* env, const uint32_t* keys /*[B][2]*/);
+int cotix_lunar_env_step_host(CotixLunarEnv* env, const float* action /*[2][B]*/,
+                              float* obs /*[8][B]*/, float* reward /*[B]*/,
+                              uint8_t* done /*[B]*/);
+/* copy the resident state out to / in from a HOST [NF][B] buffer */
+int cotix_lunar_env_get_state_host(CotixLunarEnv* env, float* state);
+int cotix_lunar_env_set_state_host(CotixLunarEnv* env, const float* state);
+/* device pointer of the resident state ([NF][B], ld = B) and the handle's stream */
+float* cotix_lunar_env_state_ptr(CotixLunarEnv* env);
+void* cotix_lunar_env_stream(CotixLunarEnv* env);
+/*
+ * Roll `n_steps` steps with a fixed DEVICE action buffer (or NULL) as ONE replayed CUDA
+ * graph of `n_steps` kernel nodes (captured on first use per n_steps).  Sum of rewards
+ * per env is accumulated into ret_sum[B] (DEVICE, may be NULL).
+ */
+int cotix_lunar_env_rollout_graph(CotixLunarEnv* env, int32_t n_steps,
+                                  const float* action_dev);
+
+/* ------------------------------------------------------------------------------------ */
+/* Small primitives exposed for parity tests of the reference's leaf functions.           */
+/* ------------------------------------------------------------------------------------ */
+/* ExplicitEulerPhysics._single_body_step, cotix/_physics_solvers.py:17-24; arrays [n]    */
+int cotix_euler_step(void* stream, int64_t n, float* px, float* py, const float* vx,
+                     const float* vy, float* ang, const float* angvel, float dt);
+/* resolve_collision, cotix/_collision_resolution.py:52-151; bodies as [n][10] floats in   */
+/* DynamicBody leaf order (mass, inertia, px, py, vx, vy, angle, angvel, elasticity,       */
+/* friction), contact as pen[n][2], cp[n][2]; updated in place                             */
+int cotix_resolve_collision(void* stream, int64_t n, float* body1, float* body2,
+                            const float* pen, const float* cp, float baumgarte,
+                            float baumgarte_dt);
+/* get_support for a batch of (record, direction) pairs -> out[n][2];                      */
+/* cotix/_convex_shapes.py:22-26,62-66,149-155                                             */
+int cotix_support(void* stream, int64_t n, const float* recs, const float* dirs,
+                  float* out);
+/* jax.random primitives on the device, for known-answer tests of the RNG restatement:    */
+/* out[i] = threefry2x32(key, (x0[i], x1[i])) ; out is [n][2]                              */
+int cotix_threefry2x32(void* stream, int64_t n, uint32_t k0, uint32_t k1,
+                       const uint32_t* x0, const uint32_t* x1, uint32_t* out);
+/* out[i] = philox4x32_10(key, ctr[i]) ; ctr, out are [n][4]                               */
+int cotix_philox4x32(void* stream, int64_t n, uint32_t k0, uint32_t k1,
+                     const uint32_t* ctr, uint32_t* out);
+
+/* ------------------------------------------------------------------------------------ */
+const char* cotix_last_error(void);
+int cotix_abi_version(void);
+/* number of kernels this library has launched in this process (all streams) */
+int64_t cotix_launch_count(void);
+/* name, SM count and compute capability of `device`; returns 0 or COTIX_E*           */
+int cotix_device_info(int device, char* name, int name_len, int* sm_count, int* cc_major,
+                      int* cc_minor);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COTIX_B200_H */
