@@ -1412,6 +1412,8 @@ void lunar_substep(Env& e, float a_main, float a_side, const CotixLunarParams& P
   build_bodies(e, P, bodies);
   // physics.step(env.bodies, dt) :26
   for (auto& b : bodies) euler_step(b, P.dt);
+  for (int b = 0; b < 3; ++b)
+    if (!(fabsf(bodies[(size_t)b].angle) < 1.0e9f)) e.f[COTIX_F_STATUS] = u2f(f2u(e.f[COTIX_F_STATUS]) | COTIX_ST_ANGLE_RANGE);
   // gravity on the lander only :27-31
   bodies[0].vel = bodies[0].vel + mk(P.gravity_dv[0], P.gravity_dv[1]);
   // engines (new): zero action leaves the step bit-identical to the reference
@@ -1445,7 +1447,6 @@ void lunar_substep(Env& e, float a_main, float a_side, const CotixLunarParams& P
   ColliderOut co;
   collider_resolve(bodies, rng, mk(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters, P.coin_p,
                    P.baumgarte, P.baumgarte_dt, dedupe, &co);
-  status |= co.status;
   // key, next_key = jr.split(key) :39
   if (P.rng_mode == COTIX_RNG_THREEFRY) {
     Key ks[2];

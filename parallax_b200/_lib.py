@@ -1,0 +1,208 @@
+"""Loader / builder of libcotix_b200.so — the C-ABI in include/cotix_b200.h.
+
+The library is built in-tree with nvcc for sm_100a only (`-gencode
+arch=compute_100a,code=sm_100a -lineinfo -fmad=false`).  There is no CPU fallback: if the
+shared object is missing or a compute entry point is called without a B200-class device the
+call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import shutil
+import subprocess
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_CSRC = os.path.join(_PKG, "csrc")
+LIB_PATH = os.path.join(_PKG, "libcotix_b200.so")
+SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu"]
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-lineinfo", "-O3", "-std=c++17",
+    "-fmad=false",            # IEEE-exact fp32: no FMA contraction (see csrc/cx_math.cuh)
+    "-Xcompiler", "-fPIC", "-shared",
+]
+
+
+class CotixError(RuntimeError):
+    pass
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise CotixError("nvcc not found; cannot build libcotix_b200.so")
+
+
+def _stale() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC)]
+    deps.append(os.path.join(_PKG, "..", "include", "cotix_b200.h"))
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile every CUDA translation unit into parallax_b200/libcotix_b200.so."""
+    if not force and not _stale():
+        return LIB_PATH
+    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH, *[os.path.join(_CSRC, s) for s in SOURCES]]
+    if verbose:
+        cmd.insert(1, "-Xptxas")
+        cmd.insert(2, "-v")
+    env = dict(os.environ)
+    env.pop("CXX", None)
+    res = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    if res.returncode != 0:
+        raise CotixError("nvcc failed:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+class NarrowParams(C.Structure):
+    """CotixNarrowParams"""
+
+    _fields_ = [
+        ("init_dir", C.c_float * 2),
+        ("gjk_max_iters", C.c_int32),
+        ("epa_iters_circle_poly", C.c_int32),
+    ]
+
+
+class LunarParams(C.Structure):
+    """CotixLunarParams (include/cotix_b200.h); defaults = the reference's literals."""
+
+    _fields_ = [
+        ("dt", C.c_float),
+        ("gravity_dv", C.c_float * 2),
+        ("init_dir", C.c_float * 2),
+        ("baumgarte", C.c_float),
+        ("baumgarte_dt", C.c_float),
+        ("coin_p", C.c_float),
+        ("spring_kp", C.c_float),
+        ("spring_kv0", C.c_float),
+        ("spring_kv", C.c_float),
+        ("leg_damping", C.c_float),
+        ("body_props", (C.c_float * 4) * 4),
+        ("lander_local", (C.c_float * 2) * 6),
+        ("leg_local", ((C.c_float * 2) * 4) * 2),
+        ("joint_local", (C.c_float * 2) * 4),
+        ("leg_joint2_local", C.c_float * 2),
+        ("lander_start", C.c_float * 3),
+        ("leg_offset", (C.c_float * 2) * 2),
+        ("ground_floor", C.c_float),
+        ("terrain_x_outer", C.c_float),
+        ("pad_half_width", C.c_float),
+        ("pad_y", C.c_float),
+        ("gjk_max_iters", C.c_int32),
+        ("rng_mode", C.c_int32),
+        ("substeps", C.c_int32),
+        ("auto_reset", C.c_int32),
+        ("judge_enabled", C.c_int32),
+        ("max_episode_steps", C.c_int32),
+        ("reset_perturb", C.c_int32),
+        ("main_engine_dv", C.c_float),
+        ("side_engine_dv", C.c_float),
+        ("side_engine_dw", C.c_float),
+        ("x_limit", C.c_float),
+        ("y_limit", C.c_float),
+        ("land_speed", C.c_float),
+        ("land_angvel", C.c_float),
+        ("reset_x", C.c_float * 2),
+        ("reset_y", C.c_float * 2),
+        ("reset_angle", C.c_float * 2),
+        ("reset_v", C.c_float),
+        ("reset_w", C.c_float),
+        ("philox_seed", C.c_uint32 * 2),
+    ]
+
+    def copy(self) -> "LunarParams":
+        q = LunarParams()
+        C.memmove(C.byref(q), C.byref(self), C.sizeof(LunarParams))
+        return q
+
+
+# every symbol include/cotix_b200.h declares
+EXPORTS = [
+    "cotix_narrowphase", "cotix_narrowphase_host", "cotix_order_clockwise",
+    "cotix_lunar_default_params", "cotix_lunar_reset", "cotix_lunar_step",
+    "cotix_lunar_env_create", "cotix_lunar_env_destroy", "cotix_lunar_env_reset_host",
+    "cotix_lunar_env_step_host", "cotix_lunar_env_get_state_host",
+    "cotix_lunar_env_set_state_host", "cotix_lunar_env_state_ptr", "cotix_lunar_env_stream",
+    "cotix_lunar_env_rollout_graph", "cotix_euler_step", "cotix_resolve_collision",
+    "cotix_support", "cotix_threefry2x32", "cotix_philox4x32", "cotix_last_error",
+    "cotix_abi_version", "cotix_launch_count", "cotix_device_info",
+]
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """The loaded shared library.  Raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CotixError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (nvcc, sm_100a).  There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    L.cotix_last_error.restype = C.c_char_p
+    L.cotix_launch_count.restype = C.c_int64
+    L.cotix_lunar_env_state_ptr.restype = C.c_void_p
+    L.cotix_lunar_env_stream.restype = C.c_void_p
+    vp, i64 = C.c_void_p, C.c_int64
+    L.cotix_narrowphase.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, C.POINTER(NarrowParams)]
+    L.cotix_narrowphase_host.argtypes = [C.c_int, i64, vp, vp, vp, vp, vp, vp, C.POINTER(NarrowParams)]
+    L.cotix_order_clockwise.argtypes = [vp, i64, vp]
+    L.cotix_support.argtypes = [vp, i64, vp, vp, vp]
+    L.cotix_lunar_default_params.argtypes = [C.POINTER(LunarParams)]
+    L.cotix_lunar_reset.argtypes = [vp, i64, vp, vp, i64, C.POINTER(LunarParams)]
+    L.cotix_lunar_step.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams)]
+    L.cotix_lunar_env_create.argtypes = [C.POINTER(vp), C.c_int, i64, C.POINTER(LunarParams)]
+    L.cotix_lunar_env_destroy.argtypes = [vp]
+    L.cotix_lunar_env_reset_host.argtypes = [vp, vp]
+    L.cotix_lunar_env_step_host.argtypes = [vp, vp, vp, vp, vp]
+    L.cotix_lunar_env_get_state_host.argtypes = [vp, vp]
+    L.cotix_lunar_env_set_state_host.argtypes = [vp, vp]
+    L.cotix_lunar_env_state_ptr.argtypes = [vp]
+    L.cotix_lunar_env_stream.argtypes = [vp]
+    L.cotix_lunar_env_rollout_graph.argtypes = [vp, C.c_int32, vp]
+    L.cotix_euler_step.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, C.c_float]
+    L.cotix_resolve_collision.argtypes = [vp, i64, vp, vp, vp, vp, C.c_float, C.c_float]
+    L.cotix_threefry2x32.argtypes = [vp, i64, C.c_uint32, C.c_uint32, vp, vp, vp]
+    L.cotix_philox4x32.argtypes = [vp, i64, C.c_uint32, C.c_uint32, vp, vp]
+    L.cotix_device_info.argtypes = [C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    if L.cotix_abi_version() != 1:
+        raise CotixError("libcotix_b200.so ABI version mismatch")
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        msg = lib().cotix_last_error()
+        raise CotixError(f"cotix error {rc}: {msg.decode() if msg else ''}")
+
+
+def launch_count() -> int:
+    return int(lib().cotix_launch_count())
+
+
+def default_lunar_params() -> LunarParams:
+    p = LunarParams()
+    check(lib().cotix_lunar_default_params(C.byref(p)))
+    return p
+
+
+def default_narrow_params() -> NarrowParams:
+    lp = default_lunar_params()
+    p = NarrowParams()
+    p.init_dir[0], p.init_dir[1] = lp.init_dir[0], lp.init_dir[1]
+    p.gjk_max_iters = 32
+    p.epa_iters_circle_poly = 128
+    return p

@@ -1,0 +1,390 @@
+// abi_lunar.cu — LunarLander entry points of the C-ABI (include/cotix_b200.h).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <new>
+
+#include "../../include/cotix_b200.h"
+#include "cx_launch.cuh"
+#include "cx_rng.cuh"
+
+extern "C" int cx_launch_lunar_step(cudaStream_t, int64_t, const float*, float*, int64_t,
+                                    const float*, float*, uint8_t*, float*, const CotixLunarParams*);
+extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, float*, int64_t,
+                                     const CotixLunarParams*);
+
+#define CXL_REQUIRE(cond, msg)               \
+  do {                                       \
+    if (!(cond)) {                           \
+      cx_set_error("%s: %s", __func__, msg); \
+      return COTIX_EINVAL;                   \
+    }                                        \
+  } while (0)
+#define CXL_CUDA(call)                                                            \
+  do {                                                                            \
+    cudaError_t e_ = (call);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      cx_set_error("%s: %s failed: %s", __func__, #call, cudaGetErrorString(e_)); \
+      return COTIX_ECUDA;                                                         \
+    }                                                                             \
+  } while (0)
+
+namespace {
+
+// ---- host-side constants of the scene (computed once, with the engine's own trig) ------
+void host_order_clockwise(float (*v)[2], int n) {  // cotix/_geometry_utils.py:60-67
+  float sx = 0.0f, sy = 0.0f;
+  for (int i = 0; i < n; ++i) {
+    sx = sx + v[i][0];
+    sy = sy + v[i][1];
+  }
+  float mx = sx / (float)n, my = sy / (float)n;
+  float ang[8];
+  int idx[8];
+  for (int i = 0; i < n; ++i) {
+    ang[i] = cx_atan2f(v[i][1] - my, v[i][0] - mx);
+    idx[i] = i;
+  }
+  for (int i = 1; i < n; ++i) {  // stable insertion sort
+    int k = idx[i];
+    int j = i - 1;
+    while (j >= 0 && ang[idx[j]] > ang[k]) {
+      idx[j + 1] = idx[j];
+      --j;
+    }
+    idx[j + 1] = k;
+  }
+  float o[8][2];
+  for (int i = 0; i < n; ++i) {
+    o[i][0] = v[idx[i]][0];
+    o[i][1] = v[idx[i]][1];
+  }
+  for (int i = 0; i < n; ++i) {
+    v[i][0] = o[i][0];
+    v[i][1] = o[i][1];
+  }
+}
+
+// XLA's float32 erf_inv (Giles), used by jax.random.normal
+float host_erf_inv(float x) {
+  float w = -log1pf(-x * x);
+  float p;
+  if (w < 5.0f) {
+    w = w - 2.5f;
+    p = 2.81022636e-08f;
+    p = 3.43273939e-07f + p * w;
+    p = -3.5233877e-06f + p * w;
+    p = -4.39150654e-06f + p * w;
+    p = 0.00021858087f + p * w;
+    p = -0.00125372503f + p * w;
+    p = -0.00417768164f + p * w;
+    p = 0.246640727f + p * w;
+    p = 1.50140941f + p * w;
+  } else {
+    w = sqrtf(w) - 3.0f;
+    p = -0.000200214257f;
+    p = 0.000100950558f + p * w;
+    p = 0.00134934322f + p * w;
+    p = -0.00367342844f + p * w;
+    p = 0.00573950773f + p * w;
+    p = -0.0076224613f + p * w;
+    p = 0.00943887047f + p * w;
+    p = 1.00167406f + p * w;
+    p = 2.83297682f + p * w;
+  }
+  return p * x;
+}
+// random_direction(PRNGKey(1)): cotix/_geometry_utils.py:37-46 via _collisions.py:287-298
+void host_init_dir(float out[2]) {
+  // jr.normal(key, (2,)): bits = threefry(key, [0], [1]); uniform in (-1, 1); sqrt(2)*erfinv
+  uint32_t o0, o1;
+  threefry2x32(0u, 1u, 0u, 1u, o0, o1);
+  const float lo = nextafterf(-1.0f, 0.0f), hi = 1.0f;
+  uint32_t bits[2] = {o0, o1};
+  float nrm[2];
+  for (int i = 0; i < 2; ++i) {
+    uint32_t fb = (bits[i] >> 9) | 0x3F800000u;
+    float f;
+    memcpy(&f, &fb, 4);
+    f = f - 1.0f;
+    float u = f * (hi - lo) + lo;
+    if (u < lo) u = lo;
+    nrm[i] = 1.41421356237309504880f * host_erf_inv(u);
+  }
+  float n = sqrtf(nrm[0] * nrm[0] + nrm[1] * nrm[1]);
+  out[0] = nrm[0] / n;
+  out[1] = nrm[1] / n;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cotix_lunar_default_params(CotixLunarParams* p) {
+  CXL_REQUIRE(p != nullptr, "params is null");
+  memset(p, 0, sizeof(*p));
+  p->dt = 1e-2f;
+  p->gravity_dv[0] = 0.0f;
+  p->gravity_dv[1] = -0.002f;
+  host_init_dir(p->init_dir);
+  p->baumgarte = 0.3f;
+  p->baumgarte_dt = 0.01f;
+  p->coin_p = 0.5f;
+  p->spring_kp = 1.0f;
+  p->spring_kv0 = 0.1f;
+  p->spring_kv = 0.05f;
+  p->leg_damping = 0.95f;
+  const float inf = std::numeric_limits<float>::infinity();
+  const float props[4][4] = {{30.0f, 30.0f, 1.0f, 0.1f},
+                             {1.0f, 1.0f, 1.0f, 0.1f},
+                             {1.0f, 1.0f, 1.0f, 0.1f},
+                             {inf, inf, 0.1f, 0.1f}};
+  memcpy(p->body_props, props, sizeof(props));
+  // lander: Polygon6(LANDER_POLY * 0.05), cotix/_lunar_lander.py:11-18,30
+  const int LP[6][2] = {{-14, 17}, {-17, 0}, {-17, -10}, {17, -10}, {17, 0}, {14, 17}};
+  for (int k = 0; k < 6; ++k) {
+    p->lander_local[k][0] = (float)LP[k][0] * 0.05f;
+    p->lander_local[k][1] = (float)LP[k][1] * 0.05f;
+  }
+  host_order_clockwise(p->lander_local, 6);
+  // legs: :32-73
+  float rect[4][2] = {{-2, -8}, {2, -8}, {2, 8}, {-2, 8}};
+  host_order_clockwise(rect, 4);
+  float s, c;
+  cx_sincosf(-0.3f, &s, &c);
+  for (int k = 0; k < 4; ++k) {
+    float x = rect[k][0] * c + rect[k][1] * s;
+    float y = rect[k][0] * (-s) + rect[k][1] * c;
+    x = x * 0.05f;
+    y = y * 0.05f;
+    p->leg_local[1][k][0] = x;
+    p->leg_local[1][k][1] = y;
+    p->leg_local[0][k][0] = x * -1.0f;
+    p->leg_local[0][k][1] = y * 1.0f;
+  }
+  const float LEG_AWAY = 24, LEG_DOWN = 8;
+  p->joint_local[0][0] = LEG_AWAY * 0.05f;
+  p->joint_local[0][1] = -LEG_DOWN * 0.05f;
+  p->joint_local[1][0] = LEG_AWAY * 0.05f;
+  p->joint_local[1][1] = (-LEG_DOWN + 8) * 0.05f;
+  p->joint_local[2][0] = -LEG_AWAY * 0.05f;
+  p->joint_local[2][1] = -LEG_DOWN * 0.05f;
+  p->joint_local[3][0] = -LEG_AWAY * 0.05f;
+  p->joint_local[3][1] = (-LEG_DOWN + 8) * 0.05f;
+  p->leg_joint2_local[0] = 0.0f;
+  p->leg_joint2_local[1] = 0.4f;
+  p->lander_start[0] = 0.0f;
+  p->lander_start[1] = 5.0f;
+  p->lander_start[2] = 0.01f;
+  p->leg_offset[0][0] = -LEG_AWAY * 0.05f;
+  p->leg_offset[0][1] = -LEG_DOWN * 0.05f;
+  p->leg_offset[1][0] = LEG_AWAY * 0.05f;
+  p->leg_offset[1][1] = -LEG_DOWN * 0.05f;
+  p->ground_floor = -10.0f;
+  p->terrain_x_outer = 100.0f;
+  p->pad_half_width = 2.0f;
+  p->pad_y = -2.0f;
+  p->gjk_max_iters = 32;
+  p->rng_mode = COTIX_RNG_THREEFRY;
+  p->substeps = 1;
+  p->auto_reset = 0;
+  p->judge_enabled = 0;
+  p->max_episode_steps = 0;
+  p->reset_perturb = 0;
+  p->main_engine_dv = 0.004f;
+  p->side_engine_dv = 0.0005f;
+  p->side_engine_dw = 0.002f;
+  p->x_limit = 12.0f;
+  p->y_limit = 20.0f;
+  p->land_speed = 0.05f;
+  p->land_angvel = 0.05f;
+  p->reset_x[0] = -6.0f;
+  p->reset_x[1] = 6.0f;
+  p->reset_y[0] = -1.5f;
+  p->reset_y[1] = 8.0f;
+  p->reset_angle[0] = -0.5f;
+  p->reset_angle[1] = 0.5f;
+  p->reset_v = 1.7320508f;
+  p->reset_w = 0.8660254f;
+  p->philox_seed[0] = 0x243F6A88u;
+  p->philox_seed[1] = 0x85A308D3u;
+  return COTIX_OK;
+}
+
+static int check_params(const CotixLunarParams* p) {
+  if (!p) return 0;
+  if (p->rng_mode != COTIX_RNG_THREEFRY && p->rng_mode != COTIX_RNG_PHILOX) return 0;
+  if (p->substeps < 1 || p->substeps > 1024) return 0;
+  if (p->gjk_max_iters < 0) return 0;
+  return 1;
+}
+
+int cotix_lunar_reset(void* stream, int64_t B, const uint32_t* keys, float* state, int64_t ld,
+                      const CotixLunarParams* p) {
+  CXL_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(B == 0 || (keys && state), "null buffer");
+  return cx_launch_lunar_reset((cudaStream_t)stream, B, keys, state, ld, p);
+}
+
+int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* state_out, int64_t ld,
+                     const float* action, float* reward, uint8_t* done, float* obs,
+                     const CotixLunarParams* p) {
+  CXL_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(B == 0 || (state_in && state_out), "null state");
+  return cx_launch_lunar_step((cudaStream_t)stream, B, state_in, state_out, ld, action, reward, done,
+                              obs, p);
+}
+
+// ---- host-facing env handle ---------------------------------------------------------
+struct CotixLunarEnv {
+  int device;
+  int64_t B;
+  CotixLunarParams P;
+  cudaStream_t stream;
+  float* state;     // [NF][B]
+  float* action;    // [2][B]
+  float* obs;       // [8][B]
+  float* reward;    // [B]
+  uint8_t* done;    // [B]
+  uint32_t* keys;   // [B][2]
+  std::map<int, cudaGraphExec_t>* graphs;
+  const float* graph_action;
+};
+
+int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B, const CotixLunarParams* p) {
+  CXL_REQUIRE(out != nullptr, "out is null");
+  CXL_REQUIRE(B > 0, "B <= 0");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CXL_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    cx_set_error("cotix_lunar_env_create: device %d is sm_%d%d; this library is sm_100a only", device,
+                 prop.major, prop.minor);
+    return COTIX_ENODEV;
+  }
+  CotixLunarEnv* e = new (std::nothrow) CotixLunarEnv();
+  CXL_REQUIRE(e != nullptr, "out of host memory");
+  memset(e, 0, sizeof(*e));
+  e->device = device;
+  e->B = B;
+  e->P = *p;
+  e->graphs = new std::map<int, cudaGraphExec_t>();
+  CXL_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  CXL_CUDA(cudaMalloc(&e->state, sizeof(float) * COTIX_LUNAR_NF * (size_t)B));
+  CXL_CUDA(cudaMalloc(&e->action, sizeof(float) * 2 * (size_t)B));
+  CXL_CUDA(cudaMalloc(&e->obs, sizeof(float) * COTIX_LUNAR_NOBS * (size_t)B));
+  CXL_CUDA(cudaMalloc(&e->reward, sizeof(float) * (size_t)B));
+  CXL_CUDA(cudaMalloc(&e->done, (size_t)B));
+  CXL_CUDA(cudaMalloc(&e->keys, sizeof(uint32_t) * 2 * (size_t)B));
+  CXL_CUDA(cudaMemsetAsync(e->state, 0, sizeof(float) * COTIX_LUNAR_NF * (size_t)B, e->stream));
+  CXL_CUDA(cudaStreamSynchronize(e->stream));
+  *out = e;
+  return COTIX_OK;
+}
+
+int cotix_lunar_env_destroy(CotixLunarEnv* e) {
+  if (!e) return COTIX_OK;
+  cudaSetDevice(e->device);
+  cudaStreamSynchronize(e->stream);
+  if (e->graphs) {
+    for (auto& kv : *e->graphs) cudaGraphExecDestroy(kv.second);
+    delete e->graphs;
+  }
+  cudaFree(e->state);
+  cudaFree(e->action);
+  cudaFree(e->obs);
+  cudaFree(e->reward);
+  cudaFree(e->done);
+  cudaFree(e->keys);
+  cudaStreamDestroy(e->stream);
+  delete e;
+  return COTIX_OK;
+}
+
+int cotix_lunar_env_reset_host(CotixLunarEnv* e, const uint32_t* keys) {
+  CXL_REQUIRE(e && keys, "null argument");
+  CXL_CUDA(cudaSetDevice(e->device));
+  CXL_CUDA(cudaMemcpyAsync(e->keys, keys, sizeof(uint32_t) * 2 * (size_t)e->B, cudaMemcpyHostToDevice,
+                           e->stream));
+  int rc = cx_launch_lunar_reset(e->stream, e->B, e->keys, e->state, e->B, &e->P);
+  if (rc) return rc;
+  CXL_CUDA(cudaStreamSynchronize(e->stream));
+  return COTIX_OK;
+}
+
+int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs, float* reward,
+                              uint8_t* done) {
+  CXL_REQUIRE(e != nullptr, "env is null");
+  CXL_CUDA(cudaSetDevice(e->device));
+  const size_t B = (size_t)e->B;
+  if (action)
+    CXL_CUDA(cudaMemcpyAsync(e->action, action, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, e->stream));
+  int rc = cx_launch_lunar_step(e->stream, e->B, e->state, e->state, e->B, action ? e->action : nullptr,
+                                e->reward, e->done, obs ? e->obs : nullptr, &e->P);
+  if (rc) return rc;
+  if (obs)
+    CXL_CUDA(cudaMemcpyAsync(obs, e->obs, sizeof(float) * COTIX_LUNAR_NOBS * B, cudaMemcpyDeviceToHost, e->stream));
+  if (reward)
+    CXL_CUDA(cudaMemcpyAsync(reward, e->reward, sizeof(float) * B, cudaMemcpyDeviceToHost, e->stream));
+  if (done) CXL_CUDA(cudaMemcpyAsync(done, e->done, B, cudaMemcpyDeviceToHost, e->stream));
+  CXL_CUDA(cudaStreamSynchronize(e->stream));
+  return COTIX_OK;
+}
+
+int cotix_lunar_env_get_state_host(CotixLunarEnv* e, float* state) {
+  CXL_REQUIRE(e && state, "null argument");
+  CXL_CUDA(cudaSetDevice(e->device));
+  CXL_CUDA(cudaMemcpyAsync(state, e->state, sizeof(float) * COTIX_LUNAR_NF * (size_t)e->B,
+                           cudaMemcpyDeviceToHost, e->stream));
+  CXL_CUDA(cudaStreamSynchronize(e->stream));
+  return COTIX_OK;
+}
+int cotix_lunar_env_set_state_host(CotixLunarEnv* e, const float* state) {
+  CXL_REQUIRE(e && state, "null argument");
+  CXL_CUDA(cudaSetDevice(e->device));
+  CXL_CUDA(cudaMemcpyAsync(e->state, state, sizeof(float) * COTIX_LUNAR_NF * (size_t)e->B,
+                           cudaMemcpyHostToDevice, e->stream));
+  CXL_CUDA(cudaStreamSynchronize(e->stream));
+  return COTIX_OK;
+}
+float* cotix_lunar_env_state_ptr(CotixLunarEnv* e) { return e ? e->state : nullptr; }
+void* cotix_lunar_env_stream(CotixLunarEnv* e) { return e ? (void*)e->stream : nullptr; }
+
+int cotix_lunar_env_rollout_graph(CotixLunarEnv* e, int32_t n_steps, const float* action_dev) {
+  CXL_REQUIRE(e != nullptr && n_steps > 0, "bad arguments");
+  CXL_CUDA(cudaSetDevice(e->device));
+  auto it = e->graphs->find(n_steps);
+  if (it != e->graphs->end() && e->graph_action != action_dev) {
+    for (auto& kv : *e->graphs) cudaGraphExecDestroy(kv.second);
+    e->graphs->clear();
+    it = e->graphs->end();
+  }
+  if (it == e->graphs->end()) {
+    cudaGraph_t g;
+    CXL_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = COTIX_OK;
+    for (int s = 0; s < n_steps && rc == COTIX_OK; ++s)
+      rc = cx_launch_lunar_step(e->stream, e->B, e->state, e->state, e->B, action_dev, e->reward,
+                                e->done, nullptr, &e->P);
+    cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+    cx_count_launch_n(-(int64_t)n_steps);  // captured, not executed
+    if (rc) return rc;
+    CXL_CUDA(ce);
+    cudaGraphExec_t ge;
+    CXL_CUDA(cudaGraphInstantiate(&ge, g, 0));
+    cudaGraphDestroy(g);
+    (*e->graphs)[n_steps] = ge;
+    e->graph_action = action_dev;
+    it = e->graphs->find(n_steps);
+  }
+  CXL_CUDA(cudaGraphLaunch(it->second, e->stream));
+  cx_count_launch_n(n_steps);
+  return COTIX_OK;
+}
+
+}  // extern "C"

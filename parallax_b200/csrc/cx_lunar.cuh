@@ -1,0 +1,186 @@
+// cx_lunar.cuh — device functions of the fused LunarLander step.
+//
+// Reference step (examples/test_viz.py:25-44):
+//   ExplicitEulerPhysics.step   cotix/_physics_solvers.py:16-33
+//   gravity on the lander       examples/test_viz.py:27-31
+//   RandomizedCollider.resolve  cotix/_colliders.py:74-351
+//   key = split(key)[0]         examples/test_viz.py:39
+//   LunarLander.step (joints)   cotix/_lunar_lander.py:145-218
+//
+// How the collider is restructured (results are identical):
+//  * the reference evaluates 81 + 225 narrowphase calls per step for 25 distinct part pairs
+//    (24 real + the left leg against itself); here each distinct pair is evaluated at most
+//    once, and only if its AABBs come within CULL_MARGIN of each other;
+//  * every (ind2, ind1) scatter entry of the reference draws a coin from its own threefry
+//    key; only the coins of entries whose contact is non-NaN can change the outcome, and for
+//    a cell the LAST heads in scan order wins — so coins are evaluated lazily, from the last
+//    entry backwards, stopping at the first heads;
+//  * the self pair (left leg vs itself) only dilutes body 2's random choice, so
+//    it is evaluated only when body 2 has another live contact.
+#pragma once
+#include "../../include/cotix_b200.h"
+#include "cx_narrow.cuh"
+#include "cx_rng.cuh"
+
+#define CX_CULL_MARGIN 1e-3f
+
+struct BodyS {
+  float px, py, vx, vy, ang, w;
+};
+struct MassP {
+  float mass, inertia, e, mu;
+};
+
+// ---- order_clockwise on a register polygon (cold path) --------------------------------
+static __device__ __noinline__ void poly_sort_cw(Poly& p) {
+  const int n = p.n;
+  float sx = 0.0f, sy = 0.0f;
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k)
+    if (k < n) {
+      sx = sx + p.x[k];
+      sy = sy + p.y[k];
+    }
+  const float mx = sx / (float)n, my = sy / (float)n;
+  float ang[CX_MAXV];
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k) ang[k] = (k < n) ? cx_atan2f(p.y[k] - my, p.x[k] - mx) : 0.0f;
+  int rank[CX_MAXV];
+#pragma unroll
+  for (int q = 0; q < CX_MAXV; ++q) {
+    int r = 0;
+    const float aq = ang[q];
+    const bool qn = aq != aq;
+#pragma unroll
+    for (int t = 0; t < CX_MAXV; ++t) {
+      if (t != q && t < n) {
+        const float at = ang[t];
+        const bool tn = at != at;
+        bool before;
+        if (tn || qn) before = (!tn && qn) || (tn == qn && t < q);
+        else before = (at < aq) || (at == aq && t < q);
+        if (before) ++r;
+      }
+    }
+    rank[q] = r;
+  }
+  Poly o = p;
+#pragma unroll
+  for (int t = 0; t < CX_MAXV; ++t) {
+#pragma unroll
+    for (int q = 0; q < CX_MAXV; ++q)
+      if (q < n && rank[q] == t) {
+        o.x[t] = p.x[q];
+        o.y[t] = p.y[q];
+      }
+  }
+  p = o;
+}
+
+// ---- resolution — cotix/_collision_resolution.py:52-151 -------------------------------
+CX_DEV void apply_impulse(BodyS& b, const MassP& m, V2 imp, V2 point) {  // :68-73
+  V2 arm = point - mk2(b.px, b.py);
+  float torque = cross2(arm, imp);
+  b.vx = b.vx + imp.x / m.mass;
+  b.vy = b.vy + imp.y / m.mass;
+  b.w = b.w + torque / m.inertia;
+}
+CX_DEV V2 velocity_at(const BodyS& b, V2 point) {  // cotix/_bodies.py:50-55
+  return mk2(b.vx, b.vy) + perp(point - mk2(b.px, b.py)) * b.w;
+}
+static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1, BodyS& b2,
+                                               const MassP& m2, V2 pen, V2 cp, float baumgarte,
+                                               float baumgarte_dt) {
+  if (isnan2(cp)) return;
+  V2 p1 = mk2(b1.px, b1.py), p2 = mk2(b2.px, b2.py);
+  V2 v1 = mk2(b1.vx, b1.vy) + perp(cp - p1) * b1.w;
+  V2 v2 = mk2(b2.vx, b2.vy) + perp(cp - p2) * b2.w;
+  V2 vrel = v2 - v1;
+  float pn = norm2(pen);
+  V2 nd = pen / pn;
+  float vn = dot2(vrel, nd);
+  float el = jmin(m1.e, m2.e);
+  V2 r1 = cp - p1, r2 = cp - p2;
+  float lever1 = sumsq2(r1), lever2 = sumsq2(r2);
+  float ang = lever1 / m1.inertia + lever2 / m2.inertia;
+  float nim = -(1.0f + el) * vn - baumgarte * norm2(pen) / baumgarte_dt;
+  float kden = 1.0f / m1.mass + 1.0f / m2.mass + ang;
+  float nimp = nim / kden;
+  V2 ivec = nimp * nd;
+  float fr = (m1.mu + m2.mu) / 2.0f;
+  V2 vdrag = vrel + vn * nd;
+  float vdn = norm2(vdrag);
+  V2 vdu = vdrag / vdn;
+  float idrag = -norm2(vdrag) / (1.0f / m1.mass + 1.0f / m2.mass + ang);
+  idrag = jclip(idrag, 0.0f, nimp * fr);
+  V2 idv = idrag * vdu;
+  ivec = ivec + idv;
+  if (dot2(pen, vrel) < 0) return;
+  apply_impulse(b1, m1, -ivec, cp);
+  apply_impulse(b2, m2, ivec, cp);
+}
+
+// ---- joints — cotix/_lunar_lander.py:145-218 -------------------------------------------
+CX_DEV void joint_constraint(BodyS& b1, const MassP& m1, V2 c1, BodyS& b2, const MassP& m2, V2 c2,
+                             const CotixLunarParams& P) {
+  V2 dp = c1 - c2;
+  V2 dv = velocity_at(b1, c1) - velocity_at(b2, c2);
+  V2 imp = dp * P.spring_kp + dv * (norm2(dv) + P.spring_kv0) * P.spring_kv;
+  apply_impulse(b1, m1, -imp, c1);
+  apply_impulse(b2, m2, imp, c2);
+}
+CX_DEV V2 rot_cs(V2 v, float c, float s) {  // rotate(): [[c,-s],[s,c]] @ v
+  return mk2(c * v.x + (-s) * v.y, s * v.x + c * v.y);
+}
+
+// ---- coin flips of the scatter scans — cotix/_colliders.py:208-268 --------------------
+struct CoinCtx {
+  int mode;           // COTIX_RNG_*
+  Key2 gkey[2];       // threefry: skey of group 0 / group 1 (after its split, :175)
+  Key2 pkey;          // philox key
+  uint32_t steps, episode;
+  float p;
+};
+// heads of entry (group g, ind2, ind1); k2 = split(gkey[g], N2)[ind2] is passed in
+CX_DEV bool coin_heads(const CoinCtx& cc, int g, int N1, Key2 k2, int ind2, int ind1) {
+  if (cc.mode == COTIX_RNG_THREEFRY) {
+    Key2 k1 = tf_split(k2, (uint32_t)N1, (uint32_t)ind1);
+    Key2 kk = tf_split(k1, 2u, 0u);
+    return tf_bernoulli(kk, cc.p);
+  }
+  uint32_t w = philox_word(cc.pkey, cc.steps, cc.episode, (uint32_t)g,
+                           (uint32_t)(ind2 * N1 + ind1), CX_TAG_COIN);
+  return bits_to_uniform(w, 0.0f, 1.0f) < cc.p;
+}
+// Winner of one all_contacts cell: the entry with the largest (ind2, ind1) whose contact is
+// live and whose coin is heads.  Entries of the cell: ind2 in [b_lo, b_hi], ind1 in
+// {a0 + q + 7*r : q live in `mask` (bit q), r < reps}.  Returns q or -1.
+static __device__ __noinline__ int cell_winner(const CoinCtx& cc, int g, int N1, int N2, int b_lo,
+                                        int b_hi, int a0, int nq, int reps, uint32_t mask) {
+  if (mask == 0u) return -1;
+  for (int ind2 = b_hi; ind2 >= b_lo; --ind2) {
+    Key2 k2;
+    k2.a = k2.b = 0u;
+    if (cc.mode == COTIX_RNG_THREEFRY) k2 = tf_split(cc.gkey[g], (uint32_t)N2, (uint32_t)ind2);
+    for (int r = reps - 1; r >= 0; --r)
+      for (int q = nq - 1; q >= 0; --q) {
+        if (!((mask >> q) & 1u)) continue;
+        int ind1 = a0 + q + nq * r;
+        if (coin_heads(cc, g, N1, k2, ind2, ind1)) return q;
+      }
+  }
+  return -1;
+}
+
+// jr.choice over the live cells of one all_contacts row — cotix/_colliders.py:274-291.
+// m[j] = cell (i, j) live; u = the uniform draw of body i's key.
+CX_DEV int choose_index(bool m0, bool m1, bool m2, float u) {
+  int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
+  float fc = (float)cnt;
+  float p0 = (m0 ? 1.0f : 0.0f) / fc, p1 = (m1 ? 1.0f : 0.0f) / fc, p2 = (m2 ? 1.0f : 0.0f) / fc;
+  float p3 = 0.0f / fc;
+  float c0 = p0, c1 = c0 + p1, c2 = c1 + p2, c3 = c2 + p3;
+  float r = c3 * (1.0f - u);
+  int ind = (c0 < r ? 1 : 0) + (c1 < r ? 1 : 0) + (c2 < r ? 1 : 0) + (c3 < r ? 1 : 0);
+  return ind > 3 ? 3 : ind;
+}

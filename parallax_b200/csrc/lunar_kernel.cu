@@ -1,0 +1,600 @@
+// lunar_kernel.cu — K1 (fused LunarLander step) and K4 (reset), one environment per thread.
+//
+// State is struct-of-arrays over the env axis (include/cotix_b200.h), so every field access
+// of a warp is one fully coalesced 128-byte transaction; a step reads 36 words + 2 action
+// words and writes back only what changed.  See DESIGN.md for why the shipped mapping is
+// env-per-thread with candidate pairs processed after an exact AABB cull rather than the
+// env-per-warp mapping the north_star sketches (measured comparison in profiles/).
+#include "cx_launch.cuh"
+#include "cx_lunar.cuh"
+
+namespace {
+
+struct EnvRegs {
+  BodyS b[3];
+  float h[8];
+  float kn[4];
+  Key2 key;
+  uint32_t steps, status;
+  float ret, shaping;
+};
+
+struct SubInfo {
+  float reward;
+  int done;
+  bool rc, lc;
+};
+
+CX_DEV void world_poly(const float (*local)[2], int n, const BodyS& b, float c, float s, Poly& out) {
+  out.n = n;
+  const float ms = -s;
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k) {
+    if (k < n) {
+      float x = local[k][0], y = local[k][1];
+      float tx = c * x + ms * y + b.px * 1.0f;
+      float ty = s * x + c * y + b.py * 1.0f;
+      float tw = 0.0f * x + 0.0f * y + 1.0f * 1.0f;
+      out.x[k] = tx / tw;
+      out.y[k] = ty / tw;
+    } else {
+      out.x[k] = 0.0f;
+      out.y[k] = 0.0f;
+    }
+  }
+}
+struct Aabb {
+  float lx, ly, hx, hy;
+};
+CX_DEV Aabb poly_aabb(const Poly& p) {
+  Aabb a;
+  a.lx = a.hx = p.x[0];
+  a.ly = a.hy = p.y[0];
+#pragma unroll
+  for (int k = 1; k < CX_MAXV; ++k)
+    if (k < p.n) {
+      a.lx = fminf(a.lx, p.x[k]);
+      a.hx = fmaxf(a.hx, p.x[k]);
+      a.ly = fminf(a.ly, p.y[k]);
+      a.hy = fmaxf(a.hy, p.y[k]);
+    }
+  return a;
+}
+CX_DEV bool aabb_near(const Aabb& a, const Aabb& b) {
+  const float m = CX_CULL_MARGIN;
+  return !(a.hx + m < b.lx || b.hx + m < a.lx || a.hy + m < b.ly || b.hy + m < a.ly);
+}
+CX_DEV float terrain_x(const EnvRegs& E, const CotixLunarParams& P, int i) {
+  switch (i) {
+    case 0: return -P.terrain_x_outer;
+    case 1: return E.kn[0];
+    case 2: return E.kn[1];
+    case 3: return -P.pad_half_width;
+    case 4: return P.pad_half_width;
+    case 5: return E.kn[2];
+    case 6: return E.kn[3];
+    default: return P.terrain_x_outer;
+  }
+}
+// ground part k as the collider sees it: Polygon4.__init__ sort (cotix/_lunar_lander.py:132)
+// followed by the identity transform + re-sort of part.transform (cotix/_colliders.py:92-94)
+static __device__ __noinline__ void ground_poly(const EnvRegs& E, const CotixLunarParams& P, int k,
+                                         bool poisoned, Poly& g) {
+  float x0 = terrain_x(E, P, k), x1 = terrain_x(E, P, k + 1);
+  float h0 = E.h[0], h1 = E.h[1];
+#pragma unroll
+  for (int q = 1; q < 7; ++q)
+    if (q == k) {
+      h0 = E.h[q];
+      h1 = E.h[q + 1];
+    }
+  g.n = 4;
+  g.x[0] = x0; g.y[0] = h0;
+  g.x[1] = x0; g.y[1] = P.ground_floor;
+  g.x[2] = x1; g.y[2] = h1;
+  g.x[3] = x1; g.y[3] = P.ground_floor;
+  g.x[4] = g.y[4] = g.x[5] = g.y[5] = 0.0f;
+  poly_sort_cw(g);
+  if (poisoned) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) g.x[q] = g.y[q] = CX_NAN;
+  }
+  poly_sort_cw(g);
+}
+
+static __device__ __noinline__ Contact poly_pair(const Poly& a, const Poly& b, V2 start, int gjk_max) {
+  return convex_vs_polygon(a, b, start, gjk_max);
+}
+
+CX_DEV float lunar_shaping(const BodyS& L, const CotixLunarParams& P, bool rc, bool lc) {
+  float dy = L.py - P.pad_y;
+  float dist = sqrtf(L.px * L.px + dy * dy);
+  float speed = sqrtf(L.vx * L.vx + L.vy * L.vy);
+  float s = -10.0f * dist;
+  s = s - 100.0f * speed;
+  s = s - 100.0f * fabsf(L.ang);
+  s = s + (rc ? 10.0f : 0.0f);
+  s = s + (lc ? 10.0f : 0.0f);
+  return s;
+}
+
+// One physics sub-step of one env = f(env, key) of examples/test_viz.py:25-44 (+ engines and
+// judge, which the reference does not have).
+__device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
+                              SubInfo& info) {
+  MassP mp[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    mp[i].mass = P.body_props[i][0];
+    mp[i].inertia = P.body_props[i][1];
+    mp[i].e = P.body_props[i][2];
+    mp[i].mu = P.body_props[i][3];
+  }
+  const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
+  BodyS G;
+  G.px = G.py = G.vx = G.vy = G.ang = G.w = poisoned ? CX_NAN : 0.0f;
+
+  // --- ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24)
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    E.b[i].px = E.b[i].px + E.b[i].vx * P.dt;
+    E.b[i].py = E.b[i].py + E.b[i].vy * P.dt;
+    E.b[i].ang = E.b[i].ang + E.b[i].w * P.dt;
+  }
+  G.px = G.px + G.vx * P.dt;
+  G.py = G.py + G.vy * P.dt;
+  G.ang = G.ang + G.w * P.dt;
+  // --- gravity on the lander only (examples/test_viz.py:27-31)
+  E.b[0].vx = E.b[0].vx + P.gravity_dv[0];
+  E.b[0].vy = E.b[0].vy + P.gravity_dv[1];
+
+  float cs[3], sn[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &sn[i], &cs[i]);
+  if (!(fabsf(E.b[0].ang) < 1.0e9f) || !(fabsf(E.b[1].ang) < 1.0e9f) || !(fabsf(E.b[2].ang) < 1.0e9f))
+    E.status |= COTIX_ST_ANGLE_RANGE;
+
+  // --- engines (new): a zero action leaves the reference step untouched
+  const float thr_main = jclip(a_main, 0.0f, 1.0f);
+  const float thr_side = jclip(a_side, -1.0f, 1.0f);
+  if (thr_main != 0.0f) {
+    float dv = P.main_engine_dv * thr_main;
+    E.b[0].vx = E.b[0].vx + (-sn[0]) * dv;
+    E.b[0].vy = E.b[0].vy + cs[0] * dv;
+  }
+  if (thr_side != 0.0f) {
+    float dv = P.side_engine_dv * thr_side;
+    E.b[0].vx = E.b[0].vx + cs[0] * dv;
+    E.b[0].vy = E.b[0].vy + sn[0] * dv;
+    E.b[0].w = E.b[0].w - P.side_engine_dw * thr_side;
+  }
+
+  // --- RandomizedCollider.resolve (cotix/_colliders.py:74-351)
+  // world polygons in local vertex order (unsorted) and their AABBs
+  Poly wl, wr, wL;  // left leg (body 2), right leg (body 1), lander (body 0)
+  world_poly(P.lander_local, 6, E.b[0], cs[0], sn[0], wL);
+  world_poly(P.leg_local[0], 4, E.b[1], cs[1], sn[1], wr);
+  world_poly(P.leg_local[1], 4, E.b[2], cs[2], sn[2], wl);
+  const Aabb bL = poly_aabb(wL), br = poly_aabb(wr), bl = poly_aabb(wl);
+  // candidate bits: 0 (rl,L) 1 (ll,L) 2..8 (g,L) 9 (ll,rl) 11..17 (g,rl) 18..24 (g,ll)
+  uint32_t cand = 0u;
+  if (aabb_near(br, bL)) cand |= 1u << 0;
+  if (aabb_near(bl, bL)) cand |= 1u << 1;
+  if (aabb_near(bl, br)) cand |= 1u << 9;
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+    float x0 = terrain_x(E, P, k), x1 = terrain_x(E, P, k + 1);
+    Aabb g;
+    g.lx = fminf(x0, x1);
+    g.hx = fmaxf(x0, x1);
+    g.ly = fminf(fminf(E.h[k], E.h[k + 1]), P.ground_floor);
+    g.hy = fmaxf(fmaxf(E.h[k], E.h[k + 1]), P.ground_floor);
+    if (aabb_near(g, bL)) cand |= 1u << (2 + k);
+    if (aabb_near(g, br)) cand |= 1u << (11 + k);
+    if (aabb_near(g, bl)) cand |= 1u << (18 + k);
+  }
+  bool any_state_nan = false;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    any_state_nan = any_state_nan || !(fabsf(E.b[i].px) <= 3.0e38f) || !(fabsf(E.b[i].py) <= 3.0e38f) ||
+                    !(fabsf(E.b[i].ang) <= 3.0e38f);
+  if (any_state_nan || poisoned) cand = 0u;  // NaN vertices: every GJK reports "no" (any-NaN rule)
+
+  bool crash = false, rc = false, lc = false;
+  if (cand != 0u) {
+    const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
+    const int gmax = P.gjk_max_iters;
+    poly_sort_cw(wL);
+    poly_sort_cw(wr);
+    poly_sort_cw(wl);
+    // narrowphase of every candidate pair; cell = all_contacts[i][j]
+    Contact c10 = contact_none(), c20 = contact_none(), c21 = contact_none();
+    uint32_t st = 0u;
+    if (cand & (1u << 0)) c10 = poly_pair(wr, wL, start, gmax);
+    if (cand & (1u << 1)) c20 = poly_pair(wl, wL, start, gmax);
+    if (cand & (1u << 9)) c21 = poly_pair(wl, wr, start, gmax);
+    st |= c10.status | c20.status | c21.status;
+    float gpx[3][7], gpy[3][7], gcx[3][7], gcy[3][7];  // ground contacts per column j
+    uint32_t gm[3] = {0u, 0u, 0u};
+    if (cand & 0x01FFF9FCu) {
+      for (int k = 0; k < 7; ++k) {
+        const bool n0 = (cand >> (2 + k)) & 1u, n1 = (cand >> (11 + k)) & 1u, n2 = (cand >> (18 + k)) & 1u;
+        if (!(n0 || n1 || n2)) continue;
+        Poly g;
+        ground_poly(E, P, k, poisoned, g);
+        if (n0) {
+          Contact c = poly_pair(g, wL, start, gmax);
+          st |= c.status;
+          if (!contact_isnan(c)) {
+            gm[0] |= 1u << k;
+            gpx[0][k] = c.pen.x; gpy[0][k] = c.pen.y; gcx[0][k] = c.cp.x; gcy[0][k] = c.cp.y;
+          }
+        }
+        if (n1) {
+          Contact c = poly_pair(g, wr, start, gmax);
+          st |= c.status;
+          if (!contact_isnan(c)) {
+            gm[1] |= 1u << k;
+            gpx[1][k] = c.pen.x; gpy[1][k] = c.pen.y; gcx[1][k] = c.cp.x; gcy[1][k] = c.cp.y;
+          }
+        }
+        if (n2) {
+          Contact c = poly_pair(g, wl, start, gmax);
+          st |= c.status;
+          if (!contact_isnan(c)) {
+            gm[2] |= 1u << k;
+            gpx[2][k] = c.pen.x; gpy[2][k] = c.pen.y; gcx[2][k] = c.cp.x; gcy[2][k] = c.cp.y;
+          }
+        }
+      }
+    }
+    (void)st;  // cap bits are reported by the sweep API only, not in the env status
+    crash = gm[0] != 0u;
+    rc = gm[1] != 0u;
+    lc = gm[2] != 0u;
+    const bool l10 = !contact_isnan(c10), l20 = !contact_isnan(c20), l21 = !contact_isnan(c21);
+    if (l10 || l20 || l21 || gm[0] || gm[1] || gm[2]) {
+      // key chain: skey = split(rkey)[0] (:142); per group skey = split(skey)[0] (:175)
+      CoinCtx cc;
+      cc.mode = P.rng_mode;
+      cc.p = P.coin_p;
+      cc.steps = E.steps;
+      cc.episode = E.status >> 8;
+      cc.pkey.a = P.philox_seed[0] ^ E.key.a;
+      cc.pkey.b = P.philox_seed[1] ^ E.key.b;
+      cc.gkey[0] = cc.gkey[1] = E.key;
+      if (P.rng_mode == COTIX_RNG_THREEFRY) {
+        Key2 sk = tf_split(E.key, 2u, 0u);
+        cc.gkey[0] = tf_split(sk, 2u, 0u);
+        cc.gkey[1] = tf_split(cc.gkey[0], 2u, 0u);
+      }
+      // group 0 = (Polygon4, Polygon6): N1 = N2 = 9; group 1 = (Polygon4, Polygon4): 15 x 15
+      bool v10 = cell_winner(cc, 0, 9, 9, 0, 8, 0, 1, 1, l10 ? 1u : 0u) >= 0;
+      bool v20 = cell_winner(cc, 0, 9, 9, 0, 8, 1, 1, 1, l20 ? 1u : 0u) >= 0;
+      int w30 = cell_winner(cc, 0, 9, 9, 0, 8, 2, 7, 1, gm[0]);
+      bool v21 = cell_winner(cc, 1, 15, 15, 0, 7, 0, 1, 1, l21 ? 1u : 0u) >= 0;
+      int w31 = cell_winner(cc, 1, 15, 15, 0, 7, 1, 7, 2, gm[1]);
+      int w32 = cell_winner(cc, 1, 15, 15, 8, 14, 1, 7, 2, gm[2]);
+      bool v22 = false;
+      if (v20 || v21) {  // the self pair only matters when body 2 has another live cell
+        Contact c22 = poly_pair(wl, wl, start, gmax);
+        v22 = cell_winner(cc, 1, 15, 15, 8, 14, 0, 1, 1, contact_isnan(c22) ? 0u : 1u) >= 0;
+      }
+      // choose_random_contact (:274-295); keys split(skey, n_bodies) with the last skey
+      int j2 = -1, j3 = -1;
+      {
+        int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
+        if (cnt == 1) j2 = v20 ? 0 : (v21 ? 1 : 2);
+        else if (cnt > 1) {
+          float u;
+          if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 2u), 0.0f, 1.0f);
+          else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 2u, CX_TAG_CHOICE), 0.0f, 1.0f);
+          j2 = choose_index(v20, v21, v22, u);
+        }
+      }
+      {
+        const bool m0 = w30 >= 0, m1 = w31 >= 0, m2 = w32 >= 0;
+        int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
+        if (cnt == 1) j3 = m0 ? 0 : (m1 ? 1 : 2);
+        else if (cnt > 1) {
+          float u;
+          if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 3u), 0.0f, 1.0f);
+          else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 3u, CX_TAG_CHOICE), 0.0f, 1.0f);
+          j3 = choose_index(m0, m1, m2, u);
+        }
+      }
+      // sequential resolution scan i = 0..3 (:310-336); row 0 is always empty
+      if (v10) resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c10.pen, c10.cp, P.baumgarte, P.baumgarte_dt);
+      if (j2 == 0 && v20) resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c20.pen, c20.cp, P.baumgarte, P.baumgarte_dt);
+      if (j2 == 1 && v21) resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c21.pen, c21.cp, P.baumgarte, P.baumgarte_dt);
+      if (j3 >= 0 && j3 <= 2) {
+        const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
+        if (w >= 0) {
+          V2 pen = mk2(gpx[j3][w], gpy[j3][w]), cp = mk2(gcx[j3][w], gcy[j3][w]);
+          if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], pen, cp, P.baumgarte, P.baumgarte_dt);
+          else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], pen, cp, P.baumgarte, P.baumgarte_dt);
+          else resolve_collision(G, mp[3], E.b[2], mp[2], pen, cp, P.baumgarte, P.baumgarte_dt);
+        }
+      }
+    }
+  }
+  if ((G.vx != 0.0f) || (G.vy != 0.0f) || (G.w != 0.0f) || (G.px != 0.0f) || (G.py != 0.0f) || (G.ang != 0.0f))
+    E.status |= COTIX_ST_GROUND_NAN;
+
+  // --- key, next_key = jr.split(key) (examples/test_viz.py:39)
+  if (P.rng_mode == COTIX_RNG_THREEFRY) E.key = tf_split(E.key, 2u, 0u);
+
+  // --- LunarLander.step (cotix/_lunar_lander.py:145-218); angles are those of this step
+  {
+    V2 p0 = mk2(E.b[0].px, E.b[0].py);
+    V2 lj0 = rot_cs(mk2(P.joint_local[0][0], P.joint_local[0][1]), cs[0], sn[0]) + p0;
+    V2 lj1 = rot_cs(mk2(P.joint_local[1][0], P.joint_local[1][1]), cs[0], sn[0]) + p0;
+    V2 lj2 = rot_cs(mk2(P.joint_local[2][0], P.joint_local[2][1]), cs[0], sn[0]) + p0;
+    V2 lj3 = rot_cs(mk2(P.joint_local[3][0], P.joint_local[3][1]), cs[0], sn[0]) + p0;
+    V2 j2l = mk2(P.leg_joint2_local[0], P.leg_joint2_local[1]);
+    V2 ll1 = mk2(E.b[2].px, E.b[2].py);
+    V2 ll2 = ll1 + rot_cs(j2l, cs[2], sn[2]);
+    V2 rl1 = mk2(E.b[1].px, E.b[1].py);
+    V2 rl2 = rl1 + rot_cs(j2l, cs[1], sn[1]);
+    joint_constraint(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
+    joint_constraint(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
+    joint_constraint(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
+    joint_constraint(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
+    E.b[1].w = E.b[1].w * P.leg_damping;
+    E.b[2].w = E.b[2].w * P.leg_damping;
+  }
+
+  bool any_nan = false;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    any_nan = any_nan || !(fabsf(E.b[i].px) <= 3.0e38f) || !(fabsf(E.b[i].py) <= 3.0e38f) ||
+              !(fabsf(E.b[i].vx) <= 3.0e38f) || !(fabsf(E.b[i].vy) <= 3.0e38f) ||
+              !(fabsf(E.b[i].ang) <= 3.0e38f) || !(fabsf(E.b[i].w) <= 3.0e38f);
+  if (any_nan) E.status |= COTIX_ST_NAN;
+  E.steps += 1u;
+
+  // --- judge (new; template cotix/_envs.py:9-28)
+  float reward = 0.0f;
+  int done = COTIX_DONE_NO;
+  if (P.judge_enabled) {
+    float sh = lunar_shaping(E.b[0], P, rc, lc);
+    if (E.shaping == E.shaping) reward = sh - E.shaping;
+    E.shaping = sh;
+    reward = reward - 0.3f * thr_main;
+    reward = reward - 0.03f * fabsf(thr_side);
+    const BodyS& L = E.b[0];
+    if (crash) {
+      done = COTIX_DONE_CRASH;
+      reward = -100.0f;
+    } else if (!(fabsf(L.px) < P.x_limit) || !(L.py < P.y_limit)) {
+      done = COTIX_DONE_OOB;
+      reward = -100.0f;
+    } else if (rc && lc && sqrtf(L.vx * L.vx + L.vy * L.vy) < P.land_speed && fabsf(L.w) < P.land_angvel) {
+      done = COTIX_DONE_LANDED;
+      reward = 100.0f;
+    }
+  }
+  if (any_nan) {
+    done = COTIX_DONE_NAN;
+    reward = P.judge_enabled ? -100.0f : 0.0f;
+  }
+  if (done == COTIX_DONE_NO && P.max_episode_steps > 0 && E.steps >= (uint32_t)P.max_episode_steps)
+    done = COTIX_DONE_TIMEOUT;
+  E.ret = E.ret + reward;
+  info.reward = reward;
+  info.done = done;
+  info.rc = rc;
+  info.lc = lc;
+}
+
+// reset(key): LunarLander.__init__, cotix/_lunar_lander.py:29-143 (+ optional pose
+// perturbation, new).  Leaves E.key untouched; the caller owns the key chain.
+static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const CotixLunarParams& P,
+                                             uint32_t episode) {
+  uint32_t pert[8];
+  if (P.rng_mode == COTIX_RNG_THREEFRY) {
+    Key2 k0 = tf_split(key, 5u, 0u);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) E.h[i] = bits_to_uniform(tf_bits_word(k0, 8u, (uint32_t)i), -5.0f, 5.0f);
+    E.kn[0] = tf_uniform(tf_split(key, 5u, 1u), -12.0f, -9.0f);
+    E.kn[1] = tf_uniform(tf_split(key, 5u, 2u), -8.0f, -4.0f);
+    E.kn[2] = tf_uniform(tf_split(key, 5u, 3u), 4.0f, 8.0f);
+    E.kn[3] = tf_uniform(tf_split(key, 5u, 4u), 9.0f, 12.0f);
+    if (P.reset_perturb) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        threefry2x32(key.a, key.b, 0x70657274u + (uint32_t)i, (uint32_t)i, pert[2 * i], pert[2 * i + 1]);
+    }
+  } else {
+    uint32_t w[20];
+#pragma unroll
+    for (int q = 0; q < 5; ++q)
+      philox4x32_10(P.philox_seed[0] ^ key.a, P.philox_seed[1] ^ key.b, 0u, episode, (uint32_t)q,
+                    CX_TAG_RESET, w + 4 * q);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) E.h[i] = bits_to_uniform(w[i], -5.0f, 5.0f);
+    E.kn[0] = bits_to_uniform(w[8], -12.0f, -9.0f);
+    E.kn[1] = bits_to_uniform(w[9], -8.0f, -4.0f);
+    E.kn[2] = bits_to_uniform(w[10], 4.0f, 8.0f);
+    E.kn[3] = bits_to_uniform(w[11], 9.0f, 12.0f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) pert[i] = w[12 + i];
+  }
+  E.h[0] = E.h[0] * 10.0f;
+  E.h[3] = P.pad_y;
+  E.h[4] = P.pad_y;
+  E.h[7] = E.h[7] * 10.0f;
+
+  float lx = P.lander_start[0], ly = P.lander_start[1], la = P.lander_start[2];
+  float lvx = 0.0f, lvy = 0.0f, lw = 0.0f;
+  if (!P.reset_perturb) {
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+      E.b[1 + l].px = P.leg_offset[l][0] + lx;
+      E.b[1 + l].py = P.leg_offset[l][1] + ly;
+      E.b[1 + l].vx = E.b[1 + l].vy = E.b[1 + l].ang = E.b[1 + l].w = 0.0f;
+    }
+  } else {
+    lx = bits_to_uniform(pert[0], P.reset_x[0], P.reset_x[1]);
+    ly = bits_to_uniform(pert[1], P.reset_y[0], P.reset_y[1]);
+    la = bits_to_uniform(pert[2], P.reset_angle[0], P.reset_angle[1]);
+    lvx = bits_to_uniform(pert[3], -P.reset_v, P.reset_v);
+    lvy = bits_to_uniform(pert[4], -P.reset_v, P.reset_v);
+    lw = bits_to_uniform(pert[5], -P.reset_w, P.reset_w);
+    float da = la - P.lander_start[2];
+    float c, s;
+    cx_sincosf(da, &s, &c);
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+      float ox = P.leg_offset[l][0], oy = P.leg_offset[l][1];
+      float rx = c * ox - s * oy, ry = s * ox + c * oy;
+      E.b[1 + l].px = rx + lx;
+      E.b[1 + l].py = ry + ly;
+      E.b[1 + l].ang = da;
+      E.b[1 + l].vx = lvx + (-ry) * lw;
+      E.b[1 + l].vy = lvy + rx * lw;
+      E.b[1 + l].w = lw;
+    }
+  }
+  E.b[0].px = lx;
+  E.b[0].py = ly;
+  E.b[0].vx = lvx;
+  E.b[0].vy = lvy;
+  E.b[0].ang = la;
+  E.b[0].w = lw;
+  E.steps = 0u;
+  E.status = episode << 8;
+  E.ret = 0.0f;
+  E.shaping = CX_NAN;
+}
+
+CX_DEV void load_env(EnvRegs& E, const float* __restrict__ s, int64_t ld, int64_t e) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    E.b[i].px = s[(i * 6 + 0) * ld + e];
+    E.b[i].py = s[(i * 6 + 1) * ld + e];
+    E.b[i].vx = s[(i * 6 + 2) * ld + e];
+    E.b[i].vy = s[(i * 6 + 3) * ld + e];
+    E.b[i].ang = s[(i * 6 + 4) * ld + e];
+    E.b[i].w = s[(i * 6 + 5) * ld + e];
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) E.h[i] = s[(COTIX_F_HEIGHT0 + i) * ld + e];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) E.kn[i] = s[(COTIX_F_KNOT0 + i) * ld + e];
+  E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
+  E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
+  E.steps = __float_as_uint(s[COTIX_F_STEPS * ld + e]);
+  E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
+  E.ret = s[COTIX_F_RETURN * ld + e];
+  E.shaping = s[COTIX_F_SHAPING * ld + e];
+}
+CX_DEV void store_env(const EnvRegs& E, float* __restrict__ s, int64_t ld, int64_t e, bool terrain) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    s[(i * 6 + 0) * ld + e] = E.b[i].px;
+    s[(i * 6 + 1) * ld + e] = E.b[i].py;
+    s[(i * 6 + 2) * ld + e] = E.b[i].vx;
+    s[(i * 6 + 3) * ld + e] = E.b[i].vy;
+    s[(i * 6 + 4) * ld + e] = E.b[i].ang;
+    s[(i * 6 + 5) * ld + e] = E.b[i].w;
+  }
+  if (terrain) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[(COTIX_F_HEIGHT0 + i) * ld + e] = E.h[i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) s[(COTIX_F_KNOT0 + i) * ld + e] = E.kn[i];
+  }
+  s[COTIX_F_KEY0 * ld + e] = __uint_as_float(E.key.a);
+  s[COTIX_F_KEY1 * ld + e] = __uint_as_float(E.key.b);
+  s[COTIX_F_STEPS * ld + e] = __uint_as_float(E.steps);
+  s[COTIX_F_STATUS * ld + e] = __uint_as_float(E.status);
+  s[COTIX_F_RETURN * ld + e] = E.ret;
+  s[COTIX_F_SHAPING * ld + e] = E.shaping;
+}
+
+__global__ void __launch_bounds__(128)
+lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__ sout, int64_t ld,
+                  const float* __restrict__ action, float* __restrict__ reward,
+                  uint8_t* __restrict__ done, float* __restrict__ obs,
+                  const __grid_constant__ CotixLunarParams P) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= B) return;
+  EnvRegs E;
+  load_env(E, sin_, ld, e);
+  const float am = action ? action[e] : 0.0f;
+  const float as = action ? action[ld + e] : 0.0f;
+  float rsum = 0.0f;
+  int d = COTIX_DONE_NO;
+  bool rc = false, lc = false;
+  const int K = P.substeps < 1 ? 1 : P.substeps;
+  for (int k = 0; k < K; ++k) {
+    SubInfo si;
+    lunar_substep(E, am, as, P, si);
+    rsum = rsum + si.reward;
+    rc = si.rc;
+    lc = si.lc;
+    if (si.done != COTIX_DONE_NO) {  // freeze on done (cotix/_envs.py:81-103)
+      d = si.done;
+      break;
+    }
+  }
+  bool terrain = (sin_ != sout);
+  if (d != COTIX_DONE_NO && P.auto_reset) {
+    Key2 rk = E.key;
+    const uint32_t episode = ((E.status >> 8) + 1u) & 0xFFFFFFu;
+    if (P.rng_mode == COTIX_RNG_THREEFRY) {
+      rk = tf_split(E.key, 2u, 1u);
+      E.key = tf_split(E.key, 2u, 0u);
+    }
+    lunar_reset_env(E, rk, P, episode);
+    rc = lc = false;
+    terrain = true;
+  }
+  store_env(E, sout, ld, e, terrain);
+  if (reward) reward[e] = rsum;
+  if (done) done[e] = (uint8_t)d;
+  if (obs) {
+    obs[0 * ld + e] = E.b[0].px;
+    obs[1 * ld + e] = E.b[0].py;
+    obs[2 * ld + e] = E.b[0].vx;
+    obs[3 * ld + e] = E.b[0].vy;
+    obs[4 * ld + e] = E.b[0].ang;
+    obs[5 * ld + e] = E.b[0].w;
+    obs[6 * ld + e] = rc ? 1.0f : 0.0f;
+    obs[7 * ld + e] = lc ? 1.0f : 0.0f;
+  }
+}
+
+__global__ void __launch_bounds__(128)
+lunar_reset_kernel(int64_t B, const uint32_t* __restrict__ keys, float* __restrict__ state,
+                   int64_t ld, const __grid_constant__ CotixLunarParams P) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= B) return;
+  EnvRegs E;
+  Key2 key;
+  key.a = keys[2 * e];
+  key.b = keys[2 * e + 1];
+  lunar_reset_env(E, key, P, 0u);
+  E.key = key;
+  store_env(E, state, ld, e, true);
+}
+
+}  // namespace
+
+extern "C" int cx_launch_lunar_step(cudaStream_t st, int64_t B, const float* sin_, float* sout,
+                                    int64_t ld, const float* action, float* reward, uint8_t* done,
+                                    float* obs, const CotixLunarParams* p) {
+  if (B == 0) return 0;
+  lunar_step_kernel<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(B, sin_, sout, ld, action, reward,
+                                                                 done, obs, *p);
+  cx_count_launch();
+  return cx_check_launch("lunar_step_kernel");
+}
+extern "C" int cx_launch_lunar_reset(cudaStream_t st, int64_t B, const uint32_t* keys, float* state,
+                                     int64_t ld, const CotixLunarParams* p) {
+  if (B == 0) return 0;
+  lunar_reset_kernel<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(B, keys, state, ld, *p);
+  cx_count_launch();
+  return cx_check_launch("lunar_reset_kernel");
+}

@@ -1,0 +1,195 @@
+"""Host-side mirror of the reference's LunarLander step for a batch of B environments.
+
+Reference surface this stands in for:
+  * `LunarLander(key)`                      cotix/_lunar_lander.py:29-143  -> `reset(keys)`
+  * `f(env, key)` (the composed step)       examples/test_viz.py:25-44     -> `step(state, action)`
+    = ExplicitEulerPhysics.step + gravity + RandomizedCollider.resolve + key split +
+      LunarLander.step, all fused into one CUDA kernel behind `cotix_lunar_step`.
+State is a `LunarState`: one [36, B] float32 device tensor, struct-of-arrays over the env axis
+(field map in include/cotix_b200.h), with converters to the reference's per-body leaves.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import LunarParams
+
+NF = 36
+NOBS = 8
+F_HEIGHT0, F_KNOT0, F_KEY0, F_KEY1, F_STEPS, F_STATUS, F_RETURN, F_SHAPING = 18, 26, 30, 31, 32, 33, 34, 35
+RNG_THREEFRY, RNG_PHILOX = 0, 1
+BODY_NAMES = ("lander", "right_leg", "left_leg")
+LEAF_NAMES = ("position_x", "position_y", "velocity_x", "velocity_y", "angle", "angular_velocity")
+
+
+def _stream_ptr(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+@dataclass
+class LunarState:
+    """[36, B] float32 SoA state on the device (uint32 fields are bit-cast)."""
+
+    data: torch.Tensor
+
+    @property
+    def batch(self) -> int:
+        return self.data.shape[1]
+
+    def body(self, i: int) -> dict:
+        """DynamicBody leaves of body i (cotix/_bodies.py:189-206) as [B] / [B, 2] views."""
+        d = self.data
+        return {
+            "position": torch.stack([d[i * 6 + 0], d[i * 6 + 1]], -1),
+            "velocity": torch.stack([d[i * 6 + 2], d[i * 6 + 3]], -1),
+            "angle": d[i * 6 + 4],
+            "angular_velocity": d[i * 6 + 5],
+        }
+
+    @property
+    def key(self) -> torch.Tensor:
+        return self.data[F_KEY0:F_KEY1 + 1].view(torch.int32).T.contiguous()
+
+    @property
+    def steps(self) -> torch.Tensor:
+        return self.data[F_STEPS].view(torch.int32)
+
+    @property
+    def status(self) -> torch.Tensor:
+        return self.data[F_STATUS].view(torch.int32)
+
+    def numpy(self) -> np.ndarray:
+        return self.data.detach().cpu().numpy()
+
+    @staticmethod
+    def from_numpy(arr: np.ndarray, device="cuda") -> "LunarState":
+        a = np.ascontiguousarray(arr, np.float32)
+        assert a.shape[0] == NF
+        return LunarState(torch.from_numpy(a).to(device))
+
+    def clone(self) -> "LunarState":
+        return LunarState(self.data.clone())
+
+
+def default_params(**overrides) -> LunarParams:
+    """The reference's literals (SURVEY §5 'config'); keyword overrides set struct fields."""
+    p = _lib.default_lunar_params()
+    for k, v in overrides.items():
+        cur = getattr(p, k)
+        if hasattr(cur, "__len__"):
+            for i, x in enumerate(v):
+                cur[i] = x
+        else:
+            setattr(p, k, v)
+    return p
+
+
+def reset(keys, params: LunarParams | None = None, device="cuda") -> LunarState:
+    """reset(key) for a batch: keys [B, 2] uint32 (jax PRNGKey words)."""
+    params = params or default_params()
+    k = np.ascontiguousarray(np.asarray(keys).astype(np.uint32)).reshape(-1, 2)
+    kd = torch.from_numpy(k.view(np.int32)).to(device)
+    B = k.shape[0]
+    state = torch.empty((NF, B), dtype=torch.float32, device=kd.device)
+    with torch.cuda.device(kd.device):
+        _lib.check(_lib.lib().cotix_lunar_reset(_stream_ptr(kd.device), B, kd.data_ptr(), state.data_ptr(),
+                                                B, C.byref(params)))
+    return LunarState(state)
+
+
+def step(state: LunarState, action: torch.Tensor | None = None, params: LunarParams | None = None,
+         inplace: bool = False, want_obs: bool = False):
+    """step(state, action) -> (state', reward[B], done[B]) (+ obs[8, B]).
+
+    action: [2, B] float32 device tensor (main throttle, side throttle) or None for the
+    reference's unactuated step.  Functional by default (a new state tensor), like the
+    reference; `inplace=True` updates `state` (what a CUDA-graph rollout wants).
+    """
+    params = params or default_params()
+    d = state.data
+    B = d.shape[1]
+    out = d if inplace else torch.empty_like(d)
+    reward = torch.empty(B, dtype=torch.float32, device=d.device)
+    done = torch.empty(B, dtype=torch.uint8, device=d.device)
+    obs = torch.empty((NOBS, B), dtype=torch.float32, device=d.device) if want_obs else None
+    if action is not None:
+        action = action.to(device=d.device, dtype=torch.float32).contiguous()
+        assert action.shape == (2, B)
+    with torch.cuda.device(d.device):
+        _lib.check(_lib.lib().cotix_lunar_step(
+            _stream_ptr(d.device), B, d.data_ptr(), out.data_ptr(), d.stride(0),
+            action.data_ptr() if action is not None else None, reward.data_ptr(), done.data_ptr(),
+            obs.data_ptr() if obs is not None else None, C.byref(params)))
+    ns = state if inplace else LunarState(out)
+    if want_obs:
+        return ns, reward, done, obs
+    return ns, reward, done
+
+
+class LunarLanderEnv:
+    """Vector env with HOST-facing reset/step (the `e2e` path of bench.py).
+
+    Owns the device state of B envs through the C handle (`cotix_lunar_env_*`): each
+    `step(action_host)` is H2D(action) -> fused kernel -> D2H(obs, reward, done).
+    """
+
+    def __init__(self, num_envs: int, params: LunarParams | None = None, device: int = 0):
+        self.B = int(num_envs)
+        self.params = params or default_params()
+        self.device = device
+        self._h = C.c_void_p()
+        _lib.check(_lib.lib().cotix_lunar_env_create(C.byref(self._h), device, self.B, C.byref(self.params)))
+        self.obs = torch.empty((NOBS, self.B), dtype=torch.float32).pin_memory()
+        self.reward = torch.empty(self.B, dtype=torch.float32).pin_memory()
+        self.done = torch.empty(self.B, dtype=torch.uint8).pin_memory()
+
+    def close(self):
+        if self._h:
+            _lib.lib().cotix_lunar_env_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self, keys) -> None:
+        k = np.ascontiguousarray(np.asarray(keys).astype(np.uint32)).reshape(self.B, 2)
+        _lib.check(_lib.lib().cotix_lunar_env_reset_host(self._h, k.ctypes.data))
+
+    def step(self, action_host: torch.Tensor | np.ndarray | None):
+        """action_host: [2, B] float32 host tensor (pinned for best speed)."""
+        ptr = None
+        if action_host is not None:
+            if isinstance(action_host, np.ndarray):
+                action_host = torch.from_numpy(np.ascontiguousarray(action_host, np.float32))
+            assert action_host.shape == (2, self.B) and action_host.dtype == torch.float32
+            ptr = action_host.data_ptr()
+        _lib.check(_lib.lib().cotix_lunar_env_step_host(self._h, ptr, self.obs.data_ptr(),
+                                                        self.reward.data_ptr(), self.done.data_ptr()))
+        return self.obs, self.reward, self.done
+
+    def get_state(self) -> np.ndarray:
+        out = np.empty((NF, self.B), np.float32)
+        _lib.check(_lib.lib().cotix_lunar_env_get_state_host(self._h, out.ctypes.data))
+        return out
+
+    def set_state(self, state: np.ndarray) -> None:
+        s = np.ascontiguousarray(state, np.float32)
+        assert s.shape == (NF, self.B)
+        _lib.check(_lib.lib().cotix_lunar_env_set_state_host(self._h, s.ctypes.data))
+
+    def rollout_graph(self, n_steps: int, action_dev: torch.Tensor | None = None) -> None:
+        """Enqueue n_steps fused steps as one replayed CUDA graph on the handle's stream."""
+        ptr = action_dev.data_ptr() if action_dev is not None else None
+        _lib.check(_lib.lib().cotix_lunar_env_rollout_graph(self._h, int(n_steps), ptr))
+
+    def synchronize(self) -> None:
+        st = _lib.lib().cotix_lunar_env_stream(self._h)
+        torch.cuda.ExternalStream(st, device=self.device).synchronize()
