@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""bench.py — LunarLander env-steps/s (BASELINE.json metric) on N B200s, one process per GPU.
+
+  python bench.py --gpus 1 --steps K --warmup W
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...      # the CPU restatement of the reference on host cores
+
+A "step" = one launch of the fused step kernel over the rank's env batch (one physics step of
+every env, with a fresh action, judge, termination and auto-reset).  Workload = BASELINE
+config 3: B = 1,048,576 envs PER GPU (weak scaling; envs are independent, so the batch is
+sharded with no data-path collective), perturbed initial poses, random actions, auto-reset on.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+ALGO_BYTES_PER_ENV_STEP = 224.0   # 136 B read + 88 B written at K=1
+ALGO_BYTES_PER_PAIR = 148.0       # 2 x 64 B read + 20 B written
+L2_BYTES = 126e6
+
+
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _traffic(kernel):
+    """DRAM bytes per launch from the committed ncu --set full capture, if any."""
+    path = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return d.get(kernel)
+    return None
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML during the timed region."""
+
+    def __init__(self, index: int, period=0.05):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._halt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
+        }
+        while not self._halt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def _dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def bench_params(ll, args):
+    return ll.default_params(judge_enabled=1, auto_reset=1, reset_perturb=1,
+                             max_episode_steps=args.max_episode_steps, substeps=args.substeps,
+                             rng_mode=1 if args.rng == "philox" else 0)
+
+
+def initial_state_host(ll, P, B, rank, device):
+    """BASELINE config 3: reset with keys (0, i) then perturb the lander pose on the host."""
+    from gen_inputs import lunar_keys, perturbed_lunar_state
+
+    keys = lunar_keys(B, offset=rank * B)
+    st = ll.reset(keys, P, device=device).numpy()
+    return perturbed_lunar_state(st, np.random.default_rng(1000 + rank), P)
+
+
+# ---------------------------------------------------------------------------------------------
+def run_reference(args):
+    """--impl reference: the reference's CPU path.  cotix itself needs jax+equinox (absent, no
+    network), so this times the C++ restatement of it (oracle/, kind "port") with all host
+    threads, on a bounded sample of the same workload per step."""
+    rank, world, _ = _dist_env()
+    if rank != 0:
+        return
+    from oracle import oracle as o
+
+    P = o.default_lunar_params()
+    P.judge_enabled, P.auto_reset, P.reset_perturb = 1, 1, 1
+    P.max_episode_steps, P.substeps = args.max_episode_steps, args.substeps
+    P.rng_mode = 1 if args.rng == "philox" else 0
+    from gen_inputs import lunar_keys, perturbed_lunar_state
+
+    Bs = args.ref_envs
+    st = perturbed_lunar_state(o.lunar_reset(lunar_keys(Bs), P), np.random.default_rng(1000), P)
+    rng = np.random.default_rng(1)
+    acts = rng.uniform(-1, 1, size=(8, 2, Bs)).astype(np.float32)
+    for w in range(args.warmup):
+        st, _, _ = o.lunar_step(st, acts[w % 8], P, dedupe=not args.ref_literal)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        st, _, _ = o.lunar_step(st, acts[k % 8], P, dedupe=not args.ref_literal)
+    dt = time.perf_counter() - t0
+    value = Bs * args.steps * args.substeps / dt
+    cores = o.num_threads()
+    sample = (f"{Bs} envs x {args.steps} steps of the bench workload per run "
+              f"({'literal 306-evaluation collider' if args.ref_literal else 'memoised duplicate pairs'}, "
+              f"OpenMP over envs)")
+    line = {
+        "impl": "reference", "metric": "LunarLander env-steps/sec", "value": value, "unit": "env-steps/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "LunarLander 1M envs/GPU, auto-reset (BASELINE config 3); CPU arm runs a "
+                               f"bounded sample of {Bs} envs per step", "envs_per_step": Bs,
+                   "substeps": args.substeps, "rng": args.rng},
+        "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+
+    import parallax_b200
+    from parallax_b200 import lunar_lander as ll
+
+    rank, world, local = _dist_env()
+    if world > 1:
+        import torch.distributed as dist
+
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        dist = None
+        torch.cuda.set_device(0)
+    dev = torch.device("cuda", local if world > 1 else 0)
+    parallax_b200._lib.lib()  # fails loudly if the CUDA library is missing
+
+    B = args.envs
+    P = bench_params(ll, args)
+    state = ll.LunarState.from_numpy(initial_state_host(ll, P, B, rank, dev), device=dev)
+    rng = np.random.default_rng(1 + 17 * rank)
+    n_act = 4
+    acts = [torch.from_numpy(rng.uniform(-1, 1, size=(2, B)).astype(np.float32)).to(dev) for _ in range(n_act)]
+    reward_sum = torch.zeros((), dtype=torch.float64, device=dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- device-resident throughput ("value") ------------------------------------------
+    for w in range(args.warmup):
+        ll.step(state, acts[w % n_act], P, inplace=True)
+    barrier()
+    sampler = ClockSampler(local if world > 1 else 0)
+    sampler.start()
+    n0 = parallax_b200.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for k in range(args.steps):
+        _, rew, done = ll.step(state, acts[k % n_act], P, inplace=True)
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = parallax_b200.launch_count() - n0
+    ms = ev0.elapsed_time(ev1)
+    reward_sum += rew.double().sum()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(reward_sum, op=dist.ReduceOp.SUM)  # the only collective: episode-return stats
+    ms_max = float(t.item())
+    total_env_steps = world * B * args.steps * args.substeps
+    value = total_env_steps / (ms_max * 1e-3)
+
+    # ---- end-to-end through the host-facing env handle ("e2e") ---------------------------
+    env = ll.LunarLanderEnv(B, P, device=dev.index)
+    env.set_state(state.numpy())
+    host_acts = [torch.from_numpy(rng.uniform(-1, 1, size=(2, B)).astype(np.float32)).pin_memory()
+                 for _ in range(n_act)]
+    e2e_steps = max(3, min(args.steps, args.e2e_steps))
+    for w in range(3):
+        env.step(host_acts[w % n_act])
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        obs, rew_h, done_h = env.step(host_acts[k % n_act])
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    e2e_launches = e2e_steps
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * e2e_steps * args.substeps / float(te.item())
+    env.close()
+
+    peak, peak_src = _peaks()
+    kern_ms = ms / args.steps  # the timed region holds only launches of the step kernel
+    achieved = ALGO_BYTES_PER_ENV_STEP * B * args.substeps / (kern_ms * 1e-3) / 1e9
+    line = {
+        "metric": "LunarLander env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": "LunarLander 1M envs/GPU, auto-reset (BASELINE config 3)",
+                   "envs_per_gpu": B, "global_batch": world * B, "substeps": args.substeps, "rng": args.rng,
+                   "max_episode_steps": args.max_episode_steps, "parallelism": f"env-shard x{world}",
+                   "l2": f"state {36 * 4 * B / 1e6:.0f} MB + actions > L2 {L2_BYTES / 1e6:.0f} MB, no flush needed"},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": _traffic("lunar_step_kernel"), "kernel": "lunar_step_kernel",
+                     "peak_source": peak_src, "algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
+                     "kernel_ms": kern_ms},
+        "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * 4 * B,
+                "d2h_bytes_per_step": (8 * 4 + 4 + 1) * B, "steps": e2e_steps},
+        "gpu_launches": int(launches + e2e_launches),
+        "clocks": clocks,
+        "mean_last_reward": float(reward_sum.item()) / (world * B),
+    }
+
+    if rank == 0 and world == 1 and not args.no_sweep:
+        line["narrowphase"] = sweep(args, dev, peak)
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_baseline(args)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def sweep(args, dev, peak):
+    """BASELINE config 2: GJK/EPA narrowphase sweep over N random pairs on one B200."""
+    import torch
+
+    import parallax_b200
+    from gen_inputs import random_pairs
+    from parallax_b200 import shapes as sh
+
+    n = args.pairs
+    rng = np.random.default_rng(2)
+    chunk = 1 << 21
+    a = torch.empty((n, 16), dtype=torch.float32, device=dev)
+    b = torch.empty((n, 16), dtype=torch.float32, device=dev)
+    for s in range(0, n, chunk):
+        ha, hb = random_pairs(rng, min(chunk, n - s))
+        a[s:s + ha.shape[0]] = torch.from_numpy(ha).to(dev)
+        b[s:s + hb.shape[0]] = torch.from_numpy(hb).to(dev)
+    A, Bt = sh.ShapeBatch(a), sh.ShapeBatch(b)
+    for _ in range(3):
+        ci = sh.narrowphase(A, Bt)
+    torch.cuda.synchronize(dev)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    ev0.record()
+    for _ in range(reps):
+        ci = sh.narrowphase(A, Bt)
+    ev1.record()
+    torch.cuda.synchronize(dev)
+    ms = ev0.elapsed_time(ev1) / reps
+    achieved = ALGO_BYTES_PER_PAIR * n / (ms * 1e-3) / 1e9
+    return {"metric": "GJK+EPA pair-tests/sec", "value": n / (ms * 1e-3), "unit": "pairs/s", "pairs": n,
+            "ms_per_sweep": ms, "hit_fraction": float(ci.exists.float().mean().item()),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": _traffic("narrowphase_kernel"),
+                         "kernel": "narrowphase_kernel"}}
+
+
+def cpu_baseline(args):
+    """The oracle (a C++ port of the reference path) on the box's host cores, bounded sample."""
+    from gen_inputs import lunar_keys, perturbed_lunar_state
+    from oracle import oracle as o
+
+    P = o.default_lunar_params()
+    P.judge_enabled, P.auto_reset, P.reset_perturb = 1, 1, 1
+    P.max_episode_steps, P.substeps = args.max_episode_steps, args.substeps
+    P.rng_mode = 1 if args.rng == "philox" else 0
+    Bs, steps = args.ref_envs, 40
+    st = perturbed_lunar_state(o.lunar_reset(lunar_keys(Bs), P), np.random.default_rng(1000), P)
+    acts = np.random.default_rng(1).uniform(-1, 1, size=(4, 2, Bs)).astype(np.float32)
+    for w in range(2):
+        st, _, _ = o.lunar_step(st, acts[w % 4], P)
+    t0 = time.perf_counter()
+    for k in range(steps):
+        st, _, _ = o.lunar_step(st, acts[k % 4], P)
+    dt = time.perf_counter() - t0
+    return {"value": Bs * steps * args.substeps / dt, "unit": "env-steps/s", "cores": o.num_threads(),
+            "kind": "port", "sample": f"{Bs} envs x {steps} steps of the bench workload, memoised duplicate "
+                                      "pairs, OpenMP over envs"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs", type=int, default=1 << 20, help="envs per GPU")
+    ap.add_argument("--substeps", type=int, default=1)
+    ap.add_argument("--rng", default="threefry", choices=["threefry", "philox"])
+    ap.add_argument("--max-episode-steps", dest="max_episode_steps", type=int, default=1000)
+    ap.add_argument("--pairs", type=int, default=1 << 24)
+    ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=50)
+    ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=16384)
+    ap.add_argument("--ref-literal", dest="ref_literal", action="store_true")
+    ap.add_argument("--no-sweep", dest="no_sweep", action="store_true")
+    ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

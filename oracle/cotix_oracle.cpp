@@ -43,6 +43,9 @@
 #include <map>
 #include <utility>
 #include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 #include "../include/cotix_b200.h"
 #include "../parallax_b200/csrc/cx_trig.h"
@@ -1860,6 +1863,13 @@ int oracle_scene_step(int nb, float* bodies10, int nparts, const int32_t* part_b
   return 0;
 }
 
+int oracle_num_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
 int oracle_sizeof_lunar_params(void) { return (int)sizeof(CotixLunarParams); }
 const char* oracle_last_error(void) { return g_err; }
 

@@ -107,6 +107,10 @@ def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
+def num_threads() -> int:
+    return int(lib().oracle_num_threads())
+
+
 def set_trig_mode(mode: int) -> None:
     """0 = libm (default), 1 = the engine's cx_trig.h definitions (for exact-equality tests)."""
     lib().oracle_set_trig_mode(int(mode))
