@@ -31,32 +31,31 @@ struct MassP {
   float mass, inertia, e, mu;
 };
 
-// ---- order_clockwise on a register polygon (cold path) --------------------------------
+// ---- order_clockwise on a register polygon of N vertices (cotix/_geometry_utils.py:60-67) ----
+template <int N>
 static __device__ __noinline__ void poly_sort_cw(Poly& p) {
-  const int n = p.n;
   float sx = 0.0f, sy = 0.0f;
 #pragma unroll
-  for (int k = 0; k < CX_MAXV; ++k)
-    if (k < n) {
-      sx = sx + p.x[k];
-      sy = sy + p.y[k];
-    }
-  const float mx = sx / (float)n, my = sy / (float)n;
-  float ang[CX_MAXV];
+  for (int k = 0; k < N; ++k) {
+    sx = sx + p.x[k];
+    sy = sy + p.y[k];
+  }
+  const float mx = sx / (float)N, my = sy / (float)N;
+  float ang[N];
 #pragma unroll
-  for (int k = 0; k < CX_MAXV; ++k) ang[k] = (k < n) ? cx_atan2f(p.y[k] - my, p.x[k] - mx) : 0.0f;
-  int rank[CX_MAXV];
+  for (int k = 0; k < N; ++k) ang[k] = cx_atan2f(p.y[k] - my, p.x[k] - mx);
+  int rank[N];
 #pragma unroll
-  for (int q = 0; q < CX_MAXV; ++q) {
+  for (int q = 0; q < N; ++q) {
     int r = 0;
     const float aq = ang[q];
     const bool qn = aq != aq;
 #pragma unroll
-    for (int t = 0; t < CX_MAXV; ++t) {
-      if (t != q && t < n) {
+    for (int t = 0; t < N; ++t) {
+      if (t != q) {
         const float at = ang[t];
         const bool tn = at != at;
-        bool before;
+        bool before;  // stable, NaN last (jnp.argsort)
         if (tn || qn) before = (!tn && qn) || (tn == qn && t < q);
         else before = (at < aq) || (at == aq && t < q);
         if (before) ++r;
@@ -64,17 +63,23 @@ static __device__ __noinline__ void poly_sort_cw(Poly& p) {
     }
     rank[q] = r;
   }
-  Poly o = p;
+  float ox[N], oy[N];
 #pragma unroll
-  for (int t = 0; t < CX_MAXV; ++t) {
+  for (int t = 0; t < N; ++t) {
+    ox[t] = p.x[0];
+    oy[t] = p.y[0];
 #pragma unroll
-    for (int q = 0; q < CX_MAXV; ++q)
-      if (q < n && rank[q] == t) {
-        o.x[t] = p.x[q];
-        o.y[t] = p.y[q];
+    for (int q = 0; q < N; ++q)
+      if (rank[q] == t) {
+        ox[t] = p.x[q];
+        oy[t] = p.y[q];
       }
   }
-  p = o;
+#pragma unroll
+  for (int t = 0; t < N; ++t) {
+    p.x[t] = ox[t];
+    p.y[t] = oy[t];
+  }
 }
 
 // ---- resolution — cotix/_collision_resolution.py:52-151 -------------------------------
@@ -121,7 +126,7 @@ static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1
 }
 
 // ---- joints — cotix/_lunar_lander.py:145-218 -------------------------------------------
-CX_DEV void joint_constraint(BodyS& b1, const MassP& m1, V2 c1, BodyS& b2, const MassP& m2, V2 c2,
+static __device__ __noinline__ void joint_constraint(BodyS& b1, const MassP& m1, V2 c1, BodyS& b2, const MassP& m2, V2 c2,
                              const CotixLunarParams& P) {
   V2 dp = c1 - c2;
   V2 dv = velocity_at(b1, c1) - velocity_at(b2, c2);

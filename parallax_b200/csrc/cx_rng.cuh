@@ -58,18 +58,23 @@ __host__ __device__ __forceinline__ void threefry2x32(uint32_t k0, uint32_t k1, 
   o1 = x1;
 }
 
+// One out-of-line copy for the key-chain code: the 20 rounds are ~110 SASS instructions and
+// the step kernel has ~50 call sites; inlining them all made the kernel 197 KB of code and
+// I-cache-miss bound (profiles/r1a).  Returns (o0, o1) packed as a uint2.
+static __device__ __noinline__ uint2 tf_call(uint32_t k0, uint32_t k1, uint32_t x0, uint32_t x1) {
+  uint32_t o0, o1;
+  threefry2x32(k0, k1, x0, x1, o0, o1);
+  return make_uint2(o0, o1);
+}
 // word w of random_bits(key, n) (n words, n even or odd)
 CX_DEV uint32_t tf_bits_word(Key2 key, uint32_t n, uint32_t w) {
   const uint32_t half = (n + 1u) >> 1;
-  uint32_t o0, o1;
-  if (w < half) {
-    uint32_t c1 = half + w;
-    if (c1 >= n) c1 = 0u;  // the zero padding of an odd count
-    threefry2x32(key.a, key.b, w, c1, o0, o1);
-    return o0;
-  }
-  threefry2x32(key.a, key.b, w - half, w, o0, o1);
-  return o1;
+  const bool lo = w < half;
+  uint32_t c0 = lo ? w : w - half;
+  uint32_t c1 = lo ? half + w : w;
+  if (c1 >= n) c1 = 0u;  // the zero padding of an odd count
+  uint2 o = tf_call(key.a, key.b, c0, c1);
+  return lo ? o.x : o.y;
 }
 // key `idx` of jax.random.split(key, num)
 CX_DEV Key2 tf_split(Key2 key, uint32_t num, uint32_t idx) {
@@ -92,7 +97,7 @@ CX_DEV bool tf_bernoulli(Key2 key, float p) { return tf_uniform(key, 0.0f, 1.0f)
 // Philox4x32-10 (Random123)
 CX_DEV void philox4x32_10(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t c2,
                           uint32_t c3, uint32_t out[4]) {
-#pragma unroll
+#pragma unroll 1
   for (int r = 0; r < 10; ++r) {
     uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
     uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;

@@ -1,14 +1,27 @@
-// lunar_kernel.cu — K1 (fused LunarLander step) and K4 (reset), one environment per thread.
+// lunar_kernel.cu — K1 (fused LunarLander step) and K4 (reset).
 //
-// State is struct-of-arrays over the env axis (include/cotix_b200.h), so every field access
-// of a warp is one fully coalesced 128-byte transaction; a step reads 36 words + 2 action
-// words and writes back only what changed.  See DESIGN.md for why the shipped mapping is
-// env-per-thread with candidate pairs processed after an exact AABB cull rather than the
-// env-per-warp mapping the north_star sketches (measured comparison in profiles/).
+// Mapping: one environment per THREAD for the regular part of the
+// step, and a block-level work queue for the irregular part:
+//   phase A  (thread = env)   integrate, engines, world polygons, exact broadphase cull;
+//                             envs with candidate pairs publish their sorted world polygons to
+//                             shared memory and push (env, pair) items
+//   phase B  (thread = item)  GJK + EPA + contact generation, one candidate pair per thread —
+//                             the 128 threads of the block drain the queue together, so the
+//                             divergent narrowphase runs at full lane occupancy instead of on
+//                             the few lanes whose env happens to be in contact
+//   phase C  (thread = env)   coin flips / random choice (lazy threefry or Philox), sequential
+//                             impulse resolution, joints, judge, auto-reset, store
+// State is struct-of-arrays over the env axis (include/cotix_b200.h): every field access of a
+// warp is one coalesced 128-byte transaction.
 #include "cx_launch.cuh"
 #include "cx_lunar.cuh"
 
 namespace {
+
+constexpr int TPB = 128;    // threads (= envs) per block
+constexpr int QCAP = 1024;  // narrowphase items per block and sub-step; overflow falls back to
+                            // the owning thread evaluating its own pairs (same results)
+constexpr uint32_t ITEM_SKIP = 0xFFFFFFFFu;
 
 struct EnvRegs {
   BodyS b[3];
@@ -19,24 +32,43 @@ struct EnvRegs {
   float ret, shaping;
 };
 
+struct SharedBlock {
+  float poly[28][TPB];  // sorted world vertices: lander 0..11, right leg 12..19, left leg 20..27
+  float terr[12][TPB];  // heights 0..7, knots 8..11
+  uint32_t item[QCAP];  // (env_local << 8) | pair id
+  float res[4][QCAP];   // pen.x, pen.y, cp.x, cp.y   (cp NaN = no contact)
+  int qcount;
+};
+
+// pair ids = bits of the candidate mask:
+//  0 (rl,L)  1 (ll,L)  2..8 (g_k,L)  9 (ll,rl)  10 (ll,ll)  11..17 (g_k,rl)  18..24 (g_k,ll)
+constexpr uint32_t GROUND_BITS = 0x01FFF9FCu;
+
+struct StepCtx {
+  float cs[3], sn[3];
+  float thr_main, thr_side;
+  uint32_t cand;
+  int base;  // first queue slot of this env's items, or -1 (evaluate inline)
+};
+
 struct SubInfo {
   float reward;
   int done;
   bool rc, lc;
 };
 
-CX_DEV void world_poly(const float (*local)[2], int n, const BodyS& b, float c, float s, Poly& out) {
-  out.n = n;
+template <int N>
+CX_DEV void world_poly(const float (*local)[2], const BodyS& b, float c, float s, Poly& out) {
+  out.n = N;
   const float ms = -s;
 #pragma unroll
   for (int k = 0; k < CX_MAXV; ++k) {
-    if (k < n) {
+    if (k < N) {
+      // forward_vector (cotix/_geometry_utils.py:134-138): matrix @ [x, y, 1] / w with
+      // w = 0*x + 0*y + 1 = 1 exactly for finite local vertices, so the division is dropped
       float x = local[k][0], y = local[k][1];
-      float tx = c * x + ms * y + b.px * 1.0f;
-      float ty = s * x + c * y + b.py * 1.0f;
-      float tw = 0.0f * x + 0.0f * y + 1.0f * 1.0f;
-      out.x[k] = tx / tw;
-      out.y[k] = ty / tw;
+      out.x[k] = c * x + ms * y + b.px * 1.0f;
+      out.y[k] = s * x + c * y + b.py * 1.0f;
     } else {
       out.x[k] = 0.0f;
       out.y[k] = 0.0f;
@@ -46,64 +78,50 @@ CX_DEV void world_poly(const float (*local)[2], int n, const BodyS& b, float c, 
 struct Aabb {
   float lx, ly, hx, hy;
 };
+template <int N>
 CX_DEV Aabb poly_aabb(const Poly& p) {
   Aabb a;
   a.lx = a.hx = p.x[0];
   a.ly = a.hy = p.y[0];
 #pragma unroll
-  for (int k = 1; k < CX_MAXV; ++k)
-    if (k < p.n) {
-      a.lx = fminf(a.lx, p.x[k]);
-      a.hx = fmaxf(a.hx, p.x[k]);
-      a.ly = fminf(a.ly, p.y[k]);
-      a.hy = fmaxf(a.hy, p.y[k]);
-    }
+  for (int k = 1; k < N; ++k) {
+    a.lx = fminf(a.lx, p.x[k]);
+    a.hx = fmaxf(a.hx, p.x[k]);
+    a.ly = fminf(a.ly, p.y[k]);
+    a.hy = fmaxf(a.hy, p.y[k]);
+  }
   return a;
 }
 CX_DEV bool aabb_near(const Aabb& a, const Aabb& b) {
   const float m = CX_CULL_MARGIN;
   return !(a.hx + m < b.lx || b.hx + m < a.lx || a.hy + m < b.ly || b.hy + m < a.ly);
 }
-CX_DEV float terrain_x(const EnvRegs& E, const CotixLunarParams& P, int i) {
+// Separating-axis test against the top edge TL=(x0,h0) -> TR=(x1,h1) of a ground trapezoid
+// (the trapezoid lies in n.(v - TL) <= 0, n = perp(TR - TL)): true when every vertex of the
+// body polygon is above that line by more than the cull margin, i.e. the pair cannot touch.
+template <int N>
+CX_DEV bool above_top_edge(const Poly& p, float x0, float h0, float x1, float h1) {
+  const float nx = -(h1 - h0), ny = x1 - x0;
+  const float thr = CX_CULL_MARGIN * (fabsf(nx) + fabsf(ny));
+  bool all_above = true;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    float s = nx * (p.x[k] - x0) + ny * (p.y[k] - h0);
+    all_above = all_above && (s > thr);
+  }
+  return all_above;
+}
+CX_DEV float terrain_x(const float kn[4], const CotixLunarParams& P, int i) {
   switch (i) {
     case 0: return -P.terrain_x_outer;
-    case 1: return E.kn[0];
-    case 2: return E.kn[1];
+    case 1: return kn[0];
+    case 2: return kn[1];
     case 3: return -P.pad_half_width;
     case 4: return P.pad_half_width;
-    case 5: return E.kn[2];
-    case 6: return E.kn[3];
+    case 5: return kn[2];
+    case 6: return kn[3];
     default: return P.terrain_x_outer;
   }
-}
-// ground part k as the collider sees it: Polygon4.__init__ sort (cotix/_lunar_lander.py:132)
-// followed by the identity transform + re-sort of part.transform (cotix/_colliders.py:92-94)
-static __device__ __noinline__ void ground_poly(const EnvRegs& E, const CotixLunarParams& P, int k,
-                                         bool poisoned, Poly& g) {
-  float x0 = terrain_x(E, P, k), x1 = terrain_x(E, P, k + 1);
-  float h0 = E.h[0], h1 = E.h[1];
-#pragma unroll
-  for (int q = 1; q < 7; ++q)
-    if (q == k) {
-      h0 = E.h[q];
-      h1 = E.h[q + 1];
-    }
-  g.n = 4;
-  g.x[0] = x0; g.y[0] = h0;
-  g.x[1] = x0; g.y[1] = P.ground_floor;
-  g.x[2] = x1; g.y[2] = h1;
-  g.x[3] = x1; g.y[3] = P.ground_floor;
-  g.x[4] = g.y[4] = g.x[5] = g.y[5] = 0.0f;
-  poly_sort_cw(g);
-  if (poisoned) {
-#pragma unroll
-    for (int q = 0; q < 4; ++q) g.x[q] = g.y[q] = CX_NAN;
-  }
-  poly_sort_cw(g);
-}
-
-static __device__ __noinline__ Contact poly_pair(const Poly& a, const Poly& b, V2 start, int gjk_max) {
-  return convex_vs_polygon(a, b, start, gjk_max);
 }
 
 CX_DEV float lunar_shaping(const BodyS& L, const CotixLunarParams& P, bool rc, bool lc) {
@@ -118,10 +136,202 @@ CX_DEV float lunar_shaping(const BodyS& L, const CotixLunarParams& P, bool rc, b
   return s;
 }
 
-// One physics sub-step of one env = f(env, key) of examples/test_viz.py:25-44 (+ engines and
-// judge, which the reference does not have).
-__device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
-                              SubInfo& info) {
+static __device__ __noinline__ Contact poly_pair(const Poly& a, const Poly& b, V2 start, int gjk_max) {
+  return convex_vs_polygon(a, b, start, gjk_max);
+}
+
+// body polygon `which` (0 lander, 1 right leg, 2 left leg) of env `el` from shared memory
+CX_DEV void load_body_poly(const SharedBlock& S, int el, int which, Poly& p) {
+  const int off = which == 0 ? 0 : (which == 1 ? 12 : 20);
+  const int n = which == 0 ? 6 : 4;
+  p.n = n;
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k) {
+    if (k < n) {
+      p.x[k] = S.poly[off + 2 * k][el];
+      p.y[k] = S.poly[off + 2 * k + 1][el];
+    } else {
+      p.x[k] = 0.0f;
+      p.y[k] = 0.0f;
+    }
+  }
+}
+// ground part k as the collider sees it: Polygon4.__init__ sort (cotix/_lunar_lander.py:132)
+// followed by the identity transform + re-sort of part.transform (cotix/_colliders.py:92-94)
+CX_DEV void load_ground_poly(const SharedBlock& S, int el, int k, const CotixLunarParams& P, Poly& g) {
+  float kn[4] = {S.terr[8][el], S.terr[9][el], S.terr[10][el], S.terr[11][el]};
+  float x0 = terrain_x(kn, P, k), x1 = terrain_x(kn, P, k + 1);
+  float h0 = S.terr[k][el], h1 = S.terr[k + 1][el];
+  g.n = 4;
+  g.x[0] = x0; g.y[0] = h0;
+  g.x[1] = x0; g.y[1] = P.ground_floor;
+  g.x[2] = x1; g.y[2] = h1;
+  g.x[3] = x1; g.y[3] = P.ground_floor;
+  g.x[4] = g.y[4] = g.x[5] = g.y[5] = 0.0f;
+  poly_sort_cw<4>(g);
+  poly_sort_cw<4>(g);
+}
+// narrowphase of one (env, pair) item
+static __device__ __noinline__ Contact eval_item(const SharedBlock& S, int el, int pid,
+                                                 const CotixLunarParams& P) {
+  Poly A, B;
+  int wa, wb, gk = -1;
+  if (pid == 0) { wa = 1; wb = 0; }
+  else if (pid == 1) { wa = 2; wb = 0; }
+  else if (pid <= 8) { gk = pid - 2; wa = -1; wb = 0; }
+  else if (pid == 9) { wa = 2; wb = 1; }
+  else if (pid == 10) { wa = 2; wb = 2; }
+  else if (pid <= 17) { gk = pid - 11; wa = -1; wb = 1; }
+  else { gk = pid - 18; wa = -1; wb = 2; }
+  if (gk >= 0) load_ground_poly(S, el, gk, P, A);
+  else load_body_poly(S, el, wa, A);
+  load_body_poly(S, el, wb, B);
+  return poly_pair(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters);
+}
+
+// ---- phase A: regular part up to the broadphase; publishes candidates --------------------
+__device__ void phase_a(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
+                        SharedBlock& S, StepCtx& cx) {
+  const int tid = threadIdx.x;
+  // ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24); the ground stays at 0
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    E.b[i].px = E.b[i].px + E.b[i].vx * P.dt;
+    E.b[i].py = E.b[i].py + E.b[i].vy * P.dt;
+    E.b[i].ang = E.b[i].ang + E.b[i].w * P.dt;
+  }
+  // gravity on the lander only (examples/test_viz.py:27-31)
+  E.b[0].vx = E.b[0].vx + P.gravity_dv[0];
+  E.b[0].vy = E.b[0].vy + P.gravity_dv[1];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &cx.sn[i], &cx.cs[i]);
+  if (!(fabsf(E.b[0].ang) < 1.0e9f) || !(fabsf(E.b[1].ang) < 1.0e9f) || !(fabsf(E.b[2].ang) < 1.0e9f))
+    E.status |= COTIX_ST_ANGLE_RANGE;
+  // engines (new): a zero action leaves the reference step untouched
+  cx.thr_main = jclip(a_main, 0.0f, 1.0f);
+  cx.thr_side = jclip(a_side, -1.0f, 1.0f);
+  if (cx.thr_main != 0.0f) {
+    float dv = P.main_engine_dv * cx.thr_main;
+    E.b[0].vx = E.b[0].vx + (-cx.sn[0]) * dv;
+    E.b[0].vy = E.b[0].vy + cx.cs[0] * dv;
+  }
+  if (cx.thr_side != 0.0f) {
+    float dv = P.side_engine_dv * cx.thr_side;
+    E.b[0].vx = E.b[0].vx + cx.cs[0] * dv;
+    E.b[0].vy = E.b[0].vy + cx.sn[0] * dv;
+    E.b[0].w = E.b[0].w - P.side_engine_dw * cx.thr_side;
+  }
+  // world polygons (local vertex order) and the broadphase — new, exact
+  Poly wL, wr, wl;
+  world_poly<6>(P.lander_local, E.b[0], cx.cs[0], cx.sn[0], wL);
+  world_poly<4>(P.leg_local[0], E.b[1], cx.cs[1], cx.sn[1], wr);
+  world_poly<4>(P.leg_local[1], E.b[2], cx.cs[2], cx.sn[2], wl);
+  const Aabb bL = poly_aabb<6>(wL), br = poly_aabb<4>(wr), bl = poly_aabb<4>(wl);
+  uint32_t cand = 0u;
+  if (aabb_near(br, bL)) cand |= 1u << 0;
+  if (aabb_near(bl, bL)) cand |= 1u << 1;
+  if (aabb_near(bl, br)) cand |= 1u << 9;
+#pragma unroll
+  for (int k = 0; k < 7; ++k) {
+    const float x0 = terrain_x(E.kn, P, k), x1 = terrain_x(E.kn, P, k + 1);
+    const float h0 = E.h[k], h1 = E.h[k + 1];
+    Aabb g;
+    g.lx = fminf(x0, x1);
+    g.hx = fmaxf(x0, x1);
+    g.ly = fminf(fminf(h0, h1), P.ground_floor);
+    g.hy = fmaxf(fmaxf(h0, h1), P.ground_floor);
+    const bool regular = (x1 > x0) && (h0 > P.ground_floor) && (h1 > P.ground_floor);
+    if (aabb_near(g, bL) && !(regular && above_top_edge<6>(wL, x0, h0, x1, h1))) cand |= 1u << (2 + k);
+    if (aabb_near(g, br) && !(regular && above_top_edge<4>(wr, x0, h0, x1, h1))) cand |= 1u << (11 + k);
+    if (aabb_near(g, bl) && !(regular && above_top_edge<4>(wl, x0, h0, x1, h1))) cand |= 1u << (18 + k);
+  }
+  bool bad = (E.status & COTIX_ST_GROUND_NAN) != 0u;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    bad = bad || !(fabsf(E.b[i].px) <= 3.0e38f) || !(fabsf(E.b[i].py) <= 3.0e38f) ||
+          !(fabsf(E.b[i].ang) <= 3.0e38f);
+  if (bad) cand = 0u;  // NaN vertices: every GJK of the reference reports "no" (any-NaN rule)
+  // the self pair (left leg vs itself) can only matter when body 2 has another
+  // live cell, i.e. when pair 1 or pair 9 is a candidate
+  if (cand & ((1u << 1) | (1u << 9))) cand |= 1u << 10;
+  cx.cand = cand;
+  cx.base = -1;
+  if (cand != 0u) {
+    poly_sort_cw<6>(wL);  // part.transform() re-sorts the world vertices (cotix/_convex_shapes.py:181-187)
+    poly_sort_cw<4>(wr);
+    poly_sort_cw<4>(wl);
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      S.poly[2 * k][tid] = wL.x[k];
+      S.poly[2 * k + 1][tid] = wL.y[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      S.poly[12 + 2 * k][tid] = wr.x[k];
+      S.poly[13 + 2 * k][tid] = wr.y[k];
+      S.poly[20 + 2 * k][tid] = wl.x[k];
+      S.poly[21 + 2 * k][tid] = wl.y[k];
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) S.terr[k][tid] = E.h[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) S.terr[8 + k][tid] = E.kn[k];
+    const int cnt = __popc(cand);
+    const int base = atomicAdd(&S.qcount, cnt);
+    if (base + cnt <= QCAP) {
+      cx.base = base;
+      uint32_t m = cand;
+      int slot = base;
+      while (m) {
+        const int bit = __ffs(m) - 1;
+        m &= m - 1u;
+        S.item[slot++] = ((uint32_t)tid << 8) | (uint32_t)bit;
+      }
+    } else {
+      for (int slot = base; slot < QCAP && slot < base + cnt; ++slot) S.item[slot] = ITEM_SKIP;
+    }
+  }
+}
+
+// ---- phase B: the block drains the narrowphase queue, one pair per thread ----------------
+__device__ void phase_b(SharedBlock& S, const CotixLunarParams& P) {
+  const int n = S.qcount < QCAP ? S.qcount : QCAP;
+  for (int i = threadIdx.x; i < n; i += TPB) {
+    const uint32_t it = S.item[i];
+    if (it == ITEM_SKIP) continue;
+    const Contact c = eval_item(S, (int)(it >> 8), (int)(it & 0xFFu), P);
+    S.res[0][i] = c.pen.x;
+    S.res[1][i] = c.pen.y;
+    S.res[2][i] = c.cp.x;
+    S.res[3][i] = c.cp.y;
+  }
+}
+
+// contact of candidate pair `bit` of this thread's env
+CX_DEV Contact get_contact(const SharedBlock& S, const StepCtx& cx, int bit, const CotixLunarParams& P) {
+  if (cx.base >= 0) {
+    const int i = cx.base + __popc(cx.cand & ((1u << bit) - 1u));
+    Contact c;
+    c.pen = mk2(S.res[0][i], S.res[1][i]);
+    c.cp = mk2(S.res[2][i], S.res[3][i]);
+    c.status = 0u;
+    return c;
+  }
+  return eval_item(S, threadIdx.x, bit, P);  // queue overflow: evaluate inline (same result)
+}
+CX_DEV bool live(const SharedBlock& S, const StepCtx& cx, int bit, const CotixLunarParams& P) {
+  if (!((cx.cand >> bit) & 1u)) return false;
+  if (cx.base >= 0) {
+    const int i = cx.base + __popc(cx.cand & ((1u << bit) - 1u));
+    const float x = S.res[2][i], y = S.res[3][i];
+    return !((x != x) || (y != y));
+  }
+  return !contact_isnan(eval_item(S, threadIdx.x, bit, P));
+}
+
+// ---- phase C: contact selection, resolution, joints, judge --------------------------------
+__device__ void phase_c(EnvRegs& E, const CotixLunarParams& P, const SharedBlock& S,
+                        const StepCtx& cx, SubInfo& info) {
   MassP mp[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -131,128 +341,29 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
     mp[i].mu = P.body_props[i][3];
   }
   const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
-  BodyS G;
+  BodyS G;  // the static ground body (mass = inertia = inf); NaN once poisoned
   G.px = G.py = G.vx = G.vy = G.ang = G.w = poisoned ? CX_NAN : 0.0f;
-
-  // --- ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24)
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    E.b[i].px = E.b[i].px + E.b[i].vx * P.dt;
-    E.b[i].py = E.b[i].py + E.b[i].vy * P.dt;
-    E.b[i].ang = E.b[i].ang + E.b[i].w * P.dt;
-  }
   G.px = G.px + G.vx * P.dt;
   G.py = G.py + G.vy * P.dt;
   G.ang = G.ang + G.w * P.dt;
-  // --- gravity on the lander only (examples/test_viz.py:27-31)
-  E.b[0].vx = E.b[0].vx + P.gravity_dv[0];
-  E.b[0].vy = E.b[0].vy + P.gravity_dv[1];
-
-  float cs[3], sn[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &sn[i], &cs[i]);
-  if (!(fabsf(E.b[0].ang) < 1.0e9f) || !(fabsf(E.b[1].ang) < 1.0e9f) || !(fabsf(E.b[2].ang) < 1.0e9f))
-    E.status |= COTIX_ST_ANGLE_RANGE;
-
-  // --- engines (new): a zero action leaves the reference step untouched
-  const float thr_main = jclip(a_main, 0.0f, 1.0f);
-  const float thr_side = jclip(a_side, -1.0f, 1.0f);
-  if (thr_main != 0.0f) {
-    float dv = P.main_engine_dv * thr_main;
-    E.b[0].vx = E.b[0].vx + (-sn[0]) * dv;
-    E.b[0].vy = E.b[0].vy + cs[0] * dv;
-  }
-  if (thr_side != 0.0f) {
-    float dv = P.side_engine_dv * thr_side;
-    E.b[0].vx = E.b[0].vx + cs[0] * dv;
-    E.b[0].vy = E.b[0].vy + sn[0] * dv;
-    E.b[0].w = E.b[0].w - P.side_engine_dw * thr_side;
-  }
-
-  // --- RandomizedCollider.resolve (cotix/_colliders.py:74-351)
-  // world polygons in local vertex order (unsorted) and their AABBs
-  Poly wl, wr, wL;  // left leg (body 2), right leg (body 1), lander (body 0)
-  world_poly(P.lander_local, 6, E.b[0], cs[0], sn[0], wL);
-  world_poly(P.leg_local[0], 4, E.b[1], cs[1], sn[1], wr);
-  world_poly(P.leg_local[1], 4, E.b[2], cs[2], sn[2], wl);
-  const Aabb bL = poly_aabb(wL), br = poly_aabb(wr), bl = poly_aabb(wl);
-  // candidate bits: 0 (rl,L) 1 (ll,L) 2..8 (g,L) 9 (ll,rl) 11..17 (g,rl) 18..24 (g,ll)
-  uint32_t cand = 0u;
-  if (aabb_near(br, bL)) cand |= 1u << 0;
-  if (aabb_near(bl, bL)) cand |= 1u << 1;
-  if (aabb_near(bl, br)) cand |= 1u << 9;
-#pragma unroll
-  for (int k = 0; k < 7; ++k) {
-    float x0 = terrain_x(E, P, k), x1 = terrain_x(E, P, k + 1);
-    Aabb g;
-    g.lx = fminf(x0, x1);
-    g.hx = fmaxf(x0, x1);
-    g.ly = fminf(fminf(E.h[k], E.h[k + 1]), P.ground_floor);
-    g.hy = fmaxf(fmaxf(E.h[k], E.h[k + 1]), P.ground_floor);
-    if (aabb_near(g, bL)) cand |= 1u << (2 + k);
-    if (aabb_near(g, br)) cand |= 1u << (11 + k);
-    if (aabb_near(g, bl)) cand |= 1u << (18 + k);
-  }
-  bool any_state_nan = false;
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-    any_state_nan = any_state_nan || !(fabsf(E.b[i].px) <= 3.0e38f) || !(fabsf(E.b[i].py) <= 3.0e38f) ||
-                    !(fabsf(E.b[i].ang) <= 3.0e38f);
-  if (any_state_nan || poisoned) cand = 0u;  // NaN vertices: every GJK reports "no" (any-NaN rule)
 
   bool crash = false, rc = false, lc = false;
+  const uint32_t cand = cx.cand;
   if (cand != 0u) {
-    const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
-    const int gmax = P.gjk_max_iters;
-    poly_sort_cw(wL);
-    poly_sort_cw(wr);
-    poly_sort_cw(wl);
-    // narrowphase of every candidate pair; cell = all_contacts[i][j]
-    Contact c10 = contact_none(), c20 = contact_none(), c21 = contact_none();
-    uint32_t st = 0u;
-    if (cand & (1u << 0)) c10 = poly_pair(wr, wL, start, gmax);
-    if (cand & (1u << 1)) c20 = poly_pair(wl, wL, start, gmax);
-    if (cand & (1u << 9)) c21 = poly_pair(wl, wr, start, gmax);
-    st |= c10.status | c20.status | c21.status;
-    float gpx[3][7], gpy[3][7], gcx[3][7], gcy[3][7];  // ground contacts per column j
+    // live masks of the 7 all_contacts cells (cotix/_colliders.py:137-140)
+    const bool l10 = live(S, cx, 0, P), l20 = live(S, cx, 1, P), l21 = live(S, cx, 9, P);
     uint32_t gm[3] = {0u, 0u, 0u};
-    if (cand & 0x01FFF9FCu) {
+    if (cand & GROUND_BITS) {
+#pragma unroll 1
       for (int k = 0; k < 7; ++k) {
-        const bool n0 = (cand >> (2 + k)) & 1u, n1 = (cand >> (11 + k)) & 1u, n2 = (cand >> (18 + k)) & 1u;
-        if (!(n0 || n1 || n2)) continue;
-        Poly g;
-        ground_poly(E, P, k, poisoned, g);
-        if (n0) {
-          Contact c = poly_pair(g, wL, start, gmax);
-          st |= c.status;
-          if (!contact_isnan(c)) {
-            gm[0] |= 1u << k;
-            gpx[0][k] = c.pen.x; gpy[0][k] = c.pen.y; gcx[0][k] = c.cp.x; gcy[0][k] = c.cp.y;
-          }
-        }
-        if (n1) {
-          Contact c = poly_pair(g, wr, start, gmax);
-          st |= c.status;
-          if (!contact_isnan(c)) {
-            gm[1] |= 1u << k;
-            gpx[1][k] = c.pen.x; gpy[1][k] = c.pen.y; gcx[1][k] = c.cp.x; gcy[1][k] = c.cp.y;
-          }
-        }
-        if (n2) {
-          Contact c = poly_pair(g, wl, start, gmax);
-          st |= c.status;
-          if (!contact_isnan(c)) {
-            gm[2] |= 1u << k;
-            gpx[2][k] = c.pen.x; gpy[2][k] = c.pen.y; gcx[2][k] = c.cp.x; gcy[2][k] = c.cp.y;
-          }
-        }
+        if (live(S, cx, 2 + k, P)) gm[0] |= 1u << k;
+        if (live(S, cx, 11 + k, P)) gm[1] |= 1u << k;
+        if (live(S, cx, 18 + k, P)) gm[2] |= 1u << k;
       }
     }
-    (void)st;  // cap bits are reported by the sweep API only, not in the env status
     crash = gm[0] != 0u;
     rc = gm[1] != 0u;
     lc = gm[2] != 0u;
-    const bool l10 = !contact_isnan(c10), l20 = !contact_isnan(c20), l21 = !contact_isnan(c21);
     if (l10 || l20 || l21 || gm[0] || gm[1] || gm[2]) {
       // key chain: skey = split(rkey)[0] (:142); per group skey = split(skey)[0] (:175)
       CoinCtx cc;
@@ -269,21 +380,19 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
         cc.gkey[1] = tf_split(cc.gkey[0], 2u, 0u);
       }
       // group 0 = (Polygon4, Polygon6): N1 = N2 = 9; group 1 = (Polygon4, Polygon4): 15 x 15
-      bool v10 = cell_winner(cc, 0, 9, 9, 0, 8, 0, 1, 1, l10 ? 1u : 0u) >= 0;
-      bool v20 = cell_winner(cc, 0, 9, 9, 0, 8, 1, 1, 1, l20 ? 1u : 0u) >= 0;
-      int w30 = cell_winner(cc, 0, 9, 9, 0, 8, 2, 7, 1, gm[0]);
-      bool v21 = cell_winner(cc, 1, 15, 15, 0, 7, 0, 1, 1, l21 ? 1u : 0u) >= 0;
-      int w31 = cell_winner(cc, 1, 15, 15, 0, 7, 1, 7, 2, gm[1]);
-      int w32 = cell_winner(cc, 1, 15, 15, 8, 14, 1, 7, 2, gm[2]);
+      const bool v10 = cell_winner(cc, 0, 9, 9, 0, 8, 0, 1, 1, l10 ? 1u : 0u) >= 0;
+      const bool v20 = cell_winner(cc, 0, 9, 9, 0, 8, 1, 1, 1, l20 ? 1u : 0u) >= 0;
+      const int w30 = cell_winner(cc, 0, 9, 9, 0, 8, 2, 7, 1, gm[0]);
+      const bool v21 = cell_winner(cc, 1, 15, 15, 0, 7, 0, 1, 1, l21 ? 1u : 0u) >= 0;
+      const int w31 = cell_winner(cc, 1, 15, 15, 0, 7, 1, 7, 2, gm[1]);
+      const int w32 = cell_winner(cc, 1, 15, 15, 8, 14, 1, 7, 2, gm[2]);
       bool v22 = false;
-      if (v20 || v21) {  // the self pair only matters when body 2 has another live cell
-        Contact c22 = poly_pair(wl, wl, start, gmax);
-        v22 = cell_winner(cc, 1, 15, 15, 8, 14, 0, 1, 1, contact_isnan(c22) ? 0u : 1u) >= 0;
-      }
+      if (v20 || v21)  // the self pair only matters when body 2 has another live cell
+        v22 = cell_winner(cc, 1, 15, 15, 8, 14, 0, 1, 1, live(S, cx, 10, P) ? 1u : 0u) >= 0;
       // choose_random_contact (:274-295); keys split(skey, n_bodies) with the last skey
       int j2 = -1, j3 = -1;
       {
-        int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
+        const int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
         if (cnt == 1) j2 = v20 ? 0 : (v21 ? 1 : 2);
         else if (cnt > 1) {
           float u;
@@ -294,7 +403,7 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
       }
       {
         const bool m0 = w30 >= 0, m1 = w31 >= 0, m2 = w32 >= 0;
-        int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
+        const int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
         if (cnt == 1) j3 = m0 ? 0 : (m1 ? 1 : 2);
         else if (cnt > 1) {
           float u;
@@ -304,16 +413,25 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
         }
       }
       // sequential resolution scan i = 0..3 (:310-336); row 0 is always empty
-      if (v10) resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c10.pen, c10.cp, P.baumgarte, P.baumgarte_dt);
-      if (j2 == 0 && v20) resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c20.pen, c20.cp, P.baumgarte, P.baumgarte_dt);
-      if (j2 == 1 && v21) resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c21.pen, c21.cp, P.baumgarte, P.baumgarte_dt);
+      if (v10) {
+        const Contact c = get_contact(S, cx, 0, P);
+        resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      }
+      if (j2 == 0 && v20) {
+        const Contact c = get_contact(S, cx, 1, P);
+        resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      }
+      if (j2 == 1 && v21) {
+        const Contact c = get_contact(S, cx, 9, P);
+        resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      }
       if (j3 >= 0 && j3 <= 2) {
         const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
         if (w >= 0) {
-          V2 pen = mk2(gpx[j3][w], gpy[j3][w]), cp = mk2(gcx[j3][w], gcy[j3][w]);
-          if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], pen, cp, P.baumgarte, P.baumgarte_dt);
-          else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], pen, cp, P.baumgarte, P.baumgarte_dt);
-          else resolve_collision(G, mp[3], E.b[2], mp[2], pen, cp, P.baumgarte, P.baumgarte_dt);
+          const Contact c = get_contact(S, cx, (j3 == 0 ? 2 : (j3 == 1 ? 11 : 18)) + w, P);
+          if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+          else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+          else resolve_collision(G, mp[3], E.b[2], mp[2], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
         }
       }
     }
@@ -321,11 +439,13 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
   if ((G.vx != 0.0f) || (G.vy != 0.0f) || (G.w != 0.0f) || (G.px != 0.0f) || (G.py != 0.0f) || (G.ang != 0.0f))
     E.status |= COTIX_ST_GROUND_NAN;
 
-  // --- key, next_key = jr.split(key) (examples/test_viz.py:39)
+  // key, next_key = jr.split(key) (examples/test_viz.py:39)
   if (P.rng_mode == COTIX_RNG_THREEFRY) E.key = tf_split(E.key, 2u, 0u);
 
-  // --- LunarLander.step (cotix/_lunar_lander.py:145-218); angles are those of this step
+  // LunarLander.step (cotix/_lunar_lander.py:145-218); angles are those of this step
   {
+    const float* cs = cx.cs;
+    const float* sn = cx.sn;
     V2 p0 = mk2(E.b[0].px, E.b[0].py);
     V2 lj0 = rot_cs(mk2(P.joint_local[0][0], P.joint_local[0][1]), cs[0], sn[0]) + p0;
     V2 lj1 = rot_cs(mk2(P.joint_local[1][0], P.joint_local[1][1]), cs[0], sn[0]) + p0;
@@ -353,15 +473,15 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
   if (any_nan) E.status |= COTIX_ST_NAN;
   E.steps += 1u;
 
-  // --- judge (new; template cotix/_envs.py:9-28)
+  // judge (new; template cotix/_envs.py:9-28)
   float reward = 0.0f;
   int done = COTIX_DONE_NO;
   if (P.judge_enabled) {
     float sh = lunar_shaping(E.b[0], P, rc, lc);
     if (E.shaping == E.shaping) reward = sh - E.shaping;
     E.shaping = sh;
-    reward = reward - 0.3f * thr_main;
-    reward = reward - 0.03f * fabsf(thr_side);
+    reward = reward - 0.3f * cx.thr_main;
+    reward = reward - 0.03f * fabsf(cx.thr_side);
     const BodyS& L = E.b[0];
     if (crash) {
       done = COTIX_DONE_CRASH;
@@ -390,7 +510,7 @@ __device__ void lunar_substep(EnvRegs& E, float a_main, float a_side, const Coti
 // reset(key): LunarLander.__init__, cotix/_lunar_lander.py:29-143 (+ optional pose
 // perturbation, new).  Leaves E.key untouched; the caller owns the key chain.
 static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const CotixLunarParams& P,
-                                             uint32_t episode) {
+                                                    uint32_t episode) {
   uint32_t pert[8];
   if (P.rng_mode == COTIX_RNG_THREEFRY) {
     Key2 k0 = tf_split(key, 5u, 0u);
@@ -400,10 +520,12 @@ static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const 
     E.kn[1] = tf_uniform(tf_split(key, 5u, 2u), -8.0f, -4.0f);
     E.kn[2] = tf_uniform(tf_split(key, 5u, 3u), 4.0f, 8.0f);
     E.kn[3] = tf_uniform(tf_split(key, 5u, 4u), 9.0f, 12.0f);
-    if (P.reset_perturb) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        threefry2x32(key.a, key.b, 0x70657274u + (uint32_t)i, (uint32_t)i, pert[2 * i], pert[2 * i + 1]);
+    for (int i = 0; i < 4; ++i) {
+      uint2 o = P.reset_perturb ? tf_call(key.a, key.b, 0x70657274u + (uint32_t)i, (uint32_t)i)
+                                : make_uint2(0u, 0u);
+      pert[2 * i] = o.x;
+      pert[2 * i + 1] = o.y;
     }
   } else {
     uint32_t w[20];
@@ -513,32 +635,51 @@ CX_DEV void store_env(const EnvRegs& E, float* __restrict__ s, int64_t ld, int64
   s[COTIX_F_SHAPING * ld + e] = E.shaping;
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(TPB)
 lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__ sout, int64_t ld,
                   const float* __restrict__ action, float* __restrict__ reward,
                   uint8_t* __restrict__ done, float* __restrict__ obs,
                   const __grid_constant__ CotixLunarParams P) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= B) return;
+  __shared__ SharedBlock S;
+  const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  const bool valid = e < B;
   EnvRegs E;
-  load_env(E, sin_, ld, e);
-  const float am = action ? action[e] : 0.0f;
-  const float as = action ? action[ld + e] : 0.0f;
+  float am = 0.0f, as = 0.0f;
+  if (valid) {
+    load_env(E, sin_, ld, e);
+    if (action) {
+      am = action[e];
+      as = action[ld + e];
+    }
+  }
   float rsum = 0.0f;
   int d = COTIX_DONE_NO;
   bool rc = false, lc = false;
+  bool running = valid;
   const int K = P.substeps < 1 ? 1 : P.substeps;
   for (int k = 0; k < K; ++k) {
-    SubInfo si;
-    lunar_substep(E, am, as, P, si);
-    rsum = rsum + si.reward;
-    rc = si.rc;
-    lc = si.lc;
-    if (si.done != COTIX_DONE_NO) {  // freeze on done (cotix/_envs.py:81-103)
-      d = si.done;
-      break;
+    if (threadIdx.x == 0) S.qcount = 0;
+    __syncthreads();
+    StepCtx cx;
+    cx.cand = 0u;
+    cx.base = -1;
+    if (running) phase_a(E, am, as, P, S, cx);
+    __syncthreads();
+    phase_b(S, P);
+    __syncthreads();
+    if (running) {
+      SubInfo si;
+      phase_c(E, P, S, cx, si);
+      rsum = rsum + si.reward;
+      rc = si.rc;
+      lc = si.lc;
+      if (si.done != COTIX_DONE_NO) {  // freeze on done (cotix/_envs.py:81-103)
+        d = si.done;
+        running = false;
+      }
     }
   }
+  if (!valid) return;
   bool terrain = (sin_ != sout);
   if (d != COTIX_DONE_NO && P.auto_reset) {
     Key2 rk = E.key;
@@ -566,7 +707,7 @@ lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__
   }
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(TPB)
 lunar_reset_kernel(int64_t B, const uint32_t* __restrict__ keys, float* __restrict__ state,
                    int64_t ld, const __grid_constant__ CotixLunarParams P) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -586,15 +727,15 @@ extern "C" int cx_launch_lunar_step(cudaStream_t st, int64_t B, const float* sin
                                     int64_t ld, const float* action, float* reward, uint8_t* done,
                                     float* obs, const CotixLunarParams* p) {
   if (B == 0) return 0;
-  lunar_step_kernel<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(B, sin_, sout, ld, action, reward,
-                                                                 done, obs, *p);
+  lunar_step_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(B, sin_, sout, ld, action, reward,
+                                                                     done, obs, *p);
   cx_count_launch();
   return cx_check_launch("lunar_step_kernel");
 }
 extern "C" int cx_launch_lunar_reset(cudaStream_t st, int64_t B, const uint32_t* keys, float* state,
                                      int64_t ld, const CotixLunarParams* p) {
   if (B == 0) return 0;
-  lunar_reset_kernel<<<(unsigned)((B + 127) / 128), 128, 0, st>>>(B, keys, state, ld, *p);
+  lunar_reset_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(B, keys, state, ld, *p);
   cx_count_launch();
   return cx_check_launch("lunar_reset_kernel");
 }
