@@ -82,6 +82,65 @@ static __device__ __noinline__ void poly_sort_cw(Poly& p) {
   }
 }
 
+// Facts about the (constant) local shapes of the three dynamic bodies, derived on the host
+// once per launch (lunar_kernel.cu: derive()).
+struct LunarDerived {
+  int rigid_ok[3];  // the world-space order_clockwise of body i is a cyclic rotation of its
+                    // local vertex order (convex, centroid strictly inside, angular gaps > 1e-3)
+  int orient[3];    // +1: local order is counter-clockwise (ascending angle), -1: clockwise
+  float lext[4];    // lander local extents: min x, min y, max x, max y
+};
+
+// order_clockwise of a RIGIDLY transformed convex polygon without computing any angle.
+// The vertices keep their cyclic order under rotation + translation, so the ascending-atan2
+// order about the centroid is the counter-clockwise cyclic order started at the first vertex
+// below the centroid whose predecessor is not (the +-pi branch cut of atan2).  Angular gaps
+// between neighbours are > 1e-3 rad (checked on the host), 1000x the error of any fp32
+// atan2, so this is exactly the permutation the stable argsort produces.  Returns false (and
+// leaves p untouched) when the pattern is not found (NaN, degenerate): caller sorts generically.
+template <int N>
+CX_DEV bool poly_order_rigid(Poly& p, int orient) {
+  float sy = 0.0f;
+#pragma unroll
+  for (int k = 0; k < N; ++k) sy = sy + p.y[k];
+  const float my = sy / (float)N;
+  float cx_[N], cy_[N];
+  bool neg[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) {  // counter-clockwise copy
+    const int src = orient > 0 ? k : N - 1 - k;
+    cx_[k] = p.x[src];
+    cy_[k] = p.y[src];
+    neg[k] = (cy_[k] - my) < 0.0f;
+  }
+  int start = -1, nstart = 0;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    const bool prev_neg = neg[(k + N - 1) % N];
+    if (neg[k] && !prev_neg) {
+      start = k;
+      ++nstart;
+    }
+  }
+  bool finite = true;
+#pragma unroll
+  for (int k = 0; k < N; ++k) finite = finite && (fabsf(cx_[k]) <= 3.0e38f) && (fabsf(cy_[k]) <= 3.0e38f);
+  if (nstart != 1 || !finite) return false;
+#pragma unroll
+  for (int t = 0; t < N; ++t) {
+    float ox = cx_[0], oy = cy_[0];
+#pragma unroll
+    for (int k = 0; k < N; ++k)
+      if ((start + t) % N == k) {
+        ox = cx_[k];
+        oy = cy_[k];
+      }
+    p.x[t] = ox;
+    p.y[t] = oy;
+  }
+  return true;
+}
+
 // ---- resolution — cotix/_collision_resolution.py:52-151 -------------------------------
 CX_DEV void apply_impulse(BodyS& b, const MassP& m, V2 imp, V2 point) {  // :68-73
   V2 arm = point - mk2(b.px, b.py);

@@ -190,8 +190,25 @@ static __device__ __noinline__ Contact eval_item(const SharedBlock& S, int el, i
 }
 
 // ---- phase A: regular part up to the broadphase; publishes candidates --------------------
+// all vertices of leg polygon `w`, expressed in the lander frame, fall outside the lander's
+// local extents (by more than the cull margin) along one of its two axes
+CX_DEV bool outside_lander_obb(const Poly& w, const BodyS& L, float c, float s, const LunarDerived& D) {
+  float lox = CX_INF, loy = CX_INF, hix = -CX_INF, hiy = -CX_INF;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float dx = w.x[k] - L.px, dy = w.y[k] - L.py;
+    const float lx = c * dx + s * dy, ly = c * dy - s * dx;
+    lox = fminf(lox, lx);
+    hix = fmaxf(hix, lx);
+    loy = fminf(loy, ly);
+    hiy = fmaxf(hiy, ly);
+  }
+  const float m = CX_CULL_MARGIN;
+  return (lox > D.lext[2] + m) || (hix < D.lext[0] - m) || (loy > D.lext[3] + m) || (hiy < D.lext[1] - m);
+}
+
 __device__ void phase_a(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
-                        SharedBlock& S, StepCtx& cx) {
+                        const LunarDerived& D, SharedBlock& S, StepCtx& cx) {
   const int tid = threadIdx.x;
   // ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24); the ground stays at 0
 #pragma unroll
@@ -228,8 +245,8 @@ __device__ void phase_a(EnvRegs& E, float a_main, float a_side, const CotixLunar
   world_poly<4>(P.leg_local[1], E.b[2], cx.cs[2], cx.sn[2], wl);
   const Aabb bL = poly_aabb<6>(wL), br = poly_aabb<4>(wr), bl = poly_aabb<4>(wl);
   uint32_t cand = 0u;
-  if (aabb_near(br, bL)) cand |= 1u << 0;
-  if (aabb_near(bl, bL)) cand |= 1u << 1;
+  if (aabb_near(br, bL) && !outside_lander_obb(wr, E.b[0], cx.cs[0], cx.sn[0], D)) cand |= 1u << 0;
+  if (aabb_near(bl, bL) && !outside_lander_obb(wl, E.b[0], cx.cs[0], cx.sn[0], D)) cand |= 1u << 1;
   if (aabb_near(bl, br)) cand |= 1u << 9;
 #pragma unroll
   for (int k = 0; k < 7; ++k) {
@@ -257,9 +274,10 @@ __device__ void phase_a(EnvRegs& E, float a_main, float a_side, const CotixLunar
   cx.cand = cand;
   cx.base = -1;
   if (cand != 0u) {
-    poly_sort_cw<6>(wL);  // part.transform() re-sorts the world vertices (cotix/_convex_shapes.py:181-187)
-    poly_sort_cw<4>(wr);
-    poly_sort_cw<4>(wl);
+    // part.transform() re-sorts the world vertices (cotix/_convex_shapes.py:181-187)
+    if (!(D.rigid_ok[0] && poly_order_rigid<6>(wL, D.orient[0]))) poly_sort_cw<6>(wL);
+    if (!(D.rigid_ok[1] && poly_order_rigid<4>(wr, D.orient[1]))) poly_sort_cw<4>(wr);
+    if (!(D.rigid_ok[2] && poly_order_rigid<4>(wl, D.orient[2]))) poly_sort_cw<4>(wl);
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       S.poly[2 * k][tid] = wL.x[k];
@@ -639,7 +657,7 @@ __global__ void __launch_bounds__(TPB)
 lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__ sout, int64_t ld,
                   const float* __restrict__ action, float* __restrict__ reward,
                   uint8_t* __restrict__ done, float* __restrict__ obs,
-                  const __grid_constant__ CotixLunarParams P) {
+                  const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
   __shared__ SharedBlock S;
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   const bool valid = e < B;
@@ -663,7 +681,7 @@ lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__
     StepCtx cx;
     cx.cand = 0u;
     cx.base = -1;
-    if (running) phase_a(E, am, as, P, S, cx);
+    if (running) phase_a(E, am, as, P, D, S, cx);
     __syncthreads();
     phase_b(S, P);
     __syncthreads();
@@ -723,12 +741,54 @@ lunar_reset_kernel(int64_t B, const uint32_t* __restrict__ keys, float* __restri
 
 }  // namespace
 
+// Host-side analysis of the constant local shapes (see LunarDerived).
+static void derive_body(const float (*v)[2], int n, int* ok, int* orient) {
+  double cx = 0, cy = 0, area2 = 0;
+  for (int k = 0; k < n; ++k) {
+    cx += v[k][0];
+    cy += v[k][1];
+    const int j = (k + 1) % n;
+    area2 += (double)v[k][0] * v[j][1] - (double)v[j][0] * v[k][1];
+  }
+  cx /= n;
+  cy /= n;
+  *orient = area2 >= 0 ? 1 : -1;
+  bool good = std::isfinite(area2) && fabs(area2) > 1e-6;
+  for (int k = 0; k < n && good; ++k) {
+    const int j = (k + 1) % n, l = (k + 2) % n;
+    const double ax = v[k][0] - cx, ay = v[k][1] - cy, bx = v[j][0] - cx, by = v[j][1] - cy;
+    // angular gap between neighbours about the centroid, same turning direction all around
+    const double gap = atan2(ax * by - ay * bx, ax * bx + ay * by) * (*orient);
+    if (!(gap > 1e-3 && gap < 3.1)) good = false;
+    // convexity: consecutive edges turn the same way
+    const double e1x = v[j][0] - v[k][0], e1y = v[j][1] - v[k][1];
+    const double e2x = v[l][0] - v[j][0], e2y = v[l][1] - v[j][1];
+    if (!((e1x * e2y - e1y * e2x) * (*orient) > 0)) good = false;
+  }
+  *ok = good ? 1 : 0;
+}
+static LunarDerived derive(const CotixLunarParams* p) {
+  LunarDerived D;
+  derive_body(p->lander_local, 6, &D.rigid_ok[0], &D.orient[0]);
+  derive_body(p->leg_local[0], 4, &D.rigid_ok[1], &D.orient[1]);
+  derive_body(p->leg_local[1], 4, &D.rigid_ok[2], &D.orient[2]);
+  D.lext[0] = D.lext[1] = INFINITY;
+  D.lext[2] = D.lext[3] = -INFINITY;
+  for (int k = 0; k < 6; ++k) {
+    D.lext[0] = fminf(D.lext[0], p->lander_local[k][0]);
+    D.lext[1] = fminf(D.lext[1], p->lander_local[k][1]);
+    D.lext[2] = fmaxf(D.lext[2], p->lander_local[k][0]);
+    D.lext[3] = fmaxf(D.lext[3], p->lander_local[k][1]);
+  }
+  return D;
+}
+
 extern "C" int cx_launch_lunar_step(cudaStream_t st, int64_t B, const float* sin_, float* sout,
                                     int64_t ld, const float* action, float* reward, uint8_t* done,
                                     float* obs, const CotixLunarParams* p) {
   if (B == 0) return 0;
   lunar_step_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(B, sin_, sout, ld, action, reward,
-                                                                     done, obs, *p);
+                                                                     done, obs, *p, derive(p));
   cx_count_launch();
   return cx_check_launch("lunar_step_kernel");
 }
