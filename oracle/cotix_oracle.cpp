@@ -1863,6 +1863,17 @@ int oracle_scene_step(int nb, float* bodies10, int nparts, const int32_t* part_b
   return 0;
 }
 
+// sin/cos/atan2 under the current trig mode (tests/test_trig.py checks cx_trig.h against libm)
+int oracle_trig(int64_t n, const float* x, const float* y, float* out_sin, float* out_cos,
+                float* out_atan2) {
+  for (int64_t k = 0; k < n; ++k) {
+    out_sin[k] = o_sin(x[k]);
+    out_cos[k] = o_cos(x[k]);
+    out_atan2[k] = o_atan2(y[k], x[k]);
+  }
+  return 0;
+}
+
 int oracle_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -116,6 +116,14 @@ def set_trig_mode(mode: int) -> None:
     lib().oracle_set_trig_mode(int(mode))
 
 
+def trig(x, y):
+    """(sin x, cos x, atan2(y, x)) element-wise under the current trig mode."""
+    x, y = _f32(x), _f32(y)
+    s, c, a = np.zeros_like(x), np.zeros_like(x), np.zeros_like(x)
+    lib().oracle_trig(C.c_int64(x.size), _p(x), _p(y), _p(s), _p(c), _p(a))
+    return s, c, a
+
+
 def default_lunar_params() -> LunarParams:
     p = LunarParams()
     lib().oracle_lunar_default_params(C.byref(p))

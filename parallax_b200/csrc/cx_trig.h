@@ -7,7 +7,7 @@
  * decisions (vertex order, GJK branches).  To make the engine reproducible bit for bit on
  * any IEEE-754 machine these three functions are DEFINED here using only +, -, *, / and
  * comparisons (no FMA contraction: the CUDA side is built with -fmad=false, the host side
- * with -ffp-contract=off).  Accuracy: <= 2 ulp against libm over |x| <= 1e4 (tested in
+ * with -ffp-contract=off).  Accuracy against libm over |x| <= 1e4: sin, cos <= 2 ulp, atan2 <= 3 ulp (tested in
  * tests/test_trig.py).
  *
  * Plain C, usable from nvcc (device) and gcc (host).  The oracle links libm by default and
