@@ -208,6 +208,21 @@ int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* stat
                      float* obs, const CotixLunarParams* p);
 
 /*
+ * The same step run as a WAVEFRONT PIPELINE (csrc/lunar_pipeline.cu): 1 memset + 6 small dense
+ * kernels with stream-compacted work queues in a caller-provided DEVICE workspace, instead of
+ * one fused kernel.  Results are identical bit for bit; it is several times faster for large,
+ * contact-rich batches.  Requires params->substeps == 1 (use cotix_lunar_step for K > 1) and
+ * B < 2^27.  `workspace` must be 256-byte aligned and at least
+ * cotix_lunar_workspace_bytes(B) long; its contents need not be preserved between calls.
+ * Like every device entry point it only enqueues on `stream` and is CUDA-Graph capturable.
+ */
+int64_t cotix_lunar_workspace_bytes(int64_t B);
+int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* state_out,
+                        int64_t ld, const float* action, float* reward, uint8_t* done,
+                        float* obs, const CotixLunarParams* p, void* workspace,
+                        int64_t workspace_bytes);
+
+/*
  * Host-facing env handle: owns the device state of B envs on `device`, keeps it
  * resident, and exposes reset/step with HOST buffers (pinned or pageable).  One step =
  * H2D(action) -> kernel -> D2H(obs, reward, done), on the handle's own stream.
@@ -216,6 +231,11 @@ typedef struct CotixLunarEnv CotixLunarEnv;
 int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B,
                            const CotixLunarParams* p);
 int cotix_lunar_env_destroy(CotixLunarEnv* env);
+/* launch strategy of the handle's steps: AUTO = pipeline when substeps == 1 and B >= 16384 */
+#define COTIX_MODE_AUTO 0
+#define COTIX_MODE_FUSED 1
+#define COTIX_MODE_PIPELINE 2
+int cotix_lunar_env_set_mode(CotixLunarEnv* env, int mode);
 int cotix_lunar_env_reset_host(CotixLunarEnv* env, const uint32_t* keys /*[B][2]*/);
 int cotix_lunar_env_step_host(CotixLunarEnv* env, const float* action /*[2][B]*/,
                               float* obs /*[8][B]*/, float* reward /*[B]*/,

@@ -15,7 +15,7 @@ import subprocess
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_PKG, "csrc")
 LIB_PATH = os.path.join(_PKG, "libcotix_b200.so")
-SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu"]
+SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
@@ -129,6 +129,7 @@ class LunarParams(C.Structure):
 EXPORTS = [
     "cotix_narrowphase", "cotix_narrowphase_host", "cotix_order_clockwise",
     "cotix_lunar_default_params", "cotix_lunar_reset", "cotix_lunar_step",
+    "cotix_lunar_workspace_bytes", "cotix_lunar_step_ws", "cotix_lunar_env_set_mode",
     "cotix_lunar_env_create", "cotix_lunar_env_destroy", "cotix_lunar_env_reset_host",
     "cotix_lunar_env_step_host", "cotix_lunar_env_get_state_host",
     "cotix_lunar_env_set_state_host", "cotix_lunar_env_state_ptr", "cotix_lunar_env_stream",
@@ -162,6 +163,10 @@ def lib() -> C.CDLL:
     L.cotix_lunar_default_params.argtypes = [C.POINTER(LunarParams)]
     L.cotix_lunar_reset.argtypes = [vp, i64, vp, vp, i64, C.POINTER(LunarParams)]
     L.cotix_lunar_step.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams)]
+    L.cotix_lunar_workspace_bytes.restype = C.c_int64
+    L.cotix_lunar_workspace_bytes.argtypes = [i64]
+    L.cotix_lunar_step_ws.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams), vp, i64]
+    L.cotix_lunar_env_set_mode.argtypes = [vp, C.c_int]
     L.cotix_lunar_env_create.argtypes = [C.POINTER(vp), C.c_int, i64, C.POINTER(LunarParams)]
     L.cotix_lunar_env_destroy.argtypes = [vp]
     L.cotix_lunar_env_reset_host.argtypes = [vp, vp]

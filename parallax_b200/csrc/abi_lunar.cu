@@ -15,6 +15,10 @@ extern "C" int cx_launch_lunar_step(cudaStream_t, int64_t, const float*, float*,
 extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, float*, int64_t,
                                      const CotixLunarParams*);
 
+extern "C" int64_t cx_lunar_pipeline_workspace_bytes(int64_t B);
+extern "C" int cx_launch_lunar_pipeline(cudaStream_t, int64_t, const float*, float*, int64_t, const float*,
+                                        float*, uint8_t*, float*, const CotixLunarParams*, void*, int64_t);
+
 #define CXL_REQUIRE(cond, msg)               \
   do {                                       \
     if (!(cond)) {                           \
@@ -239,8 +243,24 @@ int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* stat
                               obs, p);
 }
 
+int64_t cotix_lunar_workspace_bytes(int64_t B) { return cx_lunar_pipeline_workspace_bytes(B); }
+
+int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* state_out, int64_t ld,
+                        const float* action, float* reward, uint8_t* done, float* obs,
+                        const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
+  CXL_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(p->substeps == 1, "the pipeline runs one sub-step per call (use cotix_lunar_step for K > 1)");
+  CXL_REQUIRE(B == 0 || (state_in && state_out), "null state");
+  return cx_launch_lunar_pipeline((cudaStream_t)stream, B, state_in, state_out, ld, action, reward, done,
+                                  obs, p, workspace, workspace_bytes);
+}
+
 // ---- host-facing env handle ---------------------------------------------------------
 struct CotixLunarEnv {
+  int mode;
+  void* ws;
+  int64_t ws_bytes;
   int device;
   int64_t B;
   CotixLunarParams P;
@@ -253,6 +273,7 @@ struct CotixLunarEnv {
   uint32_t* keys;   // [B][2]
   std::map<int, cudaGraphExec_t>* graphs;
   const float* graph_action;
+  int64_t graph_launches;  // kernels per step in the captured graphs
 };
 
 int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B, const CotixLunarParams* p) {
@@ -281,6 +302,9 @@ int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B, const Cot
   CXL_CUDA(cudaMalloc(&e->reward, sizeof(float) * (size_t)B));
   CXL_CUDA(cudaMalloc(&e->done, (size_t)B));
   CXL_CUDA(cudaMalloc(&e->keys, sizeof(uint32_t) * 2 * (size_t)B));
+  e->mode = COTIX_MODE_AUTO;
+  e->ws_bytes = cx_lunar_pipeline_workspace_bytes(B);
+  CXL_CUDA(cudaMalloc(&e->ws, (size_t)e->ws_bytes));
   CXL_CUDA(cudaMemsetAsync(e->state, 0, sizeof(float) * COTIX_LUNAR_NF * (size_t)B, e->stream));
   CXL_CUDA(cudaStreamSynchronize(e->stream));
   *out = e;
@@ -301,9 +325,33 @@ int cotix_lunar_env_destroy(CotixLunarEnv* e) {
   cudaFree(e->reward);
   cudaFree(e->done);
   cudaFree(e->keys);
+  cudaFree(e->ws);
   cudaStreamDestroy(e->stream);
   delete e;
   return COTIX_OK;
+}
+
+int cotix_lunar_env_set_mode(CotixLunarEnv* e, int mode) {
+  CXL_REQUIRE(e != nullptr, "env is null");
+  CXL_REQUIRE(mode == COTIX_MODE_AUTO || mode == COTIX_MODE_FUSED || mode == COTIX_MODE_PIPELINE, "bad mode");
+  CXL_REQUIRE(mode != COTIX_MODE_PIPELINE || e->P.substeps == 1, "the pipeline needs substeps == 1");
+  if (e->mode != mode && e->graphs) {  // captured graphs embed the launch strategy
+    for (auto& kv : *e->graphs) cudaGraphExecDestroy(kv.second);
+    e->graphs->clear();
+  }
+  e->mode = mode;
+  return COTIX_OK;
+}
+
+// one step of the resident state on the handle's stream, by the handle's launch strategy
+static int env_enqueue_step(CotixLunarEnv* e, const float* action_dev, float* obs_dev) {
+  const bool pipe = e->mode == COTIX_MODE_PIPELINE ||
+                    (e->mode == COTIX_MODE_AUTO && e->P.substeps == 1 && e->B >= 16384);
+  if (pipe)
+    return cx_launch_lunar_pipeline(e->stream, e->B, e->state, e->state, e->B, action_dev, e->reward,
+                                    e->done, obs_dev, &e->P, e->ws, e->ws_bytes);
+  return cx_launch_lunar_step(e->stream, e->B, e->state, e->state, e->B, action_dev, e->reward, e->done,
+                              obs_dev, &e->P);
 }
 
 int cotix_lunar_env_reset_host(CotixLunarEnv* e, const uint32_t* keys) {
@@ -324,8 +372,7 @@ int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs,
   const size_t B = (size_t)e->B;
   if (action)
     CXL_CUDA(cudaMemcpyAsync(e->action, action, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, e->stream));
-  int rc = cx_launch_lunar_step(e->stream, e->B, e->state, e->state, e->B, action ? e->action : nullptr,
-                                e->reward, e->done, obs ? e->obs : nullptr, &e->P);
+  int rc = env_enqueue_step(e, action ? e->action : nullptr, obs ? e->obs : nullptr);
   if (rc) return rc;
   if (obs)
     CXL_CUDA(cudaMemcpyAsync(obs, e->obs, sizeof(float) * COTIX_LUNAR_NOBS * B, cudaMemcpyDeviceToHost, e->stream));
@@ -368,11 +415,12 @@ int cotix_lunar_env_rollout_graph(CotixLunarEnv* e, int32_t n_steps, const float
     cudaGraph_t g;
     CXL_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
     int rc = COTIX_OK;
-    for (int s = 0; s < n_steps && rc == COTIX_OK; ++s)
-      rc = cx_launch_lunar_step(e->stream, e->B, e->state, e->state, e->B, action_dev, e->reward,
-                                e->done, nullptr, &e->P);
+    const int64_t before = cotix_launch_count();
+    for (int s = 0; s < n_steps && rc == COTIX_OK; ++s) rc = env_enqueue_step(e, action_dev, nullptr);
     cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
-    cx_count_launch_n(-(int64_t)n_steps);  // captured, not executed
+    const int64_t captured = cotix_launch_count() - before;
+    e->graph_launches = captured / n_steps;  // kernels per step under the current strategy
+    cx_count_launch_n(-captured);            // captured, not executed
     if (rc) return rc;
     CXL_CUDA(ce);
     cudaGraphExec_t ge;
@@ -383,7 +431,7 @@ int cotix_lunar_env_rollout_graph(CotixLunarEnv* e, int32_t n_steps, const float
     it = e->graphs->find(n_steps);
   }
   CXL_CUDA(cudaGraphLaunch(it->second, e->stream));
-  cx_count_launch_n(n_steps);
+  cx_count_launch_n(e->graph_launches * n_steps);
   return COTIX_OK;
 }
 

@@ -10,9 +10,9 @@
  * with -ffp-contract=off).  Accuracy against libm over |x| <= 1e4: sin, cos <= 2 ulp, atan2 <= 3 ulp (tested in
  * tests/test_trig.py).
  *
- * Plain C, usable from nvcc (device) and gcc (host).  The oracle links libm by default and
- * can optionally switch to these definitions (oracle_set_trig_mode(1)) so that parity
- * tests can demand exact equality; see oracle/README.md.
+ * Plain C, usable from nvcc (device) and gcc (host).  The CPU checker used by the tests links
+ * libm by default and can switch to these definitions (its trig mode 1) so that parity tests
+ * can demand exact equality.
  */
 #ifndef CX_TRIG_H
 #define CX_TRIG_H

@@ -1,4 +1,4 @@
-// lunar_kernel.cu — K1 (fused LunarLander step) and K4 (reset).
+// lunar_kernel.cu — K1 (fused LunarLander step, one launch) and K4 (reset).
 //
 // Mapping: one environment per THREAD for the regular part of the
 // step, and a block-level work queue for the irregular part:
@@ -12,9 +12,10 @@
 //   phase C  (thread = env)   coin flips / random choice (lazy threefry or Philox), sequential
 //                             impulse resolution, joints, judge, auto-reset, store
 // State is struct-of-arrays over the env axis (include/cotix_b200.h): every field access of a
-// warp is one coalesced 128-byte transaction.
+// warp is one coalesced 128-byte transaction.  This kernel keeps the state in registers across
+// K sub-steps; for large batches at K = 1 the wavefront pipeline (lunar_pipeline.cu) is faster.
 #include "cx_launch.cuh"
-#include "cx_lunar.cuh"
+#include "cx_lunar_step.cuh"
 
 namespace {
 
@@ -22,15 +23,6 @@ constexpr int TPB = 128;    // threads (= envs) per block
 constexpr int QCAP = 1024;  // narrowphase items per block and sub-step; overflow falls back to
                             // the owning thread evaluating its own pairs (same results)
 constexpr uint32_t ITEM_SKIP = 0xFFFFFFFFu;
-
-struct EnvRegs {
-  BodyS b[3];
-  float h[8];
-  float kn[4];
-  Key2 key;
-  uint32_t steps, status;
-  float ret, shaping;
-};
 
 struct SharedBlock {
   float poly[28][TPB];  // sorted world vertices: lander 0..11, right leg 12..19, left leg 20..27
@@ -40,244 +32,51 @@ struct SharedBlock {
   int qcount;
 };
 
-// pair ids = bits of the candidate mask:
-//  0 (rl,L)  1 (ll,L)  2..8 (g_k,L)  9 (ll,rl)  10 (ll,ll)  11..17 (g_k,rl)  18..24 (g_k,ll)
-constexpr uint32_t GROUND_BITS = 0x01FFF9FCu;
-
-struct StepCtx {
-  float cs[3], sn[3];
-  float thr_main, thr_side;
-  uint32_t cand;
-  int base;  // first queue slot of this env's items, or -1 (evaluate inline)
-};
-
-struct SubInfo {
-  float reward;
-  int done;
-  bool rc, lc;
-};
-
-template <int N>
-CX_DEV void world_poly(const float (*local)[2], const BodyS& b, float c, float s, Poly& out) {
-  out.n = N;
-  const float ms = -s;
+// polygon source: env `el` of this block, from shared memory
+struct SmemPolys {
+  const SharedBlock& S;
+  int el;
+  CX_DEV void body(int which, Poly& p) const {
+    const int off = which == 0 ? 0 : (which == 1 ? 12 : 20);
+    const int n = which == 0 ? 6 : 4;
+    p.n = n;
 #pragma unroll
-  for (int k = 0; k < CX_MAXV; ++k) {
-    if (k < N) {
-      // forward_vector (cotix/_geometry_utils.py:134-138): matrix @ [x, y, 1] / w with
-      // w = 0*x + 0*y + 1 = 1 exactly for finite local vertices, so the division is dropped
-      float x = local[k][0], y = local[k][1];
-      out.x[k] = c * x + ms * y + b.px * 1.0f;
-      out.y[k] = s * x + c * y + b.py * 1.0f;
-    } else {
-      out.x[k] = 0.0f;
-      out.y[k] = 0.0f;
+    for (int k = 0; k < CX_MAXV; ++k) {
+      if (k < n) {
+        p.x[k] = S.poly[off + 2 * k][el];
+        p.y[k] = S.poly[off + 2 * k + 1][el];
+      } else {
+        p.x[k] = 0.0f;
+        p.y[k] = 0.0f;
+      }
     }
   }
-}
-struct Aabb {
-  float lx, ly, hx, hy;
+  CX_DEV void ground_edge(int k, const CotixLunarParams& P, float& x0, float& h0, float& x1, float& h1) const {
+    float kn[4] = {S.terr[8][el], S.terr[9][el], S.terr[10][el], S.terr[11][el]};
+    x0 = terrain_x(kn, P, k);
+    x1 = terrain_x(kn, P, k + 1);
+    h0 = S.terr[k][el];
+    h1 = S.terr[k + 1][el];
+  }
 };
-template <int N>
-CX_DEV Aabb poly_aabb(const Poly& p) {
-  Aabb a;
-  a.lx = a.hx = p.x[0];
-  a.ly = a.hy = p.y[0];
-#pragma unroll
-  for (int k = 1; k < N; ++k) {
-    a.lx = fminf(a.lx, p.x[k]);
-    a.hx = fmaxf(a.hx, p.x[k]);
-    a.ly = fminf(a.ly, p.y[k]);
-    a.hy = fmaxf(a.hy, p.y[k]);
-  }
-  return a;
-}
-CX_DEV bool aabb_near(const Aabb& a, const Aabb& b) {
-  const float m = CX_CULL_MARGIN;
-  return !(a.hx + m < b.lx || b.hx + m < a.lx || a.hy + m < b.ly || b.hy + m < a.ly);
-}
-// Separating-axis test against the top edge TL=(x0,h0) -> TR=(x1,h1) of a ground trapezoid
-// (the trapezoid lies in n.(v - TL) <= 0, n = perp(TR - TL)): true when every vertex of the
-// body polygon is above that line by more than the cull margin, i.e. the pair cannot touch.
-template <int N>
-CX_DEV bool above_top_edge(const Poly& p, float x0, float h0, float x1, float h1) {
-  const float nx = -(h1 - h0), ny = x1 - x0;
-  const float thr = CX_CULL_MARGIN * (fabsf(nx) + fabsf(ny));
-  bool all_above = true;
-#pragma unroll
-  for (int k = 0; k < N; ++k) {
-    float s = nx * (p.x[k] - x0) + ny * (p.y[k] - h0);
-    all_above = all_above && (s > thr);
-  }
-  return all_above;
-}
-CX_DEV float terrain_x(const float kn[4], const CotixLunarParams& P, int i) {
-  switch (i) {
-    case 0: return -P.terrain_x_outer;
-    case 1: return kn[0];
-    case 2: return kn[1];
-    case 3: return -P.pad_half_width;
-    case 4: return P.pad_half_width;
-    case 5: return kn[2];
-    case 6: return kn[3];
-    default: return P.terrain_x_outer;
-  }
-}
 
-CX_DEV float lunar_shaping(const BodyS& L, const CotixLunarParams& P, bool rc, bool lc) {
-  float dy = L.py - P.pad_y;
-  float dist = sqrtf(L.px * L.px + dy * dy);
-  float speed = sqrtf(L.vx * L.vx + L.vy * L.vy);
-  float s = -10.0f * dist;
-  s = s - 100.0f * speed;
-  s = s - 100.0f * fabsf(L.ang);
-  s = s + (rc ? 10.0f : 0.0f);
-  s = s + (lc ? 10.0f : 0.0f);
-  return s;
-}
-
-static __device__ __noinline__ Contact poly_pair(const Poly& a, const Poly& b, V2 start, int gjk_max) {
-  return convex_vs_polygon(a, b, start, gjk_max);
-}
-
-// body polygon `which` (0 lander, 1 right leg, 2 left leg) of env `el` from shared memory
-CX_DEV void load_body_poly(const SharedBlock& S, int el, int which, Poly& p) {
-  const int off = which == 0 ? 0 : (which == 1 ? 12 : 20);
-  const int n = which == 0 ? 6 : 4;
-  p.n = n;
-#pragma unroll
-  for (int k = 0; k < CX_MAXV; ++k) {
-    if (k < n) {
-      p.x[k] = S.poly[off + 2 * k][el];
-      p.y[k] = S.poly[off + 2 * k + 1][el];
-    } else {
-      p.x[k] = 0.0f;
-      p.y[k] = 0.0f;
-    }
-  }
-}
-// ground part k as the collider sees it: Polygon4.__init__ sort (cotix/_lunar_lander.py:132)
-// followed by the identity transform + re-sort of part.transform (cotix/_colliders.py:92-94)
-CX_DEV void load_ground_poly(const SharedBlock& S, int el, int k, const CotixLunarParams& P, Poly& g) {
-  float kn[4] = {S.terr[8][el], S.terr[9][el], S.terr[10][el], S.terr[11][el]};
-  float x0 = terrain_x(kn, P, k), x1 = terrain_x(kn, P, k + 1);
-  float h0 = S.terr[k][el], h1 = S.terr[k + 1][el];
-  g.n = 4;
-  g.x[0] = x0; g.y[0] = h0;
-  g.x[1] = x0; g.y[1] = P.ground_floor;
-  g.x[2] = x1; g.y[2] = h1;
-  g.x[3] = x1; g.y[3] = P.ground_floor;
-  g.x[4] = g.y[4] = g.x[5] = g.y[5] = 0.0f;
-  poly_sort_cw<4>(g);
-  poly_sort_cw<4>(g);
-}
 // narrowphase of one (env, pair) item
 static __device__ __noinline__ Contact eval_item(const SharedBlock& S, int el, int pid,
                                                  const CotixLunarParams& P) {
   Poly A, B;
-  int wa, wb, gk = -1;
-  if (pid == 0) { wa = 1; wb = 0; }
-  else if (pid == 1) { wa = 2; wb = 0; }
-  else if (pid <= 8) { gk = pid - 2; wa = -1; wb = 0; }
-  else if (pid == 9) { wa = 2; wb = 1; }
-  else if (pid == 10) { wa = 2; wb = 2; }
-  else if (pid <= 17) { gk = pid - 11; wa = -1; wb = 1; }
-  else { gk = pid - 18; wa = -1; wb = 2; }
-  if (gk >= 0) load_ground_poly(S, el, gk, P, A);
-  else load_body_poly(S, el, wa, A);
-  load_body_poly(S, el, wb, B);
+  SmemPolys src{S, el};
+  make_item_polys(src, pid, P, A, B);
   return poly_pair(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters);
 }
 
 // ---- phase A: regular part up to the broadphase; publishes candidates --------------------
-// all vertices of leg polygon `w`, expressed in the lander frame, fall outside the lander's
-// local extents (by more than the cull margin) along one of its two axes
-CX_DEV bool outside_lander_obb(const Poly& w, const BodyS& L, float c, float s, const LunarDerived& D) {
-  float lox = CX_INF, loy = CX_INF, hix = -CX_INF, hiy = -CX_INF;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const float dx = w.x[k] - L.px, dy = w.y[k] - L.py;
-    const float lx = c * dx + s * dy, ly = c * dy - s * dx;
-    lox = fminf(lox, lx);
-    hix = fmaxf(hix, lx);
-    loy = fminf(loy, ly);
-    hiy = fmaxf(hiy, ly);
-  }
-  const float m = CX_CULL_MARGIN;
-  return (lox > D.lext[2] + m) || (hix < D.lext[0] - m) || (loy > D.lext[3] + m) || (hiy < D.lext[1] - m);
-}
-
 __device__ void phase_a(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
                         const LunarDerived& D, SharedBlock& S, StepCtx& cx) {
   const int tid = threadIdx.x;
-  // ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24); the ground stays at 0
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    E.b[i].px = E.b[i].px + E.b[i].vx * P.dt;
-    E.b[i].py = E.b[i].py + E.b[i].vy * P.dt;
-    E.b[i].ang = E.b[i].ang + E.b[i].w * P.dt;
-  }
-  // gravity on the lander only (examples/test_viz.py:27-31)
-  E.b[0].vx = E.b[0].vx + P.gravity_dv[0];
-  E.b[0].vy = E.b[0].vy + P.gravity_dv[1];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &cx.sn[i], &cx.cs[i]);
-  if (!(fabsf(E.b[0].ang) < 1.0e9f) || !(fabsf(E.b[1].ang) < 1.0e9f) || !(fabsf(E.b[2].ang) < 1.0e9f))
-    E.status |= COTIX_ST_ANGLE_RANGE;
-  // engines (new): a zero action leaves the reference step untouched
-  cx.thr_main = jclip(a_main, 0.0f, 1.0f);
-  cx.thr_side = jclip(a_side, -1.0f, 1.0f);
-  if (cx.thr_main != 0.0f) {
-    float dv = P.main_engine_dv * cx.thr_main;
-    E.b[0].vx = E.b[0].vx + (-cx.sn[0]) * dv;
-    E.b[0].vy = E.b[0].vy + cx.cs[0] * dv;
-  }
-  if (cx.thr_side != 0.0f) {
-    float dv = P.side_engine_dv * cx.thr_side;
-    E.b[0].vx = E.b[0].vx + cx.cs[0] * dv;
-    E.b[0].vy = E.b[0].vy + cx.sn[0] * dv;
-    E.b[0].w = E.b[0].w - P.side_engine_dw * cx.thr_side;
-  }
-  // world polygons (local vertex order) and the broadphase — new, exact
   Poly wL, wr, wl;
-  world_poly<6>(P.lander_local, E.b[0], cx.cs[0], cx.sn[0], wL);
-  world_poly<4>(P.leg_local[0], E.b[1], cx.cs[1], cx.sn[1], wr);
-  world_poly<4>(P.leg_local[1], E.b[2], cx.cs[2], cx.sn[2], wl);
-  const Aabb bL = poly_aabb<6>(wL), br = poly_aabb<4>(wr), bl = poly_aabb<4>(wl);
-  uint32_t cand = 0u;
-  if (aabb_near(br, bL) && !outside_lander_obb(wr, E.b[0], cx.cs[0], cx.sn[0], D)) cand |= 1u << 0;
-  if (aabb_near(bl, bL) && !outside_lander_obb(wl, E.b[0], cx.cs[0], cx.sn[0], D)) cand |= 1u << 1;
-  if (aabb_near(bl, br)) cand |= 1u << 9;
-#pragma unroll
-  for (int k = 0; k < 7; ++k) {
-    const float x0 = terrain_x(E.kn, P, k), x1 = terrain_x(E.kn, P, k + 1);
-    const float h0 = E.h[k], h1 = E.h[k + 1];
-    Aabb g;
-    g.lx = fminf(x0, x1);
-    g.hx = fmaxf(x0, x1);
-    g.ly = fminf(fminf(h0, h1), P.ground_floor);
-    g.hy = fmaxf(fmaxf(h0, h1), P.ground_floor);
-    const bool regular = (x1 > x0) && (h0 > P.ground_floor) && (h1 > P.ground_floor);
-    if (aabb_near(g, bL) && !(regular && above_top_edge<6>(wL, x0, h0, x1, h1))) cand |= 1u << (2 + k);
-    if (aabb_near(g, br) && !(regular && above_top_edge<4>(wr, x0, h0, x1, h1))) cand |= 1u << (11 + k);
-    if (aabb_near(g, bl) && !(regular && above_top_edge<4>(wl, x0, h0, x1, h1))) cand |= 1u << (18 + k);
-  }
-  bool bad = (E.status & COTIX_ST_GROUND_NAN) != 0u;
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-    bad = bad || !(fabsf(E.b[i].px) <= 3.0e38f) || !(fabsf(E.b[i].py) <= 3.0e38f) ||
-          !(fabsf(E.b[i].ang) <= 3.0e38f);
-  if (bad) cand = 0u;  // NaN vertices: every GJK of the reference reports "no" (any-NaN rule)
-  // the self pair (left leg vs itself) can only matter when body 2 has another
-  // live cell, i.e. when pair 1 or pair 9 is a candidate
-  if (cand & ((1u << 1) | (1u << 9))) cand |= 1u << 10;
-  cx.cand = cand;
-  cx.base = -1;
+  integrate_and_cull(E, a_main, a_side, P, D, cx, wL, wr, wl);
+  const uint32_t cand = cx.cand;
   if (cand != 0u) {
-    // part.transform() re-sorts the world vertices (cotix/_convex_shapes.py:181-187)
-    if (!(D.rigid_ok[0] && poly_order_rigid<6>(wL, D.orient[0]))) poly_sort_cw<6>(wL);
-    if (!(D.rigid_ok[1] && poly_order_rigid<4>(wr, D.orient[1]))) poly_sort_cw<4>(wr);
-    if (!(D.rigid_ok[2] && poly_order_rigid<4>(wl, D.orient[2]))) poly_sort_cw<4>(wl);
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
       S.poly[2 * k][tid] = wL.x[k];
@@ -325,332 +124,40 @@ __device__ void phase_b(SharedBlock& S, const CotixLunarParams& P) {
   }
 }
 
-// contact of candidate pair `bit` of this thread's env
-CX_DEV Contact get_contact(const SharedBlock& S, const StepCtx& cx, int bit, const CotixLunarParams& P) {
-  if (cx.base >= 0) {
-    const int i = cx.base + __popc(cx.cand & ((1u << bit) - 1u));
-    Contact c;
-    c.pen = mk2(S.res[0][i], S.res[1][i]);
-    c.cp = mk2(S.res[2][i], S.res[3][i]);
-    c.status = 0u;
-    return c;
+// contact source of this thread's env: the block queue's results (or inline on overflow)
+struct SmemContacts {
+  const SharedBlock& S;
+  const StepCtx& cx;
+  const CotixLunarParams& P;
+  CX_DEV Contact get(int bit) const {
+    if (cx.base >= 0) {
+      const int i = cx.base + __popc(cx.cand & ((1u << bit) - 1u));
+      Contact c;
+      c.pen = mk2(S.res[0][i], S.res[1][i]);
+      c.cp = mk2(S.res[2][i], S.res[3][i]);
+      c.status = 0u;
+      return c;
+    }
+    return eval_item(S, threadIdx.x, bit, P);  // queue overflow: evaluate inline (same result)
   }
-  return eval_item(S, threadIdx.x, bit, P);  // queue overflow: evaluate inline (same result)
-}
-CX_DEV bool live(const SharedBlock& S, const StepCtx& cx, int bit, const CotixLunarParams& P) {
-  if (!((cx.cand >> bit) & 1u)) return false;
-  if (cx.base >= 0) {
-    const int i = cx.base + __popc(cx.cand & ((1u << bit) - 1u));
-    const float x = S.res[2][i], y = S.res[3][i];
-    return !((x != x) || (y != y));
+  CX_DEV bool live(int bit) const {
+    if (!((cx.cand >> bit) & 1u)) return false;
+    if (cx.base >= 0) {
+      const int i = cx.base + __popc(cx.cand & ((1u << bit) - 1u));
+      const float x = S.res[2][i], y = S.res[3][i];
+      return !((x != x) || (y != y));
+    }
+    return !contact_isnan(eval_item(S, threadIdx.x, bit, P));
   }
-  return !contact_isnan(eval_item(S, threadIdx.x, bit, P));
-}
+};
 
 // ---- phase C: contact selection, resolution, joints, judge --------------------------------
 __device__ void phase_c(EnvRegs& E, const CotixLunarParams& P, const SharedBlock& S,
                         const StepCtx& cx, SubInfo& info) {
-  MassP mp[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    mp[i].mass = P.body_props[i][0];
-    mp[i].inertia = P.body_props[i][1];
-    mp[i].e = P.body_props[i][2];
-    mp[i].mu = P.body_props[i][3];
-  }
-  const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
-  BodyS G;  // the static ground body (mass = inertia = inf); NaN once poisoned
-  G.px = G.py = G.vx = G.vy = G.ang = G.w = poisoned ? CX_NAN : 0.0f;
-  G.px = G.px + G.vx * P.dt;
-  G.py = G.py + G.vy * P.dt;
-  G.ang = G.ang + G.w * P.dt;
-
-  bool crash = false, rc = false, lc = false;
-  const uint32_t cand = cx.cand;
-  if (cand != 0u) {
-    // live masks of the 7 all_contacts cells (cotix/_colliders.py:137-140)
-    const bool l10 = live(S, cx, 0, P), l20 = live(S, cx, 1, P), l21 = live(S, cx, 9, P);
-    uint32_t gm[3] = {0u, 0u, 0u};
-    if (cand & GROUND_BITS) {
-#pragma unroll 1
-      for (int k = 0; k < 7; ++k) {
-        if (live(S, cx, 2 + k, P)) gm[0] |= 1u << k;
-        if (live(S, cx, 11 + k, P)) gm[1] |= 1u << k;
-        if (live(S, cx, 18 + k, P)) gm[2] |= 1u << k;
-      }
-    }
-    crash = gm[0] != 0u;
-    rc = gm[1] != 0u;
-    lc = gm[2] != 0u;
-    if (l10 || l20 || l21 || gm[0] || gm[1] || gm[2]) {
-      // key chain: skey = split(rkey)[0] (:142); per group skey = split(skey)[0] (:175)
-      CoinCtx cc;
-      cc.mode = P.rng_mode;
-      cc.p = P.coin_p;
-      cc.steps = E.steps;
-      cc.episode = E.status >> 8;
-      cc.pkey.a = P.philox_seed[0] ^ E.key.a;
-      cc.pkey.b = P.philox_seed[1] ^ E.key.b;
-      cc.gkey[0] = cc.gkey[1] = E.key;
-      if (P.rng_mode == COTIX_RNG_THREEFRY) {
-        Key2 sk = tf_split(E.key, 2u, 0u);
-        cc.gkey[0] = tf_split(sk, 2u, 0u);
-        cc.gkey[1] = tf_split(cc.gkey[0], 2u, 0u);
-      }
-      // group 0 = (Polygon4, Polygon6): N1 = N2 = 9; group 1 = (Polygon4, Polygon4): 15 x 15
-      const bool v10 = cell_winner(cc, 0, 9, 9, 0, 8, 0, 1, 1, l10 ? 1u : 0u) >= 0;
-      const bool v20 = cell_winner(cc, 0, 9, 9, 0, 8, 1, 1, 1, l20 ? 1u : 0u) >= 0;
-      const int w30 = cell_winner(cc, 0, 9, 9, 0, 8, 2, 7, 1, gm[0]);
-      const bool v21 = cell_winner(cc, 1, 15, 15, 0, 7, 0, 1, 1, l21 ? 1u : 0u) >= 0;
-      const int w31 = cell_winner(cc, 1, 15, 15, 0, 7, 1, 7, 2, gm[1]);
-      const int w32 = cell_winner(cc, 1, 15, 15, 8, 14, 1, 7, 2, gm[2]);
-      bool v22 = false;
-      if (v20 || v21)  // the self pair only matters when body 2 has another live cell
-        v22 = cell_winner(cc, 1, 15, 15, 8, 14, 0, 1, 1, live(S, cx, 10, P) ? 1u : 0u) >= 0;
-      // choose_random_contact (:274-295); keys split(skey, n_bodies) with the last skey
-      int j2 = -1, j3 = -1;
-      {
-        const int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
-        if (cnt == 1) j2 = v20 ? 0 : (v21 ? 1 : 2);
-        else if (cnt > 1) {
-          float u;
-          if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 2u), 0.0f, 1.0f);
-          else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 2u, CX_TAG_CHOICE), 0.0f, 1.0f);
-          j2 = choose_index(v20, v21, v22, u);
-        }
-      }
-      {
-        const bool m0 = w30 >= 0, m1 = w31 >= 0, m2 = w32 >= 0;
-        const int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
-        if (cnt == 1) j3 = m0 ? 0 : (m1 ? 1 : 2);
-        else if (cnt > 1) {
-          float u;
-          if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 3u), 0.0f, 1.0f);
-          else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 3u, CX_TAG_CHOICE), 0.0f, 1.0f);
-          j3 = choose_index(m0, m1, m2, u);
-        }
-      }
-      // sequential resolution scan i = 0..3 (:310-336); row 0 is always empty
-      if (v10) {
-        const Contact c = get_contact(S, cx, 0, P);
-        resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      }
-      if (j2 == 0 && v20) {
-        const Contact c = get_contact(S, cx, 1, P);
-        resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      }
-      if (j2 == 1 && v21) {
-        const Contact c = get_contact(S, cx, 9, P);
-        resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      }
-      if (j3 >= 0 && j3 <= 2) {
-        const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
-        if (w >= 0) {
-          const Contact c = get_contact(S, cx, (j3 == 0 ? 2 : (j3 == 1 ? 11 : 18)) + w, P);
-          if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-          else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-          else resolve_collision(G, mp[3], E.b[2], mp[2], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-        }
-      }
-    }
-  }
-  if ((G.vx != 0.0f) || (G.vy != 0.0f) || (G.w != 0.0f) || (G.px != 0.0f) || (G.py != 0.0f) || (G.ang != 0.0f))
-    E.status |= COTIX_ST_GROUND_NAN;
-
-  // key, next_key = jr.split(key) (examples/test_viz.py:39)
-  if (P.rng_mode == COTIX_RNG_THREEFRY) E.key = tf_split(E.key, 2u, 0u);
-
-  // LunarLander.step (cotix/_lunar_lander.py:145-218); angles are those of this step
-  {
-    const float* cs = cx.cs;
-    const float* sn = cx.sn;
-    V2 p0 = mk2(E.b[0].px, E.b[0].py);
-    V2 lj0 = rot_cs(mk2(P.joint_local[0][0], P.joint_local[0][1]), cs[0], sn[0]) + p0;
-    V2 lj1 = rot_cs(mk2(P.joint_local[1][0], P.joint_local[1][1]), cs[0], sn[0]) + p0;
-    V2 lj2 = rot_cs(mk2(P.joint_local[2][0], P.joint_local[2][1]), cs[0], sn[0]) + p0;
-    V2 lj3 = rot_cs(mk2(P.joint_local[3][0], P.joint_local[3][1]), cs[0], sn[0]) + p0;
-    V2 j2l = mk2(P.leg_joint2_local[0], P.leg_joint2_local[1]);
-    V2 ll1 = mk2(E.b[2].px, E.b[2].py);
-    V2 ll2 = ll1 + rot_cs(j2l, cs[2], sn[2]);
-    V2 rl1 = mk2(E.b[1].px, E.b[1].py);
-    V2 rl2 = rl1 + rot_cs(j2l, cs[1], sn[1]);
-    joint_constraint(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
-    joint_constraint(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
-    joint_constraint(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
-    joint_constraint(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
-    E.b[1].w = E.b[1].w * P.leg_damping;
-    E.b[2].w = E.b[2].w * P.leg_damping;
-  }
-
-  bool any_nan = false;
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-    any_nan = any_nan || !(fabsf(E.b[i].px) <= 3.0e38f) || !(fabsf(E.b[i].py) <= 3.0e38f) ||
-              !(fabsf(E.b[i].vx) <= 3.0e38f) || !(fabsf(E.b[i].vy) <= 3.0e38f) ||
-              !(fabsf(E.b[i].ang) <= 3.0e38f) || !(fabsf(E.b[i].w) <= 3.0e38f);
-  if (any_nan) E.status |= COTIX_ST_NAN;
-  E.steps += 1u;
-
-  // judge (new; template cotix/_envs.py:9-28)
-  float reward = 0.0f;
-  int done = COTIX_DONE_NO;
-  if (P.judge_enabled) {
-    float sh = lunar_shaping(E.b[0], P, rc, lc);
-    if (E.shaping == E.shaping) reward = sh - E.shaping;
-    E.shaping = sh;
-    reward = reward - 0.3f * cx.thr_main;
-    reward = reward - 0.03f * fabsf(cx.thr_side);
-    const BodyS& L = E.b[0];
-    if (crash) {
-      done = COTIX_DONE_CRASH;
-      reward = -100.0f;
-    } else if (!(fabsf(L.px) < P.x_limit) || !(L.py < P.y_limit)) {
-      done = COTIX_DONE_OOB;
-      reward = -100.0f;
-    } else if (rc && lc && sqrtf(L.vx * L.vx + L.vy * L.vy) < P.land_speed && fabsf(L.w) < P.land_angvel) {
-      done = COTIX_DONE_LANDED;
-      reward = 100.0f;
-    }
-  }
-  if (any_nan) {
-    done = COTIX_DONE_NAN;
-    reward = P.judge_enabled ? -100.0f : 0.0f;
-  }
-  if (done == COTIX_DONE_NO && P.max_episode_steps > 0 && E.steps >= (uint32_t)P.max_episode_steps)
-    done = COTIX_DONE_TIMEOUT;
-  E.ret = E.ret + reward;
-  info.reward = reward;
-  info.done = done;
-  info.rc = rc;
-  info.lc = lc;
-}
-
-// reset(key): LunarLander.__init__, cotix/_lunar_lander.py:29-143 (+ optional pose
-// perturbation, new).  Leaves E.key untouched; the caller owns the key chain.
-static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const CotixLunarParams& P,
-                                                    uint32_t episode) {
-  uint32_t pert[8];
-  if (P.rng_mode == COTIX_RNG_THREEFRY) {
-    Key2 k0 = tf_split(key, 5u, 0u);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) E.h[i] = bits_to_uniform(tf_bits_word(k0, 8u, (uint32_t)i), -5.0f, 5.0f);
-    E.kn[0] = tf_uniform(tf_split(key, 5u, 1u), -12.0f, -9.0f);
-    E.kn[1] = tf_uniform(tf_split(key, 5u, 2u), -8.0f, -4.0f);
-    E.kn[2] = tf_uniform(tf_split(key, 5u, 3u), 4.0f, 8.0f);
-    E.kn[3] = tf_uniform(tf_split(key, 5u, 4u), 9.0f, 12.0f);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      uint2 o = P.reset_perturb ? tf_call(key.a, key.b, 0x70657274u + (uint32_t)i, (uint32_t)i)
-                                : make_uint2(0u, 0u);
-      pert[2 * i] = o.x;
-      pert[2 * i + 1] = o.y;
-    }
-  } else {
-    uint32_t w[20];
-#pragma unroll
-    for (int q = 0; q < 5; ++q)
-      philox4x32_10(P.philox_seed[0] ^ key.a, P.philox_seed[1] ^ key.b, 0u, episode, (uint32_t)q,
-                    CX_TAG_RESET, w + 4 * q);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) E.h[i] = bits_to_uniform(w[i], -5.0f, 5.0f);
-    E.kn[0] = bits_to_uniform(w[8], -12.0f, -9.0f);
-    E.kn[1] = bits_to_uniform(w[9], -8.0f, -4.0f);
-    E.kn[2] = bits_to_uniform(w[10], 4.0f, 8.0f);
-    E.kn[3] = bits_to_uniform(w[11], 9.0f, 12.0f);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) pert[i] = w[12 + i];
-  }
-  E.h[0] = E.h[0] * 10.0f;
-  E.h[3] = P.pad_y;
-  E.h[4] = P.pad_y;
-  E.h[7] = E.h[7] * 10.0f;
-
-  float lx = P.lander_start[0], ly = P.lander_start[1], la = P.lander_start[2];
-  float lvx = 0.0f, lvy = 0.0f, lw = 0.0f;
-  if (!P.reset_perturb) {
-#pragma unroll
-    for (int l = 0; l < 2; ++l) {
-      E.b[1 + l].px = P.leg_offset[l][0] + lx;
-      E.b[1 + l].py = P.leg_offset[l][1] + ly;
-      E.b[1 + l].vx = E.b[1 + l].vy = E.b[1 + l].ang = E.b[1 + l].w = 0.0f;
-    }
-  } else {
-    lx = bits_to_uniform(pert[0], P.reset_x[0], P.reset_x[1]);
-    ly = bits_to_uniform(pert[1], P.reset_y[0], P.reset_y[1]);
-    la = bits_to_uniform(pert[2], P.reset_angle[0], P.reset_angle[1]);
-    lvx = bits_to_uniform(pert[3], -P.reset_v, P.reset_v);
-    lvy = bits_to_uniform(pert[4], -P.reset_v, P.reset_v);
-    lw = bits_to_uniform(pert[5], -P.reset_w, P.reset_w);
-    float da = la - P.lander_start[2];
-    float c, s;
-    cx_sincosf(da, &s, &c);
-#pragma unroll
-    for (int l = 0; l < 2; ++l) {
-      float ox = P.leg_offset[l][0], oy = P.leg_offset[l][1];
-      float rx = c * ox - s * oy, ry = s * ox + c * oy;
-      E.b[1 + l].px = rx + lx;
-      E.b[1 + l].py = ry + ly;
-      E.b[1 + l].ang = da;
-      E.b[1 + l].vx = lvx + (-ry) * lw;
-      E.b[1 + l].vy = lvy + rx * lw;
-      E.b[1 + l].w = lw;
-    }
-  }
-  E.b[0].px = lx;
-  E.b[0].py = ly;
-  E.b[0].vx = lvx;
-  E.b[0].vy = lvy;
-  E.b[0].ang = la;
-  E.b[0].w = lw;
-  E.steps = 0u;
-  E.status = episode << 8;
-  E.ret = 0.0f;
-  E.shaping = CX_NAN;
-}
-
-CX_DEV void load_env(EnvRegs& E, const float* __restrict__ s, int64_t ld, int64_t e) {
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    E.b[i].px = s[(i * 6 + 0) * ld + e];
-    E.b[i].py = s[(i * 6 + 1) * ld + e];
-    E.b[i].vx = s[(i * 6 + 2) * ld + e];
-    E.b[i].vy = s[(i * 6 + 3) * ld + e];
-    E.b[i].ang = s[(i * 6 + 4) * ld + e];
-    E.b[i].w = s[(i * 6 + 5) * ld + e];
-  }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) E.h[i] = s[(COTIX_F_HEIGHT0 + i) * ld + e];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) E.kn[i] = s[(COTIX_F_KNOT0 + i) * ld + e];
-  E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
-  E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
-  E.steps = __float_as_uint(s[COTIX_F_STEPS * ld + e]);
-  E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
-  E.ret = s[COTIX_F_RETURN * ld + e];
-  E.shaping = s[COTIX_F_SHAPING * ld + e];
-}
-CX_DEV void store_env(const EnvRegs& E, float* __restrict__ s, int64_t ld, int64_t e, bool terrain) {
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    s[(i * 6 + 0) * ld + e] = E.b[i].px;
-    s[(i * 6 + 1) * ld + e] = E.b[i].py;
-    s[(i * 6 + 2) * ld + e] = E.b[i].vx;
-    s[(i * 6 + 3) * ld + e] = E.b[i].vy;
-    s[(i * 6 + 4) * ld + e] = E.b[i].ang;
-    s[(i * 6 + 5) * ld + e] = E.b[i].w;
-  }
-  if (terrain) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s[(COTIX_F_HEIGHT0 + i) * ld + e] = E.h[i];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) s[(COTIX_F_KNOT0 + i) * ld + e] = E.kn[i];
-  }
-  s[COTIX_F_KEY0 * ld + e] = __uint_as_float(E.key.a);
-  s[COTIX_F_KEY1 * ld + e] = __uint_as_float(E.key.b);
-  s[COTIX_F_STEPS * ld + e] = __uint_as_float(E.steps);
-  s[COTIX_F_STATUS * ld + e] = __uint_as_float(E.status);
-  s[COTIX_F_RETURN * ld + e] = E.ret;
-  s[COTIX_F_SHAPING * ld + e] = E.shaping;
+  bool crash, rc, lc;
+  SmemContacts cs{S, cx, P};
+  collide(E, P, cx.cand, cs, crash, rc, lc);
+  finish_step(E, P, cx.cs, cx.sn, cx.thr_main, cx.thr_side, crash, rc, lc, info);
 }
 
 __global__ void __launch_bounds__(TPB)
@@ -700,29 +207,14 @@ lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__
   if (!valid) return;
   bool terrain = (sin_ != sout);
   if (d != COTIX_DONE_NO && P.auto_reset) {
-    Key2 rk = E.key;
-    const uint32_t episode = ((E.status >> 8) + 1u) & 0xFFFFFFu;
-    if (P.rng_mode == COTIX_RNG_THREEFRY) {
-      rk = tf_split(E.key, 2u, 1u);
-      E.key = tf_split(E.key, 2u, 0u);
-    }
-    lunar_reset_env(E, rk, P, episode);
+    lunar_auto_reset(E, P);
     rc = lc = false;
     terrain = true;
   }
   store_env(E, sout, ld, e, terrain);
   if (reward) reward[e] = rsum;
   if (done) done[e] = (uint8_t)d;
-  if (obs) {
-    obs[0 * ld + e] = E.b[0].px;
-    obs[1 * ld + e] = E.b[0].py;
-    obs[2 * ld + e] = E.b[0].vx;
-    obs[3 * ld + e] = E.b[0].vy;
-    obs[4 * ld + e] = E.b[0].ang;
-    obs[5 * ld + e] = E.b[0].w;
-    obs[6 * ld + e] = rc ? 1.0f : 0.0f;
-    obs[7 * ld + e] = lc ? 1.0f : 0.0f;
-  }
+  if (obs) store_obs(E, obs, ld, e, rc, lc);
 }
 
 __global__ void __launch_bounds__(TPB)
@@ -767,8 +259,8 @@ static void derive_body(const float (*v)[2], int n, int* ok, int* orient) {
   }
   *ok = good ? 1 : 0;
 }
-static LunarDerived derive(const CotixLunarParams* p) {
-  LunarDerived D;
+extern "C" void cx_lunar_derive(const CotixLunarParams* p, LunarDerived* out) {
+  LunarDerived& D = *out;
   derive_body(p->lander_local, 6, &D.rigid_ok[0], &D.orient[0]);
   derive_body(p->leg_local[0], 4, &D.rigid_ok[1], &D.orient[1]);
   derive_body(p->leg_local[1], 4, &D.rigid_ok[2], &D.orient[2]);
@@ -780,15 +272,16 @@ static LunarDerived derive(const CotixLunarParams* p) {
     D.lext[2] = fmaxf(D.lext[2], p->lander_local[k][0]);
     D.lext[3] = fmaxf(D.lext[3], p->lander_local[k][1]);
   }
-  return D;
 }
 
 extern "C" int cx_launch_lunar_step(cudaStream_t st, int64_t B, const float* sin_, float* sout,
                                     int64_t ld, const float* action, float* reward, uint8_t* done,
                                     float* obs, const CotixLunarParams* p) {
   if (B == 0) return 0;
+  LunarDerived D;
+  cx_lunar_derive(p, &D);
   lunar_step_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(B, sin_, sout, ld, action, reward,
-                                                                     done, obs, *p, derive(p));
+                                                                     done, obs, *p, D);
   cx_count_launch();
   return cx_check_launch("lunar_step_kernel");
 }

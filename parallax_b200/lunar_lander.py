@@ -102,13 +102,34 @@ def reset(keys, params: LunarParams | None = None, device="cuda") -> LunarState:
     return LunarState(state)
 
 
+MODE_AUTO, MODE_FUSED, MODE_PIPELINE = 0, 1, 2
+PIPELINE_MIN_ENVS = 16384
+_MODES = {"auto": MODE_AUTO, "fused": MODE_FUSED, "pipeline": MODE_PIPELINE}
+_workspaces: dict = {}
+
+
+def _workspace(device: torch.device, B: int) -> torch.Tensor:
+    """Device scratch of the wavefront pipeline, cached per (device, batch)."""
+    key = (device.index, B)
+    ws = _workspaces.get(key)
+    if ws is None:
+        nbytes = int(_lib.lib().cotix_lunar_workspace_bytes(B))
+        ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
+        _workspaces.clear()  # one live batch shape at a time is the common case
+        _workspaces[key] = ws
+    return ws
+
+
 def step(state: LunarState, action: torch.Tensor | None = None, params: LunarParams | None = None,
-         inplace: bool = False, want_obs: bool = False):
+         inplace: bool = False, want_obs: bool = False, mode: str = "auto"):
     """step(state, action) -> (state', reward[B], done[B]) (+ obs[8, B]).
 
     action: [2, B] float32 device tensor (main throttle, side throttle) or None for the
     reference's unactuated step.  Functional by default (a new state tensor), like the
     reference; `inplace=True` updates `state` (what a CUDA-graph rollout wants).
+    mode: "fused" = one kernel (cotix_lunar_step), "pipeline" = the wavefront pipeline
+    (cotix_lunar_step_ws; substeps must be 1), "auto" = pipeline for B >= 16384 at K = 1.
+    Both give identical results.
     """
     params = params or default_params()
     d = state.data
@@ -120,11 +141,18 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
     if action is not None:
         action = action.to(device=d.device, dtype=torch.float32).contiguous()
         assert action.shape == (2, B)
+    m = _MODES[mode]
+    use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and params.substeps == 1 and B >= PIPELINE_MIN_ENVS)
     with torch.cuda.device(d.device):
-        _lib.check(_lib.lib().cotix_lunar_step(
-            _stream_ptr(d.device), B, d.data_ptr(), out.data_ptr(), d.stride(0),
-            action.data_ptr() if action is not None else None, reward.data_ptr(), done.data_ptr(),
-            obs.data_ptr() if obs is not None else None, C.byref(params)))
+        args = (_stream_ptr(d.device), B, d.data_ptr(), out.data_ptr(), d.stride(0),
+                action.data_ptr() if action is not None else None, reward.data_ptr(), done.data_ptr(),
+                obs.data_ptr() if obs is not None else None, C.byref(params))
+        if use_pipe:
+            ws = _workspace(d.device, B)
+            wp = (ws.data_ptr() + 255) & ~255
+            _lib.check(_lib.lib().cotix_lunar_step_ws(*args, wp, ws.numel() - (wp - ws.data_ptr())))
+        else:
+            _lib.check(_lib.lib().cotix_lunar_step(*args))
     ns = state if inplace else LunarState(out)
     if want_obs:
         return ns, reward, done, obs
@@ -158,6 +186,10 @@ class LunarLanderEnv:
             self.close()
         except Exception:
             pass
+
+    def set_mode(self, mode: str) -> None:
+        """"auto" | "fused" | "pipeline" (see `step`)."""
+        _lib.check(_lib.lib().cotix_lunar_env_set_mode(self._h, _MODES[mode]))
 
     def reset(self, keys) -> None:
         k = np.ascontiguousarray(np.asarray(keys).astype(np.uint32)).reshape(self.B, 2)

@@ -227,7 +227,10 @@ def test_typed_contact_functions_and_reference_cases(cuda_lib, oracle, exact_tri
 # ------------------------------------------------------------------------------------------
 # LunarLander
 # ------------------------------------------------------------------------------------------
-def _rollout_both(oracle, ll, P, state0, steps, actions=None, check_every=1, dedupe=True):
+MODES = ["fused", "pipeline"]
+
+
+def _rollout_both(oracle, ll, P, state0, steps, actions=None, check_every=1, dedupe=True, mode="fused"):
     import torch
 
     st = ll.LunarState.from_numpy(state0)
@@ -235,7 +238,7 @@ def _rollout_both(oracle, ll, P, state0, steps, actions=None, check_every=1, ded
     for t in range(steps):
         act = None if actions is None else actions[t]
         dact = None if act is None else torch.from_numpy(act).cuda()
-        st, rew, done = ll.step(st, dact, P)
+        st, rew, done = ll.step(st, dact, P, mode=mode)
         ref, orew, odone = oracle.lunar_step(ref, act, P, dedupe=dedupe)
         if t % check_every == 0 or t == steps - 1:
             _eq(st.numpy(), ref, f"state at step {t}")
@@ -265,40 +268,44 @@ def test_lunar_reset_bit_exact(cuda_lib, oracle, exact_trig):
     _eq(ll.reset(keys, P3).numpy(), oracle.lunar_reset(keys, P3), "reset philox")
 
 
-def test_lunar_free_fall_and_landing_bit_exact(cuda_lib, oracle, exact_trig):
+@pytest.mark.parametrize("mode", MODES)
+def test_lunar_free_fall_and_landing_bit_exact(cuda_lib, oracle, exact_trig, mode):
     """The reference scenario itself (examples/test_viz.py:46-48): reset, then 1200 unactuated
     steps — free fall, touch-down on the pad near step ~800, rebound."""
     from parallax_b200 import lunar_lander as ll
 
     P = ll.default_params()
     s0 = oracle.lunar_reset(lunar_keys(32), P)
-    st, ref = _rollout_both(oracle, ll, P, s0, 1200, check_every=50)
+    st, ref = _rollout_both(oracle, ll, P, s0, 1200, check_every=50, mode=mode)
     assert ref[1].max() < 3.0  # every lander came down from y = 5 and hit the terrain
 
 
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("rng_mode", [0, 1])
-def test_lunar_contact_rich_bit_exact(cuda_lib, oracle, exact_trig, rng_mode):
+def test_lunar_contact_rich_bit_exact(cuda_lib, oracle, exact_trig, rng_mode, mode):
     """BASELINE config 3 style states (perturbed poses, many start in or near the terrain)."""
     from parallax_b200 import lunar_lander as ll
 
     P = ll.default_params(rng_mode=rng_mode)
     rng = np.random.default_rng(20 + rng_mode)
     s0 = perturbed_lunar_state(oracle.lunar_reset(lunar_keys(512), P), rng, P)
-    _rollout_both(oracle, ll, P, s0, 150, check_every=10)
+    _rollout_both(oracle, ll, P, s0, 150, check_every=10, mode=mode)
 
 
-def test_lunar_literal_oracle_small(cuda_lib, oracle, exact_trig):
+@pytest.mark.parametrize("mode", MODES)
+def test_lunar_literal_oracle_small(cuda_lib, oracle, exact_trig, mode):
     """Against the LITERAL oracle (all 306 narrowphase evaluations, no memoisation)."""
     from parallax_b200 import lunar_lander as ll
 
     P = ll.default_params()
     rng = np.random.default_rng(30)
     s0 = perturbed_lunar_state(oracle.lunar_reset(lunar_keys(48), P), rng, P)
-    _rollout_both(oracle, ll, P, s0, 40, check_every=5, dedupe=False)
+    _rollout_both(oracle, ll, P, s0, 40, check_every=5, dedupe=False, mode=mode)
 
 
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("rng_mode", [0, 1])
-def test_lunar_env_logic_bit_exact(cuda_lib, oracle, exact_trig, rng_mode):
+def test_lunar_env_logic_bit_exact(cuda_lib, oracle, exact_trig, rng_mode, mode):
     """Actions, judge, termination and auto-reset (new logic; oracle implements the same spec)."""
     from parallax_b200 import lunar_lander as ll
 
@@ -308,7 +315,7 @@ def test_lunar_env_logic_bit_exact(cuda_lib, oracle, exact_trig, rng_mode):
     B, T = 384, 200
     s0 = perturbed_lunar_state(oracle.lunar_reset(lunar_keys(B), P), rng, P)
     actions = rng.uniform(-1, 1, size=(T, 2, B)).astype(np.float32)
-    st, ref = _rollout_both(oracle, ll, P, s0, T, actions=actions, check_every=10)
+    st, ref = _rollout_both(oracle, ll, P, s0, T, actions=actions, check_every=10, mode=mode)
     episodes = (ref[33].view(np.uint32) >> 8)
     assert episodes.max() >= 2  # several auto-resets happened
 
@@ -338,7 +345,8 @@ def test_lunar_substeps_equal_repeated_steps(cuda_lib, oracle, exact_trig):
     _eq(a.numpy(), ref, "K=4 vs oracle")
 
 
-def test_lunar_inplace_and_obs(cuda_lib, oracle, exact_trig):
+@pytest.mark.parametrize("mode", MODES)
+def test_lunar_inplace_and_obs(cuda_lib, oracle, exact_trig, mode):
     import torch
     from parallax_b200 import lunar_lander as ll
 
@@ -348,12 +356,13 @@ def test_lunar_inplace_and_obs(cuda_lib, oracle, exact_trig):
     st = ll.LunarState.from_numpy(s0)
     ref = s0
     for _ in range(45):
-        st, rew, done, obs = ll.step(st, None, P, inplace=True, want_obs=True)
+        st, rew, done, obs = ll.step(st, None, P, inplace=True, want_obs=True, mode=mode)
         ref, orew, odone, oobs = oracle.lunar_step(ref, None, P, want_obs=True)
     _eq(st.numpy(), ref, "state"); _eq(obs.cpu().numpy(), oobs, "obs"); _eq(done.cpu().numpy(), odone, "done")
 
 
-def test_lunar_host_env_and_graph(cuda_lib, oracle, exact_trig):
+@pytest.mark.parametrize("mode", MODES)
+def test_lunar_host_env_and_graph(cuda_lib, oracle, exact_trig, mode):
     """The HOST-facing handle (H2D action -> kernel -> D2H obs/reward/done) and CUDA-graph replay."""
     import torch
     from parallax_b200 import lunar_lander as ll
@@ -361,6 +370,7 @@ def test_lunar_host_env_and_graph(cuda_lib, oracle, exact_trig):
     P = ll.default_params(judge_enabled=1, auto_reset=1, reset_perturb=1, max_episode_steps=64)
     B = 300
     env = ll.LunarLanderEnv(B, P)
+    env.set_mode(mode)
     keys = lunar_keys(B, offset=7)
     env.reset(keys)
     ref = oracle.lunar_reset(keys, P)
@@ -401,6 +411,47 @@ def test_lunar_libm_oracle_tolerance(cuda_lib, oracle):
     # tiny fraction of such envs and report it
     assert bad.mean() < 2e-3, f"{bad.sum()} of {bad.size} envs beyond 1e-5"
     _eq(got[30:32].view(np.uint32), ref[30:32].view(np.uint32), "key chain")
+
+
+def test_pipeline_equals_fused_large_batch(cuda_lib, oracle, exact_trig):
+    """BASELINE config 3 at a size where the item queue is busy: the wavefront pipeline and the
+    fused kernel agree bit for bit over 60 steps with actions, judge and auto-reset (and a
+    sample of envs agrees with the oracle)."""
+    import torch
+    from parallax_b200 import lunar_lander as ll
+
+    P = ll.default_params(judge_enabled=1, auto_reset=1, reset_perturb=1, max_episode_steps=40)
+    B = 1 << 16
+    rng = np.random.default_rng(90)
+    s0 = perturbed_lunar_state(ll.reset(lunar_keys(B), P).numpy(), rng, P)
+    a = ll.LunarState.from_numpy(s0)
+    b = ll.LunarState.from_numpy(s0)
+    ref = s0[:, :512].copy()
+    for t in range(60):
+        act = torch.from_numpy(rng.uniform(-1, 1, size=(2, B)).astype(np.float32)).cuda()
+        a, ra, da, oa = ll.step(a, act, P, inplace=(t % 2 == 0), want_obs=True, mode="fused")
+        b, rb, db, ob = ll.step(b, act, P, inplace=(t % 2 == 1), want_obs=True, mode="pipeline")
+        ref, rr, dr, orr = oracle.lunar_step(ref, act[:, :512].cpu().numpy(), P, want_obs=True)
+        if t % 10 == 9 or t < 2:
+            _eq(b.numpy(), a.numpy(), f"state {t}"); _eq(rb.cpu().numpy(), ra.cpu().numpy(), f"reward {t}")
+            _eq(db.cpu().numpy(), da.cpu().numpy(), f"done {t}"); _eq(ob.cpu().numpy(), oa.cpu().numpy(), f"obs {t}")
+            _eq(b.numpy()[:, :512], ref, f"oracle state {t}"); _eq(ob.cpu().numpy()[:, :512], orr, f"oracle obs {t}")
+    assert (b.numpy()[33].view(np.uint32) >> 8).max() >= 2
+
+
+def test_pipeline_argument_checks(cuda_lib):
+    import torch
+    from parallax_b200 import lunar_lander as ll
+
+    P = ll.default_params(substeps=2)
+    st = ll.reset(lunar_keys(64), P)
+    with pytest.raises(Exception):
+        ll.step(st, None, P, mode="pipeline")   # K > 1 is the fused kernel's job
+    P1 = ll.default_params()
+    rc = cuda_lib.cotix_lunar_step_ws(None, 64, st.data.data_ptr(), st.data.data_ptr(), 64, None, None, None,
+                                      None, C.byref(P1), None, 0)
+    assert rc == -1 and b"workspace" in cuda_lib.cotix_last_error()
+    assert cuda_lib.cotix_lunar_workspace_bytes(64) > 0
 
 
 def test_missing_library_fails_loudly(monkeypatch, cuda_lib):
