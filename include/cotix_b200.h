@@ -223,6 +223,16 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
                         int64_t workspace_bytes);
 
 /*
+ * Per-stage timing of the pipeline (measurement aid; not thread-safe): while enabled, every
+ * cotix_lunar_step_ws call records CUDA events between its stages on the launching stream.
+ * cotix_lunar_pipeline_stage_ms writes the average milliseconds of the six stages (integrate,
+ * gjk, epa, collide, finish, reset) since profiling was enabled and returns the steps averaged.
+ */
+#define COTIX_PIPELINE_STAGES 6
+int cotix_lunar_pipeline_profile(int enable);
+int64_t cotix_lunar_pipeline_stage_ms(double* out_ms /*[COTIX_PIPELINE_STAGES]*/);
+
+/*
  * Host-facing env handle: owns the device state of B envs on `device`, keeps it
  * resident, and exposes reset/step with HOST buffers (pinned or pageable).  One step =
  * H2D(action) -> kernel -> D2H(obs, reward, done), on the handle's own stream.

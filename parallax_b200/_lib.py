@@ -130,6 +130,7 @@ EXPORTS = [
     "cotix_narrowphase", "cotix_narrowphase_host", "cotix_order_clockwise",
     "cotix_lunar_default_params", "cotix_lunar_reset", "cotix_lunar_step",
     "cotix_lunar_workspace_bytes", "cotix_lunar_step_ws", "cotix_lunar_env_set_mode",
+    "cotix_lunar_pipeline_profile", "cotix_lunar_pipeline_stage_ms",
     "cotix_lunar_env_create", "cotix_lunar_env_destroy", "cotix_lunar_env_reset_host",
     "cotix_lunar_env_step_host", "cotix_lunar_env_get_state_host",
     "cotix_lunar_env_set_state_host", "cotix_lunar_env_state_ptr", "cotix_lunar_env_stream",
@@ -167,6 +168,9 @@ def lib() -> C.CDLL:
     L.cotix_lunar_workspace_bytes.argtypes = [i64]
     L.cotix_lunar_step_ws.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams), vp, i64]
     L.cotix_lunar_env_set_mode.argtypes = [vp, C.c_int]
+    L.cotix_lunar_pipeline_profile.argtypes = [C.c_int]
+    L.cotix_lunar_pipeline_stage_ms.restype = C.c_int64
+    L.cotix_lunar_pipeline_stage_ms.argtypes = [C.POINTER(C.c_double)]
     L.cotix_lunar_env_create.argtypes = [C.POINTER(vp), C.c_int, i64, C.POINTER(LunarParams)]
     L.cotix_lunar_env_destroy.argtypes = [vp]
     L.cotix_lunar_env_reset_host.argtypes = [vp, vp]

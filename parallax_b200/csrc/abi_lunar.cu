@@ -16,6 +16,8 @@ extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, flo
                                      const CotixLunarParams*);
 
 extern "C" int64_t cx_lunar_pipeline_workspace_bytes(int64_t B);
+extern "C" int cx_lunar_pipeline_profile(int enable);
+extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
 extern "C" int cx_launch_lunar_pipeline(cudaStream_t, int64_t, const float*, float*, int64_t, const float*,
                                         float*, uint8_t*, float*, const CotixLunarParams*, void*, int64_t);
 
@@ -241,6 +243,12 @@ int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* stat
   CXL_REQUIRE(B == 0 || (state_in && state_out), "null state");
   return cx_launch_lunar_step((cudaStream_t)stream, B, state_in, state_out, ld, action, reward, done,
                               obs, p);
+}
+
+int cotix_lunar_pipeline_profile(int enable) { return cx_lunar_pipeline_profile(enable); }
+int64_t cotix_lunar_pipeline_stage_ms(double* out_ms) {
+  if (!out_ms) return 0;
+  return cx_lunar_pipeline_stage_ms(out_ms);
 }
 
 int64_t cotix_lunar_workspace_bytes(int64_t B) { return cx_lunar_pipeline_workspace_bytes(B); }

@@ -394,6 +394,28 @@ pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
   }
 }
 
+// optional per-stage timing (bench.py's roofline of the dominant kernel): CUDA events recorded
+// between the stages on the launching stream while profiling is enabled
+constexpr int N_STAGES = 6;
+bool g_profile = false;
+cudaEvent_t g_ev[N_STAGES + 1];
+bool g_ev_made = false;
+double g_stage_ms[N_STAGES];
+int64_t g_stage_steps = 0;
+bool g_ev_pending = false;
+
+void profile_collect() {
+  if (!g_ev_pending) return;
+  if (cudaEventSynchronize(g_ev[N_STAGES]) == cudaSuccess) {
+    for (int k = 0; k < N_STAGES; ++k) {
+      float ms = 0.0f;
+      if (cudaEventElapsedTime(&ms, g_ev[k], g_ev[k + 1]) == cudaSuccess) g_stage_ms[k] += ms;
+    }
+    ++g_stage_steps;
+  }
+  g_ev_pending = false;
+}
+
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 uint32_t item_capacity(int64_t B) { return (uint32_t)(4 * B + 4096); }
 
@@ -455,16 +477,52 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
     return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
   };
   if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, st) != cudaSuccess) return cx_check_launch("pipeline memset");
+  const bool prof = g_profile;
+  if (prof) {
+    profile_collect();
+    if (!g_ev_made) {
+      for (int k = 0; k <= N_STAGES; ++k) cudaEventCreate(&g_ev[k]);
+      g_ev_made = true;
+    }
+  }
+#define CX_STAGE_MARK(k) \
+  if (prof) cudaEventRecord(g_ev[k], st)
+  CX_STAGE_MARK(0);
   pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, sin_, sout, ld, action, *p, D, ws);
+  CX_STAGE_MARK(1);
   pipe_gjk_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, ws);
+  CX_STAGE_MARK(2);
   pipe_epa_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, ws);
+  CX_STAGE_MARK(3);
   pipe_collide_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, *p, ws);
+  CX_STAGE_MARK(4);
   pipe_finish_kernel<<<env_blocks, TPB, 0, st>>>(B, sout, ld, action, reward, done, obs, *p, ws);
+  CX_STAGE_MARK(5);
   if (p->auto_reset) {
     pipe_reset_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, obs, *p, ws);
     cx_count_launch_n(6);
   } else {
     cx_count_launch_n(5);
   }
+  CX_STAGE_MARK(6);
+#undef CX_STAGE_MARK
+  if (prof) g_ev_pending = true;
   return cx_check_launch("lunar pipeline");
+}
+
+// ---- per-stage timing (single-threaded use: bench.py) ----------------------------------------
+extern "C" int cx_lunar_pipeline_profile(int enable) {
+  if (!enable) profile_collect();
+  g_profile = enable != 0;
+  if (enable) {
+    for (int k = 0; k < N_STAGES; ++k) g_stage_ms[k] = 0.0;
+    g_stage_steps = 0;
+    g_ev_pending = false;
+  }
+  return COTIX_OK;
+}
+extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out) {
+  profile_collect();
+  for (int k = 0; k < N_STAGES; ++k) out[k] = g_stage_steps ? g_stage_ms[k] / (double)g_stage_steps : 0.0;
+  return g_stage_steps;
 }

@@ -159,6 +159,21 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
     return ns, reward, done
 
 
+PIPELINE_STAGES = ("integrate", "gjk", "epa", "collide", "finish", "reset")
+
+
+def pipeline_profile(enable: bool) -> None:
+    """Start / stop per-stage CUDA-event timing of the pipeline (measurement aid)."""
+    _lib.check(_lib.lib().cotix_lunar_pipeline_profile(1 if enable else 0))
+
+
+def pipeline_stage_ms() -> tuple[dict, int]:
+    """({stage: average ms}, steps averaged) since profiling was enabled."""
+    out = (C.c_double * len(PIPELINE_STAGES))()
+    n = int(_lib.lib().cotix_lunar_pipeline_stage_ms(out))
+    return {k: float(out[i]) for i, k in enumerate(PIPELINE_STAGES)}, n
+
+
 class LunarLanderEnv:
     """Vector env with HOST-facing reset/step (the `e2e` path of bench.py).
 
