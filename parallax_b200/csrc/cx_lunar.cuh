@@ -142,12 +142,15 @@ CX_DEV bool poly_order_rigid(Poly& p, int orient) {
 }
 
 // ---- resolution — cotix/_collision_resolution.py:52-151 -------------------------------
+// x / m; a divisor of exactly 1 (the legs' mass and inertia) is skipped — x / 1 == x bit for bit —
+// and since m is a launch constant the branch is uniform
+CX_DEV float div_m(float x, float m) { return (m == 1.0f) ? x : x / m; }
 CX_DEV void apply_impulse(BodyS& b, const MassP& m, V2 imp, V2 point) {  // :68-73
   V2 arm = point - mk2(b.px, b.py);
   float torque = cross2(arm, imp);
-  b.vx = b.vx + imp.x / m.mass;
-  b.vy = b.vy + imp.y / m.mass;
-  b.w = b.w + torque / m.inertia;
+  b.vx = b.vx + div_m(imp.x, m.mass);
+  b.vy = b.vy + div_m(imp.y, m.mass);
+  b.w = b.w + div_m(torque, m.inertia);
 }
 CX_DEV V2 velocity_at(const BodyS& b, V2 point) {  // cotix/_bodies.py:50-55
   return mk2(b.vx, b.vy) + perp(point - mk2(b.px, b.py)) * b.w;

@@ -142,9 +142,30 @@ CX_DEV bool outside_lander_obb(const Poly& w, const BodyS& L, float c, float s, 
   return (lox > D.lext[2] + m) || (hix < D.lext[0] - m) || (loy > D.lext[3] + m) || (hiy < D.lext[1] - m);
 }
 
+// element k (dynamic) of an 8-vector held in registers
+CX_DEV float sel8(const float v[8], int k) {
+  float r = v[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) r = (k == i) ? v[i] : r;
+  return r;
+}
+
+// part.transform() re-sorts the world vertices (cotix/_convex_shapes.py:181-187); body = 0
+// lander (6 vertices), 1 right leg, 2 left leg (4 vertices)
+CX_DEV void order_body_poly(int body, Poly& p, const LunarDerived& D) {
+  if (body == 0) {
+    if (!(D.rigid_ok[0] && poly_order_rigid<6>(p, D.orient[0]))) poly_sort_cw<6>(p);
+  } else {
+    const int b = body == 1 ? 1 : 2;
+    if (!(D.rigid_ok[b] && poly_order_rigid<4>(p, D.orient[b]))) poly_sort_cw<4>(p);
+  }
+}
+
 // ---- integrate + broadphase -----------------------------------------------------------------
-// Updates E (poses, lander velocity, status), fills cx (sin/cos, throttles, candidate mask) and,
-// when there are candidates, leaves the world polygons in the order part.transform() gives them.
+// Updates E (poses, lander velocity, status), fills cx (sin/cos, throttles, candidate mask) and
+// returns the world polygons: with ORDER, in the order part.transform() gives them when there
+// are candidates; without, always in local vertex order (the consumer calls order_body_poly).
+template <bool ORDER>
 CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
                                const LunarDerived& D, StepCtx& cx, Poly& wL, Poly& wr, Poly& wl) {
   // ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24); the ground stays at 0
@@ -184,19 +205,37 @@ CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const Cot
   if (aabb_near(br, bL) && !outside_lander_obb(wr, E.b[0], cx.cs[0], cx.sn[0], D)) cand |= 1u << 0;
   if (aabb_near(bl, bL) && !outside_lander_obb(wl, E.b[0], cx.cs[0], cx.sn[0], D)) cand |= 1u << 1;
   if (aabb_near(bl, br)) cand |= 1u << 9;
+  {
+    // ground trapezoids: only those whose x-range comes near the x-range of the assembly are
+    // looked at (the same test aabb_near makes first), in a loop whose trip count is the number
+    // of such segments (1-3) rather than 7, so the lanes of a warp stay together
+    const float m = CX_CULL_MARGIN;
+    const float ulx = fminf(bL.lx, fminf(br.lx, bl.lx)), uhx = fmaxf(bL.hx, fmaxf(br.hx, bl.hx));
+    float X[8];
 #pragma unroll
-  for (int k = 0; k < 7; ++k) {
-    const float x0 = terrain_x(E.kn, P, k), x1 = terrain_x(E.kn, P, k + 1);
-    const float h0 = E.h[k], h1 = E.h[k + 1];
-    Aabb g;
-    g.lx = fminf(x0, x1);
-    g.hx = fmaxf(x0, x1);
-    g.ly = fminf(fminf(h0, h1), P.ground_floor);
-    g.hy = fmaxf(fmaxf(h0, h1), P.ground_floor);
-    const bool regular = (x1 > x0) && (h0 > P.ground_floor) && (h1 > P.ground_floor);
-    if (aabb_near(g, bL) && !(regular && above_top_edge<6>(wL, x0, h0, x1, h1))) cand |= 1u << (2 + k);
-    if (aabb_near(g, br) && !(regular && above_top_edge<4>(wr, x0, h0, x1, h1))) cand |= 1u << (11 + k);
-    if (aabb_near(g, bl) && !(regular && above_top_edge<4>(wl, x0, h0, x1, h1))) cand |= 1u << (18 + k);
+    for (int k = 0; k < 8; ++k) X[k] = terrain_x(E.kn, P, k);
+    uint32_t segs = 0u;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) {
+      const float glx = fminf(X[k], X[k + 1]), ghx = fmaxf(X[k], X[k + 1]);
+      // negated form so that NaN bounds keep the segment (aabb_near decides below)
+      if (!(uhx + m < glx || ghx + m < ulx)) segs |= 1u << k;
+    }
+    while (segs) {
+      const int k = __ffs(segs) - 1;
+      segs &= segs - 1u;
+      const float x0 = sel8(X, k), x1 = sel8(X, k + 1);
+      const float h0 = sel8(E.h, k), h1 = sel8(E.h, k + 1);
+      Aabb g;
+      g.lx = fminf(x0, x1);
+      g.hx = fmaxf(x0, x1);
+      g.ly = fminf(fminf(h0, h1), P.ground_floor);
+      g.hy = fmaxf(fmaxf(h0, h1), P.ground_floor);
+      const bool regular = (x1 > x0) && (h0 > P.ground_floor) && (h1 > P.ground_floor);
+      if (aabb_near(g, bL) && !(regular && above_top_edge<6>(wL, x0, h0, x1, h1))) cand |= 1u << (2 + k);
+      if (aabb_near(g, br) && !(regular && above_top_edge<4>(wr, x0, h0, x1, h1))) cand |= 1u << (11 + k);
+      if (aabb_near(g, bl) && !(regular && above_top_edge<4>(wl, x0, h0, x1, h1))) cand |= 1u << (18 + k);
+    }
   }
   bool bad = (E.status & COTIX_ST_GROUND_NAN) != 0u;
 #pragma unroll
@@ -209,11 +248,10 @@ CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const Cot
   if (cand & ((1u << 1) | (1u << 9))) cand |= 1u << 10;
   cx.cand = cand;
   cx.base = -1;
-  if (cand != 0u) {
-    // part.transform() re-sorts the world vertices (cotix/_convex_shapes.py:181-187)
-    if (!(D.rigid_ok[0] && poly_order_rigid<6>(wL, D.orient[0]))) poly_sort_cw<6>(wL);
-    if (!(D.rigid_ok[1] && poly_order_rigid<4>(wr, D.orient[1]))) poly_sort_cw<4>(wr);
-    if (!(D.rigid_ok[2] && poly_order_rigid<4>(wl, D.orient[2]))) poly_sort_cw<4>(wl);
+  if (ORDER && cand != 0u) {
+    order_body_poly(0, wL, D);
+    order_body_poly(1, wr, D);
+    order_body_poly(2, wl, D);
   }
 }
 

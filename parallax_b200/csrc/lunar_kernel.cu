@@ -74,7 +74,7 @@ __device__ void phase_a(EnvRegs& E, float a_main, float a_side, const CotixLunar
                         const LunarDerived& D, SharedBlock& S, StepCtx& cx) {
   const int tid = threadIdx.x;
   Poly wL, wr, wl;
-  integrate_and_cull(E, a_main, a_side, P, D, cx, wL, wr, wl);
+  integrate_and_cull<true>(E, a_main, a_side, P, D, cx, wL, wr, wl);
   const uint32_t cand = cx.cand;
   if (cand != 0u) {
 #pragma unroll

@@ -68,10 +68,16 @@ CX_DEV uint32_t queue_push(uint32_t* counter, bool pred) {
   return b + (uint32_t)__popc(m & lanemask_lt());
 }
 
-// polygon source: the record K_A wrote for env e
+// polygon source: the record K_A wrote for env e (world polygons in LOCAL vertex order; the
+// re-sort of part.transform() is applied here, per use, where the lanes are dense)
 struct RecPolys {
   const float4* r;
+  const LunarDerived& D;
   CX_DEV void body(int which, Poly& p) const {
+    body_raw(which, p);
+    order_body_poly(which, p, D);
+  }
+  CX_DEV void body_raw(int which, Poly& p) const {
     if (which == 0) {
       const float4 a = r[0], b = r[1], c = r[2];
       p.n = 6;
@@ -120,7 +126,7 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
     }
     StepCtx cx;
     Poly wL, wr, wl;
-    integrate_and_cull(E, am, as, P, D, cx, wL, wr, wl);
+    integrate_and_cull<false>(E, am, as, P, D, cx, wL, wr, wl);
     cand = cx.cand;
     cnt = __popc(cand);
     if (inplace) {
@@ -204,7 +210,7 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
 
 // ---- K_B1 ----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB)
-pipe_gjk_kernel(const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
+pipe_gjk_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
   const uint32_t n = min(ws.ctr[CTR_ITEMS], ws.cap);
   const uint32_t stride = gridDim.x * TPB;
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
@@ -217,7 +223,7 @@ pipe_gjk_kernel(const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
       if (it != 0xFFFFFFFFu) {
         e = it >> 5;
         Poly A, Bp;
-        RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS)};
+        RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
         make_item_polys(src, (int)(it & 31u), P, A, Bp);
         V2 s0, s1, s2;
         bool capped;
@@ -247,7 +253,7 @@ pipe_gjk_kernel(const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
 
 // ---- K_B2 ----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB)
-pipe_epa_kernel(const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
+pipe_epa_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
   const uint32_t n = ws.ctr[CTR_HITS];
   const uint32_t stride = gridDim.x * TPB;
   for (uint32_t h = blockIdx.x * TPB + threadIdx.x; h < n; h += stride) {
@@ -255,7 +261,7 @@ pipe_epa_kernel(const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
     const uint32_t it = ws.item[i];
     const uint32_t e = it >> 5;
     Poly A, Bp;
-    RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS)};
+    RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
     make_item_polys(src, (int)(it & 31u), P, A, Bp);
     const V2 s0 = mk2(ws.res[0 * (size_t)ws.cap + i], ws.res[1 * (size_t)ws.cap + i]);
     const V2 s1 = mk2(ws.res[2 * (size_t)ws.cap + i], ws.res[3 * (size_t)ws.cap + i]);
@@ -276,10 +282,11 @@ pipe_epa_kernel(const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
 struct QueueContacts {
   const PipeWs& ws;
   const CotixLunarParams& P;
+  const LunarDerived& D;
   uint32_t e, cand, base;
   CX_DEV Contact inline_eval(int bit) const {
     Poly A, Bp;
-    RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS)};
+    RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
     make_item_polys(src, bit, P, A, Bp);
     return poly_pair(A, Bp, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters);
   }
@@ -308,7 +315,7 @@ struct QueueContacts {
 // ---- K_C1 ----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB)
 pipe_collide_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
-                    const PipeWs ws) {
+                    const LunarDerived D, const PipeWs ws) {
   const uint32_t n = ws.ctr[CTR_CENV];
   const uint32_t stride = gridDim.x * TPB;
   for (uint32_t c = blockIdx.x * TPB + threadIdx.x; c < n; c += stride) {
@@ -321,7 +328,7 @@ pipe_collide_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
     E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
     const uint32_t status0 = E.status;
     const uint32_t cand = ws.cand[e] & CX_PAIR_BITS;
-    QueueContacts qc{ws, P, e, cand, ws.base[e]};
+    QueueContacts qc{ws, P, D, e, cand, ws.base[e]};
     bool crash, rc, lc;
     collide(E, P, cand, qc, crash, rc, lc);
 #pragma unroll
@@ -490,11 +497,11 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
   CX_STAGE_MARK(0);
   pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, sin_, sout, ld, action, *p, D, ws);
   CX_STAGE_MARK(1);
-  pipe_gjk_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, ws);
+  pipe_gjk_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, D, ws);
   CX_STAGE_MARK(2);
-  pipe_epa_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, ws);
+  pipe_epa_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, D, ws);
   CX_STAGE_MARK(3);
-  pipe_collide_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, *p, ws);
+  pipe_collide_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, *p, D, ws);
   CX_STAGE_MARK(4);
   pipe_finish_kernel<<<env_blocks, TPB, 0, st>>>(B, sout, ld, action, reward, done, obs, *p, ws);
   CX_STAGE_MARK(5);
