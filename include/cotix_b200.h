@@ -208,7 +208,7 @@ int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* stat
                      float* obs, const CotixLunarParams* p);
 
 /*
- * The same step run as a WAVEFRONT PIPELINE (csrc/lunar_pipeline.cu): 1 memset + 6 small dense
+ * The same step run as a WAVEFRONT PIPELINE (csrc/lunar_pipeline.cu): 1 memset + 5 small dense
  * kernels with stream-compacted work queues in a caller-provided DEVICE workspace, instead of
  * one fused kernel.  Results are identical bit for bit; it is several times faster for large,
  * contact-rich batches.  Requires params->substeps == 1 (use cotix_lunar_step for K > 1) and
@@ -225,8 +225,9 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
 /*
  * Per-stage timing of the pipeline (measurement aid; not thread-safe): while enabled, every
  * cotix_lunar_step_ws call records CUDA events between its stages on the launching stream.
- * cotix_lunar_pipeline_stage_ms writes the average milliseconds of the six stages (integrate,
- * gjk, epa, collide, finish, reset) since profiling was enabled and returns the steps averaged.
+ * cotix_lunar_pipeline_stage_ms writes the average milliseconds of integrate, narrow, contact,
+ * finish, reset and the whole step
+ * since profiling was enabled, and returns the number of steps averaged.
  */
 #define COTIX_PIPELINE_STAGES 6
 int cotix_lunar_pipeline_profile(int enable);

@@ -299,10 +299,83 @@ static __device__ __noinline__ Contact poly_pair(const Poly& a, const Poly& b, V
 }
 
 // ---- collider given the contacts — cotix/_colliders.py:137-351 ------------------------------------
-// CS (contact source) provides live(bit) and get(bit) for the candidate pairs of this env.
+// The 7 all_contacts cells that can be populated for the LunarLander body set,
+// with the scatter-scan entries that feed each of them:
+//   cell   (i, j)          group  N1  N2  ind2 range  ind1 = a0 + q + nq*r, q < nq, r < reps
+//   0 v10  (rl, L)           0     9   9    0..8       a0 0, nq 1, reps 1
+//   1 v20  (ll, L)           0     9   9    0..8       a0 1, nq 1, reps 1
+//   2 w30  (ground, L)       0     9   9    0..8       a0 2, nq 7, reps 1
+//   3 v21  (ll, rl)          1    15  15    0..7       a0 0, nq 1, reps 1
+//   4 w31  (ground, rl)      1    15  15    0..7       a0 1, nq 7, reps 2
+//   5 w32  (ground, ll)      1    15  15    8..14      a0 1, nq 7, reps 2
+//   6 v22  (ll, ll) self     1    15  15    8..14      a0 0, nq 1, reps 1
+struct CellDesc {
+  int g, N1, N2, b_lo, b_hi, a0, nq, reps;
+};
+CX_DEV CellDesc cell_desc(int c) {
+  CellDesc d;
+  d.g = c >= 3 ? 1 : 0;
+  d.N1 = d.N2 = c >= 3 ? 15 : 9;
+  d.b_lo = c >= 5 ? 8 : 0;
+  d.b_hi = c <= 2 ? 8 : (c <= 4 ? 7 : 14);
+  d.a0 = (c == 0 || c == 3 || c == 6) ? 0 : (c == 2 ? 2 : 1);
+  d.nq = (c == 2 || c == 4 || c == 5) ? 7 : 1;
+  d.reps = (c == 4 || c == 5) ? 2 : 1;
+  return d;
+}
+
+// live masks of the cells (cotix/_colliders.py:137-140) from `live` = the candidate pairs whose
+// contact is non-NaN (bit = pair id): m[c] bit q = entry q of cell c is live.  m[6] (the self
+// pair) is filled only when want_self.
+CX_DEV bool cell_masks(uint32_t live, bool want_self, uint32_t m[7], bool& crash, bool& rc, bool& lc) {
+  m[0] = live & 1u;
+  m[1] = (live >> 1) & 1u;
+  m[2] = (live >> 2) & 0x7Fu;
+  m[3] = (live >> 9) & 1u;
+  m[4] = (live >> 11) & 0x7Fu;
+  m[5] = (live >> 18) & 0x7Fu;
+  crash = m[2] != 0u;
+  rc = m[4] != 0u;
+  lc = m[5] != 0u;
+  const bool any = (m[0] | m[1] | m[2] | m[3] | m[4] | m[5]) != 0u;
+  m[6] = (any && want_self) ? ((live >> 10) & 1u) : 0u;
+  return any;
+}
+// the same, asking the contact source pair by pair (the self pair, bit 10, only if want_self)
 template <class CS>
-CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, uint32_t cand, const CS& cs,
-                    bool& crash, bool& rc, bool& lc) {
+CX_DEV bool collide_masks(uint32_t cand, const CS& cs, bool want_self, uint32_t m[7], bool& crash,
+                          bool& rc, bool& lc) {
+  uint32_t live = 0u;
+  uint32_t todo = want_self ? cand : (cand & ~(1u << 10));
+  while (todo) {
+    const int bit = __ffs(todo) - 1;
+    todo &= todo - 1u;
+    if (cs.live(bit)) live |= 1u << bit;
+  }
+  return cell_masks(live, want_self, m, crash, rc, lc);
+}
+
+// key chain: skey = split(rkey)[0] (:142); per group skey = split(skey)[0] (:175)
+CX_DEV void make_coin_ctx(const EnvRegs& E, const CotixLunarParams& P, CoinCtx& cc) {
+  cc.mode = P.rng_mode;
+  cc.p = P.coin_p;
+  cc.steps = E.steps;
+  cc.episode = E.status >> 8;
+  cc.pkey.a = P.philox_seed[0] ^ E.key.a;
+  cc.pkey.b = P.philox_seed[1] ^ E.key.b;
+  cc.gkey[0] = cc.gkey[1] = E.key;
+  if (P.rng_mode == COTIX_RNG_THREEFRY) {
+    Key2 sk = tf_split(E.key, 2u, 0u);
+    cc.gkey[0] = tf_split(sk, 2u, 0u);
+    cc.gkey[1] = tf_split(cc.gkey[0], 2u, 0u);
+  }
+}
+
+// choose_random_contact (:274-295) + the sequential resolution scan (:310-336), given the winner
+// of every cell (win[c] = winning q or -1).  Updates E (velocities, status).
+template <class CS>
+CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const CS& cs, const CoinCtx& cc,
+                          const int win[7]) {
   MassP mp[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -317,97 +390,77 @@ CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, uint32_t cand, const 
   G.px = G.px + G.vx * P.dt;
   G.py = G.py + G.vy * P.dt;
   G.ang = G.ang + G.w * P.dt;
-
-  crash = rc = lc = false;
-  if (cand != 0u) {
-    // live masks of the 7 all_contacts cells (cotix/_colliders.py:137-140)
-    const bool l10 = cs.live(0), l20 = cs.live(1), l21 = cs.live(9);
-    uint32_t gm[3] = {0u, 0u, 0u};
-    if (cand & CX_GROUND_BITS) {
-#pragma unroll 1
-      for (int k = 0; k < 7; ++k) {
-        if (cs.live(2 + k)) gm[0] |= 1u << k;
-        if (cs.live(11 + k)) gm[1] |= 1u << k;
-        if (cs.live(18 + k)) gm[2] |= 1u << k;
-      }
+  const bool v10 = win[0] >= 0, v20 = win[1] >= 0, v21 = win[3] >= 0, v22 = win[6] >= 0;
+  const int w30 = win[2], w31 = win[4], w32 = win[5];
+  // keys split(skey, n_bodies) with the last skey
+  int j2 = -1, j3 = -1;
+  {
+    const int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
+    if (cnt == 1) j2 = v20 ? 0 : (v21 ? 1 : 2);
+    else if (cnt > 1) {
+      float u;
+      if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 2u), 0.0f, 1.0f);
+      else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 2u, CX_TAG_CHOICE), 0.0f, 1.0f);
+      j2 = choose_index(v20, v21, v22, u);
     }
-    crash = gm[0] != 0u;
-    rc = gm[1] != 0u;
-    lc = gm[2] != 0u;
-    if (l10 || l20 || l21 || gm[0] || gm[1] || gm[2]) {
-      // key chain: skey = split(rkey)[0] (:142); per group skey = split(skey)[0] (:175)
-      CoinCtx cc;
-      cc.mode = P.rng_mode;
-      cc.p = P.coin_p;
-      cc.steps = E.steps;
-      cc.episode = E.status >> 8;
-      cc.pkey.a = P.philox_seed[0] ^ E.key.a;
-      cc.pkey.b = P.philox_seed[1] ^ E.key.b;
-      cc.gkey[0] = cc.gkey[1] = E.key;
-      if (P.rng_mode == COTIX_RNG_THREEFRY) {
-        Key2 sk = tf_split(E.key, 2u, 0u);
-        cc.gkey[0] = tf_split(sk, 2u, 0u);
-        cc.gkey[1] = tf_split(cc.gkey[0], 2u, 0u);
-      }
-      // group 0 = (Polygon4, Polygon6): N1 = N2 = 9; group 1 = (Polygon4, Polygon4): 15 x 15
-      const bool v10 = cell_winner(cc, 0, 9, 9, 0, 8, 0, 1, 1, l10 ? 1u : 0u) >= 0;
-      const bool v20 = cell_winner(cc, 0, 9, 9, 0, 8, 1, 1, 1, l20 ? 1u : 0u) >= 0;
-      const int w30 = cell_winner(cc, 0, 9, 9, 0, 8, 2, 7, 1, gm[0]);
-      const bool v21 = cell_winner(cc, 1, 15, 15, 0, 7, 0, 1, 1, l21 ? 1u : 0u) >= 0;
-      const int w31 = cell_winner(cc, 1, 15, 15, 0, 7, 1, 7, 2, gm[1]);
-      const int w32 = cell_winner(cc, 1, 15, 15, 8, 14, 1, 7, 2, gm[2]);
-      bool v22 = false;
-      if (v20 || v21)  // the self pair only matters when body 2 has another live cell
-        v22 = cell_winner(cc, 1, 15, 15, 8, 14, 0, 1, 1, cs.live(10) ? 1u : 0u) >= 0;
-      // choose_random_contact (:274-295); keys split(skey, n_bodies) with the last skey
-      int j2 = -1, j3 = -1;
-      {
-        const int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
-        if (cnt == 1) j2 = v20 ? 0 : (v21 ? 1 : 2);
-        else if (cnt > 1) {
-          float u;
-          if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 2u), 0.0f, 1.0f);
-          else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 2u, CX_TAG_CHOICE), 0.0f, 1.0f);
-          j2 = choose_index(v20, v21, v22, u);
-        }
-      }
-      {
-        const bool m0 = w30 >= 0, m1 = w31 >= 0, m2 = w32 >= 0;
-        const int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
-        if (cnt == 1) j3 = m0 ? 0 : (m1 ? 1 : 2);
-        else if (cnt > 1) {
-          float u;
-          if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 3u), 0.0f, 1.0f);
-          else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 3u, CX_TAG_CHOICE), 0.0f, 1.0f);
-          j3 = choose_index(m0, m1, m2, u);
-        }
-      }
-      // sequential resolution scan i = 0..3 (:310-336); row 0 is always empty
-      if (v10) {
-        const Contact c = cs.get(0);
-        resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      }
-      if (j2 == 0 && v20) {
-        const Contact c = cs.get(1);
-        resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      }
-      if (j2 == 1 && v21) {
-        const Contact c = cs.get(9);
-        resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      }
-      if (j3 >= 0 && j3 <= 2) {
-        const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
-        if (w >= 0) {
-          const Contact c = cs.get((j3 == 0 ? 2 : (j3 == 1 ? 11 : 18)) + w);
-          if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-          else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-          else resolve_collision(G, mp[3], E.b[2], mp[2], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-        }
-      }
+  }
+  {
+    const bool m0 = w30 >= 0, m1 = w31 >= 0, m2 = w32 >= 0;
+    const int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
+    if (cnt == 1) j3 = m0 ? 0 : (m1 ? 1 : 2);
+    else if (cnt > 1) {
+      float u;
+      if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 3u), 0.0f, 1.0f);
+      else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 3u, CX_TAG_CHOICE), 0.0f, 1.0f);
+      j3 = choose_index(m0, m1, m2, u);
+    }
+  }
+  // sequential resolution scan i = 0..3 (:310-336); row 0 is always empty
+  if (v10) {
+    const Contact c = cs.get(0);
+    resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+  }
+  if (j2 == 0 && v20) {
+    const Contact c = cs.get(1);
+    resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+  }
+  if (j2 == 1 && v21) {
+    const Contact c = cs.get(9);
+    resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+  }
+  if (j3 >= 0 && j3 <= 2) {
+    const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
+    if (w >= 0) {
+      const Contact c = cs.get((j3 == 0 ? 2 : (j3 == 1 ? 11 : 18)) + w);
+      if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      else resolve_collision(G, mp[3], E.b[2], mp[2], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
     }
   }
   if ((G.vx != 0.0f) || (G.vy != 0.0f) || (G.w != 0.0f) || (G.px != 0.0f) || (G.py != 0.0f) || (G.ang != 0.0f))
     E.status |= COTIX_ST_GROUND_NAN;
+}
+
+// one thread does everything for its env (the fused kernel)
+template <class CS>
+CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, uint32_t cand, const CS& cs,
+                    bool& crash, bool& rc, bool& lc) {
+  uint32_t m[7];
+  if (!collide_masks(cand, cs, false, m, crash, rc, lc)) return;
+  CoinCtx cc;
+  make_coin_ctx(E, P, cc);
+  int win[7];
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    const CellDesc d = cell_desc(c);
+    win[c] = cell_winner(cc, d.g, d.N1, d.N2, d.b_lo, d.b_hi, d.a0, d.nq, d.reps, m[c]);
+  }
+  win[6] = -1;
+  if (win[1] >= 0 || win[3] >= 0) {  // the self pair only matters when body 2 has another live cell
+    const CellDesc d = cell_desc(6);
+    win[6] = cell_winner(cc, d.g, d.N1, d.N2, d.b_lo, d.b_hi, d.a0, d.nq, d.reps, cs.live(10) ? 1u : 0u);
+  }
+  collide_apply(E, P, cs, cc, win);
 }
 
 // ---- key split, joints, judge --------------------------------------------------------------------

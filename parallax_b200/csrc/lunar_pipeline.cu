@@ -9,20 +9,20 @@
 // HBM, and run every stage as a dense kernel over its queue.
 //
 //   memset   counters
-//   K_A  integrate  (thread = env)       Euler + gravity + engines + exact broadphase; envs with
-//                                        candidate pairs write their world polygons + terrain to
-//                                        a 192-byte record and append (env, pair) items
-//   K_B1 gjk        (thread = item)      GJK; hits append to the hit queue, their envs to the
-//                                        contact-env queue (first hit of an env wins the slot)
-//   K_B2 epa        (thread = hit)       EPA + contact point
-//   K_C1 collide    (thread = contact env)  coins, random choice, sequential impulses
-//   K_C2 finish     (thread = env)       key split, joints, judge, reward/done; finished envs
-//                                        append to the reset queue
+//   K_A  integrate  (thread = env)        Euler + gravity + engines + exact broadphase; envs with
+//                                         candidate pairs write their world polygons + terrain to
+//                                         a 192-byte record, append (env, pair) items and join
+//                                         the contact-env queue
+//   K_B  narrow     (thread = item)       vertex re-sort, GJK, EPA + contact point
+//   K_C  contact    (thread = contact env; coins pooled per warp)  coin flips, random choice,
+//                                         sequential impulses
+//   K_C2 finish     (thread = env)        key split, joints, judge, reward/done; finished envs
+//                                         append to the reset queue
 //   K_R  reset      (thread = finished env)  LunarLander.__init__ (threefry or Philox)
 //
 // Queue counters live in device memory; the queue kernels are launched with a fixed grid (a
 // multiple of the SM count) and loop over the count they read on the device, so the whole step
-// is 1 memset + 6 launches with no host synchronisation and is CUDA-Graph capturable.  All
+// is 1 memset + 5 launches with no host synchronisation and is CUDA-Graph capturable.  All
 // stages call the same device functions as the fused kernel (cx_lunar_step.cuh): results are
 // identical bit for bit.
 #include "cx_launch.cuh"
@@ -181,6 +181,9 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
   uint32_t wbase = 0u;
   if (lane == 31u) wbase = atomicAdd(&ws.ctr[CTR_ITEMS], (uint32_t)total);
   wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+  // every env with candidates goes to the contact-env queue (K_C finishes those envs itself)
+  const uint32_t cslot = queue_push(&ws.ctr[CTR_CENV], cnt != 0);
+  if (cnt != 0) ws.cenv[cslot] = (uint32_t)e;
   if (!valid) return;
   if (cnt == 0) {
     ws.cand[e] = 0u;
@@ -201,81 +204,38 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
     // slots it was given inside the queue are marked empty
     for (uint32_t slot = first; slot < ws.cap && slot < first + (uint32_t)cnt; ++slot)
       ws.item[slot] = 0xFFFFFFFFu;
-    ws.cand[e] = cand | F_QUEUED;
+    ws.cand[e] = cand;
     ws.base[e] = BASE_INLINE;
-    ws.cenv[atomicAdd(&ws.ctr[CTR_CENV], 1u)] = (uint32_t)e;
     atomicAdd(&ws.ctr[CTR_OVERFLOW], 1u);
   }
 }
 
-// ---- K_B1 ----------------------------------------------------------------------------------
+// ---- K_B -----------------------------------------------------------------------------------
+// GJK, and for hits (82 % of the candidate pairs on the bench state: resting leg/lander and
+// leg/ground contacts persist) EPA + contact point, in one pass over the item queue.
 __global__ void __launch_bounds__(TPB)
-pipe_gjk_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
+pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
   const uint32_t n = min(ws.ctr[CTR_ITEMS], ws.cap);
   const uint32_t stride = gridDim.x * TPB;
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
-  for (uint32_t i0 = blockIdx.x * TPB + (threadIdx.x & ~31u); i0 < n; i0 += stride) {
-    const uint32_t i = i0 + (threadIdx.x & 31u);
-    bool hit = false, first_hit = false;
-    uint32_t e = 0u;
-    if (i < n) {
-      const uint32_t it = ws.item[i];
-      if (it != 0xFFFFFFFFu) {
-        e = it >> 5;
-        Poly A, Bp;
-        RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
-        make_item_polys(src, (int)(it & 31u), P, A, Bp);
-        V2 s0, s1, s2;
-        bool capped;
-        hit = gjk(A, Bp, start, P.gjk_max_iters, s0, s1, s2, capped);
-        if (hit) {
-          ws.res[0 * (size_t)ws.cap + i] = s0.x;
-          ws.res[1 * (size_t)ws.cap + i] = s0.y;
-          ws.res[2 * (size_t)ws.cap + i] = s1.x;
-          ws.res[3 * (size_t)ws.cap + i] = s1.y;
-          ws.res[4 * (size_t)ws.cap + i] = s2.x;
-          ws.res[5 * (size_t)ws.cap + i] = s2.y;
-          first_hit = (atomicOr(&ws.cand[e], F_QUEUED) & F_QUEUED) == 0u;
-        } else {
-          ws.res[0 * (size_t)ws.cap + i] = 0.0f;
-          ws.res[1 * (size_t)ws.cap + i] = 0.0f;
-          ws.res[2 * (size_t)ws.cap + i] = CX_NAN;
-          ws.res[3 * (size_t)ws.cap + i] = CX_NAN;
-        }
-      }
-    }
-    const uint32_t hs = queue_push(&ws.ctr[CTR_HITS], hit);
-    if (hit) ws.hit[hs] = i;
-    const uint32_t cs = queue_push(&ws.ctr[CTR_CENV], first_hit);
-    if (first_hit) ws.cenv[cs] = e;
-  }
-}
-
-// ---- K_B2 ----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB)
-pipe_epa_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
-  const uint32_t n = ws.ctr[CTR_HITS];
-  const uint32_t stride = gridDim.x * TPB;
-  for (uint32_t h = blockIdx.x * TPB + threadIdx.x; h < n; h += stride) {
-    const uint32_t i = ws.hit[h];
+  uint32_t hits = 0u;
+  for (uint32_t i = blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
     const uint32_t it = ws.item[i];
+    if (it == 0xFFFFFFFFu) continue;
     const uint32_t e = it >> 5;
     Poly A, Bp;
     RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
     make_item_polys(src, (int)(it & 31u), P, A, Bp);
-    const V2 s0 = mk2(ws.res[0 * (size_t)ws.cap + i], ws.res[1 * (size_t)ws.cap + i]);
-    const V2 s1 = mk2(ws.res[2 * (size_t)ws.cap + i], ws.res[3 * (size_t)ws.cap + i]);
-    const V2 s2 = mk2(ws.res[4 * (size_t)ws.cap + i], ws.res[5 * (size_t)ws.cap + i]);
-    int iters = A.n + Bp.n + 1;  // polygon_vs_polygon: min(48, nA + nB + 1), cotix/_contacts.py:295
-    if (iters > 13) iters = 13;
-    bool ecap;
-    const V2 pen = epa<16>(A, Bp, s0, s1, s2, iters, ecap);
-    const V2 cp = contact_from_edges(A, Bp);
-    ws.res[0 * (size_t)ws.cap + i] = pen.x;
-    ws.res[1 * (size_t)ws.cap + i] = pen.y;
-    ws.res[2 * (size_t)ws.cap + i] = cp.x;
-    ws.res[3 * (size_t)ws.cap + i] = cp.y;
+    const Contact c = poly_pair(A, Bp, start, P.gjk_max_iters);
+    ws.res[0 * (size_t)ws.cap + i] = c.pen.x;
+    ws.res[1 * (size_t)ws.cap + i] = c.pen.y;
+    ws.res[2 * (size_t)ws.cap + i] = c.cp.x;
+    ws.res[3 * (size_t)ws.cap + i] = c.cp.y;
+    if (!contact_isnan(c)) ++hits;
   }
+  // statistics only (scripts/exp_pipeline.py)
+  hits = __reduce_add_sync(0xFFFFFFFFu, hits);
+  if ((threadIdx.x & 31u) == 0u && hits) atomicAdd(&ws.ctr[CTR_HITS], hits);
 }
 
 // contact source of one env: the queue results in HBM (or inline after a queue overflow)
@@ -301,6 +261,31 @@ struct QueueContacts {
     }
     return inline_eval(bit);
   }
+  // pairs with a non-NaN contact; the env's items sit in consecutive queue slots
+  CX_DEV uint32_t live_bits() const {
+    uint32_t live = 0u;
+    if (base != BASE_INLINE) {
+      const float* cpx = ws.res + 2 * (size_t)ws.cap + base;
+      const float* cpy = ws.res + 3 * (size_t)ws.cap + base;
+      uint32_t todo = cand;
+      int k = 0;
+      while (todo) {
+        const int bit = __ffs(todo) - 1;
+        todo &= todo - 1u;
+        const float x = cpx[k], y = cpy[k];
+        ++k;
+        if (!((x != x) || (y != y))) live |= 1u << bit;
+      }
+    } else {
+      uint32_t todo = cand;
+      while (todo) {
+        const int bit = __ffs(todo) - 1;
+        todo &= todo - 1u;
+        if (!contact_isnan(inline_eval(bit))) live |= 1u << bit;
+      }
+    }
+    return live;
+  }
   CX_DEV bool live(int bit) const {
     if (!((cand >> bit) & 1u)) return false;
     if (base != BASE_INLINE) {
@@ -312,34 +297,167 @@ struct QueueContacts {
   }
 };
 
+// key split, joints, judge and the stores of one env whose dynamic state and meta are in E
+// (cotix_lunar_step's tail); returns true when the env must be reset (auto-reset on).
+CX_DEV bool finish_and_store(EnvRegs& E, int64_t e, float* __restrict__ s, int64_t ld,
+                             const float* __restrict__ action, float* __restrict__ reward,
+                             uint8_t* __restrict__ done, float* __restrict__ obs,
+                             const CotixLunarParams& P, bool crash, bool rc, bool lc) {
+  float am = 0.0f, as = 0.0f;
+  if (action) {
+    am = action[e];
+    as = action[ld + e];
+  }
+  float cs[3], sn[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &sn[i], &cs[i]);
+  SubInfo si;
+  finish_step(E, P, cs, sn, jclip(am, 0.0f, 1.0f), jclip(as, -1.0f, 1.0f), crash, rc, lc, si);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    s[(i * 6 + 2) * ld + e] = E.b[i].vx;
+    s[(i * 6 + 3) * ld + e] = E.b[i].vy;
+    s[(i * 6 + 5) * ld + e] = E.b[i].w;
+  }
+  store_meta(E, s, ld, e);
+  if (reward) reward[e] = si.reward;
+  if (done) done[e] = (uint8_t)si.done;
+  const bool want_reset = (si.done != COTIX_DONE_NO) && P.auto_reset;
+  if (obs && !want_reset) store_obs(E, obs, ld, e, si.rc, si.lc);
+  return want_reset;
+}
+
 // ---- K_C1 ----------------------------------------------------------------------------------
+// The coin flips dominate this stage in threefry mode (a coin = 7 threefry-2x32 calls down the
+// key chain split(gkey, N2)[ind2] -> split(., N1)[ind1] -> split(.)[0] -> bernoulli), and which
+// cells are live differs from env to env.  Per-thread loops over 7 cells ran at 6 of 32 lanes
+// (profiles/r1d_pipeline_v1.txt), so the warp pools the live cells of its 32 envs in a task
+// ring in shared memory and flips ONE coin per lane per round: a tails re-queues the task at
+// its next entry, a heads (or the end of the entries) retires it.  Every round is dense.
+struct WarpColl {
+  uint32_t gk[32][4];   // gkey[0], gkey[1] of lane's env
+  uint32_t pk[32][2];   // philox key
+  uint32_t st[32][2];   // steps, episode
+  uint32_t tmask[256];  // task ring: live mask of the cell
+  uint16_t tdesc[256];  //            env lane | cell << 5
+  uint16_t tidx[256];   //            next entry, in the scan order of cell_winner
+  int8_t win[32][8];
+};
+
+CX_DEV void coll_push(WarpColl& W, int& tail, bool pred, uint32_t desc, uint32_t mask, uint32_t t) {
+  const uint32_t m = __ballot_sync(0xFFFFFFFFu, pred);
+  if (pred) {
+    const int slot = (tail + __popc(m & lanemask_lt())) & 255;
+    W.tdesc[slot] = (uint16_t)desc;
+    W.tmask[slot] = mask;
+    W.tidx[slot] = (uint16_t)t;
+  }
+  tail += __popc(m);
+}
+
+CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParams& P) {
+  const int lane = threadIdx.x & 31;
+  __syncwarp();
+  while (head < tail) {
+    const int i = head + lane;
+    bool requeue = false;
+    uint32_t desc = 0u, mask = 0u, t = 0u;
+    if (i < tail) {
+      const int slot = i & 255;
+      desc = W.tdesc[slot];
+      mask = W.tmask[slot];
+      t = W.tidx[slot];
+      const int el = (int)(desc & 31u), c = (int)(desc >> 5);
+      const CellDesc d = cell_desc(c);
+      const int L = __popc(mask), per2 = d.reps * L, total = (d.b_hi - d.b_lo + 1) * per2;
+      const int ind2 = d.b_hi - (int)t / per2, rem = (int)t % per2;
+      const int r = d.reps - 1 - rem / L, j = rem % L;
+      const int q = (int)__fns(mask, 0u, L - j);  // live entries from the highest q down
+      const int ind1 = d.a0 + q + d.nq * r;
+      CoinCtx cc;
+      cc.mode = P.rng_mode;
+      cc.p = P.coin_p;
+      cc.gkey[0].a = W.gk[el][0]; cc.gkey[0].b = W.gk[el][1];
+      cc.gkey[1].a = W.gk[el][2]; cc.gkey[1].b = W.gk[el][3];
+      cc.pkey.a = W.pk[el][0]; cc.pkey.b = W.pk[el][1];
+      cc.steps = W.st[el][0]; cc.episode = W.st[el][1];
+      Key2 k2;
+      k2.a = k2.b = 0u;
+      if (cc.mode == COTIX_RNG_THREEFRY) k2 = tf_split(cc.gkey[d.g], (uint32_t)d.N2, (uint32_t)ind2);
+      if (coin_heads(cc, d.g, d.N1, k2, ind2, ind1)) W.win[el][c] = (int8_t)q;
+      else if ((int)t + 1 < total) requeue = true;
+    }
+    __syncwarp();
+    head = min(head + 32, tail);
+    coll_push(W, tail, requeue, desc, mask, t + 1u);
+    __syncwarp();
+  }
+}
+
 __global__ void __launch_bounds__(TPB)
-pipe_collide_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
+pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
                     const LunarDerived D, const PipeWs ws) {
+  __shared__ WarpColl Wall[TPB / 32];
+  WarpColl& W = Wall[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
   const uint32_t n = ws.ctr[CTR_CENV];
   const uint32_t stride = gridDim.x * TPB;
-  for (uint32_t c = blockIdx.x * TPB + threadIdx.x; c < n; c += stride) {
-    const uint32_t e = ws.cenv[c];
+  for (uint32_t c0 = blockIdx.x * TPB + (threadIdx.x & ~31u); c0 < n; c0 += stride) {
+    const uint32_t c = c0 + (uint32_t)lane;
+    const bool valid = c < n;
+    uint32_t e = 0u, cand = 0u, status0 = 0u;
     EnvRegs E;
-    load_dyn(E, s, ld, e);
-    E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
-    E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
-    E.steps = __float_as_uint(s[COTIX_F_STEPS * ld + e]);
-    E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
-    const uint32_t status0 = E.status;
-    const uint32_t cand = ws.cand[e] & CX_PAIR_BITS;
-    QueueContacts qc{ws, P, D, e, cand, ws.base[e]};
-    bool crash, rc, lc;
-    collide(E, P, cand, qc, crash, rc, lc);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      s[(i * 6 + 2) * ld + e] = E.b[i].vx;
-      s[(i * 6 + 3) * ld + e] = E.b[i].vy;
-      s[(i * 6 + 5) * ld + e] = E.b[i].w;
+    uint32_t m[7] = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
+    bool crash = false, rc = false, lc = false, any = false;
+    CoinCtx cc;
+    if (valid) {
+      e = ws.cenv[c];
+      cand = ws.cand[e] & CX_PAIR_BITS;
+      E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
+      E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
+      E.steps = __float_as_uint(s[COTIX_F_STEPS * ld + e]);
+      E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
+      status0 = E.status;
     }
-    if (E.status != status0) s[COTIX_F_STATUS * ld + e] = __uint_as_float(E.status);
-    ws.cand[e] = cand | F_QUEUED | ((crash ? 1u : 0u) << F_CRASH_SHIFT) | ((rc ? 1u : 0u) << F_RC_SHIFT) |
-                 ((lc ? 1u : 0u) << F_LC_SHIFT);
+    QueueContacts qc{ws, P, D, e, cand, valid ? ws.base[e] : 0u};
+    if (valid) any = cell_masks(qc.live_bits(), true, m, crash, rc, lc);
+    if (any) {
+      make_coin_ctx(E, P, cc);
+      W.gk[lane][0] = cc.gkey[0].a; W.gk[lane][1] = cc.gkey[0].b;
+      W.gk[lane][2] = cc.gkey[1].a; W.gk[lane][3] = cc.gkey[1].b;
+      W.pk[lane][0] = cc.pkey.a; W.pk[lane][1] = cc.pkey.b;
+      W.st[lane][0] = cc.steps; W.st[lane][1] = cc.episode;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) W.win[lane][k] = -1;
+    int head = 0, tail = 0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) coll_push(W, tail, m[k] != 0u, (uint32_t)lane | ((uint32_t)k << 5), m[k], 0u);
+    coll_rounds(W, head, tail, P);
+    // the self pair only matters when body 2 has another live cell
+    coll_push(W, tail, m[6] != 0u && (W.win[lane][1] >= 0 || W.win[lane][3] >= 0),
+              (uint32_t)lane | (6u << 5), m[6], 0u);
+    coll_rounds(W, head, tail, P);
+    if (valid) {
+      if (any) {
+        int win[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) win[k] = W.win[lane][k];
+        load_dyn(E, s, ld, e);  // only envs with a live contact need their bodies
+        collide_apply(E, P, qc, cc, win);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          s[(i * 6 + 2) * ld + e] = E.b[i].vx;
+          s[(i * 6 + 3) * ld + e] = E.b[i].vy;
+          s[(i * 6 + 5) * ld + e] = E.b[i].w;
+        }
+        if (E.status != status0) s[COTIX_F_STATUS * ld + e] = __uint_as_float(E.status);
+      }
+      if (crash || rc || lc)
+        ws.cand[e] = cand | ((crash ? 1u : 0u) << F_CRASH_SHIFT) | ((rc ? 1u : 0u) << F_RC_SHIFT) |
+                     ((lc ? 1u : 0u) << F_LC_SHIFT);
+    }
+    __syncwarp();
   }
 }
 
@@ -349,35 +467,14 @@ pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __
                    float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
                    const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
-  const bool valid = e < B;
   bool want_reset = false;
-  if (valid) {
+  if (e < B) {
     EnvRegs E;
     load_dyn(E, s, ld, e);
     load_meta(E, s, ld, e);
-    float am = 0.0f, as = 0.0f;
-    if (action) {
-      am = action[e];
-      as = action[ld + e];
-    }
     const uint32_t cw = ws.cand[e];
-    const bool crash = (cw >> F_CRASH_SHIFT) & 1u, rc = (cw >> F_RC_SHIFT) & 1u, lc = (cw >> F_LC_SHIFT) & 1u;
-    float cs[3], sn[3];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &sn[i], &cs[i]);
-    SubInfo si;
-    finish_step(E, P, cs, sn, jclip(am, 0.0f, 1.0f), jclip(as, -1.0f, 1.0f), crash, rc, lc, si);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      s[(i * 6 + 2) * ld + e] = E.b[i].vx;
-      s[(i * 6 + 3) * ld + e] = E.b[i].vy;
-      s[(i * 6 + 5) * ld + e] = E.b[i].w;
-    }
-    store_meta(E, s, ld, e);
-    if (reward) reward[e] = si.reward;
-    if (done) done[e] = (uint8_t)si.done;
-    want_reset = (si.done != COTIX_DONE_NO) && P.auto_reset;
-    if (obs && !want_reset) store_obs(E, obs, ld, e, si.rc, si.lc);
+    want_reset = finish_and_store(E, e, s, ld, action, reward, done, obs, P, (cw >> F_CRASH_SHIFT) & 1u,
+                                  (cw >> F_RC_SHIFT) & 1u, (cw >> F_LC_SHIFT) & 1u);
   }
   const uint32_t slot = queue_push(&ws.ctr[CTR_RESET], want_reset);
   if (want_reset) ws.renv[slot] = (uint32_t)e;
@@ -403,9 +500,10 @@ pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
 
 // optional per-stage timing (bench.py's roofline of the dominant kernel): CUDA events recorded
 // between the stages on the launching stream while profiling is enabled
+// stages: 0 integrate, 1 narrow, 2 contact, 3 finish, 4 reset, 5 whole step
 constexpr int N_STAGES = 6;
 bool g_profile = false;
-cudaEvent_t g_ev[N_STAGES + 1];
+cudaEvent_t g_evb[N_STAGES], g_eve[N_STAGES];
 bool g_ev_made = false;
 double g_stage_ms[N_STAGES];
 int64_t g_stage_steps = 0;
@@ -413,10 +511,10 @@ bool g_ev_pending = false;
 
 void profile_collect() {
   if (!g_ev_pending) return;
-  if (cudaEventSynchronize(g_ev[N_STAGES]) == cudaSuccess) {
+  if (cudaEventSynchronize(g_eve[N_STAGES - 1]) == cudaSuccess) {
     for (int k = 0; k < N_STAGES; ++k) {
       float ms = 0.0f;
-      if (cudaEventElapsedTime(&ms, g_ev[k], g_ev[k + 1]) == cudaSuccess) g_stage_ms[k] += ms;
+      if (cudaEventElapsedTime(&ms, g_evb[k], g_eve[k]) == cudaSuccess) g_stage_ms[k] += ms;
     }
     ++g_stage_steps;
   }
@@ -488,31 +586,41 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
   if (prof) {
     profile_collect();
     if (!g_ev_made) {
-      for (int k = 0; k <= N_STAGES; ++k) cudaEventCreate(&g_ev[k]);
+      for (int k = 0; k < N_STAGES; ++k) {
+        cudaEventCreate(&g_evb[k]);
+        cudaEventCreate(&g_eve[k]);
+      }
       g_ev_made = true;
     }
   }
-#define CX_STAGE_MARK(k) \
-  if (prof) cudaEventRecord(g_ev[k], st)
-  CX_STAGE_MARK(0);
+#define CX_MARK_B(k, stream) \
+  if (prof) cudaEventRecord(g_evb[k], stream)
+#define CX_MARK_E(k, stream) \
+  if (prof) cudaEventRecord(g_eve[k], stream)
+  CX_MARK_B(5, st);
+  CX_MARK_B(0, st);
   pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, sin_, sout, ld, action, *p, D, ws);
-  CX_STAGE_MARK(1);
-  pipe_gjk_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, D, ws);
-  CX_STAGE_MARK(2);
-  pipe_epa_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, D, ws);
-  CX_STAGE_MARK(3);
-  pipe_collide_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, *p, D, ws);
-  CX_STAGE_MARK(4);
+  CX_MARK_E(0, st);
+  CX_MARK_B(1, st);
+  pipe_narrow_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, D, ws);
+  CX_MARK_E(1, st);
+  CX_MARK_B(2, st);
+  pipe_contact_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, *p, D, ws);
+  CX_MARK_E(2, st);
+  CX_MARK_B(3, st);
   pipe_finish_kernel<<<env_blocks, TPB, 0, st>>>(B, sout, ld, action, reward, done, obs, *p, ws);
-  CX_STAGE_MARK(5);
+  CX_MARK_E(3, st);
+  CX_MARK_B(4, st);
   if (p->auto_reset) {
     pipe_reset_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, obs, *p, ws);
-    cx_count_launch_n(6);
-  } else {
     cx_count_launch_n(5);
+  } else {
+    cx_count_launch_n(4);
   }
-  CX_STAGE_MARK(6);
-#undef CX_STAGE_MARK
+  CX_MARK_E(4, st);
+  CX_MARK_E(5, st);
+#undef CX_MARK_B
+#undef CX_MARK_E
   if (prof) g_ev_pending = true;
   return cx_check_launch("lunar pipeline");
 }

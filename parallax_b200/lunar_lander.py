@@ -159,7 +159,7 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
     return ns, reward, done
 
 
-PIPELINE_STAGES = ("integrate", "gjk", "epa", "collide", "finish", "reset")
+PIPELINE_STAGES = ("integrate", "narrow", "contact", "finish", "reset", "step")
 
 
 def pipeline_profile(enable: bool) -> None:

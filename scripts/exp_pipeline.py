@@ -32,4 +32,23 @@ for rng_mode in (0, 1):
             torch.cuda.synchronize()
             sm, n = ll.pipeline_stage_ms()
             ll.pipeline_profile(False)
-            print("   stages us:", {k: round(v * 1e3, 1) for k, v in sm.items()}, "sum", round(sum(sm.values()) * 1e3, 1), flush=True)
+            ws = list(ll._workspaces.values())[0]
+            off = ((ws.data_ptr() + 255) & ~255) - ws.data_ptr()
+            ctr = ws[off:off + 64].view(torch.int32).cpu().numpy()
+            print("   counters: items", ctr[0], "hits", ctr[1], "contact envs", ctr[2], "resets", ctr[3], "overflow", ctr[4])
+            if "--hist" in sys.argv:
+                # layout of the workspace (csrc/lunar_pipeline.cu carve()): 256-byte aligned blocks
+                def al(x): return (x + 255) // 256 * 256
+                cap = 4 * B + 4096
+                o_ctr = 0; o_cand = al(64); o_base = o_cand + al(4 * B); o_rec = o_base + al(4 * B)
+                o_item = o_rec + al(192 * B); o_res = o_item + al(4 * cap)
+                n = int(ctr[0])
+                item = ws[off + o_item: off + o_item + 4 * n].view(torch.int32).cpu().numpy().view(np.uint32)
+                cpx = ws[off + o_res + 2 * 4 * cap: off + o_res + 2 * 4 * cap + 4 * n].view(torch.float32).cpu().numpy()
+                pid = item & 31
+                live = ~np.isnan(cpx)
+                names = {0: "rl-L", 1: "ll-L", 9: "ll-rl", 10: "ll-ll"}
+                for k in range(25):
+                    nm = names.get(k, ("g%d-L" % (k - 2)) if k <= 8 else (("g%d-rl" % (k - 11)) if k <= 17 else "g%d-ll" % (k - 18)))
+                    print(f"      pair {k:2d} {nm:6s} items {int((pid == k).sum()):7d} live {int(((pid == k) & live).sum()):7d}")
+            print("   stages us:", {k: round(v * 1e3, 1) for k, v in sm.items()}, flush=True)
