@@ -26,9 +26,11 @@
  * equinox).  The restatement is pinned by (1) the reference tests' own inputs and
  * invariants (tests/test_oracle_reference_cases.py), (2) Random123 known-answer vectors
  * for threefry, (3) golden vectors produced by executing the reference's OWN source files
- * under a numpy float32 stand-in for the jax API (oracle/jaxlite, tests/golden/).  The
- * RNG-dependent behaviour (GJK start constant, contact selection, terrain) has no test in
- * the reference: for it, "parity unpinned".
+ * under a numpy float32 stand-in for the jax API (oracle/jaxlite, oracle/gen_golden.py,
+ * tests/golden/): contacts, resolution, reset and 24-step contact-rich rollouts reproduce
+ * bit for bit, including the RNG-dependent behaviour (coin flips, choice, terrain).  Agreement
+ * with a real jax/XLA run cannot be checked here (no jax): for XLA's rounding choices the bar
+ * is the 1e-5 relative tolerance of north_star.
  *
  * Style: literal.  Every duplicated narrowphase evaluation, every coin flip and every
  * fixed-size EPA buffer of the reference is reproduced as written (set `dedupe` to memoise
