@@ -363,15 +363,11 @@ CX_DEV Contact circle_vs_aabb(const Circ& a, const Box& b) {  // :99-154
   return c;
 }
 
+// second half of circle_vs_polygon (:162-202), given the GJK simplex of a hit
 template <int MAXE>
-CX_DEV Contact circle_vs_polygon(const Circ& circle, const Poly& poly, V2 start, int gjk_max,
-                                 int epa_iters) {  // :157-202
-  V2 s0, s1, s2;
-  bool gcap, ecap;
-  Contact c = contact_none();
-  bool ex = gjk(circle, poly, start, gjk_max, s0, s1, s2, gcap);
-  if (gcap) c.status |= CX_ST_GJK_CAP;
-  if (!ex) return c;
+CX_DEV void circle_poly_finish(const Circ& circle, const Poly& poly, V2 s0, V2 s1, V2 s2, int epa_iters,
+                               Contact& c) {
+  bool ecap;
   if (epa_iters > MAXE - 3) epa_iters = MAXE - 3;
   V2 pen = epa<MAXE>(circle, poly, s0, s1, s2, epa_iters, ecap);
   if (ecap) c.status |= CX_ST_EPA_CAP;
@@ -406,6 +402,18 @@ CX_DEV Contact circle_vs_polygon(const Circ& circle, const Poly& poly, V2 start,
   if (bestd > circle.r * circle.r) cp = circle.c;
   c.pen = pen;
   c.cp = cp;
+}
+
+template <int MAXE>
+CX_DEV Contact circle_vs_polygon(const Circ& circle, const Poly& poly, V2 start, int gjk_max,
+                                 int epa_iters) {  // :157-202
+  V2 s0, s1, s2;
+  bool gcap;
+  Contact c = contact_none();
+  bool ex = gjk(circle, poly, start, gjk_max, s0, s1, s2, gcap);
+  if (gcap) c.status |= CX_ST_GJK_CAP;
+  if (!ex) return c;
+  circle_poly_finish<MAXE>(circle, poly, s0, s1, s2, epa_iters, c);
   return c;
 }
 
@@ -473,4 +481,14 @@ CX_DEV Contact convex_vs_polygon(const SA& A, const Poly& B, V2 start, int gjk_m
   if (ecap) c.status |= CX_ST_EPA_CAP;
   c.cp = contact_from_edges(A, B);
   return c;
+}
+// second half of aabb_vs_polygon / polygon_vs_polygon, given the GJK simplex of a hit
+template <class SA>
+CX_DEV void convex_poly_finish(const SA& A, const Poly& B, V2 s0, V2 s1, V2 s2, Contact& c) {
+  int iters = nverts(A) + B.n + 1;
+  if (iters > 13) iters = 13;
+  bool ecap;
+  c.pen = epa<16>(A, B, s0, s1, s2, iters, ecap);
+  if (ecap) c.status |= CX_ST_EPA_CAP;
+  c.cp = contact_from_edges(A, B);
 }

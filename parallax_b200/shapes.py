@@ -176,8 +176,27 @@ class ContactInfo:
         return ContactInfo(-self.penetration_vector, self.contact_point, self.exists, self.status)
 
 
-def narrowphase(a: ShapeBatch, b: ShapeBatch, params: _lib.NarrowParams | None = None) -> ContactInfo:
-    """One contact query per pair (a[k], b[k]) — the sweep kernel (BASELINE config 2)."""
+SWEEP_PIPELINE_MIN_PAIRS = 65536
+_sweep_ws: dict = {}
+
+
+def _sweep_workspace(device, n: int) -> torch.Tensor:
+    key = (device.index, n)
+    ws = _sweep_ws.get(key)
+    if ws is None:
+        nbytes = int(_lib.lib().cotix_narrowphase_workspace_bytes(n))
+        _sweep_ws.clear()
+        ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
+        _sweep_ws[key] = ws
+    return ws
+
+
+def narrowphase(a: ShapeBatch, b: ShapeBatch, params: _lib.NarrowParams | None = None,
+                mode: str = "auto") -> ContactInfo:
+    """One contact query per pair (a[k], b[k]) — the sweep (BASELINE config 2).
+    mode: "single" = one mixed-type kernel (cotix_narrowphase), "pipeline" = classify / GJK / EPA
+    passes over type-homogeneous queues (cotix_narrowphase_ws), "auto" = pipeline from 65536 pairs.
+    Identical results."""
     if len(a) != len(b):
         raise ValueError("shape batches differ in length")
     dev = a.device
@@ -187,10 +206,16 @@ def narrowphase(a: ShapeBatch, b: ShapeBatch, params: _lib.NarrowParams | None =
     pen = torch.empty((n, 2), dtype=torch.float32, device=dev)
     cp = torch.empty((n, 2), dtype=torch.float32, device=dev)
     status = torch.empty(n, dtype=torch.uint8, device=dev)
+    use_pipe = mode == "pipeline" or (mode == "auto" and n >= SWEEP_PIPELINE_MIN_PAIRS)
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().cotix_narrowphase(_stream_ptr(dev), n, a.recs.data_ptr(), b.recs.data_ptr(),
-                                                exists.data_ptr(), pen.data_ptr(), cp.data_ptr(),
-                                                status.data_ptr(), C.byref(params)))
+        args = (_stream_ptr(dev), n, a.recs.data_ptr(), b.recs.data_ptr(), exists.data_ptr(), pen.data_ptr(),
+                cp.data_ptr(), status.data_ptr(), C.byref(params))
+        if use_pipe and n > 0:
+            ws = _sweep_workspace(dev, n)
+            wp = (ws.data_ptr() + 255) & ~255
+            _lib.check(_lib.lib().cotix_narrowphase_ws(*args, wp, ws.numel() - (wp - ws.data_ptr())))
+        else:
+            _lib.check(_lib.lib().cotix_narrowphase(*args))
     return ContactInfo(pen, cp, exists.bool(), status)
 
 

@@ -89,13 +89,14 @@ def test_oracle_rollout_matches_reference_source(oracle, exact_trig, dedupe):
 
 # ---- GPU: the CUDA path against the reference source --------------------------------------------
 @pytest.mark.gpu
-def test_cuda_contacts_match_reference_source(cuda_lib):
+@pytest.mark.parametrize("sweep_mode", ["single", "pipeline"])
+def test_cuda_contacts_match_reference_source(cuda_lib, sweep_mode):
     from parallax_b200 import _lib, shapes as sh
 
     g = _gold("contacts.npz")
     p = _lib.default_narrow_params()
     p.init_dir[0], p.init_dir[1] = float(g["init_dir"][0]), float(g["init_dir"][1])
-    ci = sh.narrowphase(sh.from_records(g["a"]), sh.from_records(g["b"]), p)
+    ci = sh.narrowphase(sh.from_records(g["a"]), sh.from_records(g["b"]), p, mode=sweep_mode)
     _eq(ci.penetration_vector.cpu().numpy(), g["pen"], "penetration_vector")
     _eq(ci.contact_point.cpu().numpy(), g["cp"], "contact_point")
 

@@ -140,13 +140,14 @@ def test_resolve_collision(cuda_lib, oracle):
 # ------------------------------------------------------------------------------------------
 # narrowphase
 # ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("sweep_mode", ["single", "pipeline"])
 @pytest.mark.parametrize("seed,n", [(10, 200_000), (11, 50_001)])
-def test_narrowphase_bit_exact(cuda_lib, oracle, exact_trig, seed, n):
+def test_narrowphase_bit_exact(cuda_lib, oracle, exact_trig, seed, n, sweep_mode):
     from parallax_b200 import shapes as sh
 
     rng = np.random.default_rng(seed)
     a, b = random_pairs(rng, n)
-    ci = sh.narrowphase(sh.from_records(a), sh.from_records(b))
+    ci = sh.narrowphase(sh.from_records(a), sh.from_records(b), mode=sweep_mode)
     ex, pen, cp, st = oracle.narrowphase(a, b)
     _eq(ci.exists.cpu().numpy(), ex.astype(bool), "exists")
     _eq(ci.penetration_vector.cpu().numpy(), pen, "pen")
@@ -155,7 +156,8 @@ def test_narrowphase_bit_exact(cuda_lib, oracle, exact_trig, seed, n):
     assert 0.2 < ex.mean() < 0.95  # the sweep exercises both hits and misses
 
 
-def test_narrowphase_edge_cases(cuda_lib, oracle, exact_trig):
+@pytest.mark.parametrize("sweep_mode", ["single", "pipeline"])
+def test_narrowphase_edge_cases(cuda_lib, oracle, exact_trig, sweep_mode):
     from parallax_b200 import shapes as sh
 
     o = oracle
@@ -177,7 +179,7 @@ def test_narrowphase_edge_cases(cuda_lib, oracle, exact_trig):
     ]
     a = np.stack([c[0] for c in cases])
     b = np.stack([c[1] for c in cases])
-    ci = sh.narrowphase(sh.from_records(a), sh.from_records(b))
+    ci = sh.narrowphase(sh.from_records(a), sh.from_records(b), mode=sweep_mode)
     ex, pen, cp, st = o.narrowphase(a, b)
     _eq(ci.exists.cpu().numpy(), ex.astype(bool), "exists")
     _eq(ci.penetration_vector.cpu().numpy(), pen, "pen")
@@ -185,7 +187,8 @@ def test_narrowphase_edge_cases(cuda_lib, oracle, exact_trig):
     _eq(ci.status.cpu().numpy(), st, "status")
     assert st[11] & 0x80
     # empty batch
-    e = sh.narrowphase(sh.from_records(np.zeros((0, 16), np.float32)), sh.from_records(np.zeros((0, 16), np.float32)))
+    e = sh.narrowphase(sh.from_records(np.zeros((0, 16), np.float32)), sh.from_records(np.zeros((0, 16), np.float32)),
+                       mode=sweep_mode)
     assert e.exists.numel() == 0
 
 
