@@ -31,8 +31,27 @@ ALGO_BYTES_PER_ENV_STEP = 224.0   # 136 B read + 88 B written at 
 #   integrate: read 18 dyn + 12 terrain + status + 2 action words, write 12 changed words + cand
 #   finish   : read 18 dyn + 6 meta + 2 action + cand words, write 9 velocity + 6 meta words,
 #              reward (4 B) and done (1 B)
+#   narrow   : per collision item: item word + two 4-gons (2 x 32 B) read, 24-B contact written
+#   contact  : per env with a candidate contact: 18 dyn + key (8 B) + cand word read, 9 velocity
+#              words + status written; plus 24 B read per item
+#   reset    : per reset env: key read, 36 state words written
 STAGE_ALGO_BYTES = {"integrate": 4.0 * (18 + 12 + 1 + 2) + 4.0 * (12 + 1),
                     "finish": 4.0 * (18 + 6 + 2 + 1) + 4.0 * (9 + 6) + 5.0}
+
+
+def stage_algo_bytes(stage, B, ctr):
+    """Algorithmic bytes of one launch of a pipeline stage."""
+    if stage in STAGE_ALGO_BYTES:
+        return STAGE_ALGO_BYTES[stage] * B
+    if ctr is None:
+        return None
+    if stage == "narrow":
+        return (4.0 + 64.0 + 24.0) * ctr["items"]
+    if stage == "contact":
+        return (72.0 + 8.0 + 4.0 + 36.0 + 4.0) * ctr["contact_envs"] + 24.0 * ctr["items"]
+    if stage == "reset":
+        return (8.0 + 144.0) * ctr["resets"]
+    return None
 ALGO_BYTES_PER_PAIR = 148.0       # SURVEY §8(d): 2 x 64 B read + 20 B written
 L2_BYTES = 126e6
 
@@ -258,7 +277,7 @@ def run_ours(args):
     # per-stage durations (CUDA events between the stages on the launching stream), measured
     # live on a continuation of the same rollout; the dominant kernel carries the roofline
     pipeline = args.substeps == 1 and B >= ll.PIPELINE_MIN_ENVS
-    stage_ms, dom, dom_ms = None, "lunar_step_kernel", step_ms
+    stage_ms, dom, dom_ms, counters, stage_frac = None, "lunar_step_kernel", step_ms, None, None
     achieved = step_achieved
     algo_dom = ALGO_BYTES_PER_ENV_STEP
     if pipeline:
@@ -270,8 +289,12 @@ def run_ours(args):
         ll.pipeline_profile(False)
         dom = max((k for k in stage_ms if k != "step"), key=stage_ms.get)
         dom_ms = stage_ms[dom]
-        algo_dom = STAGE_ALGO_BYTES.get(dom)
-        achieved = algo_dom * B / (dom_ms * 1e-3) / 1e9 if algo_dom else None
+        counters = ll.pipeline_counters(dev)
+        launch_bytes = stage_algo_bytes(dom, B, counters)
+        algo_dom = launch_bytes / B if launch_bytes else None
+        achieved = launch_bytes / (dom_ms * 1e-3) / 1e9 if launch_bytes else None
+        stage_frac = {k: (stage_algo_bytes(k, B, counters) or 0.0) / (stage_ms[k] * 1e-3) / 1e9 / peak
+                      for k in stage_ms if k != "step" and stage_ms[k] > 0}
         dom = f"pipe_{dom}_kernel"
     line = {
         "metric": "LunarLander env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world,
@@ -287,6 +310,7 @@ def run_ours(args):
                      "frac": (achieved / peak) if achieved else None,
                      "traffic": _traffic(dom), "kernel": dom, "peak_source": peak_src,
                      "algorithmic_bytes_per_env": algo_dom, "kernel_ms": dom_ms, "stage_ms": stage_ms,
+                     "stage_frac": stage_frac, "queue_counts": counters,
                      "whole_step": {"algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
                                     "achieved": step_achieved, "frac": step_achieved / peak, "ms": step_ms}},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * 4 * B,
@@ -340,8 +364,8 @@ def sweep(args, dev, peak):
     return {"metric": "GJK+EPA pair-tests/sec", "value": n / (ms * 1e-3), "unit": "pairs/s", "pairs": n,
             "ms_per_sweep": ms, "hit_fraction": float(ci.exists.float().mean().item()),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": _traffic("narrowphase_kernel"),
-                         "kernel": "narrowphase_kernel"}}
+                         "frac": achieved / peak, "traffic": _traffic("narrowphase_sweep"),
+                         "kernel": "sweep_classify + sweep_gjk<3> + sweep_epa<3> (7 launches, whole sweep)"}}
 
 
 def cpu_baseline(args):

@@ -174,6 +174,17 @@ def pipeline_stage_ms() -> tuple[dict, int]:
     return {k: float(out[i]) for i, k in enumerate(PIPELINE_STAGES)}, n
 
 
+def pipeline_counters(device: torch.device | None = None) -> dict | None:
+    """Queue lengths of the last pipeline step on the cached workspace (measurement aid):
+    collision items, live contacts, envs with a candidate contact, auto-resets, overflow."""
+    for (idx, _B), ws in _workspaces.items():
+        if device is None or device.index in (None, idx):
+            off = ((ws.data_ptr() + 255) & ~255) - ws.data_ptr()
+            c = ws[off:off + 32].view(torch.int32).cpu().tolist()
+            return {"items": c[0], "hits": c[1], "contact_envs": c[2], "resets": c[3], "overflow": c[4]}
+    return None
+
+
 class LunarLanderEnv:
     """Vector env with HOST-facing reset/step (the `e2e` path of bench.py).
 
