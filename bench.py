@@ -259,12 +259,13 @@ def run_ours(args):
     for w in range(3):
         env.step(host_acts[w % n_act])
     barrier()
+    n1 = parallax_b200.launch_count()
     t0 = time.perf_counter()
     for k in range(e2e_steps):
         obs, rew_h, done_h = env.step(host_acts[k % n_act])
     barrier()
     e2e_s = time.perf_counter() - t0
-    e2e_launches = e2e_steps
+    e2e_launches = parallax_b200.launch_count() - n1
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
@@ -314,7 +315,8 @@ def run_ours(args):
                      "whole_step": {"algorithmic_bytes_per_env_step": ALGO_BYTES_PER_ENV_STEP,
                                     "achieved": step_achieved, "frac": step_achieved / peak, "ms": step_ms}},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * 4 * B,
-                "d2h_bytes_per_step": (8 * 4 + 4 + 1) * B, "steps": e2e_steps},
+                "d2h_bytes_per_step": (8 * 4 + 4 + 1) * B, "steps": e2e_steps,
+                "overlap": "4 env ranges: H2D(c+1) | kernels(c) | D2H(c-1) on three streams"},
         "gpu_launches": int(launches + e2e_launches),
         "clocks": clocks,
         "mean_last_reward": float(reward_sum.item()) / (world * B),

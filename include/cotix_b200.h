@@ -247,7 +247,8 @@ int64_t cotix_lunar_pipeline_stage_ms(double* out_ms /*[COTIX_PIPELINE_STAGES]*/
 /*
  * Host-facing env handle: owns the device state of B envs on `device`, keeps it
  * resident, and exposes reset/step with HOST buffers (pinned or pageable).  One step =
- * H2D(action) -> kernel -> D2H(obs, reward, done), on the handle's own stream.
+ * H2D(action) -> kernels -> D2H(obs, reward, done), software-pipelined over ranges of envs
+ * (cotix_lunar_env_set_chunks); the call returns when the host buffers are complete.
  */
 typedef struct CotixLunarEnv CotixLunarEnv;
 int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B,
@@ -258,6 +259,22 @@ int cotix_lunar_env_destroy(CotixLunarEnv* env);
 #define COTIX_MODE_FUSED 1
 #define COTIX_MODE_PIPELINE 2
 int cotix_lunar_env_set_mode(CotixLunarEnv* env, int mode);
+/*
+ * Host-step chunking: cotix_lunar_env_step_host splits the batch into `chunks` ranges of envs
+ * and runs H2D(action) of range c+1, the kernels of range c and D2H(obs, reward, done) of range
+ * c-1 concurrently (three streams, PCIe in both directions at once).  Envs are independent, so
+ * the results do not depend on `chunks`.  0 = automatic (ranges of >= 256K envs, at most 4:
+ * each range pays the fixed latency of the kernels, about 0.1 ms).
+ */
+#define COTIX_MAX_CHUNKS 16
+int cotix_lunar_env_set_chunks(CotixLunarEnv* env, int chunks);
+/*
+ * Optional (default off): when every host buffer of a chunked step is page-locked, the whole
+ * step (copies on three streams + kernels) is captured once per set of buffers and replayed as
+ * ONE CUDA graph — one driver call per step instead of ~50; with pageable buffers the same work
+ * is enqueued call by call.
+ */
+int cotix_lunar_env_set_host_graphs(CotixLunarEnv* env, int enable);
 int cotix_lunar_env_reset_host(CotixLunarEnv* env, const uint32_t* keys /*[B][2]*/);
 int cotix_lunar_env_step_host(CotixLunarEnv* env, const float* action /*[2][B]*/,
                               float* obs /*[8][B]*/, float* reward /*[B]*/,

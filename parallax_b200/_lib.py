@@ -130,7 +130,7 @@ EXPORTS = [
     "cotix_narrowphase", "cotix_narrowphase_host", "cotix_order_clockwise",
     "cotix_narrowphase_workspace_bytes", "cotix_narrowphase_ws",
     "cotix_lunar_default_params", "cotix_lunar_reset", "cotix_lunar_step",
-    "cotix_lunar_workspace_bytes", "cotix_lunar_step_ws", "cotix_lunar_env_set_mode",
+    "cotix_lunar_workspace_bytes", "cotix_lunar_step_ws", "cotix_lunar_env_set_mode", "cotix_lunar_env_set_chunks", "cotix_lunar_env_set_host_graphs",
     "cotix_lunar_pipeline_profile", "cotix_lunar_pipeline_stage_ms",
     "cotix_lunar_env_create", "cotix_lunar_env_destroy", "cotix_lunar_env_reset_host",
     "cotix_lunar_env_step_host", "cotix_lunar_env_get_state_host",
@@ -172,6 +172,8 @@ def lib() -> C.CDLL:
     L.cotix_lunar_workspace_bytes.argtypes = [i64]
     L.cotix_lunar_step_ws.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams), vp, i64]
     L.cotix_lunar_env_set_mode.argtypes = [vp, C.c_int]
+    L.cotix_lunar_env_set_chunks.argtypes = [vp, C.c_int]
+    L.cotix_lunar_env_set_host_graphs.argtypes = [vp, C.c_int]
     L.cotix_lunar_pipeline_profile.argtypes = [C.c_int]
     L.cotix_lunar_pipeline_stage_ms.restype = C.c_int64
     L.cotix_lunar_pipeline_stage_ms.argtypes = [C.POINTER(C.c_double)]

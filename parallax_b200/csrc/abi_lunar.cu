@@ -2,9 +2,11 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <limits>
 #include <map>
 #include <new>
+#include <vector>
 
 #include "../../include/cotix_b200.h"
 #include "cx_launch.cuh"
@@ -17,6 +19,7 @@ extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, flo
 
 extern "C" int64_t cx_lunar_pipeline_workspace_bytes(int64_t B);
 extern "C" int cx_lunar_pipeline_profile(int enable);
+extern "C" int cx_lunar_pipeline_profiling();
 extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
 extern "C" int cx_launch_lunar_pipeline(cudaStream_t, int64_t, const float*, float*, int64_t, const float*,
                                         float*, uint8_t*, float*, const CotixLunarParams*, void*, int64_t);
@@ -265,6 +268,19 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
 }
 
 // ---- host-facing env handle ---------------------------------------------------------
+struct HostGraph {  // one captured host step, keyed by the host buffers it copies from / to
+  const float* action;
+  float* obs;
+  float* reward;
+  uint8_t* done;
+  int chunks, mode;
+  cudaGraphExec_t exec;
+  int64_t launches;
+};
+
+struct CotixLunarEnv;
+static void drop_host_graphs(CotixLunarEnv* e);
+
 struct CotixLunarEnv {
   int mode;
   void* ws;
@@ -282,6 +298,11 @@ struct CotixLunarEnv {
   std::map<int, cudaGraphExec_t>* graphs;
   const float* graph_action;
   int64_t graph_launches;  // kernels per step in the captured graphs
+  int chunks;              // host-step ranges; 0 = automatic
+  int host_graphs;         // replay the pipelined host step as a CUDA graph when the buffers are pinned
+  cudaStream_t s_in, s_out;
+  cudaEvent_t ev_in[COTIX_MAX_CHUNKS], ev_done[COTIX_MAX_CHUNKS], ev_fork, ev_join[2];
+  std::vector<HostGraph>* hgraphs;
 };
 
 int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B, const CotixLunarParams* p) {
@@ -304,6 +325,17 @@ int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B, const Cot
   e->P = *p;
   e->graphs = new std::map<int, cudaGraphExec_t>();
   CXL_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  CXL_CUDA(cudaStreamCreateWithFlags(&e->s_in, cudaStreamNonBlocking));
+  CXL_CUDA(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
+  for (int c = 0; c < COTIX_MAX_CHUNKS; ++c) {
+    CXL_CUDA(cudaEventCreateWithFlags(&e->ev_in[c], cudaEventDisableTiming));
+    CXL_CUDA(cudaEventCreateWithFlags(&e->ev_done[c], cudaEventDisableTiming));
+  }
+  CXL_CUDA(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+  CXL_CUDA(cudaEventCreateWithFlags(&e->ev_join[0], cudaEventDisableTiming));
+  CXL_CUDA(cudaEventCreateWithFlags(&e->ev_join[1], cudaEventDisableTiming));
+  e->hgraphs = new std::vector<HostGraph>();
+  e->host_graphs = 0;
   CXL_CUDA(cudaMalloc(&e->state, sizeof(float) * COTIX_LUNAR_NF * (size_t)B));
   CXL_CUDA(cudaMalloc(&e->action, sizeof(float) * 2 * (size_t)B));
   CXL_CUDA(cudaMalloc(&e->obs, sizeof(float) * COTIX_LUNAR_NOBS * (size_t)B));
@@ -334,6 +366,17 @@ int cotix_lunar_env_destroy(CotixLunarEnv* e) {
   cudaFree(e->done);
   cudaFree(e->keys);
   cudaFree(e->ws);
+  for (int c = 0; c < COTIX_MAX_CHUNKS; ++c) {
+    cudaEventDestroy(e->ev_in[c]);
+    cudaEventDestroy(e->ev_done[c]);
+  }
+  cudaEventDestroy(e->ev_fork);
+  cudaEventDestroy(e->ev_join[0]);
+  cudaEventDestroy(e->ev_join[1]);
+  drop_host_graphs(e);
+  delete e->hgraphs;
+  cudaStreamDestroy(e->s_in);
+  cudaStreamDestroy(e->s_out);
   cudaStreamDestroy(e->stream);
   delete e;
   return COTIX_OK;
@@ -351,15 +394,45 @@ int cotix_lunar_env_set_mode(CotixLunarEnv* e, int mode) {
   return COTIX_OK;
 }
 
-// one step of the resident state on the handle's stream, by the handle's launch strategy
-static int env_enqueue_step(CotixLunarEnv* e, const float* action_dev, float* obs_dev) {
+int cotix_lunar_env_set_chunks(CotixLunarEnv* e, int chunks) {
+  CXL_REQUIRE(e != nullptr, "env is null");
+  CXL_REQUIRE(chunks >= 0 && chunks <= COTIX_MAX_CHUNKS, "chunks out of range");
+  if (chunks != e->chunks) drop_host_graphs(e);
+  e->chunks = chunks;
+  return COTIX_OK;
+}
+
+// one step of envs [off, off + n) of the resident state on the handle's stream, by the handle's
+// launch strategy (the strategy is chosen on the whole batch so that it does not vary with the
+// chunking)
+static int env_enqueue_range(CotixLunarEnv* e, int64_t off, int64_t n, const float* action_dev,
+                             float* obs_dev) {
+  cudaStream_t stream = e->stream;
   const bool pipe = e->mode == COTIX_MODE_PIPELINE ||
                     (e->mode == COTIX_MODE_AUTO && e->P.substeps == 1 && e->B >= 16384);
+  float* st = e->state + off;
+  const float* act = action_dev ? action_dev + off : nullptr;
+  float* ob = obs_dev ? obs_dev + off : nullptr;
   if (pipe)
-    return cx_launch_lunar_pipeline(e->stream, e->B, e->state, e->state, e->B, action_dev, e->reward,
-                                    e->done, obs_dev, &e->P, e->ws, e->ws_bytes);
-  return cx_launch_lunar_step(e->stream, e->B, e->state, e->state, e->B, action_dev, e->reward, e->done,
-                              obs_dev, &e->P);
+    return cx_launch_lunar_pipeline(stream, n, st, st, e->B, act, e->reward + off, e->done + off, ob,
+                                    &e->P, e->ws, e->ws_bytes);
+  return cx_launch_lunar_step(stream, n, st, st, e->B, act, e->reward + off, e->done + off, ob, &e->P);
+}
+static int env_enqueue_step(CotixLunarEnv* e, const float* action_dev, float* obs_dev) {
+  return env_enqueue_range(e, 0, e->B, action_dev, obs_dev);
+}
+// number of env ranges of a host step and their length (a multiple of 32 envs = 128 bytes)
+static int plan_chunks(const CotixLunarEnv* e, int64_t* len) {
+  int64_t C = e->chunks;
+  if (C == 0) {
+    C = e->B / 262144;
+    if (C > 4) C = 4;
+  }
+  if (C < 1) C = 1;
+  int64_t L = (e->B + C - 1) / C;
+  L = (L + 31) / 32 * 32;
+  *len = L;
+  return (int)((e->B + L - 1) / L);
 }
 
 int cotix_lunar_env_reset_host(CotixLunarEnv* e, const uint32_t* keys) {
@@ -373,21 +446,163 @@ int cotix_lunar_env_reset_host(CotixLunarEnv* e, const uint32_t* keys) {
   return COTIX_OK;
 }
 
+// enqueue one host step as a software pipeline over C env ranges: s_in copies actions in, the
+// handle's stream computes, s_out copies the results out; [rows][B] host arrays are copied as
+// 2-D blocks of pitch B.  With `forkjoin` the side streams are forked from and joined back into
+// the handle's stream (what stream capture needs).
+// COTIX_TRACE=<step>: print the device timeline of that host step (un-graphed path) to stderr
+static cudaEvent_t g_tr[4][COTIX_MAX_CHUNKS], g_tr_base;
+static int g_tr_state = -1, g_tr_step = 0;  // -1 unknown, 0 off, 1 armed
+static bool trace_armed() {
+  if (g_tr_state < 0) {
+    const char* v = getenv("COTIX_TRACE");
+    g_tr_state = v ? 1 : 0;
+    if (v) {
+      g_tr_step = atoi(v);
+      cudaEventCreate(&g_tr_base);
+      for (int i = 0; i < 4; ++i)
+        for (int c = 0; c < COTIX_MAX_CHUNKS; ++c) cudaEventCreate(&g_tr[i][c]);
+    }
+  }
+  return g_tr_state == 1;
+}
+static void trace_print(int C) {
+  fprintf(stderr, "[cotix trace] range: h2d done | compute start..end | d2h done  (ms)\n");
+  for (int c = 0; c < C; ++c) {
+    float t[4];
+    for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&t[i], g_tr_base, g_tr[i][c]);
+    fprintf(stderr, "[cotix trace] %2d: %.3f | %.3f .. %.3f | %.3f\n", c, t[0], t[1], t[2], t[3]);
+  }
+}
+
+static int enqueue_chunked(CotixLunarEnv* e, int C, int64_t len, const float* action, float* obs,
+                           float* reward, uint8_t* done, bool forkjoin, bool trace = false) {
+  const size_t pitch = sizeof(float) * (size_t)e->B;
+  if (trace) cudaEventRecord(g_tr_base, e->s_in);
+  if (forkjoin) {
+    CXL_CUDA(cudaEventRecord(e->ev_fork, e->stream));
+    CXL_CUDA(cudaStreamWaitEvent(e->s_in, e->ev_fork, 0));
+    CXL_CUDA(cudaStreamWaitEvent(e->s_out, e->ev_fork, 0));
+  }
+  for (int c = 0; c < C; ++c) {
+    const int64_t off = (int64_t)c * len;
+    const int64_t n = (off + len <= e->B) ? len : e->B - off;
+    if (action) {
+      CXL_CUDA(cudaMemcpy2DAsync(e->action + off, pitch, action + off, pitch, sizeof(float) * (size_t)n, 2,
+                                 cudaMemcpyHostToDevice, e->s_in));
+      CXL_CUDA(cudaEventRecord(e->ev_in[c], e->s_in));
+      CXL_CUDA(cudaStreamWaitEvent(e->stream, e->ev_in[c], 0));
+    }
+    if (trace) {
+      cudaEventRecord(g_tr[0][c], e->s_in);
+      cudaEventRecord(g_tr[1][c], e->stream);
+    }
+    int rc = env_enqueue_range(e, off, n, action ? e->action : nullptr, obs ? e->obs : nullptr);
+    if (rc) return rc;
+    if (trace) cudaEventRecord(g_tr[2][c], e->stream);
+    CXL_CUDA(cudaEventRecord(e->ev_done[c], e->stream));
+    CXL_CUDA(cudaStreamWaitEvent(e->s_out, e->ev_done[c], 0));
+    if (obs)
+      CXL_CUDA(cudaMemcpy2DAsync(obs + off, pitch, e->obs + off, pitch, sizeof(float) * (size_t)n,
+                                 COTIX_LUNAR_NOBS, cudaMemcpyDeviceToHost, e->s_out));
+    if (reward)
+      CXL_CUDA(cudaMemcpyAsync(reward + off, e->reward + off, sizeof(float) * (size_t)n,
+                               cudaMemcpyDeviceToHost, e->s_out));
+    if (done)
+      CXL_CUDA(cudaMemcpyAsync(done + off, e->done + off, (size_t)n, cudaMemcpyDeviceToHost, e->s_out));
+    if (trace) cudaEventRecord(g_tr[3][c], e->s_out);
+  }
+  if (forkjoin) {
+    CXL_CUDA(cudaEventRecord(e->ev_join[0], e->s_in));
+    CXL_CUDA(cudaEventRecord(e->ev_join[1], e->s_out));
+    CXL_CUDA(cudaStreamWaitEvent(e->stream, e->ev_join[0], 0));
+    CXL_CUDA(cudaStreamWaitEvent(e->stream, e->ev_join[1], 0));
+  }
+  return COTIX_OK;
+}
+
+// page-locked host memory (or NULL): what a captured copy node needs
+static bool host_pinned(const void* p) {
+  if (!p) return true;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+static void drop_host_graphs(CotixLunarEnv* e) {
+  if (!e->hgraphs) return;
+  for (auto& g : *e->hgraphs) cudaGraphExecDestroy(g.exec);
+  e->hgraphs->clear();
+}
+
 int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs, float* reward,
                               uint8_t* done) {
   CXL_REQUIRE(e != nullptr, "env is null");
   CXL_CUDA(cudaSetDevice(e->device));
   const size_t B = (size_t)e->B;
-  if (action)
-    CXL_CUDA(cudaMemcpyAsync(e->action, action, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, e->stream));
-  int rc = env_enqueue_step(e, action ? e->action : nullptr, obs ? e->obs : nullptr);
-  if (rc) return rc;
-  if (obs)
-    CXL_CUDA(cudaMemcpyAsync(obs, e->obs, sizeof(float) * COTIX_LUNAR_NOBS * B, cudaMemcpyDeviceToHost, e->stream));
-  if (reward)
-    CXL_CUDA(cudaMemcpyAsync(reward, e->reward, sizeof(float) * B, cudaMemcpyDeviceToHost, e->stream));
-  if (done) CXL_CUDA(cudaMemcpyAsync(done, e->done, B, cudaMemcpyDeviceToHost, e->stream));
+  int64_t len = 0;
+  const int C = plan_chunks(e, &len);
+  if (C == 1) {
+    if (action)
+      CXL_CUDA(cudaMemcpyAsync(e->action, action, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, e->stream));
+    int rc = env_enqueue_step(e, action ? e->action : nullptr, obs ? e->obs : nullptr);
+    if (rc) return rc;
+    if (obs)
+      CXL_CUDA(cudaMemcpyAsync(obs, e->obs, sizeof(float) * COTIX_LUNAR_NOBS * B, cudaMemcpyDeviceToHost, e->stream));
+    if (reward)
+      CXL_CUDA(cudaMemcpyAsync(reward, e->reward, sizeof(float) * B, cudaMemcpyDeviceToHost, e->stream));
+    if (done) CXL_CUDA(cudaMemcpyAsync(done, e->done, B, cudaMemcpyDeviceToHost, e->stream));
+    CXL_CUDA(cudaStreamSynchronize(e->stream));
+    return COTIX_OK;
+  }
+  const bool graphable = e->host_graphs && !cx_lunar_pipeline_profiling() && host_pinned(action) &&
+                         host_pinned(obs) && host_pinned(reward) && host_pinned(done);
+  if (!graphable) {
+    const bool trace = trace_armed() && (g_tr_step-- == 0);
+    int rc = enqueue_chunked(e, C, len, action, obs, reward, done, false, trace);
+    if (rc) return rc;
+    CXL_CUDA(cudaStreamSynchronize(e->s_out));
+    CXL_CUDA(cudaStreamSynchronize(e->stream));
+    if (trace) trace_print(C);
+    return COTIX_OK;
+  }
+  // the whole pipelined step as one replayed CUDA graph, cached per set of host buffers (an RL
+  // loop passes the same few pinned buffers every step)
+  HostGraph* hit = nullptr;
+  for (auto& g : *e->hgraphs)
+    if (g.action == action && g.obs == obs && g.reward == reward && g.done == done && g.chunks == C &&
+        g.mode == e->mode)
+      hit = &g;
+  if (!hit) {
+    if (e->hgraphs->size() >= 8) drop_host_graphs(e);
+    cudaGraph_t g;
+    CXL_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+    const int64_t before = cotix_launch_count();
+    int rc = enqueue_chunked(e, C, len, action, obs, reward, done, true);
+    cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+    const int64_t captured = cotix_launch_count() - before;
+    cx_count_launch_n(-captured);  // captured, not executed
+    if (rc) return rc;
+    CXL_CUDA(ce);
+    HostGraph hg{action, obs, reward, done, C, e->mode, nullptr, captured};
+    CXL_CUDA(cudaGraphInstantiate(&hg.exec, g, 0));
+    cudaGraphDestroy(g);
+    e->hgraphs->push_back(hg);
+    hit = &e->hgraphs->back();
+  }
+  CXL_CUDA(cudaGraphLaunch(hit->exec, e->stream));
+  cx_count_launch_n(hit->launches);
   CXL_CUDA(cudaStreamSynchronize(e->stream));
+  return COTIX_OK;
+}
+
+int cotix_lunar_env_set_host_graphs(CotixLunarEnv* e, int enable) {
+  CXL_REQUIRE(e != nullptr, "env is null");
+  e->host_graphs = enable ? 1 : 0;
+  if (!enable) drop_host_graphs(e);
   return COTIX_OK;
 }
 

@@ -626,6 +626,7 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
 }
 
 // ---- per-stage timing (single-threaded use: bench.py) ----------------------------------------
+extern "C" int cx_lunar_pipeline_profiling() { return g_profile ? 1 : 0; }
 extern "C" int cx_lunar_pipeline_profile(int enable) {
   if (!enable) profile_collect();
   g_profile = enable != 0;

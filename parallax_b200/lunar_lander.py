@@ -189,7 +189,8 @@ class LunarLanderEnv:
     """Vector env with HOST-facing reset/step (the `e2e` path of bench.py).
 
     Owns the device state of B envs through the C handle (`cotix_lunar_env_*`): each
-    `step(action_host)` is H2D(action) -> fused kernel -> D2H(obs, reward, done).
+    `step(action_host)` is H2D(action) -> kernels -> D2H(obs, reward, done), overlapped over
+    ranges of envs (`set_chunks`).
     """
 
     def __init__(self, num_envs: int, params: LunarParams | None = None, device: int = 0):
@@ -216,6 +217,14 @@ class LunarLanderEnv:
     def set_mode(self, mode: str) -> None:
         """"auto" | "fused" | "pipeline" (see `step`)."""
         _lib.check(_lib.lib().cotix_lunar_env_set_mode(self._h, _MODES[mode]))
+
+    def set_chunks(self, chunks: int) -> None:
+        """Env ranges a host step is software-pipelined over (0 = automatic, 1 = no overlap)."""
+        _lib.check(_lib.lib().cotix_lunar_env_set_chunks(self._h, int(chunks)))
+
+    def set_host_graphs(self, enable: bool) -> None:
+        """Replay the chunked host step as one CUDA graph when all host buffers are pinned."""
+        _lib.check(_lib.lib().cotix_lunar_env_set_host_graphs(self._h, 1 if enable else 0))
 
     def reset(self, keys) -> None:
         k = np.ascontiguousarray(np.asarray(keys).astype(np.uint32)).reshape(self.B, 2)

@@ -395,6 +395,35 @@ def test_lunar_host_env_and_graph(cuda_lib, oracle, exact_trig, mode):
     env.close()
 
 
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("chunks", [3, 16])
+def test_lunar_host_env_chunked_overlap(cuda_lib, oracle, exact_trig, mode, chunks):
+    """The software-pipelined host step (ranges of envs on three streams) gives the oracle's
+    observations, rewards, dones and state; ragged last range (B is not a multiple of 32)."""
+    import torch
+    from parallax_b200 import lunar_lander as ll
+
+    P = ll.default_params(judge_enabled=1, auto_reset=1, reset_perturb=1, max_episode_steps=16)
+    B = 1000 + 7
+    env = ll.LunarLanderEnv(B, P)
+    env.set_mode(mode)
+    env.set_chunks(chunks)
+    env.set_host_graphs(chunks == 3)  # odd steps pass pinned actions: those replay a captured graph
+    keys = lunar_keys(B, offset=11)
+    env.reset(keys)
+    ref = oracle.lunar_reset(keys, P)
+    rng = np.random.default_rng(71)
+    for t in range(24):
+        act = rng.uniform(-1, 1, size=(2, B)).astype(np.float32)
+        obs, rew, done = env.step(torch.from_numpy(act).pin_memory() if t % 2 else act)
+        ref, orew, odone, oobs = oracle.lunar_step(ref, act, P, want_obs=True)
+        _eq(obs.numpy(), oobs, f"obs {t}"); _eq(rew.numpy(), orew, f"rew {t}"); _eq(done.numpy(), odone, f"done {t}")
+    _eq(env.get_state(), ref, "state after chunked host steps")
+    with pytest.raises(Exception):
+        env.set_chunks(17)
+    env.close()
+
+
 def test_lunar_libm_oracle_tolerance(cuda_lib, oracle):
     """Against the oracle with libm trig (the independent definition): one step from IDENTICAL
     input states agrees within 1e-5 relative (north_star), flags identical."""
