@@ -294,6 +294,53 @@ int cotix_lunar_env_rollout_graph(CotixLunarEnv* env, int32_t n_steps,
                                   const float* action_dev);
 
 /* ------------------------------------------------------------------------------------ */
+/* Generic scene step (K2): bodies with circle / AABB / polygon parts, e.g. the RoboCup     */
+/* scene of cotix/_robocup.py:14-130.  One call = ExplicitEulerPhysics.step                 */
+/* (cotix/_physics_solvers.py:16-33) + RandomizedCollider.resolve                           */
+/* (cotix/_colliders.py:74-351) (+ key, _ = split(key), examples/test_viz.py:39) for B envs */
+/* that share the static description and differ in their dynamic state and key.             */
+/* ------------------------------------------------------------------------------------ */
+#define COTIX_SCENE_MAX_BODIES 20
+#define COTIX_SCENE_MAX_PARTS 28
+#define COTIX_SCENE_MAX_PAIRS 254    /* distinct (part, part) evaluations with body_i >= body_j */
+#define COTIX_SCENE_MAX_ENTRIES 256  /* part pairs over all groups (sum of n_g)                  */
+typedef struct CotixScene CotixScene;
+typedef struct CotixSceneParams {
+  float dt;                /* 1e-2 */
+  float init_dir[2];       /* random_direction(PRNGKey(1)), cotix/_collisions.py:287-298 */
+  int32_t gjk_max_iters;   /* 32 */
+  float coin_p;            /* 0.5, cotix/_colliders.py:222-224 */
+  float baumgarte;         /* 0.3 */
+  float baumgarte_dt;      /* 0.01 */
+  int32_t advance_key;     /* 1: keys <- split(key)[0] after the step */
+} CotixSceneParams;
+void cotix_scene_default_params(CotixSceneParams* p);
+/*
+ * Static analysis of a scene (host) and its upload to `device` (device < 0: host analysis only,
+ * for cotix_scene_info).  body_props [nb][4] = mass, inertia, elasticity, friction_coefficient
+ * (cotix/_bodies.py:189-206; inf mass = static); part_body[nparts] = owning body, parts of a
+ * body in the order of its UniversalShape; part_recs [nparts][16] = LOCAL shape records.  Fails
+ * with COTIX_EINVAL where the reference raises: a pair of part types that is not a key of
+ * _contact_funcs in (higher body index, lower body index) order (cotix/_colliders.py:99-111).
+ */
+int cotix_scene_create(CotixScene** out, int device, int32_t nb, const float* body_props,
+                       int32_t nparts, const int32_t* part_body, const float* part_recs);
+int cotix_scene_destroy(CotixScene* scene);
+/* groups (type pairs in first-appearance order), distinct evaluations per step, and the
+ * sum of n_g^2 evaluations the reference's vmap-squared makes (cotix/_colliders.py:149-173) */
+int cotix_scene_info(const CotixScene* scene, int32_t* n_groups, int32_t* n_pairs,
+                     int64_t* n_reference_evals, int32_t* group_sizes /*[<= 9] or NULL*/);
+/*
+ * state [nb * 6][ld] (DEVICE, in place): px, py, vx, vy, angle, angular_velocity of body b at
+ * rows 6b .. 6b+5; keys [2][ld] uint32 (DEVICE); optional outputs: cell [nb * nb][ld] (live
+ * cells of all_contacts after the coin flips), chosen [nb][ld] (contact_index per body),
+ * status [ld] (COTIX_ST_* bits).  Enqueues one kernel on `stream`; never syncs or allocates.
+ */
+int cotix_scene_step(void* stream, const CotixScene* scene, int64_t B, float* state, int64_t ld,
+                     uint32_t* keys, const CotixSceneParams* p, uint8_t* cell, int32_t* chosen,
+                     uint32_t* status);
+
+/* ------------------------------------------------------------------------------------ */
 /* Small primitives exposed for parity tests of the reference's leaf functions.           */
 /* ------------------------------------------------------------------------------------ */
 /* ExplicitEulerPhysics._single_body_step, cotix/_physics_solvers.py:17-24; arrays [n]    */

@@ -906,9 +906,9 @@ bool in_contact_funcs(int t1, int t2) {
 struct ColliderOut {
   int error;               // 1: illegal shape pair (RuntimeError in the reference)
   unsigned status;         // OR of narrowphase status bits
-  bool cell[8][8];         // all_contacts[i][j] non-NaN after the coin flips
-  bool candidate[8][8];    // some part pair of (i, j) produced a non-NaN contact
-  int chosen[8];           // contact_index per body
+  bool cell[COTIX_SCENE_MAX_BODIES][COTIX_SCENE_MAX_BODIES];       // all_contacts[i][j] non-NaN after the coin flips
+  bool candidate[COTIX_SCENE_MAX_BODIES][COTIX_SCENE_MAX_BODIES];  // some part pair of (i, j) gave a non-NaN contact
+  int chosen[COTIX_SCENE_MAX_BODIES];                              // contact_index per body
 };
 
 // RandomizedCollider.resolve — _colliders.py:74-351.  Canonical order = insertion order
@@ -1820,8 +1820,9 @@ int oracle_lunar_collider_debug(int64_t B, const float* state, int64_t ld,
 int oracle_scene_step(int nb, float* bodies10, int nparts, const int32_t* part_body,
                       const float* part_recs, uint32_t k0, uint32_t k1, float dt,
                       const float* init_dir, int gjk_max, float coin_p, float baumgarte,
-                      float baumgarte_dt, int dedupe, uint8_t* cell, int32_t* chosen) {
-  if (nb > 8) return -1;
+                      float baumgarte_dt, int dedupe, uint8_t* cell, int32_t* chosen,
+                      uint32_t* status) {
+  if (nb > COTIX_SCENE_MAX_BODIES) return -1;
   std::vector<Body> bodies((size_t)nb);
   for (int b = 0; b < nb; ++b) {
     float* s = bodies10 + 10 * b;
@@ -1862,6 +1863,7 @@ int oracle_scene_step(int nb, float* bodies10, int nparts, const int32_t* part_b
       for (int j = 0; j < nb; ++j) cell[i * nb + j] = co.cell[i][j];
   if (chosen)
     for (int i = 0; i < nb; ++i) chosen[i] = co.chosen[i];
+  if (status) *status = co.status;
   return 0;
 }
 

@@ -7,14 +7,17 @@ API (the real jax cannot be installed here: no network).  Run in the build conta
 
 What is executed: cotix/_contacts.py (all six contact functions), cotix/_collisions.py (GJK, EPA),
 cotix/_collision_resolution.py, cotix/_lunar_lander.py (constructor = reset, step = joints),
-cotix/_physics_solvers.py, cotix/_colliders.py (RandomizedCollider.resolve) and the composed
-step of examples/test_viz.py:25-44.
+cotix/_physics_solvers.py, cotix/_colliders.py (RandomizedCollider.resolve), the composed
+step of examples/test_viz.py:25-44, and cotix/_robocup.py (RoboCupEnv) with cotix/_bodies.py
+(AnyBody) and cotix/_universal_shape.py.
 
 Two harness choices, both documented in SURVEY A.6 / DESIGN.md §5:
   * `list(set(...))` at cotix/_colliders.py:116-120 hashes tracers by identity, so it removes
     nothing and leaves an order that differs from process to process; here `set` is bound to an
     order-preserving identity inside that module (canonical order = insertion order);
-  * sin / cos / arctan2 are the engine's cx_trig.h definitions (oracle trig mode 1).
+  * sin / cos / arctan2 are the engine's cx_trig.h definitions (oracle trig mode 1);
+  * RoboCup only: after showing that the shipped scene raises on its first step, `eqx.error_if`
+    is switched to record-and-continue (the engine's status-bit semantics).
 """
 import os
 import sys
@@ -225,8 +228,100 @@ def gen_rollout(n_env=6, steps=24, seed=11):
     np.savez_compressed(os.path.join(GOLD, "lunar_rollout.npz"), keys=keys, state0=s0, traj=traj, keytraj=keytraj)
 
 
+# ---------------------------------------------------------------------------------------------
+def rec_of_shape(p):
+    """Local shape record (include/cotix_b200.h) of a reference Circle / AABB / polygon part."""
+    r = np.zeros(16, np.float32)
+    if isinstance(p, Circle):
+        r[0], r[2] = 0, f32(p.radius)
+        r[4:6] = f32(p.position)
+    elif isinstance(p, AABB):
+        r[0] = 1
+        r[4:6], r[6:8] = f32(p.lower), f32(p.upper)
+    else:
+        v = f32(p.vertices)
+        r[0], r[1] = 2, v.shape[0]
+        r[4:4 + 2 * v.shape[0]] = v.reshape(-1)
+    return r
+
+
+def scene_arrays(bodies):
+    props = np.array([[f32(b.mass), f32(b.inertia), f32(b.elasticity), f32(b.friction_coefficient)]
+                      for b in bodies], np.float32)
+    part_body, recs = [], []
+    for i, b in enumerate(bodies):
+        for p in b.shape.parts:
+            part_body.append(i)
+            recs.append(rec_of_shape(p))
+    return props, np.array(part_body, np.int32), np.stack(recs)
+
+
+def state6(bodies):
+    return np.array([[*f32(b.position), *f32(b.velocity), f32(b.angle), f32(b.angular_velocity)]
+                     for b in bodies], np.float32)
+
+
+def roll_scene(bodies, key, steps):
+    """physics.step -> collider.resolve -> key split, the loop of examples/test_viz.py:25-44
+    without the lander-specific lines."""
+    physics = ExplicitEulerPhysics()
+    collider = ref_colliders.RandomizedCollider()
+    traj = [state6(bodies)]
+    keys = [np.asarray(key, np.uint32)]
+    errs = []
+    for t in range(steps):
+        n0 = len(eqx.ERROR_LOG)
+        bodies, _ = physics.step(bodies, dt=1e-2)
+        bodies = collider.resolve(bodies, key)
+        key, _n = jr.split(key)
+        traj.append(state6(bodies))
+        keys.append(np.asarray(key, np.uint32))
+        errs.append(len(eqx.ERROR_LOG) > n0)
+    return np.stack(traj), np.stack(keys), np.array(errs)
+
+
+def gen_robocup(steps=30):
+    """(1) RoboCupEnv() exactly as shipped (cotix/_robocup.py:14-130) for 3 steps — the static
+    AABBs overlap and the scene goes NaN, which is the reference's behaviour; (2) the goals, the
+    ball and two circular robots built with the reference's own classes, ball driven into the
+    yellow goal, robots into each other and into the ball."""
+    from cotix._robocup import RoboCupEnv
+    from cotix._universal_shape import UniversalShape
+
+    t0 = time.time()
+    env = RoboCupEnv()
+    bodies = list(env.bodies)
+    out = {}
+    out["a_props"], out["a_part_body"], out["a_recs"] = scene_arrays(bodies)
+    # as shipped, the first step already trips eqx.error_if at cotix/_contacts.py:105-107 (the
+    # closest point bc + clip(c - bc) rounds one ulp outside a thin goal box): the reference raises
+    try:
+        roll_scene(bodies, jnp.array(np.array([0, 5], np.uint32)), 1)
+        out["a_raises"] = np.array(False)
+    except RuntimeError as ex:
+        out["a_raises"] = np.array(True)
+        print("as shipped, step 1 raises:", ex)
+    # from here on error_if records and lets the value through (the engine reports COTIX_ST_CCP_ERR)
+    eqx.ERROR_MODE = "record"
+    out["a_traj"], out["a_keys"], out["a_err"] = roll_scene(bodies, jnp.array(np.array([0, 5], np.uint32)), 3)
+    print(f"robocup as shipped: 3 steps, {time.time() - t0:.0f}s", flush=True)
+
+    def robot(x, y, vx, vy, w):
+        return AnyBody(shape=UniversalShape(Circle(position=jnp.zeros((2,)), radius=jnp.array(0.09))),
+                       mass=jnp.array(2.0), inertia=jnp.array(0.0081), position=jnp.array([x, y]),
+                       angle=jnp.array(0.0), velocity=jnp.array([vx, vy]), angular_velocity=jnp.array(w),
+                       elasticity=jnp.array(0.5), friction_coefficient=jnp.array(0.5))
+
+    ball = bodies[4].set_position(jnp.array([-4.58, 0.1])).set_velocity(jnp.array([-3.0, 0.5]))
+    scene = [bodies[2], bodies[3], ball, robot(-4.40, 0.12, -4.0, 0.0, 0.0), robot(-4.18, 0.15, -6.0, -0.2, 1.0)]
+    out["b_props"], out["b_part_body"], out["b_recs"] = scene_arrays(scene)
+    out["b_traj"], out["b_keys"], out["b_err"] = roll_scene(scene, jnp.array(np.array([0, 9], np.uint32)), steps)
+    print(f"robocup goals + ball + 2 robots: {steps} steps, {time.time() - t0:.0f}s", flush=True)
+    np.savez_compressed(os.path.join(GOLD, "robocup.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["contacts", "resolve", "reset", "rollout"]
+    which = sys.argv[1:] or ["contacts", "resolve", "reset", "rollout", "robocup"]
     if "contacts" in which:
         gen_contacts()
     if "resolve" in which:
@@ -235,3 +330,5 @@ if __name__ == "__main__":
         gen_reset()
     if "rollout" in which:
         gen_rollout()
+    if "robocup" in which:
+        gen_robocup()

@@ -119,9 +119,17 @@ def filter_vmap(fn=None, *, in_axes=None, out_axes=None, **kw):
     return g
 
 
+# eqx.error_if: "raise" (equinox's default, EQX_ON_ERROR=raise) or "record" — the value passes
+# through and the message is appended to ERROR_LOG (what the engine's status bits stand for)
+ERROR_MODE = "raise"
+ERROR_LOG = []
+
+
 def error_if(x, pred, msg=""):
     if bool(_np.any(_np.asarray(pred))):
-        raise RuntimeError(msg)
+        if ERROR_MODE == "raise":
+            raise RuntimeError(msg)
+        ERROR_LOG.append(msg)
     return x
 
 

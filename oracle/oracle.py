@@ -302,7 +302,7 @@ def lunar_collider_debug(state, params: LunarParams | None = None, dedupe=True):
     return cell.astype(bool), cand.astype(bool), chosen
 
 
-def scene_step(bodies10, part_body, part_recs, key, dt=1e-2, init_dir=None, dedupe=True):
+def scene_step(bodies10, part_body, part_recs, key, dt=1e-2, init_dir=None, dedupe=True, want_status=False):
     bodies10 = _f32(bodies10).reshape(-1, 10).copy()
     nb = bodies10.shape[0]
     part_body = np.ascontiguousarray(part_body, np.int32)
@@ -313,13 +313,16 @@ def scene_step(bodies10, part_body, part_recs, key, dt=1e-2, init_dir=None, dedu
     init_dir = _f32(init_dir)
     cell = np.zeros((nb, nb), np.uint8)
     chosen = np.zeros(nb, np.int32)
+    status = C.c_uint32(0)
     rc = lib().oracle_scene_step(
         C.c_int(nb), _p(bodies10), C.c_int(part_recs.shape[0]), _p(part_body, C.c_int32), _p(part_recs),
         C.c_uint32(int(key[0])), C.c_uint32(int(key[1])), C.c_float(dt), _p(init_dir), C.c_int(32),
         C.c_float(0.5), C.c_float(0.3), C.c_float(0.01), C.c_int(1 if dedupe else 0),
-        _p(cell, C.c_uint8), _p(chosen, C.c_int32))
+        _p(cell, C.c_uint8), _p(chosen, C.c_int32), C.byref(status))
     if rc != 0:
         raise RuntimeError(f"oracle_scene_step failed: {rc}")
+    if want_status:
+        return bodies10, cell.astype(bool), chosen, int(status.value)
     return bodies10, cell.astype(bool), chosen
 
 

@@ -15,7 +15,8 @@ import subprocess
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_PKG, "csrc")
 LIB_PATH = os.path.join(_PKG, "libcotix_b200.so")
-SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu"]
+SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu",
+           "scene_kernel.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
@@ -69,6 +70,20 @@ class NarrowParams(C.Structure):
         ("init_dir", C.c_float * 2),
         ("gjk_max_iters", C.c_int32),
         ("epa_iters_circle_poly", C.c_int32),
+    ]
+
+
+class SceneParams(C.Structure):
+    """CotixSceneParams"""
+
+    _fields_ = [
+        ("dt", C.c_float),
+        ("init_dir", C.c_float * 2),
+        ("gjk_max_iters", C.c_int32),
+        ("coin_p", C.c_float),
+        ("baumgarte", C.c_float),
+        ("baumgarte_dt", C.c_float),
+        ("advance_key", C.c_int32),
     ]
 
 
@@ -138,6 +153,8 @@ EXPORTS = [
     "cotix_lunar_env_rollout_graph", "cotix_euler_step", "cotix_resolve_collision",
     "cotix_support", "cotix_threefry2x32", "cotix_philox4x32", "cotix_last_error",
     "cotix_abi_version", "cotix_launch_count", "cotix_device_info",
+    "cotix_scene_default_params", "cotix_scene_create", "cotix_scene_destroy", "cotix_scene_info",
+    "cotix_scene_step",
 ]
 
 _lib = None
@@ -186,6 +203,12 @@ def lib() -> C.CDLL:
     L.cotix_lunar_env_state_ptr.argtypes = [vp]
     L.cotix_lunar_env_stream.argtypes = [vp]
     L.cotix_lunar_env_rollout_graph.argtypes = [vp, C.c_int32, vp]
+    L.cotix_scene_default_params.argtypes = [C.POINTER(SceneParams)]
+    L.cotix_scene_default_params.restype = None
+    L.cotix_scene_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int32, vp, C.c_int32, vp, vp]
+    L.cotix_scene_destroy.argtypes = [vp]
+    L.cotix_scene_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int64), vp]
+    L.cotix_scene_step.argtypes = [vp, vp, i64, vp, i64, vp, C.POINTER(SceneParams), vp, vp, vp]
     L.cotix_euler_step.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, C.c_float]
     L.cotix_resolve_collision.argtypes = [vp, i64, vp, vp, vp, vp, C.c_float, C.c_float]
     L.cotix_threefry2x32.argtypes = [vp, i64, C.c_uint32, C.c_uint32, vp, vp, vp]

@@ -1,0 +1,486 @@
+// scene_kernel.cu — K2: the composed step for an ARBITRARY static scene description (bodies with
+// circle / AABB / polygon parts), one env per thread.  This is the path the RoboCup scene takes
+// (cotix/_robocup.py:14-130: AABB areas and goals + a circle ball, optionally robots).
+//
+//   ExplicitEulerPhysics.step            cotix/_physics_solvers.py:16-33
+//   part.transform(body transform)       cotix/_convex_shapes.py:37-41, 113-117, 181-187
+//   RandomizedCollider.resolve           cotix/_colliders.py:74-351
+//   resolve_collision                    cotix/_collision_resolution.py:52-151
+//   key, _ = jr.split(key)               examples/test_viz.py:39 (optional)
+//
+// What is static is analysed once on the host (cotix_scene_create): the groups of part pairs per
+// shape-type pair in first-appearance order (:86-131), the entry lists of each group, and the
+// table of DISTINCT (part, part) evaluations with body_i >= body_j — the reference evaluates the
+// full n_g x n_g grid of every group (:149-173), most of it duplicates or i < j (NaN).  Per env
+// and step the kernel evaluates each distinct pair once, flips a coin only where the contact is
+// live (a coin on a NaN contact cannot change all_contacts, :231-246; every key is a counter-
+// mode function of (group, ind2, ind1), so skipping the others changes nothing), then runs the
+// per-body choice (:274-295) and the sequential resolve scan (:310-336).
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "../../include/cotix_b200.h"
+#include "cx_launch.cuh"
+#include "cx_lunar.cuh"
+#include "cx_narrow.cuh"
+#include "cx_rng.cuh"
+
+#define CXS_REQUIRE(cond, msg)               \
+  do {                                       \
+    if (!(cond)) {                           \
+      cx_set_error("%s: %s", __func__, msg); \
+      return COTIX_EINVAL;                   \
+    }                                        \
+  } while (0)
+#define CXS_CUDA(call)                                                            \
+  do {                                                                            \
+    cudaError_t e_ = (call);                                                      \
+    if (e_ != cudaSuccess) {                                                      \
+      cx_set_error("%s: %s failed: %s", __func__, #call, cudaGetErrorString(e_)); \
+      return COTIX_ECUDA;                                                         \
+    }                                                                             \
+  } while (0)
+
+namespace {
+
+constexpr int MAXB = COTIX_SCENE_MAX_BODIES;
+constexpr int MAXP = COTIX_SCENE_MAX_PARTS;
+constexpr int MAXPAIR = COTIX_SCENE_MAX_PAIRS;
+constexpr int MAXENT = COTIX_SCENE_MAX_ENTRIES;
+constexpr int MAXG = 9;  // at most 9 keys of _contact_funcs can appear
+
+// the static analysis of a scene; lives in device memory, read uniformly by all threads
+struct SceneDesc {
+  int32_t nb, nparts, ngroups, npairs;
+  float props[MAXB][4];       // mass, inertia, elasticity, friction_coefficient
+  float rec[MAXP][16];        // local shape records (include/cotix_b200.h)
+  uint8_t part_body[MAXP];
+  uint8_t pair_a[MAXPAIR], pair_b[MAXPAIR];  // distinct evaluations: part ids
+  uint8_t pair_id[MAXP][MAXP];               // (part of list 0, part of list 1) -> pair or 0xFF
+  int32_t g_n[MAXG], g_off[MAXG];            // entries of group g: ent0/ent1[g_off .. g_off + g_n)
+  uint8_t ent0[MAXENT], ent1[MAXENT];        // part id of the k-th entry of list 0 / list 1
+};
+
+CX_DEV void sort_generic(Poly& p) {
+  switch (p.n) {
+    case 3: poly_sort_cw<3>(p); break;
+    case 4: poly_sort_cw<4>(p); break;
+    case 5: poly_sort_cw<5>(p); break;
+    case 6: poly_sort_cw<6>(p); break;
+    default: break;  // n <= 2: nothing to order for a point; a segment keeps argsort order below
+  }
+}
+
+// part.transform(transformer of the body): circles and boxes translate only (the angle is
+// ignored, cotix/_convex_shapes.py:37-41, 113-117); polygons rotate, translate and re-sort
+CX_DEV void world_part(const float* r, float px, float py, float c, float s, float out[12], int& type,
+                       int& n, float& radius) {
+  type = (int)r[0];
+  n = (int)r[1];
+  radius = r[2];
+  if (type == COTIX_SHAPE_CIRCLE) {
+    out[0] = r[4] + px;
+    out[1] = r[5] + py;
+  } else if (type == COTIX_SHAPE_AABB) {
+    out[0] = r[4] + px;
+    out[1] = r[5] + py;
+    out[2] = r[6] + px;
+    out[3] = r[7] + py;
+  } else {
+    Poly p;
+    p.n = n < 1 ? 1 : (n > CX_MAXV ? CX_MAXV : n);
+    const float ms = -s;
+#pragma unroll
+    for (int k = 0; k < CX_MAXV; ++k) {
+      if (k < p.n) {
+        const float x = r[4 + 2 * k], y = r[5 + 2 * k];
+        // forward_vector: matrix @ [x, y, 1] / w, w = 1 exactly (cotix/_geometry_utils.py:134-138)
+        p.x[k] = c * x + ms * y + px * 1.0f;
+        p.y[k] = s * x + c * y + py * 1.0f;
+      } else {
+        p.x[k] = 0.0f;
+        p.y[k] = 0.0f;
+      }
+    }
+    sort_generic(p);
+#pragma unroll
+    for (int k = 0; k < CX_MAXV; ++k) {
+      out[2 * k] = p.x[k];
+      out[2 * k + 1] = p.y[k];
+    }
+    n = p.n;
+  }
+}
+
+struct WPart {
+  float v[12];
+  int type, n;
+  float radius;
+};
+CX_DEV Poly wp_poly(const WPart& w) {
+  Poly p;
+  p.n = w.n;
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k) {
+    p.x[k] = w.v[2 * k];
+    p.y[k] = w.v[2 * k + 1];
+  }
+  return p;
+}
+CX_DEV Circ wp_circ(const WPart& w) {
+  Circ c;
+  c.c = mk2(w.v[0], w.v[1]);
+  c.r = w.radius;
+  return c;
+}
+CX_DEV Box wp_box(const WPart& w) {
+  Box b;
+  b.lo = mk2(w.v[0], w.v[1]);
+  b.hi = mk2(w.v[2], w.v[3]);
+  return b;
+}
+
+// _contact_funcs[(type(a), type(b))](a, b), cotix/_colliders.py:21-35 (the host has checked that
+// every pair of the scene is a key in this order)
+static __device__ __noinline__ Contact contact_of(const WPart& a, const WPart& b, V2 start, int gjk_max) {
+  const int ta = a.type, tb = b.type;
+  if (ta == COTIX_SHAPE_POLYGON && tb == COTIX_SHAPE_POLYGON)
+    return convex_vs_polygon(wp_poly(a), wp_poly(b), start, gjk_max);
+  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_POLYGON)
+    return circle_vs_polygon<131>(wp_circ(a), wp_poly(b), start, gjk_max, 128);
+  if (ta == COTIX_SHAPE_AABB && tb == COTIX_SHAPE_POLYGON)
+    return convex_vs_polygon(wp_box(a), wp_poly(b), start, gjk_max);
+  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_CIRCLE) return circle_vs_circle(wp_circ(a), wp_circ(b));
+  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_AABB) return circle_vs_aabb(wp_circ(a), wp_box(b));
+  return aabb_vs_aabb(wp_box(a), wp_box(b));
+}
+
+// jr.choice(key, nb, p=probs) for one body: cumsum / uniform / searchsorted(side='left')
+CX_DEV int choose_generic(const bool* live, int nb, float u) {
+  int cnt = 0;
+  for (int j = 0; j < nb; ++j) cnt += live[j] ? 1 : 0;
+  const float fc = (float)cnt;
+  float cum[MAXB];
+  float acc = 0.0f;
+  for (int j = 0; j < nb; ++j) {
+    const float p = (live[j] ? 1.0f : 0.0f) / fc;
+    acc = (j == 0) ? p : acc + p;
+    cum[j] = acc;
+  }
+  const float r = cum[nb - 1] * (1.0f - u);
+  int ind = 0;
+  for (int j = 0; j < nb; ++j)
+    if (cum[j] < r) ++ind;
+  return ind >= nb ? nb - 1 : ind;  // jnp indexing clamps
+}
+
+__global__ void __launch_bounds__(128)
+scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict__ state, int64_t ld,
+                  uint32_t* __restrict__ keys, const CotixSceneParams P, uint8_t* __restrict__ cell,
+                  int32_t* __restrict__ chosen_out, uint32_t* __restrict__ status_out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= B) return;
+  const int nb = S->nb, nparts = S->nparts, npairs = S->npairs;
+  BodyS body[MAXB];
+  MassP mass[MAXB];
+  for (int b = 0; b < nb; ++b) {
+    body[b].px = state[(b * 6 + 0) * ld + e];
+    body[b].py = state[(b * 6 + 1) * ld + e];
+    body[b].vx = state[(b * 6 + 2) * ld + e];
+    body[b].vy = state[(b * 6 + 3) * ld + e];
+    body[b].ang = state[(b * 6 + 4) * ld + e];
+    body[b].w = state[(b * 6 + 5) * ld + e];
+    mass[b].mass = S->props[b][0];
+    mass[b].inertia = S->props[b][1];
+    mass[b].e = S->props[b][2];
+    mass[b].mu = S->props[b][3];
+    // ExplicitEulerPhysics._single_body_step
+    body[b].px = body[b].px + body[b].vx * P.dt;
+    body[b].py = body[b].py + body[b].vy * P.dt;
+    body[b].ang = body[b].ang + body[b].w * P.dt;
+  }
+  uint32_t status = 0u;
+  // world parts
+  WPart W[MAXP];
+  for (int q = 0; q < nparts; ++q) {
+    const int b = S->part_body[q];
+    float sn = 0.0f, cs = 1.0f;  // only polygons rotate
+    if ((int)S->rec[q][0] == COTIX_SHAPE_POLYGON) cx_sincosf(body[b].ang, &sn, &cs);
+    world_part(S->rec[q], body[b].px, body[b].py, cs, sn, W[q].v, W[q].type, W[q].n, W[q].radius);
+  }
+  // distinct narrowphase evaluations
+  const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
+  float cpen[MAXPAIR][2], ccp[MAXPAIR][2];
+  for (int q = 0; q < npairs; ++q) {
+    const Contact c = contact_of(W[S->pair_a[q]], W[S->pair_b[q]], start, P.gjk_max_iters);
+    cpen[q][0] = c.pen.x; cpen[q][1] = c.pen.y;
+    ccp[q][0] = c.cp.x; ccp[q][1] = c.cp.y;
+    status |= c.status;
+  }
+  // coin-flip scatter into all_contacts (:208-268): the last heads in (ind2, ind1) order wins
+  int16_t all[MAXB][MAXB];
+  for (int i = 0; i < nb; ++i)
+    for (int j = 0; j < nb; ++j) all[i][j] = -1;
+  Key2 rkey;
+  rkey.a = keys[e];
+  rkey.b = keys[ld + e];
+  Key2 skey = tf_split(rkey, 2u, 0u);
+  for (int g = 0; g < S->ngroups; ++g) {
+    skey = tf_split(skey, 2u, 0u);
+    const int n = S->g_n[g], off = S->g_off[g];
+    for (int ind2 = 0; ind2 < n; ++ind2) {
+      const int pb = S->ent1[off + ind2];
+      bool have_k2 = false;
+      Key2 k2;
+      k2.a = k2.b = 0u;
+      for (int ind1 = 0; ind1 < n; ++ind1) {
+        const int pa = S->ent0[off + ind1];
+        const int q = S->pair_id[pa][pb];
+        if (q == 0xFF) continue;                         // i < j: NaN (:163)
+        if ((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1])) continue;  // NaN contact
+        if (!have_k2) {
+          k2 = tf_split(skey, (uint32_t)n, (uint32_t)ind2);
+          have_k2 = true;
+        }
+        const Key2 k1 = tf_split(k2, (uint32_t)n, (uint32_t)ind1);
+        const Key2 kk = tf_split(k1, 2u, 0u);
+        if (tf_bernoulli(kk, P.coin_p)) all[S->part_body[pa]][S->part_body[pb]] = (int16_t)q;
+      }
+    }
+  }
+  // choose_random_contact (:274-295)
+  int chosen[MAXB];
+  for (int i = 0; i < nb; ++i) {
+    bool live[MAXB];
+    int cnt = 0;
+    for (int j = 0; j < nb; ++j) {
+      live[j] = all[i][j] >= 0;
+      cnt += live[j] ? 1 : 0;
+      if (cell) cell[(int64_t)(i * nb + j) * ld + e] = live[j] ? 1 : 0;
+    }
+    int idx = i;
+    if (cnt != 0) idx = choose_generic(live, nb, tf_uniform(tf_split(skey, (uint32_t)nb, (uint32_t)i), 0.0f, 1.0f));
+    chosen[i] = idx;
+    if (chosen_out) chosen_out[(int64_t)i * ld + e] = idx;
+  }
+  // sequential resolution scan (:310-336)
+  for (int i = 0; i < nb; ++i) {
+    const int j = chosen[i];
+    if (i == j) continue;
+    const int q = all[i][j];
+    if (q < 0) continue;  // NaN contact: resolve_collision returns the bodies unchanged
+    resolve_collision(body[i], mass[i], body[j], mass[j], mk2(cpen[q][0], cpen[q][1]),
+                      mk2(ccp[q][0], ccp[q][1]), P.baumgarte, P.baumgarte_dt);
+  }
+  for (int b = 0; b < nb; ++b) {
+    state[(b * 6 + 0) * ld + e] = body[b].px;
+    state[(b * 6 + 1) * ld + e] = body[b].py;
+    state[(b * 6 + 2) * ld + e] = body[b].vx;
+    state[(b * 6 + 3) * ld + e] = body[b].vy;
+    state[(b * 6 + 4) * ld + e] = body[b].ang;
+    state[(b * 6 + 5) * ld + e] = body[b].w;
+  }
+  if (P.advance_key) {
+    const Key2 nk = tf_split(rkey, 2u, 0u);
+    keys[e] = nk.a;
+    keys[ld + e] = nk.b;
+  }
+  if (status_out) status_out[e] = status;
+}
+
+// ---- host-side analysis ----------------------------------------------------------------
+// dictionary label of a part (Polygon4 and Polygon6 are distinct classes,
+// cotix/_convex_shapes.py:197-229; any other vertex count is the generic Polygon)
+int type_label(const float* r) {
+  const int t = (int)r[0];
+  if (t == COTIX_SHAPE_CIRCLE) return 0;
+  if (t == COTIX_SHAPE_AABB) return 1;
+  return 2 + (int)r[1];  // Polygon<n>
+}
+// is (t1, t2) a key of _contact_funcs (cotix/_colliders.py:21-35)?
+bool legal_pair(int t1, int t2) {
+  const bool p1 = t1 >= 2, p2 = t2 >= 2;
+  if (t1 == 0) return true;                 // (Circle, Circle|AABB|Polygon*)
+  if (t1 == 1) return t2 == 1 || p2;        // (AABB, AABB|Polygon*)
+  if (p1 && p2) {
+    const int n1 = t1 - 2, n2 = t2 - 2;
+    if (n1 == 4) return n2 == 4 || n2 == 6;  // (Polygon4, Polygon4|Polygon6)
+    if (n1 == 6) return n2 == 6;             // (Polygon6, Polygon6)
+    return n2 != 4 && n2 != 6;               // (Polygon, Polygon): the generic class
+  }
+  return false;
+}
+
+}  // namespace
+
+struct CotixScene {
+  int device;
+  SceneDesc host;
+  SceneDesc* dev;
+  int64_t n_evals;  // sum of n_g^2: what the reference's vmap^2 evaluates per step
+};
+
+extern "C" {
+
+int cotix_scene_create(CotixScene** out, int device, int32_t nb, const float* body_props, int32_t nparts,
+                       const int32_t* part_body, const float* part_recs) {
+  CXS_REQUIRE(out && body_props && part_body && part_recs, "null argument");
+  CXS_REQUIRE(nb >= 1 && nb <= MAXB, "number of bodies out of range");
+  CXS_REQUIRE(nparts >= 1 && nparts <= MAXP, "number of parts out of range");
+  CotixScene* sc = new (std::nothrow) CotixScene();
+  CXS_REQUIRE(sc != nullptr, "out of host memory");
+  SceneDesc& S = sc->host;
+  memset(&S, 0, sizeof(S));
+  memset(S.pair_id, 0xFF, sizeof(S.pair_id));
+  S.nb = nb;
+  S.nparts = nparts;
+  memcpy(S.props, body_props, sizeof(float) * 4 * (size_t)nb);
+  for (int q = 0; q < nparts; ++q) {
+    if (part_body[q] < 0 || part_body[q] >= nb) {
+      delete sc;
+      CXS_REQUIRE(false, "part_body out of range");
+    }
+    const int t = (int)part_recs[16 * q];
+    const int n = (int)part_recs[16 * q + 1];
+    if (t < 0 || t > 2 || (t == COTIX_SHAPE_POLYGON && (n < 3 || n > COTIX_MAX_POLY))) {
+      delete sc;
+      CXS_REQUIRE(false, "bad shape record");
+    }
+    S.part_body[q] = (uint8_t)part_body[q];
+    memcpy(S.rec[q], part_recs + 16 * q, sizeof(float) * 16);
+  }
+  // groups in first-appearance order over (i, j, part of i, part of j), i > j (:86-113)
+  int gkey[MAXG][2];
+  std::vector<uint8_t> l0[MAXG], l1[MAXG];
+  int ng = 0;
+  for (int i = 0; i < nb; ++i)
+    for (int j = 0; j < i; ++j)
+      for (int pa = 0; pa < nparts; ++pa) {
+        if (S.part_body[pa] != i) continue;
+        for (int pb = 0; pb < nparts; ++pb) {
+          if (S.part_body[pb] != j) continue;
+          const int t1 = type_label(S.rec[pa]), t2 = type_label(S.rec[pb]);
+          if (!legal_pair(t1, t2)) {
+            delete sc;
+            cx_set_error("cotix_scene_create: parts %d (body %d) and %d (body %d): this order of shape "
+                         "types is not a key of _contact_funcs (the reference raises)", pa, i, pb, j);
+            return COTIX_EINVAL;
+          }
+          int g = 0;
+          while (g < ng && !(gkey[g][0] == t1 && gkey[g][1] == t2)) ++g;
+          if (g == ng) {
+            gkey[g][0] = t1;
+            gkey[g][1] = t2;
+            ++ng;
+          }
+          l0[g].push_back((uint8_t)pa);
+          l1[g].push_back((uint8_t)pb);
+        }
+      }
+  S.ngroups = ng;
+  int off = 0, npairs = 0;
+  int64_t evals = 0;
+  for (int g = 0; g < ng; ++g) {
+    const int n = (int)l0[g].size();
+    if (off + n > MAXENT) {
+      delete sc;
+      CXS_REQUIRE(false, "too many part pairs for COTIX_SCENE_MAX_ENTRIES");
+    }
+    S.g_n[g] = n;
+    S.g_off[g] = off;
+    for (int k = 0; k < n; ++k) {
+      S.ent0[off + k] = l0[g][(size_t)k];
+      S.ent1[off + k] = l1[g][(size_t)k];
+    }
+    off += n;
+    evals += (int64_t)n * n;
+    // the vmap^2 grid: entry a of list 0 against entry b of list 1, kept when body_i >= body_j
+    for (int a = 0; a < n; ++a)
+      for (int b = 0; b < n; ++b) {
+        const int pa = l0[g][(size_t)a], pb = l1[g][(size_t)b];
+        if (S.part_body[pa] < S.part_body[pb]) continue;
+        if (S.pair_id[pa][pb] != 0xFF) continue;
+        if (npairs >= MAXPAIR) {
+          delete sc;
+          CXS_REQUIRE(false, "too many distinct part pairs for COTIX_SCENE_MAX_PAIRS");
+        }
+        S.pair_id[pa][pb] = (uint8_t)npairs;
+        S.pair_a[npairs] = (uint8_t)pa;
+        S.pair_b[npairs] = (uint8_t)pb;
+        ++npairs;
+      }
+  }
+  S.npairs = npairs;
+  sc->n_evals = evals;
+  sc->device = device;
+  sc->dev = nullptr;
+  if (device >= 0) {
+    cudaError_t ce = cudaSetDevice(device);
+    if (ce == cudaSuccess) ce = cudaMalloc(&sc->dev, sizeof(SceneDesc));
+    if (ce == cudaSuccess) ce = cudaMemcpy(sc->dev, &S, sizeof(SceneDesc), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) {
+      cx_set_error("cotix_scene_create: %s", cudaGetErrorString(ce));
+      cudaGetLastError();
+      delete sc;
+      return COTIX_ECUDA;
+    }
+  }
+  *out = sc;
+  return COTIX_OK;
+}
+
+int cotix_scene_destroy(CotixScene* sc) {
+  if (!sc) return COTIX_OK;
+  if (sc->dev) {
+    cudaSetDevice(sc->device);
+    cudaFree(sc->dev);
+  }
+  delete sc;
+  return COTIX_OK;
+}
+
+int cotix_scene_info(const CotixScene* sc, int32_t* n_groups, int32_t* n_pairs, int64_t* n_reference_evals,
+                     int32_t* group_sizes) {
+  CXS_REQUIRE(sc != nullptr, "scene is null");
+  if (n_groups) *n_groups = sc->host.ngroups;
+  if (n_pairs) *n_pairs = sc->host.npairs;
+  if (n_reference_evals) *n_reference_evals = sc->n_evals;
+  if (group_sizes)
+    for (int g = 0; g < sc->host.ngroups; ++g) group_sizes[g] = sc->host.g_n[g];
+  return COTIX_OK;
+}
+
+void cotix_scene_default_params(CotixSceneParams* p) {
+  if (!p) return;
+  CotixLunarParams lp;
+  cotix_lunar_default_params(&lp);
+  memset(p, 0, sizeof(*p));
+  p->dt = lp.dt;
+  p->init_dir[0] = lp.init_dir[0];
+  p->init_dir[1] = lp.init_dir[1];
+  p->gjk_max_iters = lp.gjk_max_iters;
+  p->coin_p = lp.coin_p;
+  p->baumgarte = lp.baumgarte;
+  p->baumgarte_dt = lp.baumgarte_dt;
+  p->advance_key = 1;
+}
+
+int cotix_scene_step(void* stream, const CotixScene* sc, int64_t B, float* state, int64_t ld, uint32_t* keys,
+                     const CotixSceneParams* p, uint8_t* cell, int32_t* chosen, uint32_t* status) {
+  CXS_REQUIRE(sc != nullptr && p != nullptr, "null argument");
+  CXS_REQUIRE(sc->dev != nullptr, "the scene was created without a device");
+  CXS_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
+  CXS_REQUIRE(B == 0 || (state && keys), "null buffer");
+  CXS_REQUIRE(p->gjk_max_iters >= 0, "bad params");
+  if (B == 0) return COTIX_OK;
+  const int tpb = 128;
+  const int64_t blocks = (B + tpb - 1) / tpb;
+  CXS_REQUIRE(blocks <= 0x7FFFFFFF, "batch too large");
+  scene_step_kernel<<<(unsigned)blocks, tpb, 0, (cudaStream_t)stream>>>(sc->dev, B, state, ld, keys, *p, cell,
+                                                                          chosen, status);
+  cx_count_launch();
+  return cx_check_launch("scene_step_kernel");
+}
+
+}  // extern "C"

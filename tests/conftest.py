@@ -40,3 +40,13 @@ def exact_trig(oracle):
     oracle.set_trig_mode(1)
     yield
     oracle.set_trig_mode(0)
+
+
+@pytest.fixture(scope="session")
+def cuda_lib_cpu():
+    """The built C-ABI library for host-only entry points (no device needed, no compute calls)."""
+    import parallax_b200
+
+    if not os.path.exists(parallax_b200._lib.LIB_PATH):
+        parallax_b200.build()
+    return parallax_b200._lib.lib()
