@@ -60,6 +60,15 @@ struct SceneDesc {
   uint8_t pair_id[MAXP][MAXP];               // (part of list 0, part of list 1) -> pair or 0xFF
   int32_t g_n[MAXG], g_off[MAXG];            // entries of group g: ent0/ent1[g_off .. g_off + g_n)
   uint8_t ent0[MAXENT], ent1[MAXENT];        // part id of the k-th entry of list 0 / list 1
+  // all_contacts cells that have grid entries: for cell c = (i, j) the distinct pairs that can
+  // land in it and its grid entries in DESCENDING scan order (group, ind2, ind1), each packed as
+  // pair | ind1 << 8 | ind2 << 16 | group << 24 (device arrays of the scene)
+  int32_t ncells;
+  const uint16_t* cell_ij;      // [ncells] i << 8 | j
+  const int32_t* cell_pair_off; // [ncells + 1] into cell_pairs
+  const uint8_t* cell_pairs;
+  const int32_t* cell_ent_off;  // [ncells + 1] into cell_ents
+  const uint32_t* cell_ents;
 };
 
 CX_DEV void sort_generic(Poly& p) {
@@ -225,27 +234,37 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
   Key2 rkey;
   rkey.a = keys[e];
   rkey.b = keys[ld + e];
+  // group keys: skey is split once more before every group (:175)
   Key2 skey = tf_split(rkey, 2u, 0u);
+  Key2 gk[MAXG];
   for (int g = 0; g < S->ngroups; ++g) {
     skey = tf_split(skey, 2u, 0u);
-    const int n = S->g_n[g], off = S->g_off[g];
-    for (int ind2 = 0; ind2 < n; ++ind2) {
-      const int pb = S->ent1[off + ind2];
-      bool have_k2 = false;
-      Key2 k2;
-      k2.a = k2.b = 0u;
-      for (int ind1 = 0; ind1 < n; ++ind1) {
-        const int pa = S->ent0[off + ind1];
-        const int q = S->pair_id[pa][pb];
-        if (q == 0xFF) continue;                         // i < j: NaN (:163)
-        if ((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1])) continue;  // NaN contact
-        if (!have_k2) {
-          k2 = tf_split(skey, (uint32_t)n, (uint32_t)ind2);
-          have_k2 = true;
-        }
-        const Key2 k1 = tf_split(k2, (uint32_t)n, (uint32_t)ind1);
-        const Key2 kk = tf_split(k1, 2u, 0u);
-        if (tf_bernoulli(kk, P.coin_p)) all[S->part_body[pa]][S->part_body[pb]] = (int16_t)q;
+    gk[g] = skey;
+  }
+  // The scans write cell (i, j) at every grid entry whose coin is heads and whose contact is
+  // live, in (group, ind2, ind1) order, so the cell ends up with the LAST such entry.  Every
+  // coin is a counter-mode function of its (group, ind2, ind1), hence: walk the entries of a
+  // cell from the last backwards, skip dead contacts, stop at the first heads.
+  for (int c = 0; c < S->ncells; ++c) {
+    bool any = false;
+    for (int k = S->cell_pair_off[c]; k < S->cell_pair_off[c + 1]; ++k) {
+      const int q = S->cell_pairs[k];
+      any = any || !((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1]));
+    }
+    if (!any) continue;
+    const int ij = S->cell_ij[c];
+    for (int k = S->cell_ent_off[c]; k < S->cell_ent_off[c + 1]; ++k) {
+      const uint32_t ent = S->cell_ents[k];
+      const int q = (int)(ent & 0xFFu);
+      if ((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1])) continue;  // NaN contact
+      const uint32_t ind1 = (ent >> 8) & 0xFFu, ind2 = (ent >> 16) & 0xFFu, g = ent >> 24;
+      const uint32_t n = (uint32_t)S->g_n[g];
+      const Key2 k2 = tf_split(gk[g], n, ind2);
+      const Key2 k1 = tf_split(k2, n, ind1);
+      const Key2 kk = tf_split(k1, 2u, 0u);
+      if (tf_bernoulli(kk, P.coin_p)) {
+        all[ij >> 8][ij & 0xFF] = (int16_t)q;
+        break;
       }
     }
   }
@@ -317,7 +336,7 @@ bool legal_pair(int t1, int t2) {
 struct CotixScene {
   int device;
   SceneDesc host;
-  SceneDesc* dev;
+  SceneDesc* dev;   // one device block: the description followed by its cell tables
   int64_t n_evals;  // sum of n_g^2: what the reference's vmap^2 evaluates per step
 };
 
@@ -415,13 +434,67 @@ int cotix_scene_create(CotixScene** out, int device, int32_t nb, const float* bo
   sc->n_evals = evals;
   sc->device = device;
   sc->dev = nullptr;
+  // per-cell pair lists and grid entries (ascending here, reversed below)
+  std::vector<std::vector<uint8_t>> cpairs((size_t)nb * nb);
+  std::vector<std::vector<uint32_t>> cents((size_t)nb * nb);
+  for (int g = 0; g < ng; ++g) {
+    const int n = S.g_n[g];
+    for (int ind2 = 0; ind2 < n; ++ind2)
+      for (int ind1 = 0; ind1 < n; ++ind1) {
+        const int pa = l0[g][(size_t)ind1], pb = l1[g][(size_t)ind2];
+        const int q = S.pair_id[pa][pb];
+        if (q == 0xFF) continue;  // i < j: NaN (:163)
+        const size_t c = (size_t)S.part_body[pa] * nb + S.part_body[pb];
+        bool seen = false;
+        for (uint8_t x : cpairs[c]) seen = seen || x == q;
+        if (!seen) cpairs[c].push_back((uint8_t)q);
+        cents[c].push_back((uint32_t)q | ((uint32_t)ind1 << 8) | ((uint32_t)ind2 << 16) | ((uint32_t)g << 24));
+      }
+  }
+  std::vector<uint16_t> h_ij;
+  std::vector<int32_t> h_poff(1, 0), h_eoff(1, 0);
+  std::vector<uint8_t> h_pairs;
+  std::vector<uint32_t> h_ents;
+  for (int i = 0; i < nb; ++i)
+    for (int j = 0; j < nb; ++j) {
+      const size_t c = (size_t)i * nb + j;
+      if (cents[c].empty()) continue;
+      h_ij.push_back((uint16_t)((i << 8) | j));
+      h_pairs.insert(h_pairs.end(), cpairs[c].begin(), cpairs[c].end());
+      h_ents.insert(h_ents.end(), cents[c].rbegin(), cents[c].rend());
+      h_poff.push_back((int32_t)h_pairs.size());
+      h_eoff.push_back((int32_t)h_ents.size());
+    }
+  S.ncells = (int32_t)h_ij.size();
   if (device >= 0) {
+    // one device block: [SceneDesc | cell_ij | cell_pair_off | cell_ent_off | cell_ents | cell_pairs]
+    auto al = [](size_t x) { return (x + 15) / 16 * 16; };
+    const size_t o_ij = al(sizeof(SceneDesc)), o_poff = o_ij + al(2 * h_ij.size()),
+                 o_eoff = o_poff + al(4 * h_poff.size()), o_ents = o_eoff + al(4 * h_eoff.size()),
+                 o_pairs = o_ents + al(4 * h_ents.size()), total = o_pairs + al(h_pairs.size());
+    std::vector<char> blob(total, 0);
     cudaError_t ce = cudaSetDevice(device);
-    if (ce == cudaSuccess) ce = cudaMalloc(&sc->dev, sizeof(SceneDesc));
-    if (ce == cudaSuccess) ce = cudaMemcpy(sc->dev, &S, sizeof(SceneDesc), cudaMemcpyHostToDevice);
+    char* d = nullptr;
+    if (ce == cudaSuccess) ce = cudaMalloc(&d, total);
+    if (ce == cudaSuccess) {
+      S.cell_ij = reinterpret_cast<const uint16_t*>(d + o_ij);
+      S.cell_pair_off = reinterpret_cast<const int32_t*>(d + o_poff);
+      S.cell_ent_off = reinterpret_cast<const int32_t*>(d + o_eoff);
+      S.cell_ents = reinterpret_cast<const uint32_t*>(d + o_ents);
+      S.cell_pairs = reinterpret_cast<const uint8_t*>(d + o_pairs);
+      memcpy(blob.data(), &S, sizeof(SceneDesc));
+      memcpy(blob.data() + o_ij, h_ij.data(), 2 * h_ij.size());
+      memcpy(blob.data() + o_poff, h_poff.data(), 4 * h_poff.size());
+      memcpy(blob.data() + o_eoff, h_eoff.data(), 4 * h_eoff.size());
+      memcpy(blob.data() + o_ents, h_ents.data(), 4 * h_ents.size());
+      memcpy(blob.data() + o_pairs, h_pairs.data(), h_pairs.size());
+      sc->dev = reinterpret_cast<SceneDesc*>(d);
+      ce = cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice);
+    }
     if (ce != cudaSuccess) {
       cx_set_error("cotix_scene_create: %s", cudaGetErrorString(ce));
       cudaGetLastError();
+      if (d) cudaFree(d);
       delete sc;
       return COTIX_ECUDA;
     }

@@ -196,6 +196,22 @@ def test_cuda_scene_step_robocup_with_robots_vs_oracle(cuda_lib, oracle, exact_t
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("areas", [False, True])
+def test_cuda_scene_step_robocup_config4_vs_oracle(cuda_lib, oracle, exact_trig, areas):
+    """BASELINE config 4: the RoboCup scene with 6 + 6 robots (17 bodies, 19 or 21 parts, 176 / 246
+    distinct part pairs), robots and ball scattered over the yellow half so that they collide."""
+    from parallax_b200 import scene as sc
+
+    spec = sc.robocup_scene(n_robots=12, areas_collide=areas)
+    rng = np.random.default_rng(34)
+    B = 96
+    st = _random_states(spec, B, rng, ((-4.9, -3.6), (-0.9, 0.9)))
+    keys = np.stack([np.full(B, 11, np.uint32), np.arange(B, dtype=np.uint32) * 5], 1)
+    hits = _run_against_oracle(oracle, spec, st, keys, steps=5)
+    assert hits > 1000
+
+
+@pytest.mark.gpu
 def test_cuda_scene_step_shipped_robocup_batch_vs_oracle(cuda_lib, oracle, exact_trig):
     """RoboCupEnv as shipped (overlapping area AABBs, NaN statics) with the ball anywhere on the field."""
     from parallax_b200 import scene as sc
