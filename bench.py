@@ -324,6 +324,7 @@ def run_ours(args):
 
     if rank == 0 and world == 1 and not args.no_sweep:
         line["narrowphase"] = sweep(args, dev, peak)
+        line["robocup"] = robocup(args, dev)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:
@@ -370,6 +371,56 @@ def sweep(args, dev, peak):
                          "kernel": "sweep_classify + sweep_gjk<3> + sweep_epa<3> (7 launches, whole sweep)"}}
 
 
+def robocup(args, dev):
+    """BASELINE config 4: the RoboCup scene with 6 + 6 robots, B = 262144, through the generic
+    scene step (cotix_scene_step); the oracle's generic collider on a small sample beside it."""
+    import torch
+
+    from oracle import oracle as o
+    from parallax_b200 import scene as sc
+
+    B = args.robocup_envs
+    spec = sc.robocup_scene(n_robots=12, areas_collide=False)
+    scene = sc.Scene(spec, device=dev.index)
+    rng = np.random.default_rng(3)
+    st = np.repeat(spec.init_state[:, :, None], B, axis=2).astype(np.float32)
+    for b in np.nonzero(np.isfinite(spec.body_props[:, 0]))[0]:
+        st[b, 0:2] += rng.normal(0, 0.3, (2, B)).astype(np.float32)
+        st[b, 2:4] += rng.normal(0, 1.0, (2, B)).astype(np.float32)
+    state = torch.from_numpy(np.ascontiguousarray(st.reshape(spec.nb * 6, B))).to(dev)
+    keys_h = np.stack([np.zeros(B, np.uint32), np.arange(B, dtype=np.uint32)])
+    keys = torch.from_numpy(keys_h.view(np.int32)).to(dev)
+    for _ in range(5):
+        scene.step(state, keys)
+    torch.cuda.synchronize(dev)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 20
+    ev0.record()
+    for _ in range(reps):
+        scene.step(state, keys)
+    ev1.record()
+    torch.cuda.synchronize(dev)
+    ms = ev0.elapsed_time(ev1) / reps
+    info = scene.info()
+    scene.close()
+    # CPU: the oracle's generic collider (memoised duplicate pairs), one core, 64 envs x 2 steps
+    o.set_trig_mode(1)
+    n_cpu = 64
+    t0 = time.perf_counter()
+    for e in range(n_cpu):
+        b10 = spec.bodies10(st[:, :, e])
+        for _ in range(2):
+            b10, _c, _ch = o.scene_step(b10, spec.part_body, spec.part_recs, keys_h[:, e])
+    cpu = 2 * n_cpu / (time.perf_counter() - t0)
+    o.set_trig_mode(0)
+    return {"metric": "RoboCup env-steps/sec", "value": B / (ms * 1e-3), "unit": "env-steps/s", "envs": B,
+            "ms_per_step": ms, "bodies": spec.nb, "parts": int(spec.part_recs.shape[0]),
+            "distinct_pairs_per_step": info["distinct_pairs"],
+            "reference_evaluations_per_step": info["reference_evaluations"],
+            "kernel": "scene_step_kernel (one env per thread)",
+            "cpu_port": {"value": cpu, "unit": "env-steps/s", "cores": 1, "sample": f"{n_cpu} envs x 2 steps"}}
+
+
 def cpu_baseline(args):
     """The oracle (a C++ port of the reference path) on the box's host cores, bounded sample."""
     from gen_inputs import lunar_keys, perturbed_lunar_state
@@ -404,6 +455,7 @@ def main():
     ap.add_argument("--rng", default="threefry", choices=["threefry", "philox"])
     ap.add_argument("--max-episode-steps", dest="max_episode_steps", type=int, default=1000)
     ap.add_argument("--pairs", type=int, default=1 << 24)
+    ap.add_argument("--robocup-envs", dest="robocup_envs", type=int, default=1 << 18)
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=50)
     ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=16384)
     ap.add_argument("--ref-literal", dest="ref_literal", action="store_true")
