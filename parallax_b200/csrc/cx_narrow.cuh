@@ -363,14 +363,9 @@ CX_DEV Contact circle_vs_aabb(const Circ& a, const Box& b) {  // :99-154
   return c;
 }
 
-// second half of circle_vs_polygon (:162-202), given the GJK simplex of a hit
-template <int MAXE>
-CX_DEV void circle_poly_finish(const Circ& circle, const Poly& poly, V2 s0, V2 s1, V2 s2, int epa_iters,
-                               Contact& c) {
-  bool ecap;
-  if (epa_iters > MAXE - 3) epa_iters = MAXE - 3;
-  V2 pen = epa<MAXE>(circle, poly, s0, s1, s2, epa_iters, ecap);
-  if (ecap) c.status |= CX_ST_EPA_CAP;
+// contact point of circle_vs_polygon (:166-197): the point of the polygon's boundary nearest to
+// the circle centre, or the centre itself when that point is farther than the radius
+CX_DEV V2 circle_poly_contact_point(const Circ& circle, const Poly& poly) {
   EdgeList e;
   edges_of(poly, e);
   float bestd = 0.0f;
@@ -400,8 +395,19 @@ CX_DEV void circle_poly_finish(const Circ& circle, const Poly& poly, V2 s0, V2 s
   }
   V2 cp = circle.c + bestdisp;
   if (bestd > circle.r * circle.r) cp = circle.c;
+  return cp;
+}
+
+// second half of circle_vs_polygon (:162-202), given the GJK simplex of a hit
+template <int MAXE>
+CX_DEV void circle_poly_finish(const Circ& circle, const Poly& poly, V2 s0, V2 s1, V2 s2, int epa_iters,
+                               Contact& c) {
+  bool ecap;
+  if (epa_iters > MAXE - 3) epa_iters = MAXE - 3;
+  V2 pen = epa<MAXE>(circle, poly, s0, s1, s2, epa_iters, ecap);
+  if (ecap) c.status |= CX_ST_EPA_CAP;
   c.pen = pen;
-  c.cp = cp;
+  c.cp = circle_poly_contact_point(circle, poly);
 }
 
 template <int MAXE>

@@ -38,6 +38,14 @@ constexpr int F_CRASH_SHIFT = 25, F_RC_SHIFT = 26, F_LC_SHIFT = 27;
 
 enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 4, CTR_WORDS = 16 };
 
+// minimum resident blocks per SM asked of ptxas for the two dense kernels (register caps)
+#ifndef CX_INTEGRATE_MINB
+#define CX_INTEGRATE_MINB 6
+#endif
+#ifndef CX_FINISH_MINB
+#define CX_FINISH_MINB 6
+#endif
+
 struct PipeWs {
   uint32_t* ctr;   // [CTR_WORDS]
   uint32_t* cand;  // [B] candidate mask | flags
@@ -104,7 +112,7 @@ struct RecPolys {
 };
 
 // ---- K_A -----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB)
+__global__ void __launch_bounds__(TPB, CX_INTEGRATE_MINB)
 pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__ sout, int64_t ld,
                       const float* __restrict__ action, const __grid_constant__ CotixLunarParams P,
                       const LunarDerived D, const PipeWs ws) {
@@ -355,41 +363,58 @@ CX_DEV void coll_push(WarpColl& W, int& tail, bool pred, uint32_t desc, uint32_t
   tail += __popc(m);
 }
 
+// One round: the first T = min(32, pending) tasks of the ring, m = 32 / T consecutive entries of
+// each (m = 1 while the ring is full).  The extra entries are flipped speculatively: a task takes
+// the FIRST heads among its m entries, exactly what flipping them one per round would find, so the
+// thin rounds at the end of a warp's work (16, 8, 4, ... tasks left) collapse into one or two.
 CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParams& P) {
   const int lane = threadIdx.x & 31;
   __syncwarp();
   while (head < tail) {
-    const int i = head + lane;
-    bool requeue = false;
-    uint32_t desc = 0u, mask = 0u, t = 0u;
-    if (i < tail) {
-      const int slot = i & 255;
+    const int T = min(tail - head, 32);
+    const int m = 32 / T;
+    const int task = lane / m, off = lane - task * m;
+    const bool has = task < T;
+    bool heads = false;
+    uint32_t desc = 0u, mask = 0u, t0 = 0u;
+    int el = 0, c = 0, q = 0, total = 0;
+    if (has) {
+      const int slot = (head + task) & 255;
       desc = W.tdesc[slot];
       mask = W.tmask[slot];
-      t = W.tidx[slot];
-      const int el = (int)(desc & 31u), c = (int)(desc >> 5);
+      t0 = W.tidx[slot];
+      el = (int)(desc & 31u);
+      c = (int)(desc >> 5);
       const CellDesc d = cell_desc(c);
-      const int L = __popc(mask), per2 = d.reps * L, total = (d.b_hi - d.b_lo + 1) * per2;
-      const int ind2 = d.b_hi - (int)t / per2, rem = (int)t % per2;
-      const int r = d.reps - 1 - rem / L, j = rem % L;
-      const int q = (int)__fns(mask, 0u, L - j);  // live entries from the highest q down
-      const int ind1 = d.a0 + q + d.nq * r;
-      CoinCtx cc;
-      cc.mode = P.rng_mode;
-      cc.p = P.coin_p;
-      cc.gkey[0].a = W.gk[el][0]; cc.gkey[0].b = W.gk[el][1];
-      cc.gkey[1].a = W.gk[el][2]; cc.gkey[1].b = W.gk[el][3];
-      cc.pkey.a = W.pk[el][0]; cc.pkey.b = W.pk[el][1];
-      cc.steps = W.st[el][0]; cc.episode = W.st[el][1];
-      Key2 k2;
-      k2.a = k2.b = 0u;
-      if (cc.mode == COTIX_RNG_THREEFRY) k2 = tf_split(cc.gkey[d.g], (uint32_t)d.N2, (uint32_t)ind2);
-      if (coin_heads(cc, d.g, d.N1, k2, ind2, ind1)) W.win[el][c] = (int8_t)q;
-      else if ((int)t + 1 < total) requeue = true;
+      const int L = __popc(mask), per2 = d.reps * L;
+      total = (d.b_hi - d.b_lo + 1) * per2;
+      const int t = (int)t0 + off;
+      if (t < total) {
+        const int ind2 = d.b_hi - t / per2, rem = t % per2;
+        const int r = d.reps - 1 - rem / L, j = rem % L;
+        q = (int)__fns(mask, 0u, L - j);  // live entries from the highest q down
+        const int ind1 = d.a0 + q + d.nq * r;
+        CoinCtx cc;
+        cc.mode = P.rng_mode;
+        cc.p = P.coin_p;
+        cc.gkey[0].a = W.gk[el][0]; cc.gkey[0].b = W.gk[el][1];
+        cc.gkey[1].a = W.gk[el][2]; cc.gkey[1].b = W.gk[el][3];
+        cc.pkey.a = W.pk[el][0]; cc.pkey.b = W.pk[el][1];
+        cc.steps = W.st[el][0]; cc.episode = W.st[el][1];
+        Key2 k2;
+        k2.a = k2.b = 0u;
+        if (cc.mode == COTIX_RNG_THREEFRY) k2 = tf_split(cc.gkey[d.g], (uint32_t)d.N2, (uint32_t)ind2);
+        heads = coin_heads(cc, d.g, d.N1, k2, ind2, ind1);
+      }
     }
+    const uint32_t hb = __ballot_sync(0xFFFFFFFFu, heads);
+    const uint32_t seg = (m >= 32 ? 0xFFFFFFFFu : ((1u << m) - 1u)) << (has ? task * m : 0);
+    const uint32_t mine = has ? (hb & seg) : 0u;
+    if (mine != 0u && lane == __ffs(mine) - 1) W.win[el][c] = (int8_t)q;
+    const bool requeue = has && off == 0 && mine == 0u && (int)t0 + m < total;
     __syncwarp();
-    head = min(head + 32, tail);
-    coll_push(W, tail, requeue, desc, mask, t + 1u);
+    head += T;
+    coll_push(W, tail, requeue, desc, mask, t0 + (uint32_t)m);
     __syncwarp();
   }
 }
@@ -462,7 +487,7 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
 }
 
 // ---- K_C2 ----------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPB)
+__global__ void __launch_bounds__(TPB, CX_FINISH_MINB)
 pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __restrict__ action,
                    float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
                    const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
