@@ -223,6 +223,7 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
 // leg/ground contacts persist) EPA + contact point, in one pass over the item queue.
 __global__ void __launch_bounds__(TPB)
 pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const uint32_t n = min(ws.ctr[CTR_ITEMS], ws.cap);
   const uint32_t stride = gridDim.x * TPB;
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
@@ -422,6 +423,7 @@ CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParam
 __global__ void __launch_bounds__(TPB)
 pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
                     const LunarDerived D, const PipeWs ws) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   __shared__ WarpColl Wall[TPB / 32];
   WarpColl& W = Wall[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
@@ -491,6 +493,7 @@ __global__ void __launch_bounds__(TPB, CX_FINISH_MINB)
 pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __restrict__ action,
                    float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
                    const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   bool want_reset = false;
   if (e < B) {
@@ -509,6 +512,7 @@ pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __
 __global__ void __launch_bounds__(TPB)
 pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
                   const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
+  cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const uint32_t n = ws.ctr[CTR_RESET];
   const uint32_t stride = gridDim.x * TPB;
   for (uint32_t r = blockIdx.x * TPB + threadIdx.x; r < n; r += stride) {
@@ -528,6 +532,7 @@ pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
 // stages: 0 integrate, 1 narrow, 2 contact, 3 finish, 4 reset, 5 whole step
 constexpr int N_STAGES = 6;
 bool g_profile = false;
+bool g_pdl = true;  // programmatic dependent launch between the stages
 cudaEvent_t g_evb[N_STAGES], g_eve[N_STAGES];
 bool g_ev_made = false;
 double g_stage_ms[N_STAGES];
@@ -622,22 +627,38 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
   if (prof) cudaEventRecord(g_evb[k], stream)
 #define CX_MARK_E(k, stream) \
   if (prof) cudaEventRecord(g_eve[k], stream)
+  // stages 2..5 are launched with programmatic stream serialization: their blocks may be set up
+  // while the previous stage drains, and wait in cudaGridDependencySynchronize() for its results
+  cudaLaunchAttribute pdl_attr[1];
+  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.blockDim = dim3(TPB);
+  cfg.stream = st;
+  cfg.attrs = pdl_attr;
+  cfg.numAttrs = (prof || !g_pdl) ? 0 : 1;
+#define CX_PDL_LAUNCH(kernel, grid, ...) \
+  do {                                   \
+    cfg.gridDim = dim3(grid);            \
+    cudaLaunchKernelEx(&cfg, kernel, __VA_ARGS__); \
+  } while (0)
   CX_MARK_B(5, st);
   CX_MARK_B(0, st);
   pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, sin_, sout, ld, action, *p, D, ws);
   CX_MARK_E(0, st);
   CX_MARK_B(1, st);
-  pipe_narrow_kernel<<<qgrid((int64_t)ws.cap), TPB, 0, st>>>(*p, D, ws);
+  CX_PDL_LAUNCH(pipe_narrow_kernel, qgrid((int64_t)ws.cap), *p, D, ws);
   CX_MARK_E(1, st);
   CX_MARK_B(2, st);
-  pipe_contact_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, *p, D, ws);
+  CX_PDL_LAUNCH(pipe_contact_kernel, qgrid(B), sout, ld, *p, D, ws);
   CX_MARK_E(2, st);
   CX_MARK_B(3, st);
-  pipe_finish_kernel<<<env_blocks, TPB, 0, st>>>(B, sout, ld, action, reward, done, obs, *p, ws);
+  CX_PDL_LAUNCH(pipe_finish_kernel, env_blocks, B, sout, ld, action, reward, done, obs, *p, ws);
   CX_MARK_E(3, st);
   CX_MARK_B(4, st);
   if (p->auto_reset) {
-    pipe_reset_kernel<<<qgrid(B), TPB, 0, st>>>(sout, ld, obs, *p, ws);
+    CX_PDL_LAUNCH(pipe_reset_kernel, qgrid(B), sout, ld, obs, *p, ws);
     cx_count_launch_n(5);
   } else {
     cx_count_launch_n(4);
@@ -646,9 +667,12 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
   CX_MARK_E(5, st);
 #undef CX_MARK_B
 #undef CX_MARK_E
+#undef CX_PDL_LAUNCH
   if (prof) g_ev_pending = true;
   return cx_check_launch("lunar pipeline");
 }
+
+extern "C" void cx_lunar_pipeline_set_pdl(int on) { g_pdl = on != 0; }
 
 // ---- per-stage timing (single-threaded use: bench.py) ----------------------------------------
 extern "C" int cx_lunar_pipeline_profiling() { return g_profile ? 1 : 0; }

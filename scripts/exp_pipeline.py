@@ -9,6 +9,9 @@ if os.environ.get("EXP_LIB"):  # time a variant build of the library (scripts on
 from parallax_b200 import lunar_lander as ll
 from gen_inputs import lunar_keys, perturbed_lunar_state
 
+if os.environ.get("EXP_NO_PDL"):
+    from parallax_b200 import _lib as _LL
+    _LL.lib().cx_lunar_pipeline_set_pdl(0)
 B = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 1 << 20
 for rng_mode in (0, 1):
     P = ll.default_params(judge_enabled=1, auto_reset=1, reset_perturb=1, max_episode_steps=1000, rng_mode=rng_mode)
