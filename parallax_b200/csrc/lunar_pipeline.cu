@@ -228,19 +228,46 @@ pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerive
   const uint32_t stride = gridDim.x * TPB;
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
   uint32_t hits = 0u;
-  for (uint32_t i = blockIdx.x * TPB + threadIdx.x; i < n; i += stride) {
-    const uint32_t it = ws.item[i];
-    if (it == 0xFFFFFFFFu) continue;
-    const uint32_t e = it >> 5;
-    Poly A, Bp;
-    RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
-    make_item_polys(src, (int)(it & 31u), P, A, Bp);
-    const Contact c = poly_pair(A, Bp, start, P.gjk_max_iters);
-    ws.res[0 * (size_t)ws.cap + i] = c.pen.x;
-    ws.res[1 * (size_t)ws.cap + i] = c.pen.y;
-    ws.res[2 * (size_t)ws.cap + i] = c.cp.x;
-    ws.res[3 * (size_t)ws.cap + i] = c.cp.y;
-    if (!contact_isnan(c)) ++hits;
+  // The 128 items a block takes are binned by pair class (leg-lander, ground-lander, ground-leg,
+  // leg-leg) through a counting sort in shared memory before they are handed to the threads, so
+  // that a warp mostly runs one kind of pair: same polygon sizes, same EPA trip bound, ground
+  // polygon built or not.  Results go to the item's own slot, so nothing downstream changes.
+  __shared__ uint32_t s_slot[TPB];
+  __shared__ uint32_t s_cnt[4];
+  for (uint32_t base = blockIdx.x * TPB; base < n; base += stride) {
+    if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t i0 = base + threadIdx.x;
+    uint32_t it0 = 0xFFFFFFFFu;
+    if (i0 < n) it0 = ws.item[i0];
+    int cls = -1;
+    uint32_t rank = 0u;
+    if (it0 != 0xFFFFFFFFu) {
+      const uint32_t pid = it0 & 31u;
+      cls = pid <= 1u ? 0 : (pid <= 8u ? 1 : (pid <= 10u ? 3 : 2));
+      rank = atomicAdd(&s_cnt[cls], 1u);
+    }
+    __syncthreads();
+    const uint32_t c0 = s_cnt[0], c1 = s_cnt[1], c2 = s_cnt[2], c3 = s_cnt[3];
+    if (cls >= 0) {
+      const uint32_t off = cls == 0 ? 0u : (cls == 1 ? c0 : (cls == 2 ? c0 + c1 : c0 + c1 + c2));
+      s_slot[off + rank] = i0;
+    }
+    __syncthreads();
+    if (threadIdx.x < c0 + c1 + c2 + c3) {
+      const uint32_t i = s_slot[threadIdx.x];
+      const uint32_t it = ws.item[i];
+      const uint32_t e = it >> 5;
+      Poly A, Bp;
+      RecPolys src{reinterpret_cast<const float4*>(ws.rec + (size_t)e * REC_FLOATS), D};
+      make_item_polys(src, (int)(it & 31u), P, A, Bp);
+      const Contact c = poly_pair(A, Bp, start, P.gjk_max_iters);
+      ws.res[0 * (size_t)ws.cap + i] = c.pen.x;
+      ws.res[1 * (size_t)ws.cap + i] = c.pen.y;
+      ws.res[2 * (size_t)ws.cap + i] = c.cp.x;
+      ws.res[3 * (size_t)ws.cap + i] = c.cp.y;
+      if (!contact_isnan(c)) ++hits;
+    }
   }
   // statistics only (scripts/exp_pipeline.py)
   hits = __reduce_add_sync(0xFFFFFFFFu, hits);
