@@ -541,6 +541,7 @@ CX_DEV void finish_step(EnvRegs& E, const CotixLunarParams& P, const float cs[3]
   info.lc = lc;
 }
 
+CX_DEV void lunar_reset_finish(EnvRegs& E, const uint32_t pert[8], const CotixLunarParams& P, uint32_t episode);
 // reset(key): LunarLander.__init__, cotix/_lunar_lander.py:29-143 (+ optional pose
 // perturbation, new).  Leaves E.key untouched; the caller owns the key chain.
 static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const CotixLunarParams& P,
@@ -576,6 +577,11 @@ static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const 
 #pragma unroll
     for (int i = 0; i < 8; ++i) pert[i] = w[12 + i];
   }
+  lunar_reset_finish(E, pert, P, episode);
+}
+// the part of reset(key) after the random draws: E.h[0..7] hold the uniform(-5, 5) heights, E.kn the
+// x-knots, pert the eight words of the pose perturbation
+CX_DEV void lunar_reset_finish(EnvRegs& E, const uint32_t pert[8], const CotixLunarParams& P, uint32_t episode) {
   E.h[0] = E.h[0] * 10.0f;
   E.h[3] = P.pad_y;
   E.h[4] = P.pad_y;
@@ -622,6 +628,69 @@ static __device__ __noinline__ void lunar_reset_env(EnvRegs& E, Key2 key, const 
   E.status = episode << 8;
   E.ret = 0.0f;
   E.shaping = CX_NAN;
+}
+// lunar_auto_reset for one env by EIGHT consecutive lanes (sub = lane & 7; all 32 lanes of the warp
+// must call it, `valid` says whether this group has an env).  The ~30 dependent threefry calls of
+// a reset (key chain, 8 heights, 4 knots, 4 perturbation pairs) are independent of each other, so
+// each lane takes its share — at most 8 in a row — and the group's first lane collects the draws
+// by shuffle and finishes.  Same calls, same arguments: same bits.  E is complete in lane sub == 0.
+CX_DEV void lunar_auto_reset_coop(EnvRegs& E, const CotixLunarParams& P, bool valid) {
+  const unsigned lane = threadIdx.x & 31u, sub = lane & 7u, g0 = lane & ~7u;
+  const uint32_t episode = ((E.status >> 8) + 1u) & 0xFFFFFFu;
+  Key2 rk = E.key;
+  float hv = 0.0f, kv = 0.0f;
+  uint32_t w0 = 0u, w1 = 0u, w2 = 0u, w3 = 0u;
+  if (valid) {
+    if (P.rng_mode == COTIX_RNG_THREEFRY) {
+      rk = tf_split(E.key, 2u, 1u);
+      if (sub == 0u) E.key = tf_split(E.key, 2u, 0u);
+      const Key2 k0 = tf_split(rk, 5u, 0u);
+      hv = bits_to_uniform(tf_bits_word(k0, 8u, sub), -5.0f, 5.0f);
+      if (sub < 4u) {
+        const float lo = sub == 0u ? -12.0f : (sub == 1u ? -8.0f : (sub == 2u ? 4.0f : 9.0f));
+        const float hi = sub == 0u ? -9.0f : (sub == 1u ? -4.0f : (sub == 2u ? 8.0f : 12.0f));
+        kv = tf_uniform(tf_split(rk, 5u, 1u + sub), lo, hi);
+      } else if (P.reset_perturb) {
+        const uint32_t i = sub - 4u;
+        const uint2 o = tf_call(rk.a, rk.b, 0x70657274u + i, i);
+        w0 = o.x;
+        w1 = o.y;
+      }
+    } else if (sub < 5u) {
+      uint32_t w[4];
+      philox4x32_10(P.philox_seed[0] ^ rk.a, P.philox_seed[1] ^ rk.b, 0u, episode, sub, CX_TAG_RESET, w);
+      w0 = w[0]; w1 = w[1]; w2 = w[2]; w3 = w[3];
+    }
+  }
+  uint32_t pert[8];
+  if (P.rng_mode == COTIX_RNG_THREEFRY) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) E.h[i] = __shfl_sync(0xFFFFFFFFu, hv, (int)g0 + i);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      E.kn[i] = __shfl_sync(0xFFFFFFFFu, kv, (int)g0 + i);
+      pert[2 * i] = __shfl_sync(0xFFFFFFFFu, w0, (int)g0 + 4 + i);
+      pert[2 * i + 1] = __shfl_sync(0xFFFFFFFFu, w1, (int)g0 + 4 + i);
+    }
+  } else {
+    uint32_t w[20];
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+      w[4 * q + 0] = __shfl_sync(0xFFFFFFFFu, w0, (int)g0 + q);
+      w[4 * q + 1] = __shfl_sync(0xFFFFFFFFu, w1, (int)g0 + q);
+      w[4 * q + 2] = __shfl_sync(0xFFFFFFFFu, w2, (int)g0 + q);
+      w[4 * q + 3] = __shfl_sync(0xFFFFFFFFu, w3, (int)g0 + q);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) E.h[i] = bits_to_uniform(w[i], -5.0f, 5.0f);
+    E.kn[0] = bits_to_uniform(w[8], -12.0f, -9.0f);
+    E.kn[1] = bits_to_uniform(w[9], -8.0f, -4.0f);
+    E.kn[2] = bits_to_uniform(w[10], 4.0f, 8.0f);
+    E.kn[3] = bits_to_uniform(w[11], 9.0f, 12.0f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) pert[i] = w[12 + i];
+  }
+  if (valid && sub == 0u) lunar_reset_finish(E, pert, P, episode);
 }
 // auto-reset of a finished env (same launch): fresh key from the chain, next episode number
 CX_DEV void lunar_auto_reset(EnvRegs& E, const CotixLunarParams& P) {

@@ -540,17 +540,29 @@ __global__ void __launch_bounds__(TPB)
 pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
                   const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
+  // eight lanes per finished env (lunar_auto_reset_coop): a reset is a chain of ~30 threefry calls,
+  // and this stage is pure latency (a few hundred envs per step)
   const uint32_t n = ws.ctr[CTR_RESET];
-  const uint32_t stride = gridDim.x * TPB;
-  for (uint32_t r = blockIdx.x * TPB + threadIdx.x; r < n; r += stride) {
-    const uint32_t e = ws.renv[r];
+  const uint32_t warp = (blockIdx.x * TPB + threadIdx.x) >> 5, nwarps = (gridDim.x * TPB) >> 5;
+  const uint32_t grp = (threadIdx.x & 31u) >> 3, sub = threadIdx.x & 7u;
+  for (uint32_t r0 = warp * 4u; r0 < n; r0 += nwarps * 4u) {
+    const uint32_t r = r0 + grp;
+    const bool valid = r < n;
+    uint32_t e = 0u;
     EnvRegs E;
-    E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
-    E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
-    E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
-    lunar_auto_reset(E, P);
-    store_env(E, s, ld, e, true);
-    if (obs) store_obs(E, obs, ld, e, false, false);
+    E.key.a = E.key.b = 0u;
+    E.status = 0u;
+    if (valid) {
+      e = ws.renv[r];
+      E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
+      E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
+      E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
+    }
+    lunar_auto_reset_coop(E, P, valid);
+    if (valid && sub == 0u) {
+      store_env(E, s, ld, e, true);
+      if (obs) store_obs(E, obs, ld, e, false, false);
+    }
   }
 }
 
