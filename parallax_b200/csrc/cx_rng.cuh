@@ -76,11 +76,24 @@ CX_DEV uint32_t tf_bits_word(Key2 key, uint32_t n, uint32_t w) {
   uint2 o = tf_call(key.a, key.b, c0, c1);
   return lo ? o.x : o.y;
 }
-// key `idx` of jax.random.split(key, num)
+// two independent blocks under one key in one out-of-line call: the scheduler interleaves the two
+// dependency chains, so a split costs the latency of one block instead of two
+static __device__ __noinline__ uint4 tf_call2(uint32_t k0, uint32_t k1, uint32_t a0, uint32_t a1, uint32_t b0,
+                                              uint32_t b1) {
+  uint32_t oa0, oa1, ob0, ob1;
+  threefry2x32(k0, k1, a0, a1, oa0, oa1);
+  threefry2x32(k0, k1, b0, b1, ob0, ob1);
+  return make_uint4(oa0, oa1, ob0, ob1);
+}
+// key `idx` of jax.random.split(key, num): words 2 idx and 2 idx + 1 of random_bits(key, 2 num)
 CX_DEV Key2 tf_split(Key2 key, uint32_t num, uint32_t idx) {
+  const uint32_t half = num, wa = 2u * idx, wb = wa + 1u;
+  const bool la = wa < half, lb = wb < half;
+  const uint4 o = tf_call2(key.a, key.b, la ? wa : wa - half, la ? half + wa : wa, lb ? wb : wb - half,
+                           lb ? half + wb : wb);
   Key2 r;
-  r.a = tf_bits_word(key, 2u * num, 2u * idx);
-  r.b = tf_bits_word(key, 2u * num, 2u * idx + 1u);
+  r.a = la ? o.x : o.y;
+  r.b = lb ? o.z : o.w;
   return r;
 }
 CX_DEV float bits_to_uniform(uint32_t bits, float lo, float hi) {
