@@ -106,6 +106,42 @@ def test_scene_analysis_matches_the_reference_grouping(cuda_lib_cpu):
     assert b"_contact_funcs" in L.cotix_last_error()
 
 
+def test_scene_create_argument_checks(cuda_lib_cpu):
+    """Limits and malformed descriptions are refused with COTIX_EINVAL and a message; a scene
+    analysed without a device cannot be stepped."""
+    from parallax_b200 import scene as sc
+
+    L = cuda_lib_cpu
+
+    def create(nb, props, pb, recs, device=-1):
+        h = C.c_void_p()
+        props = np.ascontiguousarray(props, np.float32); pb = np.ascontiguousarray(pb, np.int32)
+        recs = np.ascontiguousarray(recs, np.float32)
+        rc = L.cotix_scene_create(C.byref(h), device, nb, props.ctypes.data, pb.shape[0], pb.ctypes.data, recs.ctypes.data)
+        return rc, h
+
+    ball = sc.circle_rec(0.1, (0, 0))
+    ok_props = np.ones((21, 4), np.float32)
+    assert create(21, ok_props, [0], [ball])[0] == -1                      # more than COTIX_SCENE_MAX_BODIES
+    assert create(2, ok_props, [0] * 29, [ball] * 29)[0] == -1             # more than COTIX_SCENE_MAX_PARTS
+    assert create(2, ok_props, [0, 2], [ball, ball])[0] == -1              # part of a body that does not exist
+    bad = ball.copy(); bad[0] = 7
+    assert create(2, ok_props, [0, 1], [ball, bad])[0] == -1               # unknown shape type
+    tri = sc.polygon_rec([(0, 0), (1, 0), (0, 1)]); tri[1] = 9
+    assert create(2, ok_props, [0, 1], [ball, tri])[0] == -1               # polygon with 9 vertices
+    # 20 single-circle bodies: 190 pairs + 18 self cells fit; the entry lists are 190 long
+    rc, h = create(20, ok_props, list(range(20)), [ball] * 20)
+    assert rc == 0
+    ng, npairs, ev = C.c_int32(), C.c_int32(), C.c_int64()
+    assert L.cotix_scene_info(h, C.byref(ng), C.byref(npairs), C.byref(ev), None) == 0
+    assert (ng.value, npairs.value, ev.value) == (1, 190 + 18, 190 * 190)
+    # host-only analysis: stepping it is an error, not a crash
+    P = sc.SceneParams(); L.cotix_scene_default_params(C.byref(P))
+    assert L.cotix_scene_step(None, h, 1, None, 1, None, C.byref(P), None, None, None) == -1
+    assert L.cotix_scene_destroy(h) == 0
+    assert L.cotix_scene_destroy(None) == 0
+
+
 # ---------------------------------------------------------------------------------------------
 # GPU
 # ---------------------------------------------------------------------------------------------
