@@ -222,8 +222,9 @@ int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* stat
  * The same step run as a WAVEFRONT PIPELINE (csrc/lunar_pipeline.cu): 1 memset + 5 small dense
  * kernels with stream-compacted work queues in a caller-provided DEVICE workspace, instead of
  * one fused kernel.  Results are identical bit for bit; it is several times faster for large,
- * contact-rich batches.  Requires params->substeps == 1 (use cotix_lunar_step for K > 1) and
- * B < 2^27.  `workspace` must be 256-byte aligned and at least
+ * contact-rich batches.  K = params->substeps sub-steps run the four step stages K times (an env
+ * that finishes in a sub-step is frozen for the rest of the call, rewards add up) and the reset
+ * stage once.  Requires B < 2^27.  `workspace` must be 256-byte aligned and at least
  * cotix_lunar_workspace_bytes(B) long; its contents need not be preserved between calls.
  * Like every device entry point it only enqueues on `stream` and is CUDA-Graph capturable.
  */
@@ -254,7 +255,7 @@ typedef struct CotixLunarEnv CotixLunarEnv;
 int cotix_lunar_env_create(CotixLunarEnv** out, int device, int64_t B,
                            const CotixLunarParams* p);
 int cotix_lunar_env_destroy(CotixLunarEnv* env);
-/* launch strategy of the handle's steps: AUTO = pipeline when substeps == 1 and B >= 16384 */
+/* launch strategy of the handle's steps: AUTO = pipeline when B >= 16384 */
 #define COTIX_MODE_AUTO 0
 #define COTIX_MODE_FUSED 1
 #define COTIX_MODE_PIPELINE 2

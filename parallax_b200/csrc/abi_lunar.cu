@@ -261,7 +261,6 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
                         const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
   CXL_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
   CXL_REQUIRE(check_params(p), "bad params");
-  CXL_REQUIRE(p->substeps == 1, "the pipeline runs one sub-step per call (use cotix_lunar_step for K > 1)");
   CXL_REQUIRE(B == 0 || (state_in && state_out), "null state");
   return cx_launch_lunar_pipeline((cudaStream_t)stream, B, state_in, state_out, ld, action, reward, done,
                                   obs, p, workspace, workspace_bytes);
@@ -385,7 +384,6 @@ int cotix_lunar_env_destroy(CotixLunarEnv* e) {
 int cotix_lunar_env_set_mode(CotixLunarEnv* e, int mode) {
   CXL_REQUIRE(e != nullptr, "env is null");
   CXL_REQUIRE(mode == COTIX_MODE_AUTO || mode == COTIX_MODE_FUSED || mode == COTIX_MODE_PIPELINE, "bad mode");
-  CXL_REQUIRE(mode != COTIX_MODE_PIPELINE || e->P.substeps == 1, "the pipeline needs substeps == 1");
   if (e->mode != mode && e->graphs) {  // captured graphs embed the launch strategy
     for (auto& kv : *e->graphs) cudaGraphExecDestroy(kv.second);
     e->graphs->clear();
@@ -409,7 +407,7 @@ static int env_enqueue_range(CotixLunarEnv* e, int64_t off, int64_t n, const flo
                              float* obs_dev) {
   cudaStream_t stream = e->stream;
   const bool pipe = e->mode == COTIX_MODE_PIPELINE ||
-                    (e->mode == COTIX_MODE_AUTO && e->P.substeps == 1 && e->B >= 16384);
+                    (e->mode == COTIX_MODE_AUTO && e->B >= 16384);
   float* st = e->state + off;
   const float* act = action_dev ? action_dev + off : nullptr;
   float* ob = obs_dev ? obs_dev + off : nullptr;

@@ -56,6 +56,8 @@ struct PipeWs {
   uint32_t* hit;   // [cap] item slots whose GJK said yes
   uint32_t* cenv;  // [B] envs with at least one GJK hit
   uint32_t* renv;  // [B] envs to reset
+  float* racc;     // [B] reward accumulated over the sub-steps of this call (K > 1)
+  uint32_t* latch; // [B] done code | rc << 8 | lc << 9 of an env that finished in an earlier sub-step
   uint32_t cap;
 };
 
@@ -115,9 +117,11 @@ struct RecPolys {
 __global__ void __launch_bounds__(TPB, CX_INTEGRATE_MINB)
 pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__ sout, int64_t ld,
                       const float* __restrict__ action, const __grid_constant__ CotixLunarParams P,
-                      const LunarDerived D, const PipeWs ws) {
+                      const LunarDerived D, const PipeWs ws, int k, int K) {
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
-  const bool valid = e < B;
+  // sub-step k of K: an env that finished in an earlier sub-step of this call is frozen
+  // (cotix/_envs.py:81-103) — nothing of it is read, written or queued
+  const bool valid = e < B && !(k > 0 && (ws.latch[e] & 0xFFu) != 0u);
   const bool inplace = (sin_ == sout);
   uint32_t cand = 0u;
   int cnt = 0;
@@ -182,6 +186,7 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
     if ((int)lane >= d) incl += n;
   }
   const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+  if (e < B && !valid) ws.cand[e] = 0u;  // frozen
   if (total == 0) {
     if (valid) ws.cand[e] = 0u;
     return;
@@ -334,11 +339,14 @@ struct QueueContacts {
 };
 
 // key split, joints, judge and the stores of one env whose dynamic state and meta are in E
-// (cotix_lunar_step's tail); returns true when the env must be reset (auto-reset on).
+// (cotix_lunar_step's tail), for sub-step k of K: rewards add up over the sub-steps, an env that
+// finishes is latched (done code and leg contacts) and frozen, and reward / done / obs leave with
+// the last sub-step.  Returns true when the env must be reset (auto-reset on, last sub-step).
 CX_DEV bool finish_and_store(EnvRegs& E, int64_t e, float* __restrict__ s, int64_t ld,
                              const float* __restrict__ action, float* __restrict__ reward,
                              uint8_t* __restrict__ done, float* __restrict__ obs,
-                             const CotixLunarParams& P, bool crash, bool rc, bool lc) {
+                             const CotixLunarParams& P, bool crash, bool rc, bool lc, const PipeWs& ws, int k,
+                             int K) {
   float am = 0.0f, as = 0.0f;
   if (action) {
     am = action[e];
@@ -356,7 +364,16 @@ CX_DEV bool finish_and_store(EnvRegs& E, int64_t e, float* __restrict__ s, int64
     s[(i * 6 + 5) * ld + e] = E.b[i].w;
   }
   store_meta(E, s, ld, e);
-  if (reward) reward[e] = si.reward;
+  float rsum = si.reward;
+  if (K > 1) {
+    rsum = (k > 0 ? ws.racc[e] : 0.0f) + si.reward;
+    if (k + 1 < K) {
+      ws.racc[e] = rsum;
+      ws.latch[e] = (uint32_t)si.done | ((si.rc ? 1u : 0u) << 8) | ((si.lc ? 1u : 0u) << 9);
+      return false;
+    }
+  }
+  if (reward) reward[e] = rsum;
   if (done) done[e] = (uint8_t)si.done;
   const bool want_reset = (si.done != COTIX_DONE_NO) && P.auto_reset;
   if (obs && !want_reset) store_obs(E, obs, ld, e, si.rc, si.lc);
@@ -519,17 +536,32 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
 __global__ void __launch_bounds__(TPB, CX_FINISH_MINB)
 pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __restrict__ action,
                    float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
-                   const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
+                   const __grid_constant__ CotixLunarParams P, const PipeWs ws, int k, int K) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   bool want_reset = false;
   if (e < B) {
-    EnvRegs E;
-    load_dyn(E, s, ld, e);
-    load_meta(E, s, ld, e);
-    const uint32_t cw = ws.cand[e];
-    want_reset = finish_and_store(E, e, s, ld, action, reward, done, obs, P, (cw >> F_CRASH_SHIFT) & 1u,
-                                  (cw >> F_RC_SHIFT) & 1u, (cw >> F_LC_SHIFT) & 1u);
+    const uint32_t latch = k > 0 ? ws.latch[e] : 0u;
+    if ((latch & 0xFFu) != 0u) {
+      // finished in an earlier sub-step: frozen; its outputs leave with the last sub-step
+      if (k + 1 == K) {
+        if (reward) reward[e] = ws.racc[e];
+        if (done) done[e] = (uint8_t)(latch & 0xFFu);
+        want_reset = P.auto_reset != 0;
+        if (obs && !want_reset) {
+          EnvRegs E;
+          load_dyn(E, s, ld, e);
+          store_obs(E, obs, ld, e, ((latch >> 8) & 1u) != 0u, ((latch >> 9) & 1u) != 0u);
+        }
+      }
+    } else {
+      EnvRegs E;
+      load_dyn(E, s, ld, e);
+      load_meta(E, s, ld, e);
+      const uint32_t cw = ws.cand[e];
+      want_reset = finish_and_store(E, e, s, ld, action, reward, done, obs, P, (cw >> F_CRASH_SHIFT) & 1u,
+                                    (cw >> F_RC_SHIFT) & 1u, (cw >> F_LC_SHIFT) & 1u, ws, k, K);
+    }
   }
   const uint32_t slot = queue_push(&ws.ctr[CTR_RESET], want_reset);
   if (want_reset) ws.renv[slot] = (uint32_t)e;
@@ -612,7 +644,11 @@ size_t carve(int64_t B, void* base, PipeWs* ws) {
   uint32_t* hit = reinterpret_cast<uint32_t*>(take(cap * 4));
   uint32_t* cenv = reinterpret_cast<uint32_t*>(take((size_t)B * 4));
   uint32_t* renv = reinterpret_cast<uint32_t*>(take((size_t)B * 4));
+  float* racc = reinterpret_cast<float*>(take((size_t)B * 4));
+  uint32_t* latch = reinterpret_cast<uint32_t*>(take((size_t)B * 4));
   if (ws) {
+    ws->racc = racc;
+    ws->latch = latch;
     ws->ctr = ctr; ws->cand = cand; ws->base = bs; ws->rec = rec; ws->item = item; ws->res = res;
     ws->hit = hit; ws->cenv = cenv; ws->renv = renv; ws->cap = (uint32_t)cap;
   }
@@ -650,8 +686,8 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
     const int64_t cap = (int64_t)sms * 8;
     return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
   };
-  if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, st) != cudaSuccess) return cx_check_launch("pipeline memset");
-  const bool prof = g_profile;
+  const int K = p->substeps < 1 ? 1 : p->substeps;
+  const bool prof = g_profile && K == 1;
   if (prof) {
     profile_collect();
     if (!g_ev_made) {
@@ -683,24 +719,30 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
     cudaLaunchKernelEx(&cfg, kernel, __VA_ARGS__); \
   } while (0)
   CX_MARK_B(5, st);
-  CX_MARK_B(0, st);
-  pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, sin_, sout, ld, action, *p, D, ws);
-  CX_MARK_E(0, st);
-  CX_MARK_B(1, st);
-  CX_PDL_LAUNCH(pipe_narrow_kernel, qgrid((int64_t)ws.cap), *p, D, ws);
-  CX_MARK_E(1, st);
-  CX_MARK_B(2, st);
-  CX_PDL_LAUNCH(pipe_contact_kernel, qgrid(B), sout, ld, *p, D, ws);
-  CX_MARK_E(2, st);
-  CX_MARK_B(3, st);
-  CX_PDL_LAUNCH(pipe_finish_kernel, env_blocks, B, sout, ld, action, reward, done, obs, *p, ws);
-  CX_MARK_E(3, st);
+  // K sub-steps with the same action (cotix/_envs.py:72-103: WFE_scale forward steps per control):
+  // the four step stages K times — sub-steps after the first run in place on the output state —
+  // then one reset stage
+  for (int k = 0; k < K; ++k) {
+    if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, st) != cudaSuccess) return cx_check_launch("pipeline memset");
+    CX_MARK_B(0, st);
+    pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, k == 0 ? sin_ : sout, sout, ld, action, *p, D, ws, k, K);
+    CX_MARK_E(0, st);
+    CX_MARK_B(1, st);
+    CX_PDL_LAUNCH(pipe_narrow_kernel, qgrid((int64_t)ws.cap), *p, D, ws);
+    CX_MARK_E(1, st);
+    CX_MARK_B(2, st);
+    CX_PDL_LAUNCH(pipe_contact_kernel, qgrid(B), sout, ld, *p, D, ws);
+    CX_MARK_E(2, st);
+    CX_MARK_B(3, st);
+    CX_PDL_LAUNCH(pipe_finish_kernel, env_blocks, B, sout, ld, action, reward, done, obs, *p, ws, k, K);
+    CX_MARK_E(3, st);
+  }
   CX_MARK_B(4, st);
   if (p->auto_reset) {
     CX_PDL_LAUNCH(pipe_reset_kernel, qgrid(B), sout, ld, obs, *p, ws);
-    cx_count_launch_n(5);
+    cx_count_launch_n(4 * K + 1);
   } else {
-    cx_count_launch_n(4);
+    cx_count_launch_n(4 * K);
   }
   CX_MARK_E(4, st);
   CX_MARK_E(5, st);

@@ -128,7 +128,7 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
     reference's unactuated step.  Functional by default (a new state tensor), like the
     reference; `inplace=True` updates `state` (what a CUDA-graph rollout wants).
     mode: "fused" = one kernel (cotix_lunar_step), "pipeline" = the wavefront pipeline
-    (cotix_lunar_step_ws; substeps must be 1), "auto" = pipeline for B >= 16384 at K = 1.
+    (cotix_lunar_step_ws), "auto" = pipeline for B >= 16384.
     Both give identical results.
     """
     params = params or default_params()
@@ -142,7 +142,7 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
         action = action.to(device=d.device, dtype=torch.float32).contiguous()
         assert action.shape == (2, B)
     m = _MODES[mode]
-    use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and params.substeps == 1 and B >= PIPELINE_MIN_ENVS)
+    use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and B >= PIPELINE_MIN_ENVS)
     with torch.cuda.device(d.device):
         args = (_stream_ptr(d.device), B, d.data_ptr(), out.data_ptr(), d.stride(0),
                 action.data_ptr() if action is not None else None, reward.data_ptr(), done.data_ptr(),
