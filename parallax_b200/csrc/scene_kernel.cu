@@ -17,6 +17,7 @@
 // mode function of (group, ind2, ind1), so skipping the others changes nothing), then runs the
 // per-body choice (:274-295) and the sequential resolve scan (:310-336).
 #include <cstring>
+#include <algorithm>
 #include <new>
 #include <vector>
 
@@ -60,13 +61,13 @@ struct SceneDesc {
   uint8_t pair_id[MAXP][MAXP];               // (part of list 0, part of list 1) -> pair or 0xFF
   int32_t g_n[MAXG], g_off[MAXG];            // entries of group g: ent0/ent1[g_off .. g_off + g_n)
   uint8_t ent0[MAXENT], ent1[MAXENT];        // part id of the k-th entry of list 0 / list 1
-  // all_contacts cells that have grid entries: for cell c = (i, j) the distinct pairs that can
-  // land in it and its grid entries in DESCENDING scan order (group, ind2, ind1), each packed as
-  // pair | ind1 << 8 | ind2 << 16 | group << 24 (device arrays of the scene)
+  // all_contacts cells that have grid entries: cell c = (i, j) holds its grid entries in
+  // DESCENDING scan order (group, ind2, ind1), each packed as
+  // pair | ind1 << 8 | ind2 << 16 | group << 24 (device arrays of the scene).  The distinct pairs
+  // are numbered in cell order, so the pairs of one cell are consecutive.
   int32_t ncells;
+  uint16_t pair_cell[MAXPAIR];  // pair -> its cell
   const uint16_t* cell_ij;      // [ncells] i << 8 | j
-  const int32_t* cell_pair_off; // [ncells + 1] into cell_pairs
-  const uint8_t* cell_pairs;
   const int32_t* cell_ent_off;  // [ncells + 1] into cell_ents
   const uint32_t* cell_ents;
 };
@@ -165,22 +166,24 @@ static __device__ __noinline__ Contact contact_of(const WPart& a, const WPart& b
   return aabb_vs_aabb(wp_box(a), wp_box(b));
 }
 
-// jr.choice(key, nb, p=probs) for one body: cumsum / uniform / searchsorted(side='left')
-CX_DEV int choose_generic(const bool* live, int nb, float u) {
-  int cnt = 0;
-  for (int j = 0; j < nb; ++j) cnt += live[j] ? 1 : 0;
-  const float fc = (float)cnt;
-  float cum[MAXB];
+// jr.choice(key, nb, p=probs) for one body: cumsum / uniform / searchsorted(side='left').
+// probs[j] is 1/cnt on the live cells (bit j of `live`) and 0/cnt = 0 elsewhere.
+CX_DEV int choose_generic(uint32_t live, int nb, float u) {
+  const float fc = (float)__popc(live);
+  const float p1 = 1.0f / fc;
+  float total = 0.0f;
+  for (int j = 0; j < nb; ++j) {
+    const float p = ((live >> j) & 1u) ? p1 : 0.0f;
+    total = (j == 0) ? p : total + p;
+  }
+  const float r = total * (1.0f - u);
+  int ind = 0;
   float acc = 0.0f;
   for (int j = 0; j < nb; ++j) {
-    const float p = (live[j] ? 1.0f : 0.0f) / fc;
+    const float p = ((live >> j) & 1u) ? p1 : 0.0f;
     acc = (j == 0) ? p : acc + p;
-    cum[j] = acc;
+    if (acc < r) ++ind;
   }
-  const float r = cum[nb - 1] * (1.0f - u);
-  int ind = 0;
-  for (int j = 0; j < nb; ++j)
-    if (cum[j] < r) ++ind;
   return ind >= nb ? nb - 1 : ind;  // jnp indexing clamps
 }
 
@@ -218,19 +221,32 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
     if ((int)S->rec[q][0] == COTIX_SHAPE_POLYGON) cx_sincosf(body[b].ang, &sn, &cs);
     world_part(S->rec[q], body[b].px, body[b].py, cs, sn, W[q].v, W[q].type, W[q].n, W[q].radius);
   }
-  // distinct narrowphase evaluations
+  // distinct narrowphase evaluations.  A contact is live when its contact point is not NaN
+  // (:255-262); the cells with a live contact are collected on the way (the pairs of a cell are
+  // consecutive), so nothing later scans the whole cell table.
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
   float cpen[MAXPAIR][2], ccp[MAXPAIR][2];
+  constexpr int LIVE_CAP = 64;
+  uint16_t lcell[LIVE_CAP];
+  int nlive = 0, last_cell = -1;
+  bool spill = false;  // more live cells than LIVE_CAP: fall back to a scan of the cell table
   for (int q = 0; q < npairs; ++q) {
     const Contact c = contact_of(W[S->pair_a[q]], W[S->pair_b[q]], start, P.gjk_max_iters);
-    cpen[q][0] = c.pen.x; cpen[q][1] = c.pen.y;
     ccp[q][0] = c.cp.x; ccp[q][1] = c.cp.y;
     status |= c.status;
+    if ((c.cp.x != c.cp.x) || (c.cp.y != c.cp.y)) continue;
+    cpen[q][0] = c.pen.x; cpen[q][1] = c.pen.y;
+    const int cc = S->pair_cell[q];
+    if (cc == last_cell) continue;
+    last_cell = cc;
+    if (nlive < LIVE_CAP) lcell[nlive++] = (uint16_t)cc;
+    else spill = true;
   }
-  // coin-flip scatter into all_contacts (:208-268): the last heads in (ind2, ind1) order wins
-  int16_t all[MAXB][MAXB];
-  for (int i = 0; i < nb; ++i)
-    for (int j = 0; j < nb; ++j) all[i][j] = -1;
+  // coin-flip scatter into all_contacts (:208-268): the last heads in (ind2, ind1) order wins.
+  // row[i] bit j = all_contacts[i][j] is live; allq[i][j] is its pair (written only when live).
+  uint32_t row[MAXB];
+  uint8_t allq[MAXB][MAXB];
+  for (int i = 0; i < nb; ++i) row[i] = 0u;
   Key2 rkey;
   rkey.a = keys[e];
   rkey.b = keys[ld + e];
@@ -245,41 +261,63 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
   // live, in (group, ind2, ind1) order, so the cell ends up with the LAST such entry.  Every
   // coin is a counter-mode function of its (group, ind2, ind1), hence: walk the entries of a
   // cell from the last backwards, skip dead contacts, stop at the first heads.
-  for (int c = 0; c < S->ncells; ++c) {
-    bool any = false;
-    for (int k = S->cell_pair_off[c]; k < S->cell_pair_off[c + 1]; ++k) {
-      const int q = S->cell_pairs[k];
-      any = any || !((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1]));
-    }
-    if (!any) continue;
-    const int ij = S->cell_ij[c];
-    for (int k = S->cell_ent_off[c]; k < S->cell_ent_off[c + 1]; ++k) {
-      const uint32_t ent = S->cell_ents[k];
-      const int q = (int)(ent & 0xFFu);
-      if ((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1])) continue;  // NaN contact
+  //
+  // A coin costs ~700 instructions and the number of coins per cell is geometric, so the walk is
+  // ONE flat loop over (live cell, entry): every trip flips one coin in every lane that still has
+  // one to flip, whichever of its cells that lane has reached.  (A loop per cell would run
+  // max-over-lanes trips for every cell.)
+  {
+    int t = 0, k = 0, kend = 0, ij = 0, scan = 0;
+    uint32_t c_g = 0xFFFFFFFFu, c_ind2 = 0u;  // the (group, ind2) that k2 below belongs to
+    Key2 k2 = rkey;
+    for (;;) {
+      uint32_t ent = 0u;
+      int q = 0;
+      bool have = false;
+      while (!have) {
+        if (k >= kend) {  // next live cell
+          int c;
+          if (!spill) {
+            if (t >= nlive) break;
+            c = lcell[t++];
+          } else {
+            if (scan >= S->ncells) break;
+            c = scan++;
+          }
+          k = S->cell_ent_off[c];
+          kend = S->cell_ent_off[c + 1];
+          ij = S->cell_ij[c];
+          continue;
+        }
+        ent = S->cell_ents[k++];
+        q = (int)(ent & 0xFFu);
+        have = !((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1]));
+      }
+      if (!have) break;
       const uint32_t ind1 = (ent >> 8) & 0xFFu, ind2 = (ent >> 16) & 0xFFu, g = ent >> 24;
       const uint32_t n = (uint32_t)S->g_n[g];
-      const Key2 k2 = tf_split(gk[g], n, ind2);
+      if (g != c_g || ind2 != c_ind2) {
+        k2 = tf_split(gk[g], n, ind2);
+        c_g = g;
+        c_ind2 = ind2;
+      }
       const Key2 k1 = tf_split(k2, n, ind1);
       const Key2 kk = tf_split(k1, 2u, 0u);
       if (tf_bernoulli(kk, P.coin_p)) {
-        all[ij >> 8][ij & 0xFF] = (int16_t)q;
-        break;
+        row[ij >> 8] |= 1u << (ij & 0xFF);
+        allq[ij >> 8][ij & 0xFF] = (uint8_t)q;
+        k = kend;
       }
     }
   }
   // choose_random_contact (:274-295)
   int chosen[MAXB];
   for (int i = 0; i < nb; ++i) {
-    bool live[MAXB];
-    int cnt = 0;
-    for (int j = 0; j < nb; ++j) {
-      live[j] = all[i][j] >= 0;
-      cnt += live[j] ? 1 : 0;
-      if (cell) cell[(int64_t)(i * nb + j) * ld + e] = live[j] ? 1 : 0;
-    }
+    const uint32_t live = row[i];
+    if (cell)
+      for (int j = 0; j < nb; ++j) cell[(int64_t)(i * nb + j) * ld + e] = (uint8_t)((live >> j) & 1u);
     int idx = i;
-    if (cnt != 0) idx = choose_generic(live, nb, tf_uniform(tf_split(skey, (uint32_t)nb, (uint32_t)i), 0.0f, 1.0f));
+    if (live != 0u) idx = choose_generic(live, nb, tf_uniform(tf_split(skey, (uint32_t)nb, (uint32_t)i), 0.0f, 1.0f));
     chosen[i] = idx;
     if (chosen_out) chosen_out[(int64_t)i * ld + e] = idx;
   }
@@ -287,8 +325,8 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
   for (int i = 0; i < nb; ++i) {
     const int j = chosen[i];
     if (i == j) continue;
-    const int q = all[i][j];
-    if (q < 0) continue;  // NaN contact: resolve_collision returns the bodies unchanged
+    if (!((row[i] >> j) & 1u)) continue;  // NaN contact: resolve_collision returns the bodies unchanged
+    const int q = allq[i][j];
     resolve_collision(body[i], mass[i], body[j], mass[j], mk2(cpen[q][0], cpen[q][1]),
                       mk2(ccp[q][0], ccp[q][1]), P.baumgarte, P.baumgarte_dt);
   }
@@ -431,11 +469,27 @@ int cotix_scene_create(CotixScene** out, int device, int32_t nb, const float* bo
       }
   }
   S.npairs = npairs;
+  {
+    // renumber the pairs in cell order (body_a, body_b), stable inside a cell
+    std::vector<int> order((size_t)npairs);
+    for (int q = 0; q < npairs; ++q) order[(size_t)q] = q;
+    auto cell_of = [&](int q) { return (int)S.part_body[S.pair_a[q]] * nb + (int)S.part_body[S.pair_b[q]]; };
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return cell_of(x) < cell_of(y); });
+    uint8_t na[MAXPAIR], nbp[MAXPAIR];
+    for (int q = 0; q < npairs; ++q) {
+      na[q] = S.pair_a[order[(size_t)q]];
+      nbp[q] = S.pair_b[order[(size_t)q]];
+    }
+    for (int q = 0; q < npairs; ++q) {
+      S.pair_a[q] = na[q];
+      S.pair_b[q] = nbp[q];
+      S.pair_id[na[q]][nbp[q]] = (uint8_t)q;
+    }
+  }
   sc->n_evals = evals;
   sc->device = device;
   sc->dev = nullptr;
-  // per-cell pair lists and grid entries (ascending here, reversed below)
-  std::vector<std::vector<uint8_t>> cpairs((size_t)nb * nb);
+  // per-cell grid entries (ascending here, reversed below)
   std::vector<std::vector<uint32_t>> cents((size_t)nb * nb);
   for (int g = 0; g < ng; ++g) {
     const int n = S.g_n[g];
@@ -445,49 +499,39 @@ int cotix_scene_create(CotixScene** out, int device, int32_t nb, const float* bo
         const int q = S.pair_id[pa][pb];
         if (q == 0xFF) continue;  // i < j: NaN (:163)
         const size_t c = (size_t)S.part_body[pa] * nb + S.part_body[pb];
-        bool seen = false;
-        for (uint8_t x : cpairs[c]) seen = seen || x == q;
-        if (!seen) cpairs[c].push_back((uint8_t)q);
         cents[c].push_back((uint32_t)q | ((uint32_t)ind1 << 8) | ((uint32_t)ind2 << 16) | ((uint32_t)g << 24));
       }
   }
   std::vector<uint16_t> h_ij;
-  std::vector<int32_t> h_poff(1, 0), h_eoff(1, 0);
-  std::vector<uint8_t> h_pairs;
+  std::vector<int32_t> h_eoff(1, 0);
   std::vector<uint32_t> h_ents;
   for (int i = 0; i < nb; ++i)
     for (int j = 0; j < nb; ++j) {
       const size_t c = (size_t)i * nb + j;
       if (cents[c].empty()) continue;
+      for (uint32_t ent : cents[c]) S.pair_cell[ent & 0xFFu] = (uint16_t)h_ij.size();
       h_ij.push_back((uint16_t)((i << 8) | j));
-      h_pairs.insert(h_pairs.end(), cpairs[c].begin(), cpairs[c].end());
       h_ents.insert(h_ents.end(), cents[c].rbegin(), cents[c].rend());
-      h_poff.push_back((int32_t)h_pairs.size());
       h_eoff.push_back((int32_t)h_ents.size());
     }
   S.ncells = (int32_t)h_ij.size();
   if (device >= 0) {
-    // one device block: [SceneDesc | cell_ij | cell_pair_off | cell_ent_off | cell_ents | cell_pairs]
+    // one device block: [SceneDesc | cell_ij | cell_ent_off | cell_ents]
     auto al = [](size_t x) { return (x + 15) / 16 * 16; };
-    const size_t o_ij = al(sizeof(SceneDesc)), o_poff = o_ij + al(2 * h_ij.size()),
-                 o_eoff = o_poff + al(4 * h_poff.size()), o_ents = o_eoff + al(4 * h_eoff.size()),
-                 o_pairs = o_ents + al(4 * h_ents.size()), total = o_pairs + al(h_pairs.size());
+    const size_t o_ij = al(sizeof(SceneDesc)), o_eoff = o_ij + al(2 * h_ij.size()),
+                 o_ents = o_eoff + al(4 * h_eoff.size()), total = o_ents + al(4 * h_ents.size());
     std::vector<char> blob(total, 0);
     cudaError_t ce = cudaSetDevice(device);
     char* d = nullptr;
     if (ce == cudaSuccess) ce = cudaMalloc(&d, total);
     if (ce == cudaSuccess) {
       S.cell_ij = reinterpret_cast<const uint16_t*>(d + o_ij);
-      S.cell_pair_off = reinterpret_cast<const int32_t*>(d + o_poff);
       S.cell_ent_off = reinterpret_cast<const int32_t*>(d + o_eoff);
       S.cell_ents = reinterpret_cast<const uint32_t*>(d + o_ents);
-      S.cell_pairs = reinterpret_cast<const uint8_t*>(d + o_pairs);
       memcpy(blob.data(), &S, sizeof(SceneDesc));
       memcpy(blob.data() + o_ij, h_ij.data(), 2 * h_ij.size());
-      memcpy(blob.data() + o_poff, h_poff.data(), 4 * h_poff.size());
       memcpy(blob.data() + o_eoff, h_eoff.data(), 4 * h_eoff.size());
       memcpy(blob.data() + o_ents, h_ents.data(), 4 * h_ents.size());
-      memcpy(blob.data() + o_pairs, h_pairs.data(), h_pairs.size());
       sc->dev = reinterpret_cast<SceneDesc*>(d);
       ce = cudaMemcpy(d, blob.data(), total, cudaMemcpyHostToDevice);
     }

@@ -285,3 +285,26 @@ def test_cuda_scene_step_mixed_shapes_vs_oracle(cuda_lib, oracle, exact_trig):
     keys = np.stack([np.arange(B, dtype=np.uint32) * 3 + 1, np.arange(B, dtype=np.uint32)], 1)
     hits = _run_against_oracle(oracle, spec, st, keys, steps=6)
     assert hits > 1000
+
+
+@pytest.mark.gpu
+def test_cuda_scene_step_pile_of_circles_overflows_the_live_cell_list(cuda_lib, oracle, exact_trig):
+    """14 circles dropped on one spot: every one of the 105 cells (i >= j) is live, more than the
+    kernel's per-env list of live cells holds, so half of the envs take the table-scan path; the
+    other half are spread out and have only their self contacts."""
+    from parallax_b200 import scene as sc
+
+    nb = 14
+    props = np.tile(np.array([[1.0, 0.3, 0.8, 0.4]], np.float32), (nb, 1))
+    props[:, 0] += np.arange(nb, dtype=np.float32) * 0.25
+    recs = np.stack([sc.circle_rec(0.3 + 0.01 * i, (0, 0)) for i in range(nb)])
+    spec = sc.SceneSpec([f"c{i}" for i in range(nb)], props, np.arange(nb, dtype=np.int32), recs,
+                        np.zeros((nb, 6), np.float32))
+    rng = np.random.default_rng(35)
+    B = 64
+    st = _random_states(spec, B, rng, ((-0.05, 0.05), (-0.05, 0.05)))
+    far = _random_states(spec, B, rng, ((-40.0, 40.0), (-40.0, 40.0)))
+    st[:, :, 1::2] = far[:, :, 1::2]
+    keys = np.stack([np.full(B, 5, np.uint32), np.arange(B, dtype=np.uint32) + 9], 1)
+    hits = _run_against_oracle(oracle, spec, st, keys, steps=3)
+    assert hits > 32 * 100
