@@ -300,15 +300,14 @@ CX_DEV bool contact_isnan(const Contact& c) { return isnan2(c.cp); }
 CX_DEV Contact circle_vs_circle(const Circ& a, const Circ& b) {  // :30-58
   V2 delta = a.c - b.c;
   float distance = norm2(delta);
+  Contact c = contact_none();
+  if (!(distance <= a.r + b.r)) return c;  // nothing below is kept when the circles are apart
   V2 dir = (distance == 0.0f) ? mk2(1.0f, 0.0f) : delta / distance;
   V2 pv = dir * jmin(distance - (a.r + b.r), 0.0f);
   V2 cp = (b.c + dir * (b.r - a.r) + a.c) / 2.0f;
   if (!(dot2(a.c - cp, b.c - cp) <= 0)) cp = contains(a, b.c) ? b.c : a.c;
-  Contact c = contact_none();
-  if (distance <= a.r + b.r) {
-    c.pen = -pv;
-    c.cp = cp;
-  }
+  c.pen = -pv;
+  c.cp = cp;
   return c;
 }
 
@@ -341,9 +340,9 @@ CX_DEV Contact circle_vs_aabb(const Circ& a, const Box& b) {  // :99-154
   V2 ccp = bc + cd;
   Contact c = contact_none();
   if (!contains(b, ccp)) c.status |= CX_ST_CCP_ERR;
-  bool pv = (norm2(b.lo - ccp) < eps) || (norm2(mk2(b.lo.x, b.hi.y) - ccp) < eps) ||
-            (norm2(b.hi - ccp) < eps) || (norm2(mk2(b.hi.x, b.lo.y) - ccp) < eps);
   if (contains(a, ccp)) {
+    bool pv = (norm2(b.lo - ccp) < eps) || (norm2(mk2(b.lo.x, b.hi.y) - ccp) < eps) ||
+              (norm2(b.hi - ccp) < eps) || (norm2(mk2(b.hi.x, b.lo.y) - ccp) < eps);
     if (pv) {
       V2 dir = ccp - a.c;
       V2 dn = dir / norm2(dir);

@@ -84,11 +84,8 @@ CX_DEV void sort_generic(Poly& p) {
 
 // part.transform(transformer of the body): circles and boxes translate only (the angle is
 // ignored, cotix/_convex_shapes.py:37-41, 113-117); polygons rotate, translate and re-sort
-CX_DEV void world_part(const float* r, float px, float py, float c, float s, float out[12], int& type,
-                       int& n, float& radius) {
-  type = (int)r[0];
-  n = (int)r[1];
-  radius = r[2];
+CX_DEV void world_part(const float* r, float px, float py, float c, float s, float out[12]) {
+  const int type = (int)r[0], n = (int)r[1];
   if (type == COTIX_SHAPE_CIRCLE) {
     out[0] = r[4] + px;
     out[1] = r[5] + py;
@@ -119,18 +116,20 @@ CX_DEV void world_part(const float* r, float px, float py, float c, float s, flo
       out[2 * k] = p.x[k];
       out[2 * k + 1] = p.y[k];
     }
-    n = p.n;
   }
 }
 
+// a part in world coordinates; type, vertex count and radius are the scene's (rec[0..2])
 struct WPart {
   float v[12];
-  int type, n;
-  float radius;
 };
-CX_DEV Poly wp_poly(const WPart& w) {
+CX_DEV int rec_n(const float* r) {
+  const int n = (int)r[1];
+  return n < 1 ? 1 : (n > CX_MAXV ? CX_MAXV : n);
+}
+CX_DEV Poly wp_poly(const WPart& w, const float* r) {
   Poly p;
-  p.n = w.n;
+  p.n = rec_n(r);
 #pragma unroll
   for (int k = 0; k < CX_MAXV; ++k) {
     p.x[k] = w.v[2 * k];
@@ -138,10 +137,10 @@ CX_DEV Poly wp_poly(const WPart& w) {
   }
   return p;
 }
-CX_DEV Circ wp_circ(const WPart& w) {
+CX_DEV Circ wp_circ(const WPart& w, const float* r) {
   Circ c;
   c.c = mk2(w.v[0], w.v[1]);
-  c.r = w.radius;
+  c.r = r[2];
   return c;
 }
 CX_DEV Box wp_box(const WPart& w) {
@@ -153,16 +152,18 @@ CX_DEV Box wp_box(const WPart& w) {
 
 // _contact_funcs[(type(a), type(b))](a, b), cotix/_colliders.py:21-35 (the host has checked that
 // every pair of the scene is a key in this order)
-static __device__ __noinline__ Contact contact_of(const WPart& a, const WPart& b, V2 start, int gjk_max) {
-  const int ta = a.type, tb = b.type;
+static __device__ __noinline__ Contact contact_of(const WPart& a, const float* ra, const WPart& b,
+                                                  const float* rb, V2 start, int gjk_max) {
+  const int ta = (int)ra[0], tb = (int)rb[0];
   if (ta == COTIX_SHAPE_POLYGON && tb == COTIX_SHAPE_POLYGON)
-    return convex_vs_polygon(wp_poly(a), wp_poly(b), start, gjk_max);
+    return convex_vs_polygon(wp_poly(a, ra), wp_poly(b, rb), start, gjk_max);
   if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_POLYGON)
-    return circle_vs_polygon<131>(wp_circ(a), wp_poly(b), start, gjk_max, 128);
+    return circle_vs_polygon<131>(wp_circ(a, ra), wp_poly(b, rb), start, gjk_max, 128);
   if (ta == COTIX_SHAPE_AABB && tb == COTIX_SHAPE_POLYGON)
-    return convex_vs_polygon(wp_box(a), wp_poly(b), start, gjk_max);
-  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_CIRCLE) return circle_vs_circle(wp_circ(a), wp_circ(b));
-  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_AABB) return circle_vs_aabb(wp_circ(a), wp_box(b));
+    return convex_vs_polygon(wp_box(a), wp_poly(b, rb), start, gjk_max);
+  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_CIRCLE)
+    return circle_vs_circle(wp_circ(a, ra), wp_circ(b, rb));
+  if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_AABB) return circle_vs_aabb(wp_circ(a, ra), wp_box(b));
   return aabb_vs_aabb(wp_box(a), wp_box(b));
 }
 
@@ -187,7 +188,10 @@ CX_DEV int choose_generic(uint32_t live, int nb, float u) {
   return ind >= nb ? nb - 1 : ind;  // jnp indexing clamps
 }
 
-__global__ void __launch_bounds__(128)
+#ifndef CXS_MINB
+#define CXS_MINB 8
+#endif
+__global__ void __launch_bounds__(128, CXS_MINB)
 scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict__ state, int64_t ld,
                   uint32_t* __restrict__ keys, const CotixSceneParams P, uint8_t* __restrict__ cell,
                   int32_t* __restrict__ chosen_out, uint32_t* __restrict__ status_out) {
@@ -195,7 +199,6 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
   if (e >= B) return;
   const int nb = S->nb, nparts = S->nparts, npairs = S->npairs;
   BodyS body[MAXB];
-  MassP mass[MAXB];
   for (int b = 0; b < nb; ++b) {
     body[b].px = state[(b * 6 + 0) * ld + e];
     body[b].py = state[(b * 6 + 1) * ld + e];
@@ -203,10 +206,6 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
     body[b].vy = state[(b * 6 + 3) * ld + e];
     body[b].ang = state[(b * 6 + 4) * ld + e];
     body[b].w = state[(b * 6 + 5) * ld + e];
-    mass[b].mass = S->props[b][0];
-    mass[b].inertia = S->props[b][1];
-    mass[b].e = S->props[b][2];
-    mass[b].mu = S->props[b][3];
     // ExplicitEulerPhysics._single_body_step
     body[b].px = body[b].px + body[b].vx * P.dt;
     body[b].py = body[b].py + body[b].vy * P.dt;
@@ -219,7 +218,7 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
     const int b = S->part_body[q];
     float sn = 0.0f, cs = 1.0f;  // only polygons rotate
     if ((int)S->rec[q][0] == COTIX_SHAPE_POLYGON) cx_sincosf(body[b].ang, &sn, &cs);
-    world_part(S->rec[q], body[b].px, body[b].py, cs, sn, W[q].v, W[q].type, W[q].n, W[q].radius);
+    world_part(S->rec[q], body[b].px, body[b].py, cs, sn, W[q].v);
   }
   // distinct narrowphase evaluations.  A contact is live when its contact point is not NaN
   // (:255-262); the cells with a live contact are collected on the way (the pairs of a cell are
@@ -230,11 +229,15 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
   uint16_t lcell[LIVE_CAP];
   int nlive = 0, last_cell = -1;
   bool spill = false;  // more live cells than LIVE_CAP: fall back to a scan of the cell table
+  uint32_t lm[(MAXPAIR + 31) / 32];  // bit q: contact q is live (only live contacts are stored)
+  for (int w = 0; w < (MAXPAIR + 31) / 32; ++w) lm[w] = 0u;
   for (int q = 0; q < npairs; ++q) {
-    const Contact c = contact_of(W[S->pair_a[q]], W[S->pair_b[q]], start, P.gjk_max_iters);
-    ccp[q][0] = c.cp.x; ccp[q][1] = c.cp.y;
+    const int pa = S->pair_a[q], pb = S->pair_b[q];
+    const Contact c = contact_of(W[pa], S->rec[pa], W[pb], S->rec[pb], start, P.gjk_max_iters);
     status |= c.status;
     if ((c.cp.x != c.cp.x) || (c.cp.y != c.cp.y)) continue;
+    lm[q >> 5] |= 1u << (q & 31);
+    ccp[q][0] = c.cp.x; ccp[q][1] = c.cp.y;
     cpen[q][0] = c.pen.x; cpen[q][1] = c.pen.y;
     const int cc = S->pair_cell[q];
     if (cc == last_cell) continue;
@@ -291,7 +294,7 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
         }
         ent = S->cell_ents[k++];
         q = (int)(ent & 0xFFu);
-        have = !((ccp[q][0] != ccp[q][0]) || (ccp[q][1] != ccp[q][1]));
+        have = (lm[q >> 5] >> (q & 31)) & 1u;
       }
       if (!have) break;
       const uint32_t ind1 = (ent >> 8) & 0xFFu, ind2 = (ent >> 16) & 0xFFu, g = ent >> 24;
@@ -327,7 +330,10 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
     if (i == j) continue;
     if (!((row[i] >> j) & 1u)) continue;  // NaN contact: resolve_collision returns the bodies unchanged
     const int q = allq[i][j];
-    resolve_collision(body[i], mass[i], body[j], mass[j], mk2(cpen[q][0], cpen[q][1]),
+    MassP mi, mj;
+    mi.mass = S->props[i][0]; mi.inertia = S->props[i][1]; mi.e = S->props[i][2]; mi.mu = S->props[i][3];
+    mj.mass = S->props[j][0]; mj.inertia = S->props[j][1]; mj.e = S->props[j][2]; mj.mu = S->props[j][3];
+    resolve_collision(body[i], mi, body[j], mj, mk2(cpen[q][0], cpen[q][1]),
                       mk2(ccp[q][0], ccp[q][1]), P.baumgarte, P.baumgarte_dt);
   }
   for (int b = 0; b < nb; ++b) {

@@ -3,6 +3,9 @@ import os, sys
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
 import numpy as np, torch
+if os.environ.get("EXP_LIB"):  # time a variant build of the library
+    import parallax_b200._lib as _L
+    _L.LIB_PATH = os.path.abspath(os.environ["EXP_LIB"])
 from parallax_b200 import scene as sc
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 262144
