@@ -295,6 +295,55 @@ int cotix_lunar_env_rollout_graph(CotixLunarEnv* env, int32_t n_steps,
                                   const float* action_dev);
 
 /* ------------------------------------------------------------------------------------ */
+/* Differentiable rollout (K5, BASELINE config 5): hand-written adjoint of the step, the     */
+/* replacement for jax.grad / jax.vjp of f(env, key) (examples/test_viz.py:25-44) composed   */
+/* over T steps.  The reference differentiates by tracing its Python through jax; here the   */
+/* backward pass is one CUDA kernel per step (csrc/lunar_adjoint.cu) that reloads the state  */
+/* before the step, replays it with the forward kernels' own device functions (so every     */
+/* discrete decision is reproduced) and walks it backwards.  Differentiated: the 18 dynamic  */
+/* leaves (COTIX_LUNAR_NDYN rows: body b, leaf l -> row 6*b + l, leaves px, py, vx, vy,      */
+/* angle, angular velocity, i.e. rows 0..17 of the state) and the action.  Held fixed, as   */
+/* jax.grad holds them: broadphase / GJK outcomes, the EPA expansion sequence, argmax /      */
+/* argsort selections, coin flips, jr.choice, early-outs, clip saturation; the terrain and   */
+/* the PRNG key carry no cotangent.  Requires substeps == 1 and auto_reset == 0 (a reset     */
+/* cuts the dependence on the past; roll episodes separately).                               */
+#define COTIX_LUNAR_NDYN 18
+/* per-env flag bits (OR-ed into `flags`; the caller zeroes the buffer) */
+#define COTIX_ADJ_REPLAY_MISMATCH 0x1u /* the replayed step differs from state_next        */
+#define COTIX_ADJ_NONFINITE 0x2u       /* non-finite step: cotangent dropped (set to zero) */
+#define COTIX_ADJ_CONTACT_SHIFT 8      /* bits 8..10: resolve_collision calls in the step   */
+/*
+ * Vector-Jacobian product of ONE step.
+ *   state_in    DEVICE [NF][ld]   the state before the step (what cotix_lunar_step read)
+ *   state_next  DEVICE [NF][ld] or NULL: the state the forward step wrote; when given, the
+ *               replay is compared with it bit for bit (COTIX_ADJ_REPLAY_MISMATCH)
+ *   action      DEVICE [2][ld] or NULL (as in the forward call)
+ *   g_out       DEVICE [NDYN][ld] cotangent of the next state's dynamic leaves
+ *   g_in        DEVICE [NDYN][ld] receives the cotangent of state_in's; may alias g_out
+ *   g_action    DEVICE [2][ld] or NULL
+ *   flags       DEVICE uint32 [B] or NULL
+ */
+int cotix_lunar_step_bwd(void* stream, int64_t B, const float* state_in, const float* state_next,
+                         int64_t ld, const float* action, const float* g_out, float* g_in,
+                         float* g_action, uint32_t* flags, const CotixLunarParams* p);
+/*
+ * Forward rollout that keeps the tape: tape is DEVICE [T+1][NF][ld]; slot 0 holds the initial
+ * state on entry, slot t+1 receives the state after step t.  actions DEVICE [T][2][ld] or NULL.
+ * workspace / workspace_bytes as for cotix_lunar_step_ws, or NULL / 0 for the fused kernel.
+ */
+int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t ld,
+                        const float* actions, const CotixLunarParams* p, void* workspace,
+                        int64_t workspace_bytes);
+/*
+ * Backward pass over the tape of cotix_lunar_rollout: on entry g holds dL/d(state_T) (DEVICE
+ * [NDYN][ld]), on return dL/d(state_0); g_actions DEVICE [T][2][ld] or NULL receives
+ * dL/d(action_t).  T kernel launches on `stream`, no synchronisation, graph-capturable.
+ */
+int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
+                            const float* actions, float* g, float* g_actions, uint32_t* flags,
+                            const CotixLunarParams* p);
+
+/* ------------------------------------------------------------------------------------ */
 /* Generic scene step (K2): bodies with circle / AABB / polygon parts, e.g. the RoboCup     */
 /* scene of cotix/_robocup.py:14-130.  One call = ExplicitEulerPhysics.step                 */
 /* (cotix/_physics_solvers.py:16-33) + RandomizedCollider.resolve                           */

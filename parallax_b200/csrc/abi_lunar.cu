@@ -21,6 +21,9 @@ extern "C" int64_t cx_lunar_pipeline_workspace_bytes(int64_t B);
 extern "C" int cx_lunar_pipeline_profile(int enable);
 extern "C" int cx_lunar_pipeline_profiling();
 extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
+extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, const float*, int64_t,
+                                        const float*, const float*, float*, float*, uint32_t*,
+                                        const CotixLunarParams*);
 extern "C" int cx_launch_lunar_pipeline(cudaStream_t, int64_t, const float*, float*, int64_t, const float*,
                                         float*, uint8_t*, float*, const CotixLunarParams*, void*, int64_t);
 
@@ -264,6 +267,56 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
   CXL_REQUIRE(B == 0 || (state_in && state_out), "null state");
   return cx_launch_lunar_pipeline((cudaStream_t)stream, B, state_in, state_out, ld, action, reward, done,
                                   obs, p, workspace, workspace_bytes);
+}
+
+// ---- differentiable rollout (K5) ----------------------------------------------------
+int cotix_lunar_step_bwd(void* stream, int64_t B, const float* state_in, const float* state_next,
+                         int64_t ld, const float* action, const float* g_out, float* g_in,
+                         float* g_action, uint32_t* flags, const CotixLunarParams* p) {
+  CXL_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
+  CXL_REQUIRE(B == 0 || (state_in && g_out && g_in), "null state / cotangent");
+  return cx_launch_lunar_step_bwd((cudaStream_t)stream, B, state_in, state_next, ld, action, g_out, g_in,
+                                  g_action, flags, p);
+}
+
+int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t ld, const float* actions,
+                        const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
+  CXL_REQUIRE(B >= 0 && ld >= B && T >= 0, "bad batch size / leading dimension / step count");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(B == 0 || tape, "null tape");
+  const int64_t slot = (int64_t)COTIX_LUNAR_NF * ld;
+  for (int32_t t = 0; t < T; ++t) {
+    const float* a = actions ? actions + (int64_t)t * 2 * ld : nullptr;
+    int rc;
+    if (workspace)
+      rc = cx_launch_lunar_pipeline((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot, ld, a,
+                                    nullptr, nullptr, nullptr, p, workspace, workspace_bytes);
+    else
+      rc = cx_launch_lunar_step((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot, ld, a,
+                                nullptr, nullptr, nullptr, p);
+    if (rc != 0) return rc;
+  }
+  return 0;
+}
+
+int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
+                            const float* actions, float* g, float* g_actions, uint32_t* flags,
+                            const CotixLunarParams* p) {
+  CXL_REQUIRE(B >= 0 && ld >= B && T >= 0, "bad batch size / leading dimension / step count");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
+  CXL_REQUIRE(B == 0 || (tape && g), "null tape / cotangent");
+  const int64_t slot = (int64_t)COTIX_LUNAR_NF * ld;
+  for (int32_t t = T - 1; t >= 0; --t) {
+    const float* a = actions ? actions + (int64_t)t * 2 * ld : nullptr;
+    float* ga = g_actions ? g_actions + (int64_t)t * 2 * ld : nullptr;
+    const int rc = cx_launch_lunar_step_bwd((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot,
+                                            ld, a, g, g, ga, flags, p);
+    if (rc != 0) return rc;
+  }
+  return 0;
 }
 
 // ---- host-facing env handle ---------------------------------------------------------

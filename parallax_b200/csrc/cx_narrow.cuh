@@ -233,8 +233,11 @@ CX_DEV int argmin_first(const float* d, int n) {
   return best;
 }
 
+// epa_edge leaves the closest edge (ba, bb) of the expanded polytope in oa / ob; the penetration
+// vector is closest_to_origin(oa, ob).  The adjoint kernel (lunar_adjoint.cu) needs the edge.
 template <int MAXE, class SA, class SB>
-CX_DEV V2 epa(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, bool& capped) {
+CX_DEV void epa_edge(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, bool& capped, V2& oa,
+                     V2& ob) {
   float eax[MAXE], eay[MAXE], ebx[MAXE], eby[MAXE], dist[MAXE];
   eax[0] = s0.x; eay[0] = s0.y; ebx[0] = s1.x; eby[0] = s1.y;
   eax[1] = s1.x; eay[1] = s1.y; ebx[1] = s2.x; eby[1] = s2.y;
@@ -277,6 +280,13 @@ CX_DEV V2 epa(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, bool& ca
     ++ran;
   }
   capped = ran >= iters;
+  oa = ba;
+  ob = bb;
+}
+template <int MAXE, class SA, class SB>
+CX_DEV V2 epa(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, bool& capped) {
+  V2 ba, bb;
+  epa_edge<MAXE>(A, B, s0, s1, s2, iters, capped, ba, bb);
   return closest_to_origin(ba, bb);
 }
 

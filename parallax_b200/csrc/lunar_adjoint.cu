@@ -1,0 +1,635 @@
+// lunar_adjoint.cu — K5: hand-written adjoint (reverse mode) of the LunarLander step, for
+// jax.grad / jax.custom_vjp of a differentiable rollout (BASELINE config 5).
+//
+// What is differentiated: the composed step f of examples/test_viz.py:25-44 with engines,
+//   ExplicitEulerPhysics.step   cotix/_physics_solvers.py:16-33
+//   gravity + engines           examples/test_viz.py:27-31 (+ the action model of this engine)
+//   RandomizedCollider.resolve  cotix/_colliders.py:74-351  -> resolve_collision
+//                               cotix/_collision_resolution.py:52-151 on ContactInfo from
+//                               polygon_vs_polygon cotix/_contacts.py:294-315 (EPA penetration
+//                               vector cotix/_collisions.py:313-329, contact point :205-267)
+//   LunarLander.step (joints)   cotix/_lunar_lander.py:145-218
+// with respect to the 18 dynamic leaves of the state (3 bodies x px, py, vx, vy, angle, angular
+// velocity) and the 2 action components.  This is the derivative jax.grad takes of the
+// reference: every discrete decision (broadphase, GJK, the EPA expansion sequence, argmax /
+// argmin / argsort selections, coin flips, jr.choice, the `pen . v_rel < 0` early-out, clip
+// saturation) is held fixed, everything else is differentiated exactly:
+//   * the penetration vector is closest_to_origin(a, b) of the final EPA edge, whose end points
+//     are differences of one world vertex of each polygon (supports are argmax selections);
+//   * the contact point is the mean of the vertices of one polygon inside the other and of the
+//     edge-edge intersections;
+//   * world vertices move with their body: d vertex = d p + perp(vertex - p) d angle.
+//
+// Strategy: recompute-and-reverse.  The tape of a rollout is just the state before every step
+// (the forward kernels write it anyway); this kernel reloads state_t, re-runs the step with the
+// SAME device functions the forward kernels use (so every decision is reproduced bit for bit —
+// checked against state_{t+1} when the caller passes it), keeps the few intermediates the
+// adjoint needs in registers / local memory and walks the step backwards.  One env per thread.
+#include "cx_launch.cuh"
+#include "cx_lunar_step.cuh"
+
+namespace {
+
+constexpr int TPB = 64;
+
+struct G6 {  // cotangent of a BodyS
+  float px, py, vx, vy, ang, w;
+};
+CX_DEV G6 g6_zero() {
+  G6 g;
+  g.px = g.py = g.vx = g.vy = g.ang = g.w = 0.0f;
+  return g;
+}
+
+// polygon source: this thread's world polygons and terrain, from registers
+struct RegPolys {
+  const Poly& wL;
+  const Poly& wr;
+  const Poly& wl;
+  const float* h;
+  const float* kn;
+  CX_DEV void body(int which, Poly& p) const { p = which == 0 ? wL : (which == 1 ? wr : wl); }
+  CX_DEV void ground_edge(int k, const CotixLunarParams& P, float& x0, float& h0, float& x1,
+                          float& h1) const {
+    x0 = terrain_x(kn, P, k);
+    x1 = terrain_x(kn, P, k + 1);
+    h0 = sel8(h, k);
+    h1 = sel8(h, k + 1);
+  }
+};
+struct LocalContacts {
+  const Contact* res;
+  uint32_t cand;
+  CX_DEV Contact get(int bit) const { return res[bit]; }
+  CX_DEV bool live(int bit) const { return ((cand >> bit) & 1u) && !contact_isnan(res[bit]); }
+};
+
+// The resolve_collision calls RandomizedCollider.resolve makes this step, in scan order
+// (cotix/_colliders.py:310-336): pair id, first body, second body (3 = the static ground).
+struct Plan {
+  int n;
+  int pid[4], b1[4], b2[4];
+};
+CX_DEV void plan_add(Plan& pl, int pid, int b1, int b2) {
+  pl.pid[pl.n] = pid;
+  pl.b1[pl.n] = b1;
+  pl.b2[pl.n] = b2;
+  ++pl.n;
+}
+// same decisions as collide() + collide_apply() of cx_lunar_step.cuh, recorded instead of applied
+static __device__ __noinline__ void collide_plan(const EnvRegs& E, const CotixLunarParams& P,
+                                                 uint32_t cand, const LocalContacts& cs, Plan& pl) {
+  pl.n = 0;
+  uint32_t m[7];
+  bool crash, rc, lc;
+  if (!collide_masks(cand, cs, false, m, crash, rc, lc)) return;
+  CoinCtx cc;
+  make_coin_ctx(E, P, cc);
+  int win[7];
+  for (int c = 0; c < 6; ++c) {
+    const CellDesc d = cell_desc(c);
+    win[c] = cell_winner(cc, d.g, d.N1, d.N2, d.b_lo, d.b_hi, d.a0, d.nq, d.reps, m[c]);
+  }
+  win[6] = -1;
+  if (win[1] >= 0 || win[3] >= 0) {
+    const CellDesc d = cell_desc(6);
+    win[6] = cell_winner(cc, d.g, d.N1, d.N2, d.b_lo, d.b_hi, d.a0, d.nq, d.reps, cs.live(10) ? 1u : 0u);
+  }
+  const bool v10 = win[0] >= 0, v20 = win[1] >= 0, v21 = win[3] >= 0, v22 = win[6] >= 0;
+  const int w30 = win[2], w31 = win[4], w32 = win[5];
+  int j2 = -1, j3 = -1;
+  {
+    const int cnt = (v20 ? 1 : 0) + (v21 ? 1 : 0) + (v22 ? 1 : 0);
+    if (cnt == 1) j2 = v20 ? 0 : (v21 ? 1 : 2);
+    else if (cnt > 1) {
+      float u;
+      if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 2u), 0.0f, 1.0f);
+      else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 2u, CX_TAG_CHOICE), 0.0f, 1.0f);
+      j2 = choose_index(v20, v21, v22, u);
+    }
+  }
+  {
+    const bool m0 = w30 >= 0, m1 = w31 >= 0, m2 = w32 >= 0;
+    const int cnt = (m0 ? 1 : 0) + (m1 ? 1 : 0) + (m2 ? 1 : 0);
+    if (cnt == 1) j3 = m0 ? 0 : (m1 ? 1 : 2);
+    else if (cnt > 1) {
+      float u;
+      if (P.rng_mode == COTIX_RNG_THREEFRY) u = tf_uniform(tf_split(cc.gkey[1], 4u, 3u), 0.0f, 1.0f);
+      else u = bits_to_uniform(philox_word(cc.pkey, cc.steps, cc.episode, 0u, 3u, CX_TAG_CHOICE), 0.0f, 1.0f);
+      j3 = choose_index(m0, m1, m2, u);
+    }
+  }
+  if (v10) plan_add(pl, 0, 1, 0);
+  if (j2 == 0 && v20) plan_add(pl, 1, 2, 0);
+  if (j2 == 1 && v21) plan_add(pl, 9, 2, 1);
+  if (j3 >= 0 && j3 <= 2) {
+    const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
+    if (w >= 0) plan_add(pl, (j3 == 0 ? 2 : (j3 == 1 ? 11 : 18)) + w, 3, j3);
+  }
+}
+
+// ---- adjoint of apply_impulse (cotix/_collision_resolution.py:68-73) --------------------------
+// forward: arm = point - p; v += imp / m; w += cross(arm, imp) / I.   g is the cotangent of the
+// body AFTER the call on entry and BEFORE it on exit (v, w pass through; p collects -g_arm).
+CX_DEV void apply_impulse_bwd(const MassP& m, V2 arm, V2 imp, G6& g, V2& g_imp, V2& g_point) {
+  const float gt = g.w / m.inertia;
+  g_imp.x += g.vx / m.mass + (-gt * arm.y);
+  g_imp.y += g.vy / m.mass + gt * arm.x;
+  const V2 g_arm = mk2(gt * imp.y, -gt * imp.x);
+  g_point = g_point + g_arm;
+  g.px -= g_arm.x;
+  g.py -= g_arm.y;
+}
+// adjoint of velocity_at (cotix/_bodies.py:50-55): v_at = v + perp(point - p) * w
+CX_DEV void velocity_at_bwd(V2 arm, float w, V2 g_vat, G6& g, V2& g_point) {
+  g.vx += g_vat.x;
+  g.vy += g_vat.y;
+  g.w += dot2(g_vat, perp(arm));
+  const V2 g_arm = mk2(w * g_vat.y, -w * g_vat.x);
+  g_point = g_point + g_arm;
+  g.px -= g_arm.x;
+  g.py -= g_arm.y;
+}
+
+// ---- adjoint of resolve_collision (cotix/_collision_resolution.py:52-151) -----------------------
+// b1, b2: the bodies BEFORE the call.  g1, g2: cotangents after -> before.  g_pen / g_cp are
+// written (zero when the call changed nothing).
+static __device__ __noinline__ void resolve_collision_bwd(const BodyS& b1, const MassP& m1,
+                                                          const BodyS& b2, const MassP& m2, V2 pen,
+                                                          V2 cp, float baumgarte, float baumgarte_dt,
+                                                          G6& g1, G6& g2, V2& g_pen, V2& g_cp) {
+  g_pen = mk2(0.0f, 0.0f);
+  g_cp = mk2(0.0f, 0.0f);
+  if (isnan2(cp)) return;
+  // forward, same expressions as resolve_collision
+  const V2 p1 = mk2(b1.px, b1.py), p2 = mk2(b2.px, b2.py);
+  const V2 r1 = cp - p1, r2 = cp - p2;
+  const V2 v1 = mk2(b1.vx, b1.vy) + perp(r1) * b1.w;
+  const V2 v2 = mk2(b2.vx, b2.vy) + perp(r2) * b2.w;
+  const V2 vrel = v2 - v1;
+  if (dot2(pen, vrel) < 0) return;
+  const float pn = norm2(pen);
+  const V2 nd = pen / pn;
+  const float vn = dot2(vrel, nd);
+  const float el = jmin(m1.e, m2.e);
+  const float ang = sumsq2(r1) / m1.inertia + sumsq2(r2) / m2.inertia;
+  const float nim = -(1.0f + el) * vn - baumgarte * pn / baumgarte_dt;
+  const float kden = 1.0f / m1.mass + 1.0f / m2.mass + ang;
+  const float nimp = nim / kden;
+  const float fr = (m1.mu + m2.mu) / 2.0f;
+  const V2 vdrag = vrel + vn * nd;
+  const float vdn = norm2(vdrag);
+  const V2 vdu = vdrag / vdn;
+  const float idrag0 = -vdn / kden;
+  const float hi = nimp * fr;
+  const float mx = jmax(idrag0, 0.0f);
+  const float idrag = jmin(mx, hi);
+  const V2 ivec = nimp * nd + idrag * vdu;
+
+  // reverse
+  V2 g_ivec = mk2(0.0f, 0.0f), g_r1 = mk2(0.0f, 0.0f), g_r2 = mk2(0.0f, 0.0f);
+  {
+    // apply_impulse(b2, ivec, cp); apply_impulse(b1, -ivec, cp): the arms are r2 / r1, their
+    // cotangents go to cp and to the body position (inside apply_impulse_bwd)
+    apply_impulse_bwd(m2, r2, ivec, g2, g_ivec, g_cp);
+    V2 g_nivec = mk2(0.0f, 0.0f);
+    apply_impulse_bwd(m1, r1, -ivec, g1, g_nivec, g_cp);
+    g_ivec = g_ivec - g_nivec;
+  }
+  float g_nimp = dot2(g_ivec, nd);
+  V2 g_nd = g_ivec * nimp;
+  float g_kden = 0.0f;
+  V2 g_vrel = mk2(0.0f, 0.0f);
+  float g_vn = 0.0f;
+  if (idrag != 0.0f && vdn > 0.0f) {  // idrag == 0: the drag term is the constant 0 here
+    const float g_idrag = dot2(g_ivec, vdu);
+    const V2 g_vdu = g_ivec * idrag;
+    float g_idrag0 = 0.0f;
+    if (mx <= hi) {
+      if (idrag0 > 0.0f) g_idrag0 = g_idrag;
+    } else {
+      g_nimp += g_idrag * fr;
+    }
+    float g_vdn = -g_idrag0 / kden;
+    g_kden += g_idrag0 * vdn / (kden * kden);
+    V2 g_vdrag = g_vdu / vdn;
+    g_vdn += -dot2(g_vdu, vdrag) / (vdn * vdn);
+    g_vdrag = g_vdrag + vdrag * (g_vdn / vdn);
+    g_vrel = g_vrel + g_vdrag;
+    g_vn += dot2(g_vdrag, nd);
+    g_nd = g_nd + g_vdrag * vn;
+  }
+  const float g_nim = g_nimp / kden;
+  g_kden += -g_nimp * nim / (kden * kden);
+  g_vn += -(1.0f + el) * g_nim;
+  float g_pn = -(baumgarte / baumgarte_dt) * g_nim;
+  g_r1 = g_r1 + r1 * (2.0f * (g_kden / m1.inertia));
+  g_r2 = g_r2 + r2 * (2.0f * (g_kden / m2.inertia));
+  g_vrel = g_vrel + nd * g_vn;
+  g_nd = g_nd + vrel * g_vn;
+  g_pen = g_nd / pn;
+  g_pn += -dot2(g_nd, pen) / (pn * pn);
+  g_pen = g_pen + pen * (g_pn / pn);
+  // vrel = v2 - v1, v_i = v_i_lin + perp(r_i) * w_i
+  {
+    V2 gp = mk2(0.0f, 0.0f);
+    velocity_at_bwd(r2, b2.w, g_vrel, g2, gp);
+    g_cp = g_cp + gp;
+    gp = mk2(0.0f, 0.0f);
+    velocity_at_bwd(r1, b1.w, -g_vrel, g1, gp);
+    g_cp = g_cp + gp;
+  }
+  g_cp = g_cp + g_r1 + g_r2;
+  g1.px -= g_r1.x;
+  g1.py -= g_r1.y;
+  g2.px -= g_r2.x;
+  g2.py -= g_r2.y;
+}
+
+// ---- adjoint of joint_constraint (cotix/_lunar_lander.py:176-205) -------------------------------
+// b1, b2: the bodies BEFORE the call (positions never change inside a step after integration).
+static __device__ __noinline__ void joint_constraint_bwd(const BodyS& b1, const MassP& m1, V2 c1,
+                                                         const BodyS& b2, const MassP& m2, V2 c2,
+                                                         const CotixLunarParams& P, G6& g1, G6& g2,
+                                                         V2& g_c1, V2& g_c2) {
+  const V2 a1 = c1 - mk2(b1.px, b1.py), a2 = c2 - mk2(b2.px, b2.py);
+  const V2 dp = c1 - c2;
+  const V2 dv = (mk2(b1.vx, b1.vy) + perp(a1) * b1.w) - (mk2(b2.vx, b2.vy) + perp(a2) * b2.w);
+  const float n = norm2(dv);
+  const float s = (n + P.spring_kv0) * P.spring_kv;
+  const V2 imp = dp * P.spring_kp + dv * (n + P.spring_kv0) * P.spring_kv;
+  g_c1 = mk2(0.0f, 0.0f);
+  g_c2 = mk2(0.0f, 0.0f);
+  V2 g_imp = mk2(0.0f, 0.0f), g_nimp = mk2(0.0f, 0.0f);
+  apply_impulse_bwd(m2, a2, imp, g2, g_imp, g_c2);
+  apply_impulse_bwd(m1, a1, -imp, g1, g_nimp, g_c1);
+  g_imp = g_imp - g_nimp;
+  const V2 g_dp = g_imp * P.spring_kp;
+  V2 g_dv = g_imp * s;
+  const float g_n = dot2(g_imp, dv) * P.spring_kv;
+  if (n > 0.0f) g_dv = g_dv + dv * (g_n / n);
+  velocity_at_bwd(a1, b1.w, g_dv, g1, g_c1);
+  velocity_at_bwd(a2, b2.w, -g_dv, g2, g_c2);
+  g_c1 = g_c1 + g_dp;
+  g_c2 = g_c2 - g_dp;
+}
+
+// a world point rigidly attached to a body: d point = d p + perp(point - p) d angle
+CX_DEV void attached_point_bwd(V2 point, const BodyS& b, V2 g_point, G6& g) {
+  g.px += g_point.x;
+  g.py += g_point.y;
+  g.ang += dot2(g_point, perp(point - mk2(b.px, b.py)));
+}
+
+// ---- adjoint of the narrowphase outputs of one polygon pair -------------------------------------
+struct PolyGrad {
+  float x[CX_MAXV], y[CX_MAXV];
+};
+// adjoint of closest_to_origin(a, b) (get_closest_point_on_edge_to_point, cotix/_collisions.py:137-154)
+CX_DEV void closest_to_origin_bwd(V2 a, V2 b, V2 g_out, V2& g_a, V2& g_b) {
+  const V2 ab = a - b;
+  const float length = sumsq2(ab);
+  if (length == 0.0f) {
+    g_a = -g_out;
+    g_b = mk2(0.0f, 0.0f);
+    return;
+  }
+  const float num = dot2(mk2(0.0f, 0.0f) - b, ab);
+  const float t0 = num / length;
+  const float t = jclip(t0, 0.0f, 1.0f);
+  const V2 g_proj = -g_out;
+  g_b = g_proj;
+  V2 g_ab = g_proj * t;
+  if (t0 > 0.0f && t0 < 1.0f) {
+    const float g_t0 = dot2(g_proj, ab);
+    const float g_num = g_t0 / length;
+    const float g_len = -g_t0 * num / (length * length);
+    g_b = g_b - ab * g_num;
+    g_ab = g_ab - b * g_num + ab * (2.0f * g_len);
+  }
+  g_a = g_ab;
+  g_b = g_b - g_ab;
+}
+// m = sa - sb with sa a vertex of A and sb a vertex of B (minkowski_diff of two argmax supports):
+// route g_m to the vertices it came from (first exact match)
+CX_DEV void mdiff_point_bwd(const Poly& A, const Poly& B, V2 m, V2 g_m, PolyGrad& gA, PolyGrad& gB) {
+  for (int i = 0; i < A.n; ++i)
+    for (int k = 0; k < B.n; ++k)
+      if (A.x[i] - B.x[k] == m.x && A.y[i] - B.y[k] == m.y) {
+        gA.x[i] += g_m.x;
+        gA.y[i] += g_m.y;
+        gB.x[k] -= g_m.x;
+        gB.y[k] -= g_m.y;
+        return;
+      }
+}
+// adjoint of _contact_from_edges (cotix/_contacts.py:205-267)
+CX_DEV void contact_from_edges_bwd(const Poly& A, const Poly& B, V2 g_cp, PolyGrad& gA, PolyGrad& gB) {
+  EdgeList ea, eb;
+  edges_of(A, ea);
+  edges_of(B, eb);
+  // pass 1: the count, exactly as the forward does
+  float n = 0.0f;
+  for (int k = 0; k < ea.n; ++k)
+    if (poly_contains(eb, mk2(ea.ax[k], ea.ay[k]))) n = n + 1.0f;
+  for (int k = 0; k < eb.n; ++k)
+    if (poly_contains(ea, mk2(eb.ax[k], eb.ay[k]))) n = n + 1.0f;
+  for (int ib = 0; ib < eb.n; ++ib) {
+    const V2 q = mk2(eb.ax[ib], eb.ay[ib]);
+    const V2 s = mk2(eb.bx[ib], eb.by[ib]) - q;
+    for (int ia = 0; ia < ea.n; ++ia) {
+      const V2 p = mk2(ea.ax[ia], ea.ay[ia]);
+      const V2 r = mk2(ea.bx[ia], ea.by[ia]) - p;
+      const float c = r.x * s.y - s.x * r.y;
+      const V2 qp = q - p;
+      const float t = (qp.x * s.y - s.x * qp.y) / c;
+      const float u = (qp.x * r.y - r.x * qp.y) / c;
+      if ((c != 0.0f) && (t >= 0.0f) && (t <= 1.0f) && (u >= 0.0f) && (u <= 1.0f) && !isnan2(p + r * t))
+        n = n + 1.0f;
+    }
+  }
+  if (!(n > 0.0f)) return;
+  const V2 g = g_cp / n;
+  // pass 2: every term of the mean gets g
+  for (int k = 0; k < ea.n; ++k)
+    if (poly_contains(eb, mk2(ea.ax[k], ea.ay[k]))) {
+      gA.x[k] += g.x;
+      gA.y[k] += g.y;
+    }
+  for (int k = 0; k < eb.n; ++k)
+    if (poly_contains(ea, mk2(eb.ax[k], eb.ay[k]))) {
+      gB.x[k] += g.x;
+      gB.y[k] += g.y;
+    }
+  for (int ib = 0; ib < eb.n; ++ib) {
+    const int ibp = ib == 0 ? eb.n - 1 : ib - 1;  // edge ib = (v_ib, v_{ib-1})
+    const V2 q = mk2(eb.ax[ib], eb.ay[ib]);
+    const V2 s = mk2(eb.bx[ib], eb.by[ib]) - q;
+    for (int ia = 0; ia < ea.n; ++ia) {
+      const int iap = ia == 0 ? ea.n - 1 : ia - 1;
+      const V2 p = mk2(ea.ax[ia], ea.ay[ia]);
+      const V2 r = mk2(ea.bx[ia], ea.by[ia]) - p;
+      const float c = r.x * s.y - s.x * r.y;
+      const V2 qp = q - p;
+      const float num = qp.x * s.y - s.x * qp.y;
+      const float t = num / c;
+      const float u = (qp.x * r.y - r.x * qp.y) / c;
+      if (!((c != 0.0f) && (t >= 0.0f) && (t <= 1.0f) && (u >= 0.0f) && (u <= 1.0f) && !isnan2(p + r * t)))
+        continue;
+      // x = p + r * t
+      V2 g_p = g;
+      V2 g_r = g * t;
+      const float g_t = dot2(g, r);
+      const float g_num = g_t / c;
+      const float g_c = -g_t * num / (c * c);
+      const V2 g_qp = mk2(g_num * s.y, -g_num * s.x);
+      V2 g_s = mk2(-g_num * qp.y, g_num * qp.x);
+      g_r = g_r + mk2(g_c * s.y, -g_c * s.x);
+      g_s = g_s + mk2(-g_c * r.y, g_c * r.x);
+      // qp = q - p; r = p_prev - p; s = q_prev - q
+      V2 g_q = g_qp - g_s;
+      g_p = g_p - g_qp - g_r;
+      gA.x[ia] += g_p.x;
+      gA.y[ia] += g_p.y;
+      gA.x[iap] += g_r.x;
+      gA.y[iap] += g_r.y;
+      gB.x[ib] += g_q.x;
+      gB.y[ib] += g_q.y;
+      gB.x[ibp] += g_s.x;
+      gB.y[ibp] += g_s.y;
+    }
+  }
+}
+
+// g_pen, g_cp of candidate pair `pid` -> cotangents of the poses of the dynamic bodies involved
+static __device__ __noinline__ void pair_contact_bwd(const RegPolys& src, int pid, const EnvRegs& E,
+                                                     const CotixLunarParams& P, V2 g_pen, V2 g_cp,
+                                                     G6 g[4], uint32_t& flags) {
+  Poly A, B;
+  make_item_polys(src, pid, P, A, B);
+  int wa, wb, gk;
+  pair_bodies(pid, wa, wb, gk);
+  PolyGrad gA, gB;
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k) gA.x[k] = gA.y[k] = gB.x[k] = gB.y[k] = 0.0f;
+  V2 s0, s1, s2;
+  bool gcap, ecap;
+  const bool ex = gjk(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters, s0, s1, s2, gcap);
+  if (!ex) {
+    flags |= COTIX_ADJ_REPLAY_MISMATCH;
+    return;
+  }
+  int iters = A.n + B.n + 1;
+  if (iters > 13) iters = 13;
+  V2 ba, bb;
+  epa_edge<16>(A, B, s0, s1, s2, iters, ecap, ba, bb);
+  V2 g_a, g_b;
+  closest_to_origin_bwd(ba, bb, g_pen, g_a, g_b);
+  mdiff_point_bwd(A, B, ba, g_a, gA, gB);
+  mdiff_point_bwd(A, B, bb, g_b, gA, gB);
+  contact_from_edges_bwd(A, B, g_cp, gA, gB);
+  if (wa >= 0)
+    for (int k = 0; k < A.n; ++k)
+      attached_point_bwd(mk2(A.x[k], A.y[k]), E.b[wa], mk2(gA.x[k], gA.y[k]), g[wa]);
+  for (int k = 0; k < B.n; ++k)
+    attached_point_bwd(mk2(B.x[k], B.y[k]), E.b[wb], mk2(gB.x[k], gB.y[k]), g[wb]);
+}
+
+static __device__ __noinline__ Contact eval_pair(const RegPolys& src, int pid, const CotixLunarParams& P) {
+  Poly A, B;
+  make_item_polys(src, pid, P, A, B);
+  return poly_pair(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters);
+}
+
+CX_DEV bool same_bits(float a, float b) { return (a == b) || (a != a && b != b); }
+
+__global__ void __launch_bounds__(TPB)
+lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __restrict__ snext,
+                      int64_t ld, const float* __restrict__ action, const float* g_out, float* g_in,
+                      float* __restrict__ g_action, uint32_t* __restrict__ flags_out,
+                      const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
+  const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (e >= B) return;
+  EnvRegs E;
+  load_env(E, sin_, ld, e);
+  float am = 0.0f, as = 0.0f;
+  if (action) {
+    am = action[e];
+    as = action[ld + e];
+  }
+  uint32_t flags = 0u;
+  G6 g[4];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    g[i].px = g_out[(i * 6 + 0) * ld + e];
+    g[i].py = g_out[(i * 6 + 1) * ld + e];
+    g[i].vx = g_out[(i * 6 + 2) * ld + e];
+    g[i].vy = g_out[(i * 6 + 3) * ld + e];
+    g[i].ang = g_out[(i * 6 + 4) * ld + e];
+    g[i].w = g_out[(i * 6 + 5) * ld + e];
+  }
+  g[3] = g6_zero();
+
+  // ---- forward replay --------------------------------------------------------------------------
+  StepCtx cx;
+  Poly wL, wr, wl;
+  integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
+  const RegPolys src{wL, wr, wl, E.h, E.kn};
+  Contact res[CX_NPAIR];
+  {
+    uint32_t todo = cx.cand;
+    while (todo) {
+      const int bit = __ffs(todo) - 1;
+      todo &= todo - 1u;
+      res[bit] = eval_pair(src, bit, P);
+    }
+  }
+  const LocalContacts cs{res, cx.cand};
+  Plan pl;
+  collide_plan(E, P, cx.cand, cs, pl);
+  MassP mp[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    mp[i].mass = P.body_props[i][0];
+    mp[i].inertia = P.body_props[i][1];
+    mp[i].e = P.body_props[i][2];
+    mp[i].mu = P.body_props[i][3];
+  }
+  const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
+  BodyS bd[4];
+  bd[0] = E.b[0];
+  bd[1] = E.b[1];
+  bd[2] = E.b[2];
+  bd[3].px = bd[3].py = bd[3].vx = bd[3].vy = bd[3].ang = bd[3].w = 0.0f;
+  BodyS pre1[4], pre2[4];
+  for (int i = 0; i < pl.n; ++i) {
+    pre1[i] = bd[pl.b1[i]];
+    pre2[i] = bd[pl.b2[i]];
+    const Contact c = res[pl.pid[i]];
+    resolve_collision(bd[pl.b1[i]], mp[pl.b1[i]], bd[pl.b2[i]], mp[pl.b2[i]], c.pen, c.cp, P.baumgarte,
+                      P.baumgarte_dt);
+  }
+  // joints (finish_step of cx_lunar_step.cuh)
+  V2 c1[4], c2[4];
+  {
+    const V2 p0 = mk2(bd[0].px, bd[0].py);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      c1[k] = rot_cs(mk2(P.joint_local[k][0], P.joint_local[k][1]), cx.cs[0], cx.sn[0]) + p0;
+    const V2 j2l = mk2(P.leg_joint2_local[0], P.leg_joint2_local[1]);
+    c2[0] = mk2(bd[2].px, bd[2].py);
+    c2[1] = c2[0] + rot_cs(j2l, cx.cs[2], cx.sn[2]);
+    c2[2] = mk2(bd[1].px, bd[1].py);
+    c2[3] = c2[2] + rot_cs(j2l, cx.cs[1], cx.sn[1]);
+  }
+  BodyS jpre1[4], jpre2[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int leg = k < 2 ? 2 : 1;
+    jpre1[k] = bd[0];
+    jpre2[k] = bd[leg];
+    joint_constraint(bd[0], mp[0], c1[k], bd[leg], mp[leg], c2[k], P);
+  }
+  bd[1].w = bd[1].w * P.leg_damping;
+  bd[2].w = bd[2].w * P.leg_damping;
+  if (snext) {  // the replay must land on the state the forward kernel wrote
+    bool same = true;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      same = same && same_bits(bd[i].px, snext[(i * 6 + 0) * ld + e]) &&
+             same_bits(bd[i].py, snext[(i * 6 + 1) * ld + e]) &&
+             same_bits(bd[i].vx, snext[(i * 6 + 2) * ld + e]) &&
+             same_bits(bd[i].vy, snext[(i * 6 + 3) * ld + e]) &&
+             same_bits(bd[i].ang, snext[(i * 6 + 4) * ld + e]) &&
+             same_bits(bd[i].w, snext[(i * 6 + 5) * ld + e]);
+    }
+    if (!same) flags |= COTIX_ADJ_REPLAY_MISMATCH;
+  }
+  flags |= (uint32_t)pl.n << 8;
+  bool finite = !poisoned;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    finite = finite && (fabsf(bd[i].px) <= 3.0e38f) && (fabsf(bd[i].py) <= 3.0e38f) &&
+             (fabsf(bd[i].vx) <= 3.0e38f) && (fabsf(bd[i].vy) <= 3.0e38f) &&
+             (fabsf(bd[i].ang) <= 3.0e38f) && (fabsf(bd[i].w) <= 3.0e38f);
+
+  // ---- reverse ---------------------------------------------------------------------------------
+  float g_am = 0.0f, g_as = 0.0f;
+  if (!finite) {
+    // a non-finite step has no derivative: the cotangent is dropped (and flagged)
+    flags |= COTIX_ADJ_NONFINITE;
+    g[0] = g[1] = g[2] = g6_zero();
+  } else {
+    g[1].w = g[1].w * P.leg_damping;
+    g[2].w = g[2].w * P.leg_damping;
+#pragma unroll
+    for (int k = 3; k >= 0; --k) {
+      const int leg = k < 2 ? 2 : 1;
+      V2 gc1, gc2;
+      joint_constraint_bwd(jpre1[k], mp[0], c1[k], jpre2[k], mp[leg], c2[k], P, g[0], g[leg], gc1, gc2);
+      attached_point_bwd(c1[k], bd[0], gc1, g[0]);
+      attached_point_bwd(c2[k], bd[leg], gc2, g[leg]);
+    }
+    for (int i = pl.n - 1; i >= 0; --i) {
+      const Contact c = res[pl.pid[i]];
+      V2 g_pen, g_cp;
+      g[3] = g6_zero();  // the ground is static: its cotangent is discarded
+      resolve_collision_bwd(pre1[i], mp[pl.b1[i]], pre2[i], mp[pl.b2[i]], c.pen, c.cp, P.baumgarte,
+                            P.baumgarte_dt, g[pl.b1[i]], g[pl.b2[i]], g_pen, g_cp);
+      pair_contact_bwd(src, pl.pid[i], E, P, g_pen, g_cp, g, flags);
+    }
+    // engines: v0 += (-sn, cs) * dvm + (cs, sn) * dvs; w0 -= side_dw * thr_side
+    {
+      const float cs0 = cx.cs[0], sn0 = cx.sn[0];
+      float g_tm = 0.0f, g_ts = 0.0f;
+      if (cx.thr_main != 0.0f) {
+        const float dvm = P.main_engine_dv * cx.thr_main;
+        g_tm = P.main_engine_dv * (-sn0 * g[0].vx + cs0 * g[0].vy);
+        g[0].ang += (-cs0 * g[0].vx - sn0 * g[0].vy) * dvm;
+      }
+      if (cx.thr_side != 0.0f) {
+        const float dvs = P.side_engine_dv * cx.thr_side;
+        g_ts = P.side_engine_dv * (cs0 * g[0].vx + sn0 * g[0].vy) - P.side_engine_dw * g[0].w;
+        g[0].ang += (-sn0 * g[0].vx + cs0 * g[0].vy) * dvs;
+      }
+      if (am > 0.0f && am < 1.0f) g_am = g_tm;
+      if (as > -1.0f && as < 1.0f) g_as = g_ts;
+    }
+    // ExplicitEulerPhysics.step: p' = p + v dt, angle' = angle + w dt (gravity is a constant)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      g[i].vx += g[i].px * P.dt;
+      g[i].vy += g[i].py * P.dt;
+      g[i].w += g[i].ang * P.dt;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    g_in[(i * 6 + 0) * ld + e] = g[i].px;
+    g_in[(i * 6 + 1) * ld + e] = g[i].py;
+    g_in[(i * 6 + 2) * ld + e] = g[i].vx;
+    g_in[(i * 6 + 3) * ld + e] = g[i].vy;
+    g_in[(i * 6 + 4) * ld + e] = g[i].ang;
+    g_in[(i * 6 + 5) * ld + e] = g[i].w;
+  }
+  if (g_action) {
+    g_action[e] = g_am;
+    g_action[ld + e] = g_as;
+  }
+  if (flags_out) flags_out[e] = flags_out[e] | flags;
+}
+
+}  // namespace
+
+extern "C" int cx_launch_lunar_step_bwd(cudaStream_t st, int64_t B, const float* state_in,
+                                        const float* state_next, int64_t ld, const float* action,
+                                        const float* g_out, float* g_in, float* g_action,
+                                        uint32_t* flags, const CotixLunarParams* p) {
+  if (B == 0) return 0;
+  LunarDerived D;
+  cx_lunar_derive(p, &D);
+  lunar_step_bwd_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(
+      B, state_in, state_next, ld, action, g_out, g_in, g_action, flags, *p, D);
+  cx_count_launch();
+  return cx_check_launch("lunar_step_bwd_kernel");
+}

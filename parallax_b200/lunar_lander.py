@@ -159,6 +159,100 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
     return ns, reward, done
 
 
+NDYN = 18
+ADJ_REPLAY_MISMATCH, ADJ_NONFINITE, ADJ_CONTACT_SHIFT = 0x1, 0x2, 8
+
+
+def step_vjp(state: LunarState, action: torch.Tensor | None, g_next: torch.Tensor,
+             params: LunarParams | None = None, state_next: LunarState | None = None,
+             flags: torch.Tensor | None = None):
+    """Vector-Jacobian product of one step: what `jax.vjp(f, env)[1](g_next)` gives for the
+    reference's composed step (examples/test_viz.py:25-44), computed by the hand-written adjoint
+    kernel (`cotix_lunar_step_bwd`).
+
+    state: the state BEFORE the step; g_next: [18, B] cotangent of the next state's dynamic
+    leaves (row 6*body + leaf).  Returns (g_state [18, B], g_action [2, B]).  `state_next` (the
+    forward result) turns on the bit-for-bit replay check; `flags` ([B] int32, zeroed by the
+    caller) collects the ADJ_* bits.
+    """
+    params = params or default_params()
+    d = state.data
+    B = d.shape[1]
+    g_next = g_next.to(device=d.device, dtype=torch.float32).contiguous()
+    assert g_next.shape == (NDYN, B)
+    g_in = torch.empty_like(g_next)
+    g_act = torch.zeros((2, B), dtype=torch.float32, device=d.device)
+    if action is not None:
+        action = action.to(device=d.device, dtype=torch.float32).contiguous()
+        assert action.shape == (2, B)
+    with torch.cuda.device(d.device):
+        _lib.check(_lib.lib().cotix_lunar_step_bwd(
+            _stream_ptr(d.device), B, d.data_ptr(), state_next.data.data_ptr() if state_next is not None else None,
+            d.stride(0), action.data_ptr() if action is not None else None, g_next.data_ptr(), g_in.data_ptr(),
+            g_act.data_ptr(), flags.data_ptr() if flags is not None else None, C.byref(params)))
+    return g_in, g_act
+
+
+@dataclass
+class Rollout:
+    """Tape of a differentiable rollout: states [T+1, 36, B] (slot 0 = initial state), the
+    actions [T, 2, B] it was driven with (or None) and the params."""
+
+    tape: torch.Tensor
+    actions: torch.Tensor | None
+    params: LunarParams
+
+    @property
+    def final(self) -> LunarState:
+        return LunarState(self.tape[-1])
+
+    def state(self, t: int) -> LunarState:
+        return LunarState(self.tape[t])
+
+
+def rollout(state: LunarState, actions: torch.Tensor | None, n_steps: int,
+            params: LunarParams | None = None, mode: str = "auto") -> Rollout:
+    """n_steps steps of `step`, keeping every intermediate state (`cotix_lunar_rollout`): the
+    forward half of the reference's `jax.value_and_grad` over a rollout."""
+    params = params or default_params()
+    d = state.data
+    B = d.shape[1]
+    T = int(n_steps)
+    tape = torch.empty((T + 1, NF, B), dtype=torch.float32, device=d.device)
+    tape[0].copy_(d)
+    if actions is not None:
+        actions = actions.to(device=d.device, dtype=torch.float32).contiguous()
+        assert actions.shape == (T, 2, B)
+    m = _MODES[mode]
+    use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and B >= PIPELINE_MIN_ENVS)
+    with torch.cuda.device(d.device):
+        wp, wn = None, 0
+        if use_pipe:
+            ws = _workspace(d.device, B)
+            wp = (ws.data_ptr() + 255) & ~255
+            wn = ws.numel() - (wp - ws.data_ptr())
+        _lib.check(_lib.lib().cotix_lunar_rollout(
+            _stream_ptr(d.device), B, T, tape.data_ptr(), B, actions.data_ptr() if actions is not None else None,
+            C.byref(params), wp, wn))
+    return Rollout(tape, actions, params)
+
+
+def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None = None):
+    """Backward pass over a `Rollout` (`cotix_lunar_rollout_bwd`): g_final [18, B] = dL/d(final
+    dynamic leaves).  Returns (dL/d(initial dynamic leaves) [18, B], dL/d(actions) [T, 2, B])."""
+    tape = ro.tape
+    T, B = tape.shape[0] - 1, tape.shape[2]
+    g = g_final.to(device=tape.device, dtype=torch.float32).contiguous().clone()
+    assert g.shape == (NDYN, B)
+    g_act = torch.zeros((T, 2, B), dtype=torch.float32, device=tape.device)
+    with torch.cuda.device(tape.device):
+        _lib.check(_lib.lib().cotix_lunar_rollout_bwd(
+            _stream_ptr(tape.device), B, T, tape.data_ptr(), B,
+            ro.actions.data_ptr() if ro.actions is not None else None, g.data_ptr(), g_act.data_ptr(),
+            flags.data_ptr() if flags is not None else None, C.byref(ro.params)))
+    return g, g_act
+
+
 PIPELINE_STAGES = ("integrate", "narrow", "contact", "finish", "reset", "step")
 
 
