@@ -325,6 +325,7 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_sweep:
         line["narrowphase"] = sweep(args, dev, peak)
         line["robocup"] = robocup(args, dev)
+        line["differentiable"] = differentiable(args, dev)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:
@@ -421,6 +422,68 @@ def robocup(args, dev):
             "cpu_port": {"value": cpu, "unit": "env-steps/s", "cores": 1, "sample": f"{n_cpu} envs x 2 steps"}}
 
 
+def differentiable(args, dev):
+    """BASELINE config 5: B = 4096 envs x 100 steps, loss = final lander y^2, seed 4: forward rollout
+    that keeps the tape (cotix_lunar_rollout) + the hand-written adjoint (cotix_lunar_rollout_bwd,
+    one lunar_step_bwd_kernel launch per step).  Beside it: what the same gradient costs by central
+    finite differences of the oracle port on one host core (2 x (18 + 200) rollouts per env, measured
+    on a sample of rollouts) -- the reference's jax.grad cannot run here (no jax)."""
+    import torch
+
+    from gen_inputs import lunar_keys, perturbed_lunar_state
+    from oracle import oracle as o
+    from parallax_b200 import launch_count
+    from parallax_b200 import lunar_lander as ll
+
+    B, T = args.diff_envs, 100
+    P = ll.default_params()
+    rng = np.random.default_rng(4)
+    o.set_trig_mode(1)
+    s0 = perturbed_lunar_state(o.lunar_reset(lunar_keys(B), P), rng, P)
+    acts_h = rng.uniform(-1, 1, size=(T, 2, B)).astype(np.float32)
+    st0 = ll.LunarState.from_numpy(s0, device=dev)
+    acts = torch.from_numpy(acts_h).to(dev)
+    flags = torch.zeros(B, dtype=torch.int32, device=dev)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    fwd, bwd = [], []
+    n0 = launch_count()
+    reps = 5
+    for it in range(2 + reps):
+        flags.zero_()
+        ev[0].record()
+        ro = ll.rollout(st0, acts, T, P, mode="fused")
+        ev[1].record()
+        g = torch.zeros((18, B), device=dev)
+        g[1] = 2.0 * ro.tape[-1, 1]
+        g0, ga = ll.rollout_vjp(ro, g, flags)
+        ev[2].record()
+        torch.cuda.synchronize(dev)
+        if it >= 2:
+            fwd.append(ev[0].elapsed_time(ev[1]))
+            bwd.append(ev[1].elapsed_time(ev[2]))
+    f = flags.cpu().numpy()
+    fwd_ms, bwd_ms = float(np.median(fwd)), float(np.median(bwd))
+    # CPU: one forward rollout of n_cpu envs through the oracle port; a finite-difference gradient of
+    # the 18 + 2 T inputs needs 2 (18 + 2 T) of them per env
+    n_cpu = 256
+    t0 = time.perf_counter()
+    s = s0[:, :n_cpu].copy()
+    for t in range(T):
+        s = o.lunar_step(s, np.ascontiguousarray(acts_h[t][:, :n_cpu]), P)[0]
+    cpu_rollouts = n_cpu / (time.perf_counter() - t0)
+    o.set_trig_mode(0)
+    return {"metric": "differentiable rollouts/sec (100 steps forward + adjoint)", "unit": "rollouts/s",
+            "value": B / ((fwd_ms + bwd_ms) * 1e-3), "envs": B, "steps": T, "loss": "final lander y^2",
+            "forward_ms": fwd_ms, "backward_ms": bwd_ms, "launches_per_rollout": int((launch_count() - n0) / (2 + reps)),
+            "kernel": "lunar_step_kernel x T, lunar_step_bwd_kernel x T (recompute-and-reverse, one env per thread)",
+            "tape_bytes": int(ro.tape.numel() * 4), "replay_mismatch_envs": int((f & 1).sum()),
+            "nonfinite_envs": int(((f >> 1) & 1).sum()), "envs_with_contact": int((((f >> 8) & 7) > 0).sum()),
+            "grad_finite": bool(torch.isfinite(g0).all() and torch.isfinite(ga).all()),
+            "cpu_port": {"value": cpu_rollouts, "unit": "forward rollouts/s", "cores": o.num_threads(),
+                         "sample": f"{n_cpu} envs x {T} steps forward only",
+                         "fd_gradient_rollouts_per_env": 2 * (18 + 2 * T)}}
+
+
 def cpu_baseline(args):
     """The oracle (a C++ port of the reference path) on the box's host cores, bounded sample."""
     from gen_inputs import lunar_keys, perturbed_lunar_state
@@ -456,6 +519,7 @@ def main():
     ap.add_argument("--max-episode-steps", dest="max_episode_steps", type=int, default=1000)
     ap.add_argument("--pairs", type=int, default=1 << 24)
     ap.add_argument("--robocup-envs", dest="robocup_envs", type=int, default=1 << 18)
+    ap.add_argument("--diff-envs", dest="diff_envs", type=int, default=4096)
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=50)
     ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=16384)
     ap.add_argument("--ref-literal", dest="ref_literal", action="store_true")

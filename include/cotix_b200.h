@@ -344,6 +344,38 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
                             const CotixLunarParams* p);
 
 /* ------------------------------------------------------------------------------------ */
+/* Headless rasteriser (K6): the replacement for the pygame window of cotix/_viz.py — there  */
+/* is no graphics stack on the box, so the 800 x 600 "screen" is an RGB8 buffer in DEVICE    */
+/* memory, [n_img][600][800][3] uint8 (row 0 = top, as pygame).  Primitives are painted in   */
+/* list order onto a black image (PyPainter.next clears to black, :43-49).  Pixel rules: see */
+/* csrc/raster_kernel.cu; agreement with SDL's own rasteriser is unpinned (no pygame here).  */
+#define COTIX_IMG_W 800
+#define COTIX_IMG_H 600
+#define COTIX_PRIM_WORDS 16
+#define COTIX_PRIM_LINE 0    /* pygame.draw.line, width 1      cotix/_viz.py:23-26           */
+#define COTIX_PRIM_CIRCLE 1  /* pygame.draw.circle, filled     cotix/_viz.py:17-21           */
+#define COTIX_PRIM_POLYGON 2 /* pygame.draw.polygon, filled, convex, 3..6 vertices  :28-31   */
+#define COTIX_LUNAR_PRIMS 44 /* draw calls of LunarLander.draw, cotix/_lunar_lander.py:220-225 */
+/*
+ * Primitive record = int32[16]: type, colour 0x00RRGGBB, n (circle: radius in pixels; polygon:
+ * vertex count), 0, then up to 6 (x, y) PIXEL coordinates (line: 2, circle: the centre).
+ *   prims  DEVICE int32 [n_img][max_prims][16];  counts DEVICE int32 [n_img] or NULL (= max_prims)
+ */
+int cotix_raster_draw(void* stream, int64_t n_img, const int32_t* prims, const int32_t* counts,
+                      int32_t max_prims, uint8_t* image);
+/*
+ * env.draw(painter) for LunarLander envs (cotix/_lunar_lander.py:220-225 through
+ * Polygon.drawEdges cotix/_convex_shapes.py:189-194 and PyPainter._scale_vector
+ * cotix/_viz.py:33-38): image i shows env env_index[i] (DEVICE int64 [n_img], or NULL for envs
+ * 0..n_img-1) of `state` (DEVICE [NF][ld]).  cotix_lunar_prims writes the same 44 draw calls as
+ * primitive records (DEVICE int32 [n_img][44][16]) instead of painting them.
+ */
+int cotix_lunar_draw(void* stream, int64_t n_img, const float* state, int64_t ld,
+                     const int64_t* env_index, uint8_t* image, const CotixLunarParams* p);
+int cotix_lunar_prims(void* stream, int64_t n_img, const float* state, int64_t ld,
+                      const int64_t* env_index, int32_t* prims, const CotixLunarParams* p);
+
+/* ------------------------------------------------------------------------------------ */
 /* Generic scene step (K2): bodies with circle / AABB / polygon parts, e.g. the RoboCup     */
 /* scene of cotix/_robocup.py:14-130.  One call = ExplicitEulerPhysics.step                 */
 /* (cotix/_physics_solvers.py:16-33) + RandomizedCollider.resolve                           */

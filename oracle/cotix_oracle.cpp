@@ -1878,6 +1878,87 @@ int oracle_trig(int64_t n, const float* x, const float* y, float* out_sin, float
   return 0;
 }
 
+// ---- headless rasteriser (the stand-in for cotix/_viz.py's pygame window) -------------------
+// PARITY UNPINNED against pygame / SDL (not installed here): the pixel rules are the engine's own
+// definition (parallax_b200/csrc/raster_kernel.cu); this is their sequential restatement — the
+// painter's algorithm one primitive and one pixel at a time, lines by an incremental
+// error-accumulating walk (the CUDA kernel evaluates every pixel in closed form).
+//   prims int32 [n_img][max_prims][16], counts int32 [n_img] or NULL, image uint8 [n_img][600][800][3]
+static void o_put(uint8_t* img, long long x, long long y, uint32_t rgb) {
+  if (x < 0 || x >= COTIX_IMG_W || y < 0 || y >= COTIX_IMG_H) return;
+  uint8_t* p = img + (y * COTIX_IMG_W + x) * 3;
+  p[0] = (uint8_t)(rgb >> 16);
+  p[1] = (uint8_t)(rgb >> 8);
+  p[2] = (uint8_t)rgb;
+}
+int oracle_raster_draw(int64_t n_img, const int32_t* prims, const int32_t* counts, int32_t max_prims,
+                       uint8_t* image) {
+  const int64_t img_bytes = (int64_t)COTIX_IMG_W * COTIX_IMG_H * 3;
+  for (int64_t im = 0; im < n_img; ++im) {
+    uint8_t* img = image + im * img_bytes;
+    memset(img, 0, (size_t)img_bytes);  // PyPainter.next: screen.fill((0, 0, 0))
+    int cnt = counts ? counts[im] : max_prims;
+    if (cnt > max_prims) cnt = max_prims;
+    for (int k = 0; k < cnt; ++k) {
+      const int32_t* q = prims + (im * max_prims + k) * COTIX_PRIM_WORDS;
+      const uint32_t rgb = (uint32_t)q[1];
+      if (q[0] == COTIX_PRIM_LINE) {
+        long long x0 = q[4], y0 = q[5], x1 = q[6], y1 = q[7];
+        if (x1 < x0 || (x1 == x0 && y1 < y0)) {
+          std::swap(x0, x1);
+          std::swap(y0, y1);
+        }
+        const long long dx = x1 - x0, dy = y1 >= y0 ? y1 - y0 : y0 - y1, sy = y1 >= y0 ? 1 : -1;
+        if (dx >= dy) {
+          long long y = y0, err = dx;  // err / (2 dx) = the fractional position + 1/2
+          for (long long x = x0; x <= x1; ++x) {
+            // skip the off-screen run quickly (terrain edges extend far beyond the screen)
+            if (x >= 0 && x < COTIX_IMG_W) o_put(img, x, y, rgb);
+            if (x == x1) break;
+            err += 2 * dy;
+            while (dx > 0 && err >= 2 * dx) {
+              err -= 2 * dx;
+              y += sy;
+            }
+          }
+        } else {
+          long long x = x0, err = dy;
+          for (long long i = 0; i <= dy; ++i) {
+            o_put(img, x, y0 + sy * i, rgb);
+            err += 2 * dx;
+            while (err >= 2 * dy) {
+              err -= 2 * dy;
+              x += 1;
+            }
+          }
+        }
+      } else if (q[0] == COTIX_PRIM_CIRCLE) {
+        const long long cx = q[4], cy = q[5], r = q[2];
+        if (r < 1) continue;
+        for (long long y = cy - r; y <= cy + r; ++y)
+          for (long long x = cx - r; x <= cx + r; ++x)
+            if ((x - cx) * (x - cx) + (y - cy) * (y - cy) <= r * r) o_put(img, x, y, rgb);
+      } else if (q[0] == COTIX_PRIM_POLYGON) {
+        const int nv = q[2];
+        if (nv < 3 || nv > 6) continue;
+        for (long long y = 0; y < COTIX_IMG_H; ++y)
+          for (long long x = 0; x < COTIX_IMG_W; ++x) {
+            bool pos = true, neg = true;
+            for (int a = 0; a < nv; ++a) {
+              const int b = (a + 1) % nv;
+              const long long ex = (long long)q[4 + 2 * b] - q[4 + 2 * a], ey = (long long)q[5 + 2 * b] - q[5 + 2 * a];
+              const long long e = ex * (y - q[5 + 2 * a]) - ey * (x - q[4 + 2 * a]);
+              pos = pos && e >= 0;
+              neg = neg && e <= 0;
+            }
+            if (pos || neg) o_put(img, x, y, rgb);
+          }
+      }
+    }
+  }
+  return 0;
+}
+
 int oracle_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

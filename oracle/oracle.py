@@ -327,6 +327,21 @@ def scene_step(bodies10, part_body, part_recs, key, dt=1e-2, init_dir=None, dedu
 
 
 # ---- record constructors (host-side helpers for tests) ----
+def raster_draw(prims, counts=None):
+    """prims int32 [n_img, max_prims, 16] -> uint8 [n_img, 600, 800, 3] (painter's algorithm; the pixel
+    rules of parallax_b200/csrc/raster_kernel.cu restated sequentially; unpinned against pygame)."""
+    prims = np.ascontiguousarray(prims, dtype=np.int32)
+    n, mp = prims.shape[0], prims.shape[1]
+    img = np.empty((n, 600, 800, 3), np.uint8)
+    cp = None
+    if counts is not None:
+        counts = np.ascontiguousarray(counts, dtype=np.int32)
+        cp = counts.ctypes.data_as(C.c_void_p)
+    lib().oracle_raster_draw(C.c_int64(n), prims.ctypes.data_as(C.c_void_p), cp, C.c_int32(mp),
+                             img.ctypes.data_as(C.c_void_p))
+    return img
+
+
 def circle_rec(radius, position):
     r = np.zeros(REC, np.float32)
     r[0] = 0

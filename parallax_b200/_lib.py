@@ -16,7 +16,7 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_PKG, "csrc")
 LIB_PATH = os.path.join(_PKG, "libcotix_b200.so")
 SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu",
-           "scene_kernel.cu", "lunar_adjoint.cu"]
+           "scene_kernel.cu", "lunar_adjoint.cu", "raster_kernel.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
@@ -156,6 +156,7 @@ EXPORTS = [
     "cotix_scene_default_params", "cotix_scene_create", "cotix_scene_destroy", "cotix_scene_info",
     "cotix_scene_step",
     "cotix_lunar_step_bwd", "cotix_lunar_rollout", "cotix_lunar_rollout_bwd",
+    "cotix_raster_draw", "cotix_lunar_draw", "cotix_lunar_prims",
 ]
 
 _lib = None
@@ -207,6 +208,9 @@ def lib() -> C.CDLL:
     L.cotix_lunar_step_bwd.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, vp, C.POINTER(LunarParams)]
     L.cotix_lunar_rollout.argtypes = [vp, i64, C.c_int32, vp, i64, vp, C.POINTER(LunarParams), vp, i64]
     L.cotix_lunar_rollout_bwd.argtypes = [vp, i64, C.c_int32, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams)]
+    L.cotix_raster_draw.argtypes = [vp, i64, vp, vp, C.c_int32, vp]
+    L.cotix_lunar_draw.argtypes = [vp, i64, vp, i64, vp, vp, C.POINTER(LunarParams)]
+    L.cotix_lunar_prims.argtypes = [vp, i64, vp, i64, vp, vp, C.POINTER(LunarParams)]
     L.cotix_scene_default_params.argtypes = [C.POINTER(SceneParams)]
     L.cotix_scene_default_params.restype = None
     L.cotix_scene_create.argtypes = [C.POINTER(vp), C.c_int, C.c_int32, vp, C.c_int32, vp, vp]

@@ -24,6 +24,11 @@ extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, const float*, int64_t,
                                         const float*, const float*, float*, float*, uint32_t*,
                                         const CotixLunarParams*);
+extern "C" int cx_launch_raster_draw(cudaStream_t, int64_t, const int32_t*, const int32_t*, int32_t, uint8_t*);
+extern "C" int cx_launch_lunar_draw(cudaStream_t, int64_t, const float*, int64_t, const int64_t*, uint8_t*,
+                                    const CotixLunarParams*);
+extern "C" int cx_launch_lunar_prims(cudaStream_t, int64_t, const float*, int64_t, const int64_t*, int32_t*,
+                                     const CotixLunarParams*);
 extern "C" int cx_launch_lunar_pipeline(cudaStream_t, int64_t, const float*, float*, int64_t, const float*,
                                         float*, uint8_t*, float*, const CotixLunarParams*, void*, int64_t);
 
@@ -317,6 +322,33 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
     if (rc != 0) return rc;
   }
   return 0;
+}
+
+// ---- headless rasteriser (K6) -------------------------------------------------------
+int cotix_raster_draw(void* stream, int64_t n_img, const int32_t* prims, const int32_t* counts,
+                      int32_t max_prims, uint8_t* image) {
+  CXL_REQUIRE(n_img >= 0 && max_prims >= 0 && max_prims <= 65536, "bad image / primitive count");
+  CXL_REQUIRE(n_img == 0 || image, "null image");
+  CXL_REQUIRE(n_img == 0 || max_prims == 0 || prims, "null primitive list");
+  CXL_REQUIRE(((uintptr_t)image & 15u) == 0, "image must be 16-byte aligned");
+  return cx_launch_raster_draw((cudaStream_t)stream, n_img, prims, counts, max_prims, image);
+}
+int cotix_lunar_draw(void* stream, int64_t n_img, const float* state, int64_t ld, const int64_t* env_index,
+                     uint8_t* image, const CotixLunarParams* p) {
+  CXL_REQUIRE(n_img >= 0 && ld >= 0, "bad image count / leading dimension");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(n_img == 0 || (state && image), "null state / image");
+  CXL_REQUIRE(env_index || n_img <= ld, "more images than envs");
+  CXL_REQUIRE(((uintptr_t)image & 15u) == 0, "image must be 16-byte aligned");
+  return cx_launch_lunar_draw((cudaStream_t)stream, n_img, state, ld, env_index, image, p);
+}
+int cotix_lunar_prims(void* stream, int64_t n_img, const float* state, int64_t ld, const int64_t* env_index,
+                      int32_t* prims, const CotixLunarParams* p) {
+  CXL_REQUIRE(n_img >= 0 && ld >= 0, "bad image count / leading dimension");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(n_img == 0 || (state && prims), "null state / primitive list");
+  CXL_REQUIRE(env_index || n_img <= ld, "more images than envs");
+  return cx_launch_lunar_prims((cudaStream_t)stream, n_img, state, ld, env_index, prims, p);
 }
 
 // ---- host-facing env handle ---------------------------------------------------------

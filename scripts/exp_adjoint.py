@@ -84,6 +84,8 @@ def main():
         print(f"resolves={k}: n={sel.sum()} smooth={smooth.mean():.3f} rel err (smooth) p50={q[0]:.2e} p90={q[1]:.2e} "
               f"p99={q[2]:.2e} max={q[3]:.2e}; frac(rel<2e-2 | smooth)={(rel[smooth] < 2e-2).mean():.4f}")
 
+    if os.environ.get("FLIGHT"):
+        s0 = o.lunar_reset(lunar_keys(B), P)
     # ---- config 5: B envs x 100 steps, loss = final lander y^2 --------------------------------
     T = 100
     actions = torch.from_numpy(rng.uniform(-1, 1, size=(T, 2, B)).astype(np.float32)).cuda()
