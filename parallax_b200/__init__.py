@@ -9,7 +9,7 @@ __all__ = ["_lib", "CotixError", "LunarParams", "NarrowParams", "build", "launch
 
 def __getattr__(name):
     # torch-dependent modules are imported lazily so that `import parallax_b200` stays cheap
-    if name in ("shapes", "lunar_lander", "sharding"):
+    if name in ("shapes", "lunar_lander", "sharding", "scene", "viz"):
         import importlib
 
         return importlib.import_module(f"{__name__}.{name}")

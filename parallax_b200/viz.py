@@ -1,0 +1,159 @@
+"""Headless stand-in for the reference's painter (cotix/_viz.py).
+
+The reference draws into a pygame window from inside jit through `jax.debug.callback`
+(`Painter` :53-75 wrapping `PyPainter` :6-49).  There is no graphics stack on the box, so here the
+800 x 600 "screen" is an RGB8 tensor in device memory painted by the CUDA rasteriser
+(`cotix_raster_draw`, csrc/raster_kernel.cu); `next()` returns the finished frame instead of
+flipping a window.  Same method names, argument meaning and world -> pixel map as the reference.
+Pixel-for-pixel agreement with SDL's own line / circle / polygon rasteriser is unpinned (pygame is
+not installed anywhere here); the pixel rules are documented in csrc/raster_kernel.cu.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import LunarParams
+
+IMG_W, IMG_H, PRIM_WORDS = 800, 600, 16
+PRIM_LINE, PRIM_CIRCLE, PRIM_POLYGON = 0, 1, 2
+LUNAR_PRIMS = 44
+
+
+def _f32(v) -> np.float32:
+    return np.float32(v)
+
+
+def scale_vector(vector) -> tuple[int, int]:
+    """PyPainter._scale_vector (cotix/_viz.py:33-38): [-8, 8] x [-6, 6] -> [0, 800] x [0, 600], y
+    flipped, int() truncation.  float32 inputs are scaled in float32 (what numpy does with the
+    arrays a jax callback receives), Python numbers in float64 (the literal pad markers)."""
+    x, y = vector[0], vector[1]
+    if isinstance(x, (np.floating, np.ndarray)) or isinstance(y, (np.floating, np.ndarray)):
+        x, y = _f32(x), _f32(y)
+        return (int((x + _f32(8)) / _f32(16) * _f32(800)), int((-y + _f32(6)) / _f32(12) * _f32(600)))
+    return (int((x + 8) / 16 * 800), int((-y + 6) / 12 * 600))
+
+
+def scale_size(size) -> int:
+    """PyPainter._scale_size (cotix/_viz.py:40-41)."""
+    return int(size * 40)
+
+
+def _rgb(color) -> int:
+    r, g, b = (int(c) & 255 for c in color)
+    return (r << 16) | (g << 8) | b
+
+
+class Painter:
+    """`cotix._viz.Painter` without a window: draw_* queue primitives, `next()` rasterises them on
+    the GPU onto a black frame and returns it ([600, 800, 3] uint8 device tensor)."""
+
+    def __init__(self, device="cuda"):
+        self.device = torch.device(device)
+        self._prims: list[list[int]] = []
+
+    def setup(self) -> None:  # PyPainter.setup: nothing to open
+        self._prims.clear()
+
+    def draw_circle(self, center, radius, color) -> None:
+        cx, cy = scale_vector(center)
+        self._prims.append([PRIM_CIRCLE, _rgb(color), scale_size(radius), 0, cx, cy] + [0] * 10)
+
+    def draw_line(self, start, end, color) -> None:
+        x0, y0 = scale_vector(start)
+        x1, y1 = scale_vector(end)
+        self._prims.append([PRIM_LINE, _rgb(color), 0, 0, x0, y0, x1, y1] + [0] * 8)
+
+    def draw_polygon(self, vertices, color) -> None:
+        pts = [scale_vector(v) for v in vertices]
+        if not 3 <= len(pts) <= 6:
+            raise ValueError("draw_polygon takes a convex polygon of 3..6 vertices")
+        flat = [c for p in pts for c in p]
+        self._prims.append([PRIM_POLYGON, _rgb(color), len(pts), 0] + flat + [0] * (12 - len(flat)))
+
+    def primitives(self) -> np.ndarray:
+        """the queued draw calls as records, int32 [n, 16] (include/cotix_b200.h)"""
+        return np.asarray(self._prims, dtype=np.int32).reshape(-1, PRIM_WORDS)
+
+    def next(self) -> torch.Tensor:
+        """PyPainter.next (cotix/_viz.py:43-49): present the frame, start the next one black."""
+        prims = self.primitives()
+        self._prims = []
+        return raster_draw(prims[None], device=self.device)[0]
+
+    def draw_env(self, env) -> None:
+        env.draw(self)
+
+
+def raster_draw(prims, counts=None, device="cuda") -> torch.Tensor:
+    """prims int32 [n_img, max_prims, 16] (numpy or device tensor) -> uint8 [n_img, 600, 800, 3] on
+    the device: every image painted in list order onto black (`cotix_raster_draw`)."""
+    if not isinstance(prims, torch.Tensor):
+        prims = torch.from_numpy(np.ascontiguousarray(prims, dtype=np.int32))
+    prims = prims.to(device=device, dtype=torch.int32).contiguous()
+    n, mp = int(prims.shape[0]), int(prims.shape[1])
+    assert prims.dim() == 3 and prims.shape[2] == PRIM_WORDS
+    if counts is not None:
+        if not isinstance(counts, torch.Tensor):
+            counts = torch.from_numpy(np.ascontiguousarray(counts, dtype=np.int32))
+        counts = counts.to(device=prims.device, dtype=torch.int32).contiguous()
+    img = torch.empty((n, IMG_H, IMG_W, 3), dtype=torch.uint8, device=prims.device)
+    with torch.cuda.device(prims.device):
+        _lib.check(_lib.lib().cotix_raster_draw(
+            torch.cuda.current_stream(prims.device).cuda_stream, n, prims.data_ptr() if mp else None,
+            counts.data_ptr() if counts is not None else None, mp, img.data_ptr()))
+    return img
+
+
+def _index(env_index, device):
+    if env_index is None:
+        return None
+    if not isinstance(env_index, torch.Tensor):
+        env_index = torch.from_numpy(np.ascontiguousarray(env_index, dtype=np.int64))
+    return env_index.to(device=device, dtype=torch.int64).contiguous()
+
+
+def render_lunar(state, env_index=None, params: LunarParams | None = None) -> torch.Tensor:
+    """`env.draw(painter); painter.next()` for LunarLander envs (cotix/_lunar_lander.py:220-225):
+    uint8 [n_img, 600, 800, 3]; image i shows env env_index[i] (default: every env of `state`)."""
+    from . import lunar_lander as ll
+
+    params = params or ll.default_params()
+    d = state.data
+    idx = _index(env_index, d.device)
+    n = int(idx.numel()) if idx is not None else int(d.shape[1])
+    img = torch.empty((n, IMG_H, IMG_W, 3), dtype=torch.uint8, device=d.device)
+    with torch.cuda.device(d.device):
+        _lib.check(_lib.lib().cotix_lunar_draw(
+            torch.cuda.current_stream(d.device).cuda_stream, n, d.data_ptr(), d.stride(0),
+            idx.data_ptr() if idx is not None else None, img.data_ptr(), C.byref(params)))
+    return img
+
+
+def lunar_primitives(state, env_index=None, params: LunarParams | None = None) -> torch.Tensor:
+    """the 44 draw calls of LunarLander.draw per env as primitive records, int32 [n_img, 44, 16]"""
+    from . import lunar_lander as ll
+
+    params = params or ll.default_params()
+    d = state.data
+    idx = _index(env_index, d.device)
+    n = int(idx.numel()) if idx is not None else int(d.shape[1])
+    prims = torch.empty((n, LUNAR_PRIMS, PRIM_WORDS), dtype=torch.int32, device=d.device)
+    with torch.cuda.device(d.device):
+        _lib.check(_lib.lib().cotix_lunar_prims(
+            torch.cuda.current_stream(d.device).cuda_stream, n, d.data_ptr(), d.stride(0),
+            idx.data_ptr() if idx is not None else None, prims.data_ptr(), C.byref(params)))
+    return prims
+
+
+def write_ppm(path: str, image) -> None:
+    """one frame ([600, 800, 3] uint8, tensor or array) as a binary PPM file"""
+    a = image.detach().cpu().numpy() if isinstance(image, torch.Tensor) else np.asarray(image)
+    assert a.dtype == np.uint8 and a.ndim == 3 and a.shape[2] == 3
+    with open(path, "wb") as f:
+        f.write(b"P6\n%d %d\n255\n" % (a.shape[1], a.shape[0]))
+        f.write(np.ascontiguousarray(a).tobytes())
