@@ -326,6 +326,7 @@ def run_ours(args):
         line["narrowphase"] = sweep(args, dev, peak)
         line["robocup"] = robocup(args, dev)
         line["differentiable"] = differentiable(args, dev)
+        line["render"] = render(args, dev, peak)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)
     if rank == 0:
@@ -484,6 +485,56 @@ def differentiable(args, dev):
                          "fd_gradient_rollouts_per_env": 2 * (18 + 2 * T)}}
 
 
+def render(args, dev, peak):
+    """The headless rasteriser (K6, the stand-in for cotix/_viz.py's pygame window): env.draw of
+    n_img LunarLander envs into 800 x 600 RGB8 frames in HBM.  Write-bound: algorithmic bytes =
+    1.44 MB per frame (every pixel written once) + 144 B of state read."""
+    import torch
+
+    from oracle import oracle as o
+    from parallax_b200 import lunar_lander as ll
+    from parallax_b200 import viz
+
+    n = args.render_frames
+    P = ll.default_params()
+    st = ll.reset(lunar_keys_np(n), P, device=dev)
+    for _ in range(3):
+        frames = viz.render_lunar(st, params=P)
+    torch.cuda.synchronize(dev)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    idx = torch.arange(n, device=dev)
+    img = torch.empty((n, 600, 800, 3), dtype=torch.uint8, device=dev)
+    import ctypes as C
+
+    from parallax_b200 import _lib
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    ev0.record()
+    for _ in range(reps):
+        _lib.check(_lib.lib().cotix_lunar_draw(stream, n, st.data.data_ptr(), n, idx.data_ptr(), img.data_ptr(), C.byref(P)))
+    ev1.record()
+    torch.cuda.synchronize(dev)
+    ms = ev0.elapsed_time(ev1) / reps
+    algo = n * (800 * 600 * 3 + 144)
+    # CPU: the oracle's sequential painter on the same draw calls, a sample of frames, one core
+    prims = viz.lunar_primitives(st, idx[:64], P).cpu().numpy()
+    t0 = time.perf_counter()
+    ref = o.raster_draw(prims)
+    cpu = 64 / (time.perf_counter() - t0)
+    same = bool(np.array_equal(img[:64].cpu().numpy(), ref))
+    return {"metric": "frames/sec (800x600 RGB8, LunarLander env.draw)", "unit": "frames/s", "value": n / (ms * 1e-3),
+            "frames": n, "ms": ms, "kernel": "lunar_draw_kernel (band in shared memory, TMA bulk store)",
+            "roofline": {"bound": "hbm", "achieved": algo / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": algo / (ms * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_frame": 800 * 600 * 3 + 144,
+                         "l2": f"{algo / 1e6:.0f} MB written per launch > L2"},
+            "matches_oracle": same,
+            "cpu_port": {"value": cpu, "unit": "frames/s", "cores": 1, "sample": "64 frames"}}
+
+
+def lunar_keys_np(n):
+    return np.stack([np.zeros(n, np.uint32), np.arange(n, dtype=np.uint32)], 1)
+
+
 def cpu_baseline(args):
     """The oracle (a C++ port of the reference path) on the box's host cores, bounded sample."""
     from gen_inputs import lunar_keys, perturbed_lunar_state
@@ -519,6 +570,7 @@ def main():
     ap.add_argument("--max-episode-steps", dest="max_episode_steps", type=int, default=1000)
     ap.add_argument("--pairs", type=int, default=1 << 24)
     ap.add_argument("--robocup-envs", dest="robocup_envs", type=int, default=1 << 18)
+    ap.add_argument("--render-frames", dest="render_frames", type=int, default=2048)
     ap.add_argument("--diff-envs", dest="diff_envs", type=int, default=4096)
     ap.add_argument("--e2e-steps", dest="e2e_steps", type=int, default=50)
     ap.add_argument("--ref-envs", dest="ref_envs", type=int, default=16384)

@@ -49,7 +49,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Compile every CUDA translation unit into parallax_b200/libcotix_b200.so."""
     if not force and not _stale():
         return LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH, *[os.path.join(_CSRC, s) for s in SOURCES]]
+    extra = os.environ.get("COTIX_NVCC_EXTRA", "").split()  # experiments, e.g. -DCX_BAND_ROWS=12
+    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-o", LIB_PATH, *[os.path.join(_CSRC, s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

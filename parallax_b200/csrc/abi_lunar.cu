@@ -330,7 +330,7 @@ int cotix_raster_draw(void* stream, int64_t n_img, const int32_t* prims, const i
   CXL_REQUIRE(n_img >= 0 && max_prims >= 0 && max_prims <= 65536, "bad image / primitive count");
   CXL_REQUIRE(n_img == 0 || image, "null image");
   CXL_REQUIRE(n_img == 0 || max_prims == 0 || prims, "null primitive list");
-  CXL_REQUIRE(((uintptr_t)image & 15u) == 0, "image must be 16-byte aligned");
+  CXL_REQUIRE(((uintptr_t)image & 15u) == 0 && ((uintptr_t)prims & 15u) == 0, "image and prims must be 16-byte aligned");
   return cx_launch_raster_draw((cudaStream_t)stream, n_img, prims, counts, max_prims, image);
 }
 int cotix_lunar_draw(void* stream, int64_t n_img, const float* state, int64_t ld, const int64_t* env_index,

@@ -32,13 +32,17 @@
 namespace {
 
 constexpr int IMG_W = COTIX_IMG_W, IMG_H = COTIX_IMG_H;
-constexpr int BAND_ROWS = 24;                       // 600 = 25 * 24
+#ifndef CX_BAND_ROWS
+#define CX_BAND_ROWS 24
+#endif
+constexpr int BAND_ROWS = CX_BAND_ROWS;              // 600 = 25 * 24
 constexpr int BANDS = IMG_H / BAND_ROWS;
 constexpr int ROW_BYTES = IMG_W * 3;
 constexpr int BAND_BYTES = BAND_ROWS * ROW_BYTES;   // 57 600, a multiple of 16
 constexpr int RTPB = 256;
 constexpr int PW = COTIX_PRIM_WORDS;
 constexpr int LUNAR_PRIMS = 44;
+constexpr int CHUNK = RTPB / (PW / 4);                // 64 records staged per pass
 static_assert(IMG_H % BAND_ROWS == 0 && BAND_BYTES % 16 == 0, "band layout");
 
 CX_DEV void put_pixel(uint8_t* band, int row0, int x, int y, uint32_t rgb) {
@@ -51,11 +55,18 @@ CX_DEV void put_pixel(uint8_t* band, int row0, int x, int y, uint32_t rgb) {
 CX_DEV int imin(int a, int b) { return a < b ? a : b; }
 CX_DEV int imax(int a, int b) { return a > b ? a : b; }
 
-// paints primitive `q` (16 words) into the band [row0, row0 + BAND_ROWS); all threads of the block
-CX_DEV void paint_prim(const int32_t* q, uint8_t* band, int row0) {
+// minor-axis offset of step i of a line: floor((2 i dminor + dmajor) / (2 dmajor)), dmajor > 0
+CX_DEV int line_offset(int i, int dminor, int dmajor) {
+  if (dmajor < 16384)  // i <= dmajor, dminor <= dmajor: fits 32 bits (the on-screen case)
+    return (int)((2u * (unsigned)i * (unsigned)dminor + (unsigned)dmajor) / (2u * (unsigned)dmajor));
+  return (int)((2ll * i * dminor + dmajor) / (2ll * dmajor));
+}
+
+// paints primitive `q` (16 words) into the band [row0, row0 + BAND_ROWS) with the workers
+// first, first + stride, ... (a warp: lane, 32)
+CX_DEV void paint_prim(const int32_t* q, uint8_t* band, int row0, int first, int stride) {
   const int type = q[0];
   const uint32_t rgb = (uint32_t)q[1];
-  const int tid = threadIdx.x;
   const int r1 = row0 + BAND_ROWS - 1;
   if (type == COTIX_PRIM_LINE) {
     int x0 = q[4], y0 = q[5], x1 = q[6], y1 = q[7];
@@ -63,23 +74,22 @@ CX_DEV void paint_prim(const int32_t* q, uint8_t* band, int row0) {
       int t = x0; x0 = x1; x1 = t;
       t = y0; y0 = y1; y1 = t;
     }
+    if (x1 < 0 || x0 >= IMG_W || imax(y0, y1) < row0 || imin(y0, y1) > r1) return;
     const int dx = x1 - x0;                       // >= 0
     const int dy = y1 >= y0 ? y1 - y0 : y0 - y1;
     const int sy = y1 >= y0 ? 1 : -1;
     if (dx >= dy) {                               // x-major: i = x - x0
-      int lo = imax(0, -x0), hi = imin(dx, IMG_W - 1 - x0);
-      for (int i = lo + tid; i <= hi; i += RTPB) {
-        const int off = dx == 0 ? 0 : (int)((2ll * i * dy + dx) / (2ll * dx));
+      const int lo = imax(0, -x0), hi = imin(dx, IMG_W - 1 - x0);
+      for (int i = lo + first; i <= hi; i += stride) {
+        const int off = dx == 0 ? 0 : line_offset(i, dy, dx);
         put_pixel(band, row0, x0 + i, y0 + sy * off, rgb);
       }
     } else {                                      // y-major: i = |y - y0|
       int lo, hi;
       if (sy > 0) { lo = imax(0, row0 - y0); hi = imin(dy, r1 - y0); }
       else        { lo = imax(0, y0 - r1);   hi = imin(dy, y0 - row0); }
-      for (int i = lo + tid; i <= hi; i += RTPB) {
-        const int off = (int)((2ll * i * dx + dy) / (2ll * dy));
-        put_pixel(band, row0, x0 + off, y0 + sy * i, rgb);
-      }
+      for (int i = lo + first; i <= hi; i += stride)
+        put_pixel(band, row0, x0 + line_offset(i, dx, dy), y0 + sy * i, rgb);
     }
   } else if (type == COTIX_PRIM_CIRCLE) {
     const int cx = q[4], cy = q[5], r = q[2];
@@ -89,7 +99,7 @@ CX_DEV void paint_prim(const int32_t* q, uint8_t* band, int row0) {
     if (xa > xb || ya > yb) return;
     const int w = xb - xa + 1, n = w * (yb - ya + 1);
     const long long rr = (long long)r * r;
-    for (int i = tid; i < n; i += RTPB) {
+    for (int i = first; i < n; i += stride) {
       const int x = xa + i % w, y = ya + i / w;
       const long long ddx = x - cx, ddy = y - cy;
       if (ddx * ddx + ddy * ddy <= rr) put_pixel(band, row0, x, y, rgb);
@@ -106,7 +116,7 @@ CX_DEV void paint_prim(const int32_t* q, uint8_t* band, int row0) {
     ya = imax(ya, row0); yb = imin(yb, r1);
     if (xa > xb || ya > yb) return;
     const int w = xb - xa + 1, n = w * (yb - ya + 1);
-    for (int i = tid; i < n; i += RTPB) {
+    for (int i = first; i < n; i += stride) {
       const int x = xa + i % w, y = ya + i / w;
       bool pos = true, neg = true;
       for (int k = 0; k < nv; ++k) {
@@ -122,22 +132,25 @@ CX_DEV void paint_prim(const int32_t* q, uint8_t* band, int row0) {
 }
 
 // clear -> paint in order -> one bulk copy of the band to HBM
-CX_DEV void raster_band(const int32_t* prims, int count, uint8_t* band, int row0, uint8_t* gdst) {
-  {
-    uint4* b4 = reinterpret_cast<uint4*>(band);
-    for (int i = threadIdx.x; i < BAND_BYTES / 16; i += RTPB) b4[i] = make_uint4(0u, 0u, 0u, 0u);
+CX_DEV void clear_band(uint8_t* band) {
+  uint4* b4 = reinterpret_cast<uint4*>(band);
+  for (int i = threadIdx.x; i < BAND_BYTES / 16; i += RTPB) b4[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+// a run of primitives of one colour is a layer: its primitives are painted concurrently, one warp
+// each (racing writes store the same bytes); layers are separated by a barrier.  Ends with a barrier.
+CX_DEV void paint_layers(const int32_t* prims, int count, uint8_t* band, int row0) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int k = 0;
+  while (k < count) {
+    const int32_t rgb = prims[k * PW + 1];
+    int e = k + 1;
+    while (e < count && prims[e * PW + 1] == rgb) ++e;
+    for (int j = k + warp; j < e; j += RTPB / 32) paint_prim(prims + j * PW, band, row0, lane, 32);
+    k = e;
+    __syncthreads();
   }
-  __syncthreads();
-  uint32_t prev = 0xFFFFFFFFu;
-  for (int k = 0; k < count; ++k) {
-    const int32_t* q = prims + k * PW;
-    // primitives of one colour may be painted concurrently (every racing write stores the same
-    // bytes); a change of colour is a layer boundary
-    const uint32_t rgb = (uint32_t)q[1];
-    if (k > 0 && rgb != prev) __syncthreads();
-    prev = rgb;
-    paint_prim(q, band, row0);
-  }
+}
+CX_DEV void store_band(const uint8_t* band, uint8_t* gdst) {
   // generic-proxy writes to shared memory -> visible to the async proxy (TMA) -> bulk store
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   __syncthreads();
@@ -172,46 +185,43 @@ CX_DEV void emit_line(int32_t* q, uint32_t rgb, float ax, float ay, float bx, fl
 #pragma unroll
   for (int k = 8; k < PW; ++k) q[k] = 0;
 }
-template <int N>
-CX_DEV void emit_poly_edges(int32_t* out, const Poly& w) {  // edge k = (v_k, v_{k-1}), :160-163
-#pragma unroll
-  for (int k = 0; k < N; ++k) {
-    const int j = k == 0 ? N - 1 : k - 1;
-    emit_line(out + k * PW, 0xFFFFFFu, w.x[k], w.y[k], w.x[j], w.y[j]);
-  }
-}
 struct PadLines {  // the literal marker lines of cotix/_lunar_lander.py:223-224, scaled on the host
   int32_t v[2][4];
 };
 
-// the draw calls of LunarLander.draw for env e: 44 lines.  One thread builds the list.
-CX_DEV void lunar_build_prims(const float* __restrict__ state, int64_t ld, int64_t e,
-                              const CotixLunarParams& P, const PadLines& pad, int32_t* out) {
-  EnvRegs E;
-  load_dyn(E, state, ld, e);
-  load_terrain(E, state, ld, e);
-  Poly w;
-  float s, c;
-  cx_sincosf(E.b[0].ang, &s, &c);
-  world_poly<6>(P.lander_local, E.b[0], c, s, w);
-  emit_poly_edges<6>(out, w);
-  cx_sincosf(E.b[1].ang, &s, &c);
-  world_poly<4>(P.leg_local[0], E.b[1], c, s, w);
-  emit_poly_edges<4>(out + 6 * PW, w);
-  cx_sincosf(E.b[2].ang, &s, &c);
-  world_poly<4>(P.leg_local[1], E.b[2], c, s, w);
-  emit_poly_edges<4>(out + 10 * PW, w);
-  for (int k = 0; k < 7; ++k) {  // ground trapezoid k: top edge, right side, floor, left side
-    const float x0 = terrain_x(E.kn, P, k), x1 = terrain_x(E.kn, P, k + 1);
-    const float h0 = sel8(E.h, k), h1 = sel8(E.h, k + 1);
-    int32_t* q = out + (14 + 4 * k) * PW;
-    emit_line(q, 0xFFFFFFu, x0, h0, x1, h1);
-    emit_line(q + PW, 0xFFFFFFu, x1, h1, x1, P.ground_floor);
-    emit_line(q + 2 * PW, 0xFFFFFFu, x1, P.ground_floor, x0, P.ground_floor);
-    emit_line(q + 3 * PW, 0xFFFFFFu, x0, P.ground_floor, x0, h0);
-  }
-  for (int l = 0; l < 2; ++l) {
-    int32_t* q = out + (42 + l) * PW;
+CX_DEV V2 world_vertex(const float v[2], float px, float py, float c, float s) {  // as world_poly
+  const float ms = -s;
+  return mk2(c * v[0] + ms * v[1] + px * 1.0f, s * v[0] + c * v[1] + py * 1.0f);
+}
+// draw call t (0..43) of LunarLander.draw for env e: 6 + 4 + 4 body edges, 7 x 4 ground edges, 2 pad
+// markers.  One thread per draw call.
+CX_DEV void lunar_build_prim(const float* __restrict__ state, int64_t ld, int64_t e,
+                             const CotixLunarParams& P, const PadLines& pad, int t, int32_t* q) {
+  if (t < 14) {  // edge k = (v_k, v_{k-1}) of body b, cotix/_convex_shapes.py:160-163
+    const int b = t < 6 ? 0 : (t < 10 ? 1 : 2);
+    const int n = b == 0 ? 6 : 4;
+    const int k = t - (b == 0 ? 0 : (b == 1 ? 6 : 10));
+    const int j = k == 0 ? n - 1 : k - 1;
+    const float px = state[(b * 6 + 0) * ld + e], py = state[(b * 6 + 1) * ld + e];
+    float s, c;
+    cx_sincosf(state[(b * 6 + 4) * ld + e], &s, &c);
+    const float (*loc)[2] = b == 0 ? P.lander_local : P.leg_local[b - 1];
+    const V2 a = world_vertex(loc[k], px, py, c, s), z = world_vertex(loc[j], px, py, c, s);
+    emit_line(q, 0xFFFFFFu, a.x, a.y, z.x, z.y);
+  } else if (t < 42) {  // ground trapezoid g: top edge, right side, floor, left side
+    const int g = (t - 14) >> 2, side = (t - 14) & 3;
+    float kn[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) kn[i] = state[(COTIX_F_KNOT0 + i) * ld + e];
+    const float x0 = terrain_x(kn, P, g), x1 = terrain_x(kn, P, g + 1);
+    const float h0 = state[(COTIX_F_HEIGHT0 + g) * ld + e], h1 = state[(COTIX_F_HEIGHT0 + g + 1) * ld + e];
+    const float fl = P.ground_floor;
+    if (side == 0) emit_line(q, 0xFFFFFFu, x0, h0, x1, h1);
+    else if (side == 1) emit_line(q, 0xFFFFFFu, x1, h1, x1, fl);
+    else if (side == 2) emit_line(q, 0xFFFFFFu, x1, fl, x0, fl);
+    else emit_line(q, 0xFFFFFFu, x0, fl, x0, h0);
+  } else {
+    const int l = t - 42;
     q[0] = COTIX_PRIM_LINE;
     q[1] = 0xFF0000;
     q[2] = q[3] = 0;
@@ -219,6 +229,7 @@ CX_DEV void lunar_build_prims(const float* __restrict__ state, int64_t ld, int64
     q[5] = pad.v[l][1];
     q[6] = pad.v[l][2];
     q[7] = pad.v[l][3];
+#pragma unroll
     for (int k = 8; k < PW; ++k) q[k] = 0;
   }
 }
@@ -232,8 +243,19 @@ raster_draw_kernel(int64_t img0, const int32_t* __restrict__ prims, const int32_
   int count = counts ? counts[img] : max_prims;
   if (count > max_prims) count = max_prims;
   if (count < 0) count = 0;
-  raster_band(prims + img * (int64_t)max_prims * PW, count, smem, band * BAND_ROWS,
-              image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)band * BAND_BYTES);
+  int32_t* sprims = reinterpret_cast<int32_t*>(smem + BAND_BYTES);
+  const int32_t* gp = prims + img * (int64_t)max_prims * PW;
+  clear_band(smem);
+  // the list is staged through shared memory CHUNK records at a time (one 16-byte load per thread)
+  for (int c0 = 0; c0 < count; c0 += CHUNK) {
+    const int n = imin(CHUNK, count - c0);
+    __syncthreads();
+    if ((int)threadIdx.x < n * (PW / 4))
+      reinterpret_cast<int4*>(sprims)[threadIdx.x] = reinterpret_cast<const int4*>(gp + (int64_t)c0 * PW)[threadIdx.x];
+    __syncthreads();
+    paint_layers(sprims, n, smem, band * BAND_ROWS);
+  }
+  store_band(smem, image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)band * BAND_BYTES);
 }
 
 __global__ void __launch_bounds__(RTPB)
@@ -245,18 +267,20 @@ lunar_draw_kernel(int64_t img0, const float* __restrict__ state, int64_t ld,
   const int band = blockIdx.x;
   const int64_t img = img0 + blockIdx.y;
   const int64_t e = env_index ? env_index[img] : img;
-  if (threadIdx.x == 0) lunar_build_prims(state, ld, e, P, pad, sprims);
+  if (threadIdx.x < LUNAR_PRIMS) lunar_build_prim(state, ld, e, P, pad, threadIdx.x, sprims + threadIdx.x * PW);
+  clear_band(smem);
   __syncthreads();
-  raster_band(sprims, LUNAR_PRIMS, smem, band * BAND_ROWS,
-              image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)band * BAND_BYTES);
+  paint_layers(sprims, LUNAR_PRIMS, smem, band * BAND_ROWS);
+  store_band(smem, image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)band * BAND_BYTES);
 }
 
 __global__ void lunar_prims_kernel(int64_t n, const float* __restrict__ state, int64_t ld,
                                    const int64_t* __restrict__ env_index, int32_t* __restrict__ prims,
                                    const __grid_constant__ CotixLunarParams P, const PadLines pad) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  lunar_build_prims(state, ld, env_index ? env_index[i] : i, P, pad, prims + i * (int64_t)LUNAR_PRIMS * PW);
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // (image, draw call)
+  if (i >= n * LUNAR_PRIMS) return;
+  const int64_t img = i / LUNAR_PRIMS;
+  lunar_build_prim(state, ld, env_index ? env_index[img] : img, P, pad, (int)(i % LUNAR_PRIMS), prims + i * PW);
 }
 
 // Python's int((v + 8) / 16 * 800) on Python floats (float64), as LunarLander.draw passes them
@@ -282,12 +306,12 @@ extern "C" int cx_launch_raster_draw(cudaStream_t st, int64_t n_img, const int32
   if (n_img == 0) return 0;
   static bool once = false;
   if (!once) {
-    cudaFuncSetAttribute(raster_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BAND_BYTES);
+    cudaFuncSetAttribute(raster_draw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BAND_BYTES + CHUNK * PW * 4);
     once = true;
   }
   for (int64_t i0 = 0; i0 < n_img; i0 += 65535) {
     const int64_t n = n_img - i0 < 65535 ? n_img - i0 : 65535;
-    raster_draw_kernel<<<dim3(BANDS, (unsigned)n), RTPB, BAND_BYTES, st>>>(i0, prims, counts, max_prims, image);
+    raster_draw_kernel<<<dim3(BANDS, (unsigned)n), RTPB, BAND_BYTES + CHUNK * PW * 4, st>>>(i0, prims, counts, max_prims, image);
     cx_count_launch();
   }
   return cx_check_launch("raster_draw_kernel");
@@ -314,7 +338,7 @@ extern "C" int cx_launch_lunar_draw(cudaStream_t st, int64_t n_img, const float*
 extern "C" int cx_launch_lunar_prims(cudaStream_t st, int64_t n, const float* state, int64_t ld,
                                      const int64_t* env_index, int32_t* prims, const CotixLunarParams* p) {
   if (n == 0) return 0;
-  lunar_prims_kernel<<<(unsigned)((n + 63) / 64), 64, 0, st>>>(n, state, ld, env_index, prims, *p, pad_lines());
+  lunar_prims_kernel<<<(unsigned)((n * LUNAR_PRIMS + 127) / 128), 128, 0, st>>>(n, state, ld, env_index, prims, *p, pad_lines());
   cx_count_launch();
   return cx_check_launch("lunar_prims_kernel");
 }
