@@ -138,13 +138,21 @@ CX_DEV void clear_band(uint8_t* band) {
 }
 // a run of primitives of one colour is a layer: its primitives are painted concurrently, one warp
 // each (racing writes store the same bytes); layers are separated by a barrier.  Ends with a barrier.
-CX_DEV void paint_layers(const int32_t* prims, int count, uint8_t* band, int row0) {
+CX_DEV void paint_layers(const int32_t* prims, int count, uint8_t* band, int row0) {  // count <= 64
+  __shared__ uint32_t s_start[2];  // bit j: primitive j starts a layer
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x < 64) {
+    const int j = threadIdx.x;
+    const bool st = j < count && (j == 0 || prims[j * PW + 1] != prims[(j - 1) * PW + 1]);
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, st);
+    if (lane == 0) s_start[warp] = m;
+  }
+  __syncthreads();
+  const unsigned long long starts = (unsigned long long)s_start[0] | ((unsigned long long)s_start[1] << 32);
   int k = 0;
   while (k < count) {
-    const int32_t rgb = prims[k * PW + 1];
-    int e = k + 1;
-    while (e < count && prims[e * PW + 1] == rgb) ++e;
+    const unsigned long long rest = starts & ~((2ull << k) - 1ull);
+    const int e = rest ? __ffsll((long long)rest) - 1 : count;
     for (int j = k + warp; j < e; j += RTPB / 32) paint_prim(prims + j * PW, band, row0, lane, 32);
     k = e;
     __syncthreads();
