@@ -247,6 +247,11 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(reward_sum, op=dist.ReduceOp.SUM)  # the only collective: episode-return stats
     ms_max = float(t.item())
+    ms_ranks = [ms]
+    if dist is not None:  # per-rank step time, for diagnosis of the max
+        g = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(g, torch.tensor([ms], dtype=torch.float64, device=dev))
+        ms_ranks = [float(x.item()) for x in g]
     total_env_steps = world * B * args.steps * args.substeps
     value = total_env_steps / (ms_max * 1e-3)
 
@@ -300,6 +305,7 @@ def run_ours(args):
     line = {
         "metric": "LunarLander env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+        "ms_per_step_ranks": [m / args.steps for m in ms_ranks],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": "LunarLander 1M envs/GPU, auto-reset (BASELINE config 3)",

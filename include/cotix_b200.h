@@ -337,11 +337,23 @@ int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t
 /*
  * Backward pass over the tape of cotix_lunar_rollout: on entry g holds dL/d(state_T) (DEVICE
  * [NDYN][ld]), on return dL/d(state_0); g_actions DEVICE [T][2][ld] or NULL receives
- * dL/d(action_t).  T kernel launches on `stream`, no synchronisation, graph-capturable.
+ * dL/d(action_t).  Only enqueues on `stream`, no synchronisation, graph-capturable.
+ *
+ * workspace (DEVICE, 256-byte aligned, optional): the DECISION TAPE.  The replay of a step (its
+ * narrowphase and the collider's coin flips) depends only on the state before it, so with a
+ * workspace the replays of many steps run as ONE launch over (step, env) items
+ * (lunar_decide_kernel) that writes, per env-step, the <= 4 resolve_collision calls with their
+ * ContactInfo and final EPA edge (COTIX_ADJ_TAPE_WORDS words), and the sequential reverse sweep
+ * (one light launch per step) reads them.  Any size >= cotix_lunar_adjoint_workspace_bytes(ld, 1)
+ * works (the steps are processed in groups that fit); (ld, T) holds the whole rollout.  With
+ * workspace == NULL every step replays its own decisions inside the reverse sweep (T launches
+ * that are each latency-bound by the envs in contact).  Results are identical.
  */
+#define COTIX_ADJ_TAPE_WORDS 33
+int64_t cotix_lunar_adjoint_workspace_bytes(int64_t ld, int32_t T);
 int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
                             const float* actions, float* g, float* g_actions, uint32_t* flags,
-                            const CotixLunarParams* p);
+                            const CotixLunarParams* p, void* workspace, int64_t workspace_bytes);
 
 /* ------------------------------------------------------------------------------------ */
 /* Headless rasteriser (K6): the replacement for the pygame window of cotix/_viz.py — there  */

@@ -23,7 +23,9 @@ extern "C" int cx_lunar_pipeline_profiling();
 extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, const float*, int64_t,
                                         const float*, const float*, float*, float*, uint32_t*,
-                                        const CotixLunarParams*);
+                                        const float*, const CotixLunarParams*);
+extern "C" int cx_launch_lunar_decide(cudaStream_t, int64_t, int, const float*, int64_t, const float*, float*,
+                                      const CotixLunarParams*);
 extern "C" int cx_launch_raster_draw(cudaStream_t, int64_t, const int32_t*, const int32_t*, int32_t, uint8_t*);
 extern "C" int cx_launch_lunar_draw(cudaStream_t, int64_t, const float*, int64_t, const int64_t*, uint8_t*,
                                     const CotixLunarParams*);
@@ -283,7 +285,7 @@ int cotix_lunar_step_bwd(void* stream, int64_t B, const float* state_in, const f
   CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
   CXL_REQUIRE(B == 0 || (state_in && g_out && g_in), "null state / cotangent");
   return cx_launch_lunar_step_bwd((cudaStream_t)stream, B, state_in, state_next, ld, action, g_out, g_in,
-                                  g_action, flags, p);
+                                  g_action, flags, nullptr, p);
 }
 
 int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t ld, const float* actions,
@@ -306,20 +308,44 @@ int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t
   return 0;
 }
 
+int64_t cotix_lunar_adjoint_workspace_bytes(int64_t ld, int32_t T) {
+  if (ld < 0 || T < 0) return 0;
+  return (int64_t)T * COTIX_ADJ_TAPE_WORDS * ld * (int64_t)sizeof(float);
+}
+
 int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
                             const float* actions, float* g, float* g_actions, uint32_t* flags,
-                            const CotixLunarParams* p) {
+                            const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
   CXL_REQUIRE(B >= 0 && ld >= B && T >= 0, "bad batch size / leading dimension / step count");
   CXL_REQUIRE(check_params(p), "bad params");
   CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
   CXL_REQUIRE(B == 0 || (tape && g), "null tape / cotangent");
   const int64_t slot = (int64_t)COTIX_LUNAR_NF * ld;
-  for (int32_t t = T - 1; t >= 0; --t) {
-    const float* a = actions ? actions + (int64_t)t * 2 * ld : nullptr;
-    float* ga = g_actions ? g_actions + (int64_t)t * 2 * ld : nullptr;
-    const int rc = cx_launch_lunar_step_bwd((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot,
-                                            ld, a, g, g, ga, flags, p);
-    if (rc != 0) return rc;
+  const int64_t dslot = (int64_t)COTIX_ADJ_TAPE_WORDS * ld;
+  int64_t group = 0;  // steps whose decisions fit the workspace at once
+  if (workspace && B > 0) {
+    CXL_REQUIRE(((uintptr_t)workspace & 255u) == 0, "workspace must be 256-byte aligned");
+    group = workspace_bytes / (dslot * (int64_t)sizeof(float));
+    CXL_REQUIRE(group >= 1, "workspace smaller than cotix_lunar_adjoint_workspace_bytes(ld, 1)");
+  }
+  float* dt = (float*)workspace;
+  int32_t t = T;
+  while (t > 0) {
+    const int32_t nt = group > 0 ? (int32_t)(t < group ? t : group) : 1;
+    const int32_t t0 = t - nt;
+    if (group > 0) {
+      const int rc = cx_launch_lunar_decide((cudaStream_t)stream, B, nt, tape + t0 * slot, ld,
+                                            actions ? actions + (int64_t)t0 * 2 * ld : nullptr, dt, p);
+      if (rc != 0) return rc;
+    }
+    for (int32_t s = t - 1; s >= t0; --s) {
+      const float* a = actions ? actions + (int64_t)s * 2 * ld : nullptr;
+      float* ga = g_actions ? g_actions + (int64_t)s * 2 * ld : nullptr;
+      const int rc = cx_launch_lunar_step_bwd((cudaStream_t)stream, B, tape + s * slot, tape + (s + 1) * slot, ld,
+                                              a, g, g, ga, flags, group > 0 ? dt + (s - t0) * dslot : nullptr, p);
+      if (rc != 0) return rc;
+    }
+    t = t0;
   }
   return 0;
 }

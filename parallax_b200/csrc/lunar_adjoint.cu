@@ -401,10 +401,11 @@ CX_DEV void contact_from_edges_bwd(const Poly& A, const Poly& B, V2 g_cp, PolyGr
   }
 }
 
-// g_pen, g_cp of candidate pair `pid` -> cotangents of the poses of the dynamic bodies involved
+// g_pen, g_cp of candidate pair `pid` -> cotangents of the poses of the dynamic bodies involved.
+// (ba, bb) is the final EPA edge of the pair (the penetration vector is closest_to_origin(ba, bb)).
 static __device__ __noinline__ void pair_contact_bwd(const RegPolys& src, int pid, const EnvRegs& E,
-                                                     const CotixLunarParams& P, V2 g_pen, V2 g_cp,
-                                                     G6 g[4], uint32_t& flags) {
+                                                     const CotixLunarParams& P, V2 ba, V2 bb, V2 g_pen,
+                                                     V2 g_cp, G6 g[4]) {
   Poly A, B;
   make_item_polys(src, pid, P, A, B);
   int wa, wb, gk;
@@ -412,17 +413,6 @@ static __device__ __noinline__ void pair_contact_bwd(const RegPolys& src, int pi
   PolyGrad gA, gB;
 #pragma unroll
   for (int k = 0; k < CX_MAXV; ++k) gA.x[k] = gA.y[k] = gB.x[k] = gB.y[k] = 0.0f;
-  V2 s0, s1, s2;
-  bool gcap, ecap;
-  const bool ex = gjk(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters, s0, s1, s2, gcap);
-  if (!ex) {
-    flags |= COTIX_ADJ_REPLAY_MISMATCH;
-    return;
-  }
-  int iters = A.n + B.n + 1;
-  if (iters > 13) iters = 13;
-  V2 ba, bb;
-  epa_edge<16>(A, B, s0, s1, s2, iters, ecap, ba, bb);
   V2 g_a, g_b;
   closest_to_origin_bwd(ba, bb, g_pen, g_a, g_b);
   mdiff_point_bwd(A, B, ba, g_a, gA, gB);
@@ -435,58 +425,95 @@ static __device__ __noinline__ void pair_contact_bwd(const RegPolys& src, int pi
     attached_point_bwd(mk2(B.x[k], B.y[k]), E.b[wb], mk2(gB.x[k], gB.y[k]), g[wb]);
 }
 
-static __device__ __noinline__ Contact eval_pair(const RegPolys& src, int pid, const CotixLunarParams& P) {
+// polygon_vs_polygon (cotix/_contacts.py:294-315) of candidate pair `pid`, as poly_pair computes it,
+// also returning the final EPA edge
+static __device__ __noinline__ Contact eval_pair_edge(const RegPolys& src, int pid,
+                                                      const CotixLunarParams& P, V2& ea, V2& eb) {
   Poly A, B;
   make_item_polys(src, pid, P, A, B);
-  return poly_pair(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters);
+  Contact c = contact_none();
+  ea = eb = mk2(0.0f, 0.0f);
+  V2 s0, s1, s2;
+  bool gcap, ecap;
+  if (!gjk(A, B, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters, s0, s1, s2, gcap)) return c;
+  int iters = A.n + B.n + 1;
+  if (iters > 13) iters = 13;
+  epa_edge<16>(A, B, s0, s1, s2, iters, ecap, ea, eb);
+  c.pen = closest_to_origin(ea, eb);
+  c.cp = contact_from_edges(A, B);
+  return c;
+}
+
+// What the collider decided in one step of one env: the resolve_collision calls in scan order with
+// their ContactInfo and final EPA edge.  132 bytes per env-step on the decision tape:
+// word 0 = n | pid0 << 3 | pid1 << 8 | pid2 << 13 | pid3 << 18, then 8 floats per call.
+struct Decisions {
+  Plan pl;
+  V2 pen[4], cp[4], ea[4], eb[4];
+};
+constexpr int DT_WORDS = COTIX_ADJ_TAPE_WORDS;
+
+// replay of the irregular part of the step: narrowphase of the candidates + the collider's choices
+static __device__ __noinline__ void decide(const EnvRegs& E, uint32_t cand, const RegPolys& src,
+                                           const CotixLunarParams& P, Decisions& d) {
+  Contact res[CX_NPAIR];
+  V2 ea[CX_NPAIR], eb[CX_NPAIR];
+  uint32_t todo = cand;
+  while (todo) {
+    const int bit = __ffs(todo) - 1;
+    todo &= todo - 1u;
+    res[bit] = eval_pair_edge(src, bit, P, ea[bit], eb[bit]);
+  }
+  const LocalContacts cs{res, cand};
+  collide_plan(E, P, cand, cs, d.pl);
+  for (int i = 0; i < d.pl.n; ++i) {
+    const int pid = d.pl.pid[i];
+    d.pen[i] = res[pid].pen;
+    d.cp[i] = res[pid].cp;
+    d.ea[i] = ea[pid];
+    d.eb[i] = eb[pid];
+  }
+}
+CX_DEV void store_decisions(const Decisions& d, float* __restrict__ dt, int64_t ld, int64_t e) {
+  uint32_t w = (uint32_t)d.pl.n;
+  for (int i = 0; i < d.pl.n; ++i) w |= (uint32_t)d.pl.pid[i] << (3 + 5 * i);
+  dt[e] = __uint_as_float(w);
+  for (int i = 0; i < d.pl.n; ++i) {
+    float* q = dt + (1 + 8 * i) * ld + e;
+    q[0 * ld] = d.pen[i].x; q[1 * ld] = d.pen[i].y; q[2 * ld] = d.cp[i].x; q[3 * ld] = d.cp[i].y;
+    q[4 * ld] = d.ea[i].x;  q[5 * ld] = d.ea[i].y;  q[6 * ld] = d.eb[i].x; q[7 * ld] = d.eb[i].y;
+  }
+}
+CX_DEV void load_decisions(Decisions& d, const float* __restrict__ dt, int64_t ld, int64_t e) {
+  const uint32_t w = __float_as_uint(dt[e]);
+  d.pl.n = (int)(w & 7u);
+  if (d.pl.n > 4) d.pl.n = 4;
+  for (int i = 0; i < d.pl.n; ++i) {
+    const int pid = (int)((w >> (3 + 5 * i)) & 31u);
+    int wa, wb, gk;
+    pair_bodies(pid, wa, wb, gk);
+    d.pl.pid[i] = pid;
+    d.pl.b1[i] = wa >= 0 ? wa : 3;
+    d.pl.b2[i] = wb;
+    const float* q = dt + (1 + 8 * i) * ld + e;
+    d.pen[i] = mk2(q[0 * ld], q[1 * ld]);
+    d.cp[i] = mk2(q[2 * ld], q[3 * ld]);
+    d.ea[i] = mk2(q[4 * ld], q[5 * ld]);
+    d.eb[i] = mk2(q[6 * ld], q[7 * ld]);
+  }
 }
 
 CX_DEV bool same_bits(float a, float b) { return (a == b) || (a != a && b != b); }
 
-__global__ void __launch_bounds__(TPB)
-lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __restrict__ snext,
-                      int64_t ld, const float* __restrict__ action, const float* g_out, float* g_in,
-                      float* __restrict__ g_action, uint32_t* __restrict__ flags_out,
-                      const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
-  const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
-  if (e >= B) return;
-  EnvRegs E;
-  load_env(E, sin_, ld, e);
-  float am = 0.0f, as = 0.0f;
-  if (action) {
-    am = action[e];
-    as = action[ld + e];
-  }
-  uint32_t flags = 0u;
-  G6 g[4];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    g[i].px = g_out[(i * 6 + 0) * ld + e];
-    g[i].py = g_out[(i * 6 + 1) * ld + e];
-    g[i].vx = g_out[(i * 6 + 2) * ld + e];
-    g[i].vy = g_out[(i * 6 + 3) * ld + e];
-    g[i].ang = g_out[(i * 6 + 4) * ld + e];
-    g[i].w = g_out[(i * 6 + 5) * ld + e];
-  }
-  g[3] = g6_zero();
-
-  // ---- forward replay --------------------------------------------------------------------------
-  StepCtx cx;
-  Poly wL, wr, wl;
-  integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
-  const RegPolys src{wL, wr, wl, E.h, E.kn};
-  Contact res[CX_NPAIR];
-  {
-    uint32_t todo = cx.cand;
-    while (todo) {
-      const int bit = __ffs(todo) - 1;
-      todo &= todo - 1u;
-      res[bit] = eval_pair(src, bit, P);
-    }
-  }
-  const LocalContacts cs{res, cx.cand};
-  Plan pl;
-  collide_plan(E, P, cx.cand, cs, pl);
+// ---- one step backwards, given the collider's decisions -------------------------------------------
+// E, cx, src: the env after integrate_and_cull of the replay.  g: cotangent of the next state on
+// entry, of this state on exit.  snext (or NULL): the next state the forward kernel wrote.
+static __device__ __noinline__ void step_bwd_core(const EnvRegs& E, const StepCtx& cx, const RegPolys& src,
+                                                  float am, float as, const Decisions& d,
+                                                  const CotixLunarParams& P, const float* __restrict__ snext,
+                                                  int64_t ld, int64_t e, G6 g[4], float& g_am, float& g_as,
+                                                  uint32_t& flags) {
+  const Plan& pl = d.pl;
   MassP mp[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -501,15 +528,14 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
   bd[1] = E.b[1];
   bd[2] = E.b[2];
   bd[3].px = bd[3].py = bd[3].vx = bd[3].vy = bd[3].ang = bd[3].w = 0.0f;
+  // forward: the resolve_collision calls in scan order, then the joints (finish_step)
   BodyS pre1[4], pre2[4];
   for (int i = 0; i < pl.n; ++i) {
     pre1[i] = bd[pl.b1[i]];
     pre2[i] = bd[pl.b2[i]];
-    const Contact c = res[pl.pid[i]];
-    resolve_collision(bd[pl.b1[i]], mp[pl.b1[i]], bd[pl.b2[i]], mp[pl.b2[i]], c.pen, c.cp, P.baumgarte,
+    resolve_collision(bd[pl.b1[i]], mp[pl.b1[i]], bd[pl.b2[i]], mp[pl.b2[i]], d.pen[i], d.cp[i], P.baumgarte,
                       P.baumgarte_dt);
   }
-  // joints (finish_step of cx_lunar_step.cuh)
   V2 c1[4], c2[4];
   {
     const V2 p0 = mk2(bd[0].px, bd[0].py);
@@ -545,64 +571,77 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
     }
     if (!same) flags |= COTIX_ADJ_REPLAY_MISMATCH;
   }
-  flags |= (uint32_t)pl.n << 8;
+  flags |= (uint32_t)pl.n << COTIX_ADJ_CONTACT_SHIFT;
   bool finite = !poisoned;
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     finite = finite && (fabsf(bd[i].px) <= 3.0e38f) && (fabsf(bd[i].py) <= 3.0e38f) &&
              (fabsf(bd[i].vx) <= 3.0e38f) && (fabsf(bd[i].vy) <= 3.0e38f) &&
              (fabsf(bd[i].ang) <= 3.0e38f) && (fabsf(bd[i].w) <= 3.0e38f);
-
-  // ---- reverse ---------------------------------------------------------------------------------
-  float g_am = 0.0f, g_as = 0.0f;
+  g_am = g_as = 0.0f;
   if (!finite) {
     // a non-finite step has no derivative: the cotangent is dropped (and flagged)
     flags |= COTIX_ADJ_NONFINITE;
     g[0] = g[1] = g[2] = g6_zero();
-  } else {
-    g[1].w = g[1].w * P.leg_damping;
-    g[2].w = g[2].w * P.leg_damping;
-#pragma unroll
-    for (int k = 3; k >= 0; --k) {
-      const int leg = k < 2 ? 2 : 1;
-      V2 gc1, gc2;
-      joint_constraint_bwd(jpre1[k], mp[0], c1[k], jpre2[k], mp[leg], c2[k], P, g[0], g[leg], gc1, gc2);
-      attached_point_bwd(c1[k], bd[0], gc1, g[0]);
-      attached_point_bwd(c2[k], bd[leg], gc2, g[leg]);
-    }
-    for (int i = pl.n - 1; i >= 0; --i) {
-      const Contact c = res[pl.pid[i]];
-      V2 g_pen, g_cp;
-      g[3] = g6_zero();  // the ground is static: its cotangent is discarded
-      resolve_collision_bwd(pre1[i], mp[pl.b1[i]], pre2[i], mp[pl.b2[i]], c.pen, c.cp, P.baumgarte,
-                            P.baumgarte_dt, g[pl.b1[i]], g[pl.b2[i]], g_pen, g_cp);
-      pair_contact_bwd(src, pl.pid[i], E, P, g_pen, g_cp, g, flags);
-    }
-    // engines: v0 += (-sn, cs) * dvm + (cs, sn) * dvs; w0 -= side_dw * thr_side
-    {
-      const float cs0 = cx.cs[0], sn0 = cx.sn[0];
-      float g_tm = 0.0f, g_ts = 0.0f;
-      if (cx.thr_main != 0.0f) {
-        const float dvm = P.main_engine_dv * cx.thr_main;
-        g_tm = P.main_engine_dv * (-sn0 * g[0].vx + cs0 * g[0].vy);
-        g[0].ang += (-cs0 * g[0].vx - sn0 * g[0].vy) * dvm;
-      }
-      if (cx.thr_side != 0.0f) {
-        const float dvs = P.side_engine_dv * cx.thr_side;
-        g_ts = P.side_engine_dv * (cs0 * g[0].vx + sn0 * g[0].vy) - P.side_engine_dw * g[0].w;
-        g[0].ang += (-sn0 * g[0].vx + cs0 * g[0].vy) * dvs;
-      }
-      if (am > 0.0f && am < 1.0f) g_am = g_tm;
-      if (as > -1.0f && as < 1.0f) g_as = g_ts;
-    }
-    // ExplicitEulerPhysics.step: p' = p + v dt, angle' = angle + w dt (gravity is a constant)
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      g[i].vx += g[i].px * P.dt;
-      g[i].vy += g[i].py * P.dt;
-      g[i].w += g[i].ang * P.dt;
-    }
+    return;
   }
+  // reverse
+  g[1].w = g[1].w * P.leg_damping;
+  g[2].w = g[2].w * P.leg_damping;
+#pragma unroll
+  for (int k = 3; k >= 0; --k) {
+    const int leg = k < 2 ? 2 : 1;
+    V2 gc1, gc2;
+    joint_constraint_bwd(jpre1[k], mp[0], c1[k], jpre2[k], mp[leg], c2[k], P, g[0], g[leg], gc1, gc2);
+    attached_point_bwd(c1[k], bd[0], gc1, g[0]);
+    attached_point_bwd(c2[k], bd[leg], gc2, g[leg]);
+  }
+  for (int i = pl.n - 1; i >= 0; --i) {
+    V2 g_pen, g_cp;
+    g[3] = g6_zero();  // the ground is static: its cotangent is discarded
+    resolve_collision_bwd(pre1[i], mp[pl.b1[i]], pre2[i], mp[pl.b2[i]], d.pen[i], d.cp[i], P.baumgarte,
+                          P.baumgarte_dt, g[pl.b1[i]], g[pl.b2[i]], g_pen, g_cp);
+    if (!isnan2(d.cp[i])) pair_contact_bwd(src, pl.pid[i], E, P, d.ea[i], d.eb[i], g_pen, g_cp, g);
+  }
+  // engines: v0 += (-sn, cs) * dvm + (cs, sn) * dvs; w0 -= side_dw * thr_side
+  {
+    const float cs0 = cx.cs[0], sn0 = cx.sn[0];
+    float g_tm = 0.0f, g_ts = 0.0f;
+    if (cx.thr_main != 0.0f) {
+      const float dvm = P.main_engine_dv * cx.thr_main;
+      g_tm = P.main_engine_dv * (-sn0 * g[0].vx + cs0 * g[0].vy);
+      g[0].ang += (-cs0 * g[0].vx - sn0 * g[0].vy) * dvm;
+    }
+    if (cx.thr_side != 0.0f) {
+      const float dvs = P.side_engine_dv * cx.thr_side;
+      g_ts = P.side_engine_dv * (cs0 * g[0].vx + sn0 * g[0].vy) - P.side_engine_dw * g[0].w;
+      g[0].ang += (-sn0 * g[0].vx + cs0 * g[0].vy) * dvs;
+    }
+    if (am > 0.0f && am < 1.0f) g_am = g_tm;
+    if (as > -1.0f && as < 1.0f) g_as = g_ts;
+  }
+  // ExplicitEulerPhysics.step: p' = p + v dt, angle' = angle + w dt (gravity is a constant)
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    g[i].vx += g[i].px * P.dt;
+    g[i].vy += g[i].py * P.dt;
+    g[i].w += g[i].ang * P.dt;
+  }
+}
+
+CX_DEV void load_cotangent(G6 g[4], const float* g_out, int64_t ld, int64_t e) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    g[i].px = g_out[(i * 6 + 0) * ld + e];
+    g[i].py = g_out[(i * 6 + 1) * ld + e];
+    g[i].vx = g_out[(i * 6 + 2) * ld + e];
+    g[i].vy = g_out[(i * 6 + 3) * ld + e];
+    g[i].ang = g_out[(i * 6 + 4) * ld + e];
+    g[i].w = g_out[(i * 6 + 5) * ld + e];
+  }
+  g[3] = g6_zero();
+}
+CX_DEV void store_cotangent(const G6 g[4], float* g_in, int64_t ld, int64_t e) {
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     g_in[(i * 6 + 0) * ld + e] = g[i].px;
@@ -612,6 +651,43 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
     g_in[(i * 6 + 4) * ld + e] = g[i].ang;
     g_in[(i * 6 + 5) * ld + e] = g[i].w;
   }
+}
+
+// One step backwards for every env.  dtape == NULL: the collider's decisions are replayed here
+// (narrowphase of all candidates + coins); else they are read from the decision tape of this step.
+__global__ void __launch_bounds__(TPB)
+lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __restrict__ snext,
+                      int64_t ld, const float* __restrict__ action, const float* g_out, float* g_in,
+                      float* __restrict__ g_action, uint32_t* __restrict__ flags_out,
+                      const float* __restrict__ dtape, const __grid_constant__ CotixLunarParams P,
+                      const LunarDerived D) {
+  const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (e >= B) return;
+  EnvRegs E;
+  load_env(E, sin_, ld, e);
+  float am = 0.0f, as = 0.0f;
+  if (action) {
+    am = action[e];
+    as = action[ld + e];
+  }
+  G6 g[4];
+  load_cotangent(g, g_out, ld, e);
+  StepCtx cx;
+  Poly wL, wr, wl;
+  integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
+  const RegPolys src{wL, wr, wl, E.h, E.kn};
+  Decisions d;
+  if (dtape) {
+    load_decisions(d, dtape, ld, e);
+    // integrate_and_cull orders the world polygons only when it found candidates; a taped contact
+    // implies it did
+  } else {
+    decide(E, cx.cand, src, P, d);
+  }
+  uint32_t flags = 0u;
+  float g_am, g_as;
+  step_bwd_core(E, cx, src, am, as, d, P, snext, ld, e, g, g_am, g_as, flags);
+  store_cotangent(g, g_in, ld, e);
   if (g_action) {
     g_action[e] = g_am;
     g_action[ld + e] = g_as;
@@ -619,17 +695,62 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
   if (flags_out) flags_out[e] = flags_out[e] | flags;
 }
 
+// The collider's decisions of nt consecutive steps of a taped rollout in ONE launch: item = (step,
+// env).  The replay of a step depends only on the state before it, which is on the tape, so unlike
+// the reverse sweep it is not sequential in time — this is where the irregular work of the backward
+// pass (narrowphase, coins) runs, at full occupancy instead of one small launch per step.
+__global__ void __launch_bounds__(TPB)
+lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t ld,
+                    const float* __restrict__ actions, float* __restrict__ dtape,
+                    const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
+  const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  if (i >= B * nt) return;
+  const int64_t t = i / B, e = i - t * B;
+  const float* sin_ = tape + t * (int64_t)COTIX_LUNAR_NF * ld;
+  EnvRegs E;
+  load_env(E, sin_, ld, e);
+  float am = 0.0f, as = 0.0f;
+  if (actions) {
+    am = actions[t * 2 * ld + e];
+    as = actions[t * 2 * ld + ld + e];
+  }
+  StepCtx cx;
+  Poly wL, wr, wl;
+  integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
+  float* dt = dtape + t * (int64_t)DT_WORDS * ld;
+  if (cx.cand == 0u) {
+    dt[e] = 0.0f;
+    return;
+  }
+  const RegPolys src{wL, wr, wl, E.h, E.kn};
+  Decisions d;
+  decide(E, cx.cand, src, P, d);
+  store_decisions(d, dt, ld, e);
+}
+
 }  // namespace
 
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t st, int64_t B, const float* state_in,
                                         const float* state_next, int64_t ld, const float* action,
                                         const float* g_out, float* g_in, float* g_action,
-                                        uint32_t* flags, const CotixLunarParams* p) {
+                                        uint32_t* flags, const float* dtape, const CotixLunarParams* p) {
   if (B == 0) return 0;
   LunarDerived D;
   cx_lunar_derive(p, &D);
   lunar_step_bwd_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(
-      B, state_in, state_next, ld, action, g_out, g_in, g_action, flags, *p, D);
+      B, state_in, state_next, ld, action, g_out, g_in, g_action, flags, dtape, *p, D);
   cx_count_launch();
   return cx_check_launch("lunar_step_bwd_kernel");
+}
+
+// decisions of steps [t0, t0 + nt) of a taped rollout -> dtape [nt][COTIX_ADJ_TAPE_WORDS][ld]
+extern "C" int cx_launch_lunar_decide(cudaStream_t st, int64_t B, int nt, const float* tape_t0, int64_t ld,
+                                      const float* actions_t0, float* dtape, const CotixLunarParams* p) {
+  if (B == 0 || nt == 0) return 0;
+  LunarDerived D;
+  cx_lunar_derive(p, &D);
+  const int64_t n = B * nt;
+  lunar_decide_kernel<<<(unsigned)((n + TPB - 1) / TPB), TPB, 0, st>>>(B, nt, tape_t0, ld, actions_t0, dtape, *p, D);
+  cx_count_launch();
+  return cx_check_launch("lunar_decide_kernel");
 }

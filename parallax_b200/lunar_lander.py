@@ -237,19 +237,30 @@ def rollout(state: LunarState, actions: torch.Tensor | None, n_steps: int,
     return Rollout(tape, actions, params)
 
 
-def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None = None):
+def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None = None,
+                decision_tape: bool | int = True):
     """Backward pass over a `Rollout` (`cotix_lunar_rollout_bwd`): g_final [18, B] = dL/d(final
-    dynamic leaves).  Returns (dL/d(initial dynamic leaves) [18, B], dL/d(actions) [T, 2, B])."""
+    dynamic leaves).  Returns (dL/d(initial dynamic leaves) [18, B], dL/d(actions) [T, 2, B]).
+
+    decision_tape: True = scratch for the collider's decisions of the whole rollout (one batched
+    replay launch + T light reverse launches), an int = scratch for that many steps at a time,
+    False = every reverse step replays its own decisions.  Same results."""
     tape = ro.tape
     T, B = tape.shape[0] - 1, tape.shape[2]
     g = g_final.to(device=tape.device, dtype=torch.float32).contiguous().clone()
     assert g.shape == (NDYN, B)
     g_act = torch.zeros((T, 2, B), dtype=torch.float32, device=tape.device)
+    wp, wn, ws = None, 0, None
+    if decision_tape and T > 0:
+        steps = T if decision_tape is True else max(1, min(T, int(decision_tape)))
+        wn = int(_lib.lib().cotix_lunar_adjoint_workspace_bytes(B, steps))
+        ws = torch.empty(wn + 256, dtype=torch.uint8, device=tape.device)
+        wp = (ws.data_ptr() + 255) & ~255
     with torch.cuda.device(tape.device):
         _lib.check(_lib.lib().cotix_lunar_rollout_bwd(
             _stream_ptr(tape.device), B, T, tape.data_ptr(), B,
             ro.actions.data_ptr() if ro.actions is not None else None, g.data_ptr(), g_act.data_ptr(),
-            flags.data_ptr() if flags is not None else None, C.byref(ro.params)))
+            flags.data_ptr() if flags is not None else None, C.byref(ro.params), wp, wn))
     return g, g_act
 
 

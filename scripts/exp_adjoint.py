@@ -100,7 +100,7 @@ def main():
         y = ro.tape[-1, 1]
         g = torch.zeros((18, B), device="cuda")
         g[1] = 2.0 * y
-        g0, ga = ll.rollout_vjp(ro, g, flags)
+        g0, ga = ll.rollout_vjp(ro, g, flags, decision_tape=not os.environ.get("NOTAPE"))
         ev[2].record()
         torch.cuda.synchronize()
     f = flags.cpu().numpy()

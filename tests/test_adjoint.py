@@ -206,6 +206,13 @@ def test_rollout_vjp_contact_rich(cuda_lib, oracle, exact_trig):
     g0, ga = ll.rollout_vjp(ro, torch.from_numpy(gn).cuda(), flags)
     flags = flags.cpu().numpy()
     assert int((flags & ll.ADJ_REPLAY_MISMATCH).sum()) == 0
+    # the decision tape (one batched replay launch, any group size) changes nothing
+    for dt in (False, 3, 1):
+        f2 = torch.zeros(B, dtype=torch.int32, device="cuda")
+        h0, ha = ll.rollout_vjp(ro, torch.from_numpy(gn).cuda(), f2, decision_tape=dt)
+        assert torch.equal(h0.view(torch.int32), g0.view(torch.int32)), dt
+        assert torch.equal(ha.view(torch.int32), ga.view(torch.int32)), dt
+        assert np.array_equal(f2.cpu().numpy(), flags), dt
     finite = (flags & ll.ADJ_NONFINITE) == 0
     touched = ((flags >> ll.ADJ_CONTACT_SHIFT) & 7) > 0
     assert (finite & touched).sum() >= 200
