@@ -42,6 +42,8 @@ constexpr int BAND_BYTES = BAND_ROWS * ROW_BYTES;   // 57 600, a multiple of 16
 constexpr int RTPB = 256;
 constexpr int PW = COTIX_PRIM_WORDS;
 constexpr int LUNAR_PRIMS = 44;
+constexpr int LUNAR_BANDS_PER_BLOCK = 5;             // consecutive bands painted by one block (both kernels)
+static_assert(BANDS % LUNAR_BANDS_PER_BLOCK == 0, "bands per block");
 constexpr int CHUNK = RTPB / (PW / 4);                // 64 records staged per pass
 static_assert(IMG_H % BAND_ROWS == 0 && BAND_BYTES % 16 == 0, "band layout");
 
@@ -253,17 +255,24 @@ raster_draw_kernel(int64_t img0, const int32_t* __restrict__ prims, const int32_
   if (count < 0) count = 0;
   int32_t* sprims = reinterpret_cast<int32_t*>(smem + BAND_BYTES);
   const int32_t* gp = prims + img * (int64_t)max_prims * PW;
-  clear_band(smem);
-  // the list is staged through shared memory CHUNK records at a time (one 16-byte load per thread)
-  for (int c0 = 0; c0 < count; c0 += CHUNK) {
-    const int n = imin(CHUNK, count - c0);
-    __syncthreads();
-    if ((int)threadIdx.x < n * (PW / 4))
-      reinterpret_cast<int4*>(sprims)[threadIdx.x] = reinterpret_cast<const int4*>(gp + (int64_t)c0 * PW)[threadIdx.x];
-    __syncthreads();
-    paint_layers(sprims, n, smem, band * BAND_ROWS);
+  // a block paints LUNAR_BANDS_PER_BLOCK consecutive bands; the list is staged through shared memory
+  // CHUNK records at a time (one 16-byte load per thread), once if it fits
+  for (int b = 0; b < LUNAR_BANDS_PER_BLOCK; ++b) {
+    const int bi = band * LUNAR_BANDS_PER_BLOCK + b;
+    __syncthreads();  // the previous band's bulk store has read the buffer
+    clear_band(smem);
+    for (int c0 = 0; c0 < count; c0 += CHUNK) {
+      const int n = imin(CHUNK, count - c0);
+      if (b == 0 || count > CHUNK) {
+        __syncthreads();
+        if ((int)threadIdx.x < n * (PW / 4))
+          reinterpret_cast<int4*>(sprims)[threadIdx.x] = reinterpret_cast<const int4*>(gp + (int64_t)c0 * PW)[threadIdx.x];
+      }
+      __syncthreads();
+      paint_layers(sprims, n, smem, bi * BAND_ROWS);
+    }
+    store_band(smem, image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)bi * BAND_BYTES);
   }
-  store_band(smem, image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)band * BAND_BYTES);
 }
 
 __global__ void __launch_bounds__(RTPB)
@@ -276,10 +285,15 @@ lunar_draw_kernel(int64_t img0, const float* __restrict__ state, int64_t ld,
   const int64_t img = img0 + blockIdx.y;
   const int64_t e = env_index ? env_index[img] : img;
   if (threadIdx.x < LUNAR_PRIMS) lunar_build_prim(state, ld, e, P, pad, threadIdx.x, sprims + threadIdx.x * PW);
-  clear_band(smem);
-  __syncthreads();
-  paint_layers(sprims, LUNAR_PRIMS, smem, band * BAND_ROWS);
-  store_band(smem, image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)band * BAND_BYTES);
+  // the draw calls are built once per block and reused for LUNAR_BANDS_PER_BLOCK consecutive bands
+  for (int b = 0; b < LUNAR_BANDS_PER_BLOCK; ++b) {
+    const int bi = band * LUNAR_BANDS_PER_BLOCK + b;
+    __syncthreads();  // draw calls visible; the previous band's bulk store has read the buffer
+    clear_band(smem);
+    __syncthreads();
+    paint_layers(sprims, LUNAR_PRIMS, smem, bi * BAND_ROWS);
+    store_band(smem, image + img * (int64_t)IMG_H * ROW_BYTES + (int64_t)bi * BAND_BYTES);
+  }
 }
 
 __global__ void lunar_prims_kernel(int64_t n, const float* __restrict__ state, int64_t ld,
@@ -319,7 +333,7 @@ extern "C" int cx_launch_raster_draw(cudaStream_t st, int64_t n_img, const int32
   }
   for (int64_t i0 = 0; i0 < n_img; i0 += 65535) {
     const int64_t n = n_img - i0 < 65535 ? n_img - i0 : 65535;
-    raster_draw_kernel<<<dim3(BANDS, (unsigned)n), RTPB, BAND_BYTES + CHUNK * PW * 4, st>>>(i0, prims, counts, max_prims, image);
+    raster_draw_kernel<<<dim3(BANDS / LUNAR_BANDS_PER_BLOCK, (unsigned)n), RTPB, BAND_BYTES + CHUNK * PW * 4, st>>>(i0, prims, counts, max_prims, image);
     cx_count_launch();
   }
   return cx_check_launch("raster_draw_kernel");
@@ -337,7 +351,7 @@ extern "C" int cx_launch_lunar_draw(cudaStream_t st, int64_t n_img, const float*
   const PadLines pad = pad_lines();
   for (int64_t i0 = 0; i0 < n_img; i0 += 65535) {
     const int64_t n = n_img - i0 < 65535 ? n_img - i0 : 65535;
-    lunar_draw_kernel<<<dim3(BANDS, (unsigned)n), RTPB, smem, st>>>(i0, state, ld, env_index, image, *p, pad);
+    lunar_draw_kernel<<<dim3(BANDS / LUNAR_BANDS_PER_BLOCK, (unsigned)n), RTPB, smem, st>>>(i0, state, ld, env_index, image, *p, pad);
     cx_count_launch();
   }
   return cx_check_launch("lunar_draw_kernel");

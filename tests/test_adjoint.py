@@ -252,3 +252,21 @@ def test_adjoint_argument_checks(cuda_lib):
     with pytest.raises(_lib.CotixError):
         _lib.check(_lib.lib().cotix_lunar_step_bwd(None, 8, st.data.data_ptr(), None, 8, None, None, None, None, None,
                                                   C.byref(ll.default_params())))
+    # rollout_bwd: a workspace smaller than one step of decisions, or misaligned, is refused
+    L = _lib.lib()
+    tape = torch.zeros((3, 36, 8), device="cuda")
+    tape[0] = st.data
+    need = int(L.cotix_lunar_adjoint_workspace_bytes(8, 1))
+    assert need == 33 * 8 * 4 and int(L.cotix_lunar_adjoint_workspace_bytes(8, 100)) == 100 * need
+    ws = torch.zeros(need + 512, dtype=torch.uint8, device="cuda")
+    wp = (ws.data_ptr() + 255) & ~255
+    P = ll.default_params()
+    args = (None, 8, 2, tape.data_ptr(), 8, None, g.data_ptr(), None, None, C.byref(P))
+    with pytest.raises(_lib.CotixError):
+        _lib.check(L.cotix_lunar_rollout_bwd(*args, wp, need - 4))
+    with pytest.raises(_lib.CotixError):
+        _lib.check(L.cotix_lunar_rollout_bwd(*args, wp + 4, need))
+    _lib.check(L.cotix_lunar_rollout(None, 8, 2, tape.data_ptr(), 8, None, C.byref(P), None, 0))
+    _lib.check(L.cotix_lunar_rollout_bwd(*args, wp, need))
+    torch.cuda.synchronize()
+

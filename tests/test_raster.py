@@ -125,6 +125,10 @@ def test_raster_draw_matches_the_oracle(cuda_lib, oracle):
     ref = oracle.raster_draw(prims, counts)
     assert np.array_equal(img, ref)
     assert not img[1].any() and img[0].any()
+    # lists longer than one staging chunk (64 records), with a count that ends inside a chunk
+    big = _random_prims(rng, 2, 150)
+    cb = np.asarray([150, 70], np.int32)
+    assert np.array_equal(viz.raster_draw(big, cb).cpu().numpy(), oracle.raster_draw(big, cb))
     # without counts every record is drawn; an empty list gives black frames; zero images is fine
     assert np.array_equal(viz.raster_draw(prims[:3]).cpu().numpy(), oracle.raster_draw(prims[:3]))
     assert not viz.raster_draw(np.zeros((2, 0, 16), np.int32)).cpu().numpy().any()
