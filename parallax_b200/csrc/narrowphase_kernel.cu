@@ -149,8 +149,8 @@ struct SweepWs {
   uint32_t* ctr;     // [SW_WORDS]: queue counts [0..2], hit counts [3..5]
   uint32_t* q[3];    // [n] pair indices per class
   uint32_t* h[3];    // [n] pair indices of the hits per class
-  float* simplex;    // [6][n], indexed by pair
-  uint8_t* gstat;    // [n] GJK status bits of the hits
+  float* simplex[3];  // [6][n] per class, indexed by hit slot
+  uint8_t* gstat[3];  // [n] per class: GJK status bits of the hits, by hit slot
 };
 
 CX_DEV uint32_t sw_lanemask_lt() {
@@ -167,6 +167,24 @@ CX_DEV uint32_t sw_push(uint32_t* counter, bool pred) {  // must be reached by a
   b = __shfl_sync(0xFFFFFFFFu, b, leader);
   return b + (uint32_t)__popc(m & sw_lanemask_lt());
 }
+// block-wide variant: ONE atomic per block and call (the queue counters are hot addresses).  Must be
+// reached by all threads of a 128-thread block; scratch = 5 words of shared memory.
+CX_DEV uint32_t sw_push_block(uint32_t* counter, bool pred, uint32_t* scratch) {
+  const uint32_t m = __ballot_sync(0xFFFFFFFFu, pred);
+  const uint32_t w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31u) == 0u) scratch[w] = (uint32_t)__popc(m);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t tot = scratch[0] + scratch[1] + scratch[2] + scratch[3];
+    scratch[4] = tot ? atomicAdd(counter, tot) : 0u;
+  }
+  __syncthreads();
+  uint32_t base = scratch[4];
+  for (uint32_t j = 0; j < w; ++j) base += scratch[j];
+  const uint32_t r = base + (uint32_t)__popc(m & sw_lanemask_lt());
+  __syncthreads();
+  return r;
+}
 CX_DEV void sw_store(int64_t k, const Contact& c, uint32_t extra, uint8_t* exists, float* pen, float* cp,
                      uint8_t* status) {
   if (exists) exists[k] = contact_isnan(c) ? 0 : 1;
@@ -175,40 +193,57 @@ CX_DEV void sw_store(int64_t k, const Contact& c, uint32_t extra, uint8_t* exist
   if (status) status[k] = (uint8_t)(c.status | extra);
 }
 
+// Tile of SW_TILE pairs per block iteration.  The polygon classes go to the global queues; the three
+// closed-form type pairs (25 % of config 2, randomly interleaved) are first collected per formula in
+// shared memory and then evaluated with the items of one formula on consecutive lanes — evaluating
+// them in place costs every warp all three formulas at ~8 % lane occupancy each.
+constexpr int SW_TILE = 512;
 __global__ void __launch_bounds__(128)
 sweep_classify_kernel(int64_t n, const float* __restrict__ a, const float* __restrict__ b,
                       uint8_t* __restrict__ exists, float* __restrict__ pen, float* __restrict__ cp,
                       uint8_t* __restrict__ status, const SweepWs ws) {
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  const int64_t first = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31);
-  for (int64_t k0 = first; k0 < n; k0 += stride) {
-    const int64_t k = k0 + (threadIdx.x & 31);
-    int cls = -1;
-    if (k < n) {
-      // type word only: the polygon classes read their records in the GJK pass
-      const int ta = (int)__ldg(a + k * COTIX_SHAPE_REC_FLOATS), tb = (int)__ldg(b + k * COTIX_SHAPE_REC_FLOATS);
-      if (tb == COTIX_SHAPE_POLYGON && ta >= COTIX_SHAPE_CIRCLE && ta <= COTIX_SHAPE_POLYGON) {
-        cls = ta == COTIX_SHAPE_POLYGON ? 0 : (ta == COTIX_SHAPE_CIRCLE ? 1 : 2);
-      } else {
-        Contact c = contact_none();
-        uint32_t bad = 0u;
-        if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_CIRCLE) {
-          c = circle_vs_circle(rec_circ(load_rec(a, k)), rec_circ(load_rec(b, k)));
-        } else if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_AABB) {
-          c = circle_vs_aabb(rec_circ(load_rec(a, k)), rec_box(load_rec(b, k)));
-        } else if (ta == COTIX_SHAPE_AABB && tb == COTIX_SHAPE_AABB) {
-          c = aabb_vs_aabb(rec_box(load_rec(a, k)), rec_box(load_rec(b, k)));
-        } else {
-          bad = 0x80u;  // not a key of _contact_funcs in this order
-        }
-        sw_store(k, c, bad, exists, pen, cp, status);
+  __shared__ uint32_t s_item[6][SW_TILE];  // 0..2 closed-form formulas, 3..5 polygon classes
+  __shared__ int s_cnt[6];
+  __shared__ uint32_t s_base[3];
+  for (int64_t t0 = (int64_t)blockIdx.x * SW_TILE; t0 < n; t0 += (int64_t)gridDim.x * SW_TILE) {
+    if (threadIdx.x < 6) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < SW_TILE / 128; ++j) {
+      const int64_t k = t0 + j * 128 + threadIdx.x;
+      if (k < n) {
+        // type word only: the polygon classes read their records in the GJK pass
+        const int ta = (int)__ldg(a + k * COTIX_SHAPE_REC_FLOATS), tb = (int)__ldg(b + k * COTIX_SHAPE_REC_FLOATS);
+        int list = -1;
+        if (tb == COTIX_SHAPE_POLYGON && ta >= COTIX_SHAPE_CIRCLE && ta <= COTIX_SHAPE_POLYGON)
+          list = 3 + (ta == COTIX_SHAPE_POLYGON ? 0 : (ta == COTIX_SHAPE_CIRCLE ? 1 : 2));
+        else if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_CIRCLE) list = 0;
+        else if (ta == COTIX_SHAPE_CIRCLE && tb == COTIX_SHAPE_AABB) list = 1;
+        else if (ta == COTIX_SHAPE_AABB && tb == COTIX_SHAPE_AABB) list = 2;
+        if (list >= 0) s_item[list][atomicAdd(&s_cnt[list], 1)] = (uint32_t)(k - t0);
+        else sw_store(k, contact_none(), 0x80u, exists, pen, cp, status);  // not a key of _contact_funcs in this order
       }
     }
+    __syncthreads();
+    // one global atomic per class and tile (the counters are three hot addresses: one atomic per warp
+    // and class made this kernel atomic-bound), then the tile's members are copied out coalesced
+    if (threadIdx.x < 3 && s_cnt[3 + threadIdx.x] > 0)
+      s_base[threadIdx.x] = atomicAdd(&ws.ctr[SW_Q0 + threadIdx.x], (uint32_t)s_cnt[3 + threadIdx.x]);
+    __syncthreads();
 #pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      const uint32_t slot = sw_push(&ws.ctr[SW_Q0 + c], cls == c);
-      if (cls == c) ws.q[c][slot] = (uint32_t)k;
+    for (int c = 0; c < 3; ++c)
+      for (int i = threadIdx.x; i < s_cnt[3 + c]; i += 128) ws.q[c][s_base[c] + i] = (uint32_t)(t0 + s_item[3 + c][i]);
+    const int c0 = s_cnt[0], c1 = s_cnt[1], c2 = s_cnt[2];
+    for (int i = threadIdx.x; i < c0 + c1 + c2; i += 128) {
+      const int cf = i < c0 ? 0 : (i < c0 + c1 ? 1 : 2);
+      const int64_t k = t0 + s_item[cf][i - (cf == 0 ? 0 : (cf == 1 ? c0 : c0 + c1))];
+      Contact c;
+      if (cf == 0) c = circle_vs_circle(rec_circ(load_rec(a, k)), rec_circ(load_rec(b, k)));
+      else if (cf == 1) c = circle_vs_aabb(rec_circ(load_rec(a, k)), rec_box(load_rec(b, k)));
+      else c = aabb_vs_aabb(rec_box(load_rec(a, k)), rec_box(load_rec(b, k)));
+      sw_store(k, c, 0u, exists, pen, cp, status);
     }
+    __syncthreads();
   }
 }
 
@@ -217,35 +252,38 @@ __global__ void __launch_bounds__(128)
 sweep_gjk_kernel(int64_t n, const float* __restrict__ a, const float* __restrict__ b,
                  uint8_t* __restrict__ exists, float* __restrict__ pen, float* __restrict__ cp,
                  uint8_t* __restrict__ status, CotixNarrowParams prm, const SweepWs ws) {
+  __shared__ uint32_t s_push[5];
   const uint32_t cnt = ws.ctr[SW_Q0 + CLS];
   const uint32_t stride = gridDim.x * blockDim.x;
   const V2 start = mk2(prm.init_dir[0], prm.init_dir[1]);
-  for (uint32_t i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < cnt; i0 += stride) {
-    const uint32_t i = i0 + (threadIdx.x & 31u);
-    bool hit = false;
+  for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < cnt; i0 += stride) {  // uniform per block
+    const uint32_t i = i0 + threadIdx.x;
+    bool hit = false, gcap = false;
     uint32_t k = 0u;
+    V2 s0 = mk2(0.0f, 0.0f), s1 = s0, s2 = s0;
     if (i < cnt) {
       k = ws.q[CLS][i];
       const Rec ra = load_rec(a, k), rb = load_rec(b, k);
       const Poly B = rec_poly(rb);
-      V2 s0, s1, s2;
-      bool gcap;
       if (CLS == 0) hit = gjk(rec_poly(ra), B, start, prm.gjk_max_iters, s0, s1, s2, gcap);
       else if (CLS == 1) hit = gjk(rec_circ(ra), B, start, prm.gjk_max_iters, s0, s1, s2, gcap);
       else hit = gjk(rec_box(ra), B, start, prm.gjk_max_iters, s0, s1, s2, gcap);
-      if (hit) {
-        ws.simplex[0 * n + k] = s0.x; ws.simplex[1 * n + k] = s0.y;
-        ws.simplex[2 * n + k] = s1.x; ws.simplex[3 * n + k] = s1.y;
-        ws.simplex[4 * n + k] = s2.x; ws.simplex[5 * n + k] = s2.y;
-        ws.gstat[k] = gcap ? (uint8_t)CX_ST_GJK_CAP : (uint8_t)0;
-      } else {
+      if (!hit) {
         Contact c = contact_none();
         if (gcap) c.status |= CX_ST_GJK_CAP;
         sw_store(k, c, 0u, exists, pen, cp, status);
       }
     }
-    const uint32_t slot = sw_push(&ws.ctr[SW_H0 + CLS], hit);
-    if (hit) ws.h[CLS][slot] = k;
+    // the simplex and GJK status travel with the hit's queue slot (coalesced), not with the pair
+    const uint32_t slot = sw_push_block(&ws.ctr[SW_H0 + CLS], hit, s_push);
+    if (hit) {
+      ws.h[CLS][slot] = k;
+      float* sx = ws.simplex[CLS];
+      sx[0 * n + slot] = s0.x; sx[1 * n + slot] = s0.y;
+      sx[2 * n + slot] = s1.x; sx[3 * n + slot] = s1.y;
+      sx[4 * n + slot] = s2.x; sx[5 * n + slot] = s2.y;
+      ws.gstat[CLS][slot] = gcap ? (uint8_t)CX_ST_GJK_CAP : (uint8_t)0;
+    }
   }
 }
 
@@ -260,14 +298,84 @@ sweep_epa_kernel(int64_t n, const float* __restrict__ a, const float* __restrict
     const uint32_t k = ws.h[CLS][i];
     const Rec ra = load_rec(a, k), rb = load_rec(b, k);
     const Poly B = rec_poly(rb);
-    const V2 s0 = mk2(ws.simplex[0 * n + k], ws.simplex[1 * n + k]);
-    const V2 s1 = mk2(ws.simplex[2 * n + k], ws.simplex[3 * n + k]);
-    const V2 s2 = mk2(ws.simplex[4 * n + k], ws.simplex[5 * n + k]);
+    const float* sx = ws.simplex[CLS];
+    const V2 s0 = mk2(sx[0 * n + i], sx[1 * n + i]);
+    const V2 s1 = mk2(sx[2 * n + i], sx[3 * n + i]);
+    const V2 s2 = mk2(sx[4 * n + i], sx[5 * n + i]);
     Contact c = contact_none();
-    c.status = ws.gstat[k];
+    c.status = ws.gstat[CLS][i];
     if (CLS == 0) convex_poly_finish(rec_poly(ra), B, s0, s1, s2, c);
     else if (CLS == 1) circle_poly_finish<131>(rec_circ(ra), B, s0, s1, s2, prm.epa_iters_circle_poly, c);
     else convex_poly_finish(rec_box(ra), B, s0, s1, s2, c);
+    sw_store(k, c, 0u, exists, pen, cp, status);
+  }
+}
+
+// Circle-polygon EPA in two passes.  The expansion count of a circle-polygon hit is 5 ... 100
+// (the Minkowski difference has arcs), 13.5 on average, and a warp runs as long as its slowest lane:
+// the one-pass kernel keeps 10.6 of 32 lanes busy.  The SHORT pass gives every hit CX_EPA_SHORT
+// expansions (edge list of CX_EPA_SHORT + 3 entries); a hit that converges inside the budget is
+// finished — the loop stops on its own, so the result is the one the full budget gives — and the
+// others are appended to the LONG queue (the class-1 GJK queue, free by then) and run again with the
+// full budget.  Identical outputs.
+#ifndef CX_EPA_SHORT
+#define CX_EPA_SHORT 24  // measured on BASELINE config 2: 10 / 16 / 24 / 32 / 40 / 56 -> 7.42 / 6.89 / 6.53 / 6.98 / 7.24 / 7.43 ms
+#endif
+enum { SW_LONG = 6 };
+__global__ void __launch_bounds__(128)
+sweep_epa_cp_short_kernel(int64_t n, const float* __restrict__ a, const float* __restrict__ b,
+                          uint8_t* __restrict__ exists, float* __restrict__ pen, float* __restrict__ cp,
+                          uint8_t* __restrict__ status, CotixNarrowParams prm, const SweepWs ws) {
+  __shared__ uint32_t s_push[5];
+  const uint32_t cnt = ws.ctr[SW_H0 + 1];
+  const uint32_t stride = gridDim.x * blockDim.x;
+  const int budget = prm.epa_iters_circle_poly < CX_EPA_SHORT ? prm.epa_iters_circle_poly : CX_EPA_SHORT;
+  const bool whole = prm.epa_iters_circle_poly <= CX_EPA_SHORT;  // the short budget is the full one
+  const float* sx = ws.simplex[1];
+  for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < cnt; i0 += stride) {  // uniform per block
+    const uint32_t i = i0 + threadIdx.x;
+    bool defer = false;
+    if (i < cnt) {
+      const uint32_t k = ws.h[1][i];
+      const Circ circle = rec_circ(load_rec(a, k));
+      const Poly B = rec_poly(load_rec(b, k));
+      const V2 s0 = mk2(sx[0 * n + i], sx[1 * n + i]);
+      const V2 s1 = mk2(sx[2 * n + i], sx[3 * n + i]);
+      const V2 s2 = mk2(sx[4 * n + i], sx[5 * n + i]);
+      bool ecap;
+      V2 ea, eb;
+      epa_edge<CX_EPA_SHORT + 3>(circle, B, s0, s1, s2, budget, ecap, ea, eb);
+      defer = ecap && !whole;
+      if (!defer) {
+        Contact c = contact_none();
+        c.status = ws.gstat[1][i];
+        if (ecap) c.status |= CX_ST_EPA_CAP;
+        c.pen = closest_to_origin(ea, eb);
+        c.cp = circle_poly_contact_point(circle, B);
+        sw_store(k, c, 0u, exists, pen, cp, status);
+      }
+    }
+    const uint32_t slot = sw_push_block(&ws.ctr[SW_LONG], defer, s_push);
+    if (defer) ws.q[1][slot] = i;  // the hit's slot: pair index, simplex and status hang off it
+  }
+}
+__global__ void __launch_bounds__(128)
+sweep_epa_cp_long_kernel(int64_t n, const float* __restrict__ a, const float* __restrict__ b,
+                         uint8_t* __restrict__ exists, float* __restrict__ pen, float* __restrict__ cp,
+                         uint8_t* __restrict__ status, CotixNarrowParams prm, const SweepWs ws) {
+  const uint32_t cnt = ws.ctr[SW_LONG];
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cnt; i += stride) {
+    const uint32_t h = ws.q[1][i];
+    const uint32_t k = ws.h[1][h];
+    const Rec ra = load_rec(a, k), rb = load_rec(b, k);
+    const float* sx = ws.simplex[1];
+    const V2 s0 = mk2(sx[0 * n + h], sx[1 * n + h]);
+    const V2 s1 = mk2(sx[2 * n + h], sx[3 * n + h]);
+    const V2 s2 = mk2(sx[4 * n + h], sx[5 * n + h]);
+    Contact c = contact_none();
+    c.status = ws.gstat[1][h];
+    circle_poly_finish<131>(rec_circ(ra), rec_poly(rb), s0, s1, s2, prm.epa_iters_circle_poly, c);
     sw_store(k, c, 0u, exists, pen, cp, status);
   }
 }
@@ -285,8 +393,8 @@ size_t sweep_carve(int64_t n, void* base, SweepWs* ws) {
   w.ctr = reinterpret_cast<uint32_t*>(take(SW_WORDS * 4));
   for (int c = 0; c < 3; ++c) w.q[c] = reinterpret_cast<uint32_t*>(take((size_t)n * 4));
   for (int c = 0; c < 3; ++c) w.h[c] = reinterpret_cast<uint32_t*>(take((size_t)n * 4));
-  w.simplex = reinterpret_cast<float*>(take((size_t)n * 6 * 4));
-  w.gstat = reinterpret_cast<uint8_t*>(take((size_t)n));
+  for (int c = 0; c < 3; ++c) w.simplex[c] = reinterpret_cast<float*>(take((size_t)n * 6 * 4));
+  for (int c = 0; c < 3; ++c) w.gstat[c] = reinterpret_cast<uint8_t*>(take((size_t)n));
   if (ws) *ws = w;
   return off;
 }
@@ -344,13 +452,18 @@ extern "C" int cx_launch_narrowphase_ws(cudaStream_t st, int64_t n, const float*
   if (blocks > cap) blocks = cap;
   const unsigned g = (unsigned)blocks;
   if (cudaMemsetAsync(ws.ctr, 0, SW_WORDS * 4, st) != cudaSuccess) return cx_check_launch("sweep memset");
-  sweep_classify_kernel<<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, ws);
+  {
+    int64_t tb = (n + SW_TILE - 1) / SW_TILE;
+    if (tb > cap) tb = cap;
+    sweep_classify_kernel<<<(unsigned)tb, 128, 0, st>>>(n, a, b, exists, pen, cp, status, ws);
+  }
   sweep_gjk_kernel<0><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
   sweep_gjk_kernel<1><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
   sweep_gjk_kernel<2><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
   sweep_epa_kernel<0><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
-  sweep_epa_kernel<1><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
+  sweep_epa_cp_short_kernel<<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
+  sweep_epa_cp_long_kernel<<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
   sweep_epa_kernel<2><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
-  cx_count_launch_n(7);
+  cx_count_launch_n(8);
   return cx_check_launch("narrowphase sweep");
 }
