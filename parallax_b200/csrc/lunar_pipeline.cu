@@ -177,25 +177,42 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
       r[9] = make_float4(E.kn[0], E.kn[1], E.kn[2], E.kn[3]);
     }
   }
-  // warp-aggregated allocation of `cnt` consecutive item slots per env
-  const unsigned lane = threadIdx.x & 31u;
+  // block-aggregated allocation of `cnt` consecutive item slots per env and of one contact-env slot
+  // per env with candidates: ONE atomic per counter and block (the counters are hot addresses —
+  // same-address atomics retire at about one per nanosecond, 2 x 30 k of them per step otherwise)
+  __shared__ uint32_t s_items[TPB / 32], s_envs[TPB / 32], s_base[2];
+  const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   int incl = cnt;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const int n = __shfl_up_sync(0xFFFFFFFFu, incl, d);
     if ((int)lane >= d) incl += n;
   }
-  const int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
-  if (e < B && !valid) ws.cand[e] = 0u;  // frozen
-  if (total == 0) {
-    if (valid) ws.cand[e] = 0u;
-    return;
+  const uint32_t em = __ballot_sync(0xFFFFFFFFu, cnt != 0);
+  if (lane == 31u) {
+    s_items[warp] = (uint32_t)incl;
+    s_envs[warp] = (uint32_t)__popc(em);
   }
-  uint32_t wbase = 0u;
-  if (lane == 31u) wbase = atomicAdd(&ws.ctr[CTR_ITEMS], (uint32_t)total);
-  wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+  if (e < B && !valid) ws.cand[e] = 0u;  // frozen
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t ti = 0u, te = 0u;
+#pragma unroll
+    for (int j = 0; j < TPB / 32; ++j) {
+      ti += s_items[j];
+      te += s_envs[j];
+    }
+    s_base[0] = ti ? atomicAdd(&ws.ctr[CTR_ITEMS], ti) : 0u;
+    s_base[1] = te ? atomicAdd(&ws.ctr[CTR_CENV], te) : 0u;
+  }
+  __syncthreads();
+  uint32_t wbase = s_base[0], cslot = s_base[1];
+  for (unsigned j = 0; j < warp; ++j) {
+    wbase += s_items[j];
+    cslot += s_envs[j];
+  }
+  cslot += (uint32_t)__popc(em & lanemask_lt());
   // every env with candidates goes to the contact-env queue (K_C finishes those envs itself)
-  const uint32_t cslot = queue_push(&ws.ctr[CTR_CENV], cnt != 0);
   if (cnt != 0) ws.cenv[cslot] = (uint32_t)e;
   if (!valid) return;
   if (cnt == 0) {
