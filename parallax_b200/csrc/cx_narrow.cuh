@@ -251,14 +251,28 @@ CX_DEV void epa_edge(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, b
   V2 ba = mk2(eax[bi], eay[bi]), bb = mk2(ebx[bi], eby[bi]);
   V2 newp = s2;
   V2 pa = s0, pb = s1;  // prev_edge = edges[0]
+  // Two values the reference recomputes every iteration are already known here, bit for bit:
+  //  * the unit normal of prev_edge is the expansion direction n2 of the previous iteration
+  //    (same expression on the same end points);
+  //  * |closest_to_origin(prev_edge)| is the square root of that edge's cached squared distance
+  //    (edge_dist2 and closest_to_origin evaluate the same displacement; the only difference,
+  //    the all-zero edge that edge_dist2 maps to inf, falls back to the direct evaluation).
+  V2 nprev = mk2(0.0f, 0.0f);
+  float dsel = dist[0];    // cached squared distance of prev_edge when it was the best edge
+  float dcur = dist[bi];   // cached squared distance of the current best edge
   int ran = 0;
   for (int it = 0; it < iters; ++it) {
     bool c1 = sumsq2(ba - bb) > 1e-9f;
     bool c2 = cross2(ba, bb) >= 0;
-    V2 nrm = perp(pa - pb);
-    nrm = nrm / norm2(nrm);
+    V2 nrm;
+    if (it == 0) {
+      nrm = perp(pa - pb);
+      nrm = nrm / norm2(nrm);
+    } else {
+      nrm = nprev;
+    }
     float d = dot2(newp, nrm);
-    float ed = norm2(closest_to_origin(pa, pb));
+    float ed = (dsel <= 3.0e38f) ? sqrtf(dsel) : norm2(closest_to_origin(pa, pb));
     bool c4 = (d - ed > 1e-6f) || (d <= 0);
     bool bad = isnan2(ba) || isnan2(bb);
     if (!(c4 && !bad && c1 && c2)) break;  // the scan carries the state unchanged from here
@@ -273,7 +287,10 @@ CX_DEV void epa_edge(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, b
     ++cnt;
     pa = ba;
     pb = bb;
+    nprev = n2;
+    dsel = dcur;
     bi = argmin_first(dist, cnt);
+    dcur = dist[bi];
     ba = mk2(eax[bi], eay[bi]);
     bb = mk2(ebx[bi], eby[bi]);
     newp = np;
