@@ -232,6 +232,25 @@ CX_DEV int argmin_first(const float* d, int n) {
   }
   return best;
 }
+// the same over an EPA edge list.  No early exit: the loads of d[] (local memory) do not depend on
+// the running minimum, so they overlap instead of forming a chain of load -> compare -> branch.
+CX_DEV int argmin_scan(const float* d, int n) {
+  int best = 0;
+  float bv = d[0];
+  bool bnan = bv != bv;
+#pragma unroll 4
+  for (int k = 1; k < n; ++k) {
+    const float v = d[k];
+    const bool vnan = v != v;
+    const bool take = !bnan && (vnan || v < bv);
+    if (take) {
+      bv = v;
+      best = k;
+      bnan = vnan;
+    }
+  }
+  return best;
+}
 
 // epa_edge leaves the closest edge (ba, bb) of the expanded polytope in oa / ob; the penetration
 // vector is closest_to_origin(oa, ob).  The adjoint kernel (lunar_adjoint.cu) needs the edge.
@@ -247,7 +266,9 @@ CX_DEV void epa_edge(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, b
   dist[2] = edge_dist2(s2, s0);
   int cnt = 3;  // entries >= cnt are the zero padding: distance inf, never the arg-min
                 // unless every live distance is inf/NaN-free larger — impossible here
-  int bi = argmin_first(dist, cnt);
+  // short lists (polygon pairs: <= 16 entries) are scanned with the early-exit form, long ones
+  // (circle-polygon) with the overlapped one: measured, each is slower on the other's kernels
+  int bi = MAXE > 16 ? argmin_scan(dist, cnt) : argmin_first(dist, cnt);
   V2 ba = mk2(eax[bi], eay[bi]), bb = mk2(ebx[bi], eby[bi]);
   V2 newp = s2;
   V2 pa = s0, pb = s1;  // prev_edge = edges[0]
@@ -289,7 +310,7 @@ CX_DEV void epa_edge(const SA& A, const SB& B, V2 s0, V2 s1, V2 s2, int iters, b
     pb = bb;
     nprev = n2;
     dsel = dcur;
-    bi = argmin_first(dist, cnt);
+    bi = MAXE > 16 ? argmin_scan(dist, cnt) : argmin_first(dist, cnt);
     dcur = dist[bi];
     ba = mk2(eax[bi], eay[bi]);
     bb = mk2(ebx[bi], eby[bi]);

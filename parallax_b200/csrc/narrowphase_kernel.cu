@@ -326,14 +326,15 @@ __global__ void __launch_bounds__(128)
 sweep_epa_cp_short_kernel(int64_t n, const float* __restrict__ a, const float* __restrict__ b,
                           uint8_t* __restrict__ exists, float* __restrict__ pen, float* __restrict__ cp,
                           uint8_t* __restrict__ status, CotixNarrowParams prm, const SweepWs ws) {
-  __shared__ uint32_t s_push[5];
   const uint32_t cnt = ws.ctr[SW_H0 + 1];
   const uint32_t stride = gridDim.x * blockDim.x;
   const int budget = prm.epa_iters_circle_poly < CX_EPA_SHORT ? prm.epa_iters_circle_poly : CX_EPA_SHORT;
   const bool whole = prm.epa_iters_circle_poly <= CX_EPA_SHORT;  // the short budget is the full one
   const float* sx = ws.simplex[1];
-  for (uint32_t i0 = blockIdx.x * blockDim.x; i0 < cnt; i0 += stride) {  // uniform per block
-    const uint32_t i = i0 + threadIdx.x;
+  // (appends per warp, not per block: only ~10 % of the hits are deferred, and a block barrier per
+  // iteration would make every warp wait for the slowest of the block's four)
+  for (uint32_t i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < cnt; i0 += stride) {
+    const uint32_t i = i0 + (threadIdx.x & 31u);
     bool defer = false;
     if (i < cnt) {
       const uint32_t k = ws.h[1][i];
@@ -355,7 +356,7 @@ sweep_epa_cp_short_kernel(int64_t n, const float* __restrict__ a, const float* _
         sw_store(k, c, 0u, exists, pen, cp, status);
       }
     }
-    const uint32_t slot = sw_push_block(&ws.ctr[SW_LONG], defer, s_push);
+    const uint32_t slot = sw_push(&ws.ctr[SW_LONG], defer);
     if (defer) ws.q[1][slot] = i;  // the hit's slot: pair index, simplex and status hang off it
   }
 }
