@@ -376,7 +376,7 @@ def sweep(args, dev, peak):
             "ms_per_sweep": ms, "hit_fraction": float(ci.exists.float().mean().item()),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": _traffic("narrowphase_sweep"),
-                         "kernel": "sweep_classify + sweep_gjk<3> + sweep_epa<3> (7 launches, whole sweep)"}}
+                         "kernel": "sweep_classify + sweep_gjk<3> + sweep_epa<0,2> + sweep_epa_cp_short/long (8 launches, whole sweep)"}}
 
 
 def robocup(args, dev):
