@@ -57,6 +57,8 @@ class SceneSpec:
     part_recs: np.ndarray    # [nparts, 16] local shape records
     init_state: np.ndarray   # [nb, 6] px, py, vx, vy, angle, angular_velocity
     is_area: list = field(default_factory=list)
+    # what env.draw paints (cotix/_robocup.py:132-150): (body, local shape record, fill colour, edge colour)
+    draw_list: list = field(default_factory=list)
 
     @property
     def nb(self) -> int:
@@ -140,8 +142,16 @@ def robocup_scene(n_robots: int = 0, areas_collide: bool = True, robot_radius: f
         is_area.append(False)
         part_body.append(4 + 1 + r)
         recs.append(circle_rec(robot_radius, (0.0, 0.0)))
+    # RoboCupEnv.draw (cotix/_robocup.py:132-150): colours per body, edges per body; the area
+    # bodies are painted whether or not they collide; robots (new) use Circle.draw's default grey
+    green, white, yel, blu, red = (0, 180, 0), (255, 255, 255), (255, 255, 0), (0, 128, 255), (255, 0, 0)
+    draw = [(0, aabb_rec(field_lo, field_hi), green, white), (1, aabb_rec(play_lo, play_hi), green, white)]
+    draw += [(2, aabb_rec(lo, hi), yel, yel) for lo, hi in yellow]
+    draw += [(3, aabb_rec(lo, hi), blu, blu) for lo, hi in blue]
+    draw.append((4, circle_rec(_f(ball_radius) * _f(3), (0.0, 0.0)), red, None))
+    draw += [(5 + r, circle_rec(robot_radius, (0.0, 0.0)), (128, 128, 128), None) for r in range(n_robots)]
     return SceneSpec(names, np.asarray(props, _f), np.asarray(part_body, np.int32),
-                     np.stack(recs).astype(_f), np.asarray(state, _f), is_area)
+                     np.stack(recs).astype(_f), np.asarray(state, _f), is_area, draw)
 
 
 class Scene:

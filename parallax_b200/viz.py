@@ -157,3 +157,52 @@ def write_ppm(path: str, image) -> None:
     with open(path, "wb") as f:
         f.write(b"P6\n%d %d\n255\n" % (a.shape[1], a.shape[0]))
         f.write(np.ascontiguousarray(a).tobytes())
+
+
+def scene_primitives(spec, state, env_index=None) -> np.ndarray:
+    """The draw calls of `env.draw(painter)` for a generic scene (`RoboCupEnv.draw`,
+    cotix/_robocup.py:140-150) as primitive records, int32 [n_img, n_prims, 16]: per body
+    `shape.draw(painter, color)` then `shape.drawEdges(painter, edge_color)`.  An AABB part draws its
+    four edges (`AABB.draw` -> `drawEdges`, cotix/_convex_shapes.py:119-133; translated by the body
+    position only, :113-117), a circle part a filled circle (:43-44).  `state` is the scene state
+    [nb * 6, B] (tensor or array), `spec.draw_list` says what each body paints."""
+    s = state.detach().cpu().numpy() if isinstance(state, torch.Tensor) else np.asarray(state, np.float32)
+    idx = np.arange(s.shape[1]) if env_index is None else np.asarray(env_index, np.int64)
+    f = np.float32
+
+    def sx(x):
+        return np.trunc(np.nan_to_num((x + f(8)) / f(16) * f(800), nan=-1e6, posinf=1e6, neginf=-1e6).clip(-1048576, 1048576)).astype(np.int32)
+
+    def sy(y):
+        return np.trunc(np.nan_to_num((-y + f(6)) / f(12) * f(600), nan=-1e6, posinf=1e6, neginf=-1e6).clip(-1048576, 1048576)).astype(np.int32)
+
+    cols = []
+
+    def line(ax, ay, bx, by, colour):
+        q = np.zeros((idx.size, PRIM_WORDS), np.int32)
+        q[:, 0], q[:, 1] = PRIM_LINE, _rgb(colour)
+        q[:, 4], q[:, 5], q[:, 6], q[:, 7] = sx(ax), sy(ay), sx(bx), sy(by)
+        cols.append(q)
+
+    for body, rec, fill, edge in spec.draw_list:
+        px, py = s[6 * body][idx].astype(f), s[6 * body + 1][idx].astype(f)
+        kind = int(rec[0])
+        if kind == 0:  # circle: draw_circle(position, radius, color)
+            q = np.zeros((idx.size, PRIM_WORDS), np.int32)
+            q[:, 0], q[:, 1], q[:, 2] = PRIM_CIRCLE, _rgb(fill), scale_size(f(rec[2]))
+            q[:, 4], q[:, 5] = sx(f(rec[4]) + px), sy(f(rec[5]) + py)
+            cols.append(q)
+            continue
+        lo_x, lo_y, hi_x, hi_y = (f(rec[4]) + px, f(rec[5]) + py, f(rec[6]) + px, f(rec[7]) + py)
+        vx, vy = [hi_x, hi_x, lo_x, lo_x], [hi_y, lo_y, lo_y, hi_y]  # AABB.get_edges, :82-93
+        for colour in (fill, edge):
+            if colour is None:
+                continue
+            for k in range(4):
+                line(vx[k], vy[k], vx[(k + 1) & 3], vy[(k + 1) & 3], colour)
+    return np.stack(cols, 1)
+
+
+def render_scene(spec, state, env_index=None, device="cuda") -> torch.Tensor:
+    """frames of a generic scene (e.g. RoboCup), uint8 [n_img, 600, 800, 3] on the device"""
+    return raster_draw(scene_primitives(spec, state, env_index), device=device)

@@ -77,6 +77,35 @@ def test_scale_vector_is_the_reference_map():
     assert viz.scale_size(0.1) == 4 and viz.scale_size(np.float32(0.5)) == 20
 
 
+def test_robocup_draw_calls_follow_the_reference(oracle):
+    """RoboCupEnv.draw (cotix/_robocup.py:132-150): per body shape.draw(colour) then drawEdges(edge colour);
+    AABBs paint their four edges, the ball a filled circle; robots (new) Circle.draw's grey."""
+    from parallax_b200 import scene as sc
+    from parallax_b200 import viz
+
+    spec = sc.robocup_scene(n_robots=2, areas_collide=False)
+    B = 3
+    st = np.repeat(spec.init_state[:, :, None], B, axis=2).astype(np.float32).reshape(spec.nb * 6, B)
+    st[6 * 4, 1] = 1.5          # the ball of env 1 moved
+    st[6 * 4 + 1, 1] = -2.0
+    pr = viz.scene_primitives(spec, st)
+    # 2 areas + 3 + 3 goal boxes, each 4 edges in the fill colour and 4 in the edge colour; ball; 2 robots
+    assert pr.shape == (B, 8 * 8 + 1 + 2, 16)
+    sv = lambda x, y: (int((np.float32(x) + 8) / 16 * 800), int((-np.float32(y) + 6) / 12 * 600))
+    # field: upper = (5.2, 3.7), first edge (upper) -> (upper.x, lower.y)   (AABB.get_edges, _convex_shapes.py:82-93)
+    assert list(pr[0, 0, :8]) == [0, 0x00B400, 0, 0, *sv(5.2, 3.7), *sv(5.2, -3.7)]
+    assert list(pr[0, 4, :2]) == [0, 0xFFFFFF] and list(pr[0, 4, 4:8]) == list(pr[0, 0, 4:8])
+    assert list(pr[0, 16, :2]) == [0, 0xFFFF00] and list(pr[0, 40, :2]) == [0, 0x0080FF]
+    ball = pr[:, 64]
+    assert list(ball[0, :6]) == [1, 0xFF0000, int(np.float32(0.022) * np.float32(3) * 40), 0, 400, 300]
+    assert list(ball[1, 4:6]) == list(sv(1.5, -2.0))
+    assert list(pr[0, 65, :3]) == [1, 0x808080, int(0.09 * 40)]
+    img = oracle.raster_draw(pr)
+    assert tuple(img[0, 300, 400]) == (255, 0, 0) and tuple(img[1, 300, 400]) == (0, 0, 0)
+    assert tuple(img[0, 115, 400]) == (255, 255, 255)      # the field's white top edge over the green one
+    assert tuple(img[0, 300, 175]) == (255, 255, 0) or (img[0, :, 170:185] == (255, 255, 0)).all(-1).any()
+
+
 # ---- GPU: the CUDA rasteriser against the oracle, bit for bit -----------------------------------------
 def _random_prims(rng, n_img, max_prims):
     prims = np.zeros((n_img, max_prims, 16), np.int32)
@@ -256,3 +285,20 @@ def test_raster_argument_checks(cuda_lib):
         _lib.check(L.cotix_raster_draw(None, 1, pr.data_ptr(), None, 2, img.data_ptr() + 1))
     with pytest.raises(_lib.CotixError):
         _lib.check(L.cotix_raster_draw(None, -1, pr.data_ptr(), None, 2, img.data_ptr()))
+
+
+@pytest.mark.gpu
+def test_render_scene_robocup(cuda_lib, oracle):
+    from parallax_b200 import scene as sc
+    from parallax_b200 import viz
+
+    spec = sc.robocup_scene(n_robots=12, areas_collide=False)
+    B = 16
+    rng = np.random.default_rng(3)
+    st = np.repeat(spec.init_state[:, :, None], B, axis=2).astype(np.float32)
+    st[4:, 0:2] += rng.normal(0, 0.5, (spec.nb - 4, 2, B)).astype(np.float32)
+    st = st.reshape(spec.nb * 6, B)
+    frames = viz.render_scene(spec, st, env_index=[0, 3, 15]).cpu().numpy()
+    assert np.array_equal(frames, oracle.raster_draw(viz.scene_primitives(spec, st, [0, 3, 15])))
+    assert (frames[0] == (0, 128, 255)).all(-1).any() and (frames[0] == (128, 128, 128)).all(-1).any()
+
