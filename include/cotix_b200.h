@@ -339,21 +339,32 @@ int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t
  * [NDYN][ld]), on return dL/d(state_0); g_actions DEVICE [T][2][ld] or NULL receives
  * dL/d(action_t).  Only enqueues on `stream`, no synchronisation, graph-capturable.
  *
- * workspace (DEVICE, 256-byte aligned, optional): the DECISION TAPE.  The replay of a step (its
- * narrowphase and the collider's coin flips) depends only on the state before it, so with a
- * workspace the replays of many steps run as ONE launch over (step, env) items
- * (lunar_decide_kernel) that writes, per env-step, the <= 4 resolve_collision calls with their
- * ContactInfo and final EPA edge (COTIX_ADJ_TAPE_WORDS words), and the sequential reverse sweep
- * (one light launch per step) reads them.  Any size >= cotix_lunar_adjoint_workspace_bytes(ld, 1)
- * works (the steps are processed in groups that fit); (ld, T) holds the whole rollout.  With
- * workspace == NULL every step replays its own decisions inside the reverse sweep (T launches
- * that are each latency-bound by the envs in contact).  Results are identical.
+ * workspace (DEVICE, 256-byte aligned, optional).  Two things about a step's VJP do not depend on
+ * the cotangent and therefore not on the order of the reverse sweep — they depend only on the state
+ * before the step, which is on the tape — so they are computed for MANY steps in one launch over
+ * (step, env) items instead of inside T small, latency-bound launches:
+ *  1. the DECISION TAPE (lunar_decide_kernel): the replay's narrowphase and coin flips; per
+ *     env-step the <= 4 resolve_collision calls with their ContactInfo and final EPA edge
+ *     (COTIX_ADJ_TAPE_WORDS words);
+ *  2. the TRANSPOSED JACOBIANS of the env-steps that resolved a contact (lunar_jacobian_kernel):
+ *     the VJP is linear in the cotangent, so for those env-steps — the ones with the expensive,
+ *     divergent contact adjoint — the 20 x 18 matrix (g_state; g_action) = M g_next is formed in
+ *     advance and the sweep spends a matrix-vector product on them (room for one env-step in eight;
+ *     the rest fall back to the decision tape).
+ * jacobians != 0: 1 + 2, the workspace holds cotix_lunar_adjoint_workspace_bytes(ld, steps) bytes;
+ * jacobians == 0: 1 only, cotix_lunar_adjoint_decisions_bytes(ld, steps) bytes; steps = T covers
+ * the whole rollout, a smaller workspace (>= 1 step) is used for groups of steps.  With
+ * workspace == NULL every step replays its own decisions inside the sweep.  NULL and decisions-only
+ * give identical bits; the matrix form sums the same terms in another order (rounding-level
+ * differences).
  */
 #define COTIX_ADJ_TAPE_WORDS 33
 int64_t cotix_lunar_adjoint_workspace_bytes(int64_t ld, int32_t T);
+int64_t cotix_lunar_adjoint_decisions_bytes(int64_t ld, int32_t T);
 int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
                             const float* actions, float* g, float* g_actions, uint32_t* flags,
-                            const CotixLunarParams* p, void* workspace, int64_t workspace_bytes);
+                            const CotixLunarParams* p, void* workspace, int64_t workspace_bytes,
+                            int32_t jacobians);
 
 /* ------------------------------------------------------------------------------------ */
 /* Headless rasteriser (K6): the replacement for the pygame window of cotix/_viz.py — there  */

@@ -157,7 +157,7 @@ EXPORTS = [
     "cotix_scene_default_params", "cotix_scene_create", "cotix_scene_destroy", "cotix_scene_info",
     "cotix_scene_step",
     "cotix_lunar_step_bwd", "cotix_lunar_rollout", "cotix_lunar_rollout_bwd",
-    "cotix_lunar_adjoint_workspace_bytes", "cotix_raster_draw", "cotix_lunar_draw", "cotix_lunar_prims",
+    "cotix_lunar_adjoint_workspace_bytes", "cotix_lunar_adjoint_decisions_bytes", "cotix_raster_draw", "cotix_lunar_draw", "cotix_lunar_prims",
 ]
 
 _lib = None
@@ -208,9 +208,12 @@ def lib() -> C.CDLL:
     L.cotix_lunar_env_rollout_graph.argtypes = [vp, C.c_int32, vp]
     L.cotix_lunar_step_bwd.argtypes = [vp, i64, vp, vp, i64, vp, vp, vp, vp, vp, C.POINTER(LunarParams)]
     L.cotix_lunar_rollout.argtypes = [vp, i64, C.c_int32, vp, i64, vp, C.POINTER(LunarParams), vp, i64]
-    L.cotix_lunar_rollout_bwd.argtypes = [vp, i64, C.c_int32, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams), vp, i64]
+    L.cotix_lunar_rollout_bwd.argtypes = [vp, i64, C.c_int32, vp, i64, vp, vp, vp, vp, C.POINTER(LunarParams), vp, i64,
+                                          C.c_int32]
     L.cotix_lunar_adjoint_workspace_bytes.restype = C.c_int64
     L.cotix_lunar_adjoint_workspace_bytes.argtypes = [i64, C.c_int32]
+    L.cotix_lunar_adjoint_decisions_bytes.restype = C.c_int64
+    L.cotix_lunar_adjoint_decisions_bytes.argtypes = [i64, C.c_int32]
     L.cotix_raster_draw.argtypes = [vp, i64, vp, vp, C.c_int32, vp]
     L.cotix_lunar_draw.argtypes = [vp, i64, vp, i64, vp, vp, C.POINTER(LunarParams)]
     L.cotix_lunar_prims.argtypes = [vp, i64, vp, i64, vp, vp, C.POINTER(LunarParams)]

@@ -23,9 +23,9 @@ extern "C" int cx_lunar_pipeline_profiling();
 extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, const float*, int64_t,
                                         const float*, const float*, float*, float*, uint32_t*,
-                                        const float*, const CotixLunarParams*);
+                                        const float*, const float*, const CotixLunarParams*);
 extern "C" int cx_launch_lunar_decide(cudaStream_t, int64_t, int, const float*, int64_t, const float*, float*,
-                                      const CotixLunarParams*);
+                                      uint32_t*, uint32_t*, uint32_t*, float*, uint32_t, const CotixLunarParams*);
 extern "C" int cx_launch_raster_draw(cudaStream_t, int64_t, const int32_t*, const int32_t*, int32_t, uint8_t*);
 extern "C" int cx_launch_lunar_draw(cudaStream_t, int64_t, const float*, int64_t, const int64_t*, uint8_t*,
                                     const CotixLunarParams*);
@@ -285,7 +285,7 @@ int cotix_lunar_step_bwd(void* stream, int64_t B, const float* state_in, const f
   CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
   CXL_REQUIRE(B == 0 || (state_in && g_out && g_in), "null state / cotangent");
   return cx_launch_lunar_step_bwd((cudaStream_t)stream, B, state_in, state_next, ld, action, g_out, g_in,
-                                  g_action, flags, nullptr, p);
+                                  g_action, flags, nullptr, nullptr, p);
 }
 
 int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t ld, const float* actions,
@@ -308,41 +308,76 @@ int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t
   return 0;
 }
 
+// decision tape: 33 words per env-step; Jacobian area: room for one env-step in eight to have
+// contacts (slot list + 20 x 18 matrix each) + a 256-byte header
+static int64_t adj_dec_bytes(int64_t ld) { return (int64_t)COTIX_ADJ_TAPE_WORDS * ld * (int64_t)sizeof(float); }
+static int64_t adj_jac_cap(int64_t ld) { return ld / 8 + 1; }
+static int64_t adj_jac_bytes(int64_t ld) { return adj_jac_cap(ld) * (4 + 20 * COTIX_LUNAR_NDYN * (int64_t)sizeof(float)); }
+int64_t cotix_lunar_adjoint_decisions_bytes(int64_t ld, int32_t T) {
+  if (ld < 0 || T < 0) return 0;
+  return (int64_t)T * adj_dec_bytes(ld);
+}
 int64_t cotix_lunar_adjoint_workspace_bytes(int64_t ld, int32_t T) {
   if (ld < 0 || T < 0) return 0;
-  return (int64_t)T * COTIX_ADJ_TAPE_WORDS * ld * (int64_t)sizeof(float);
+  return 512 + (int64_t)T * (adj_dec_bytes(ld) + adj_jac_bytes(ld));  // header + alignment of the header
 }
 
 int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
                             const float* actions, float* g, float* g_actions, uint32_t* flags,
-                            const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
+                            const CotixLunarParams* p, void* workspace, int64_t workspace_bytes,
+                            int32_t jacobians) {
   CXL_REQUIRE(B >= 0 && ld >= B && T >= 0, "bad batch size / leading dimension / step count");
   CXL_REQUIRE(check_params(p), "bad params");
   CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
   CXL_REQUIRE(B == 0 || (tape && g), "null tape / cotangent");
   const int64_t slot = (int64_t)COTIX_LUNAR_NF * ld;
   const int64_t dslot = (int64_t)COTIX_ADJ_TAPE_WORDS * ld;
-  int64_t group = 0;  // steps whose decisions fit the workspace at once
+  int64_t group = 0;  // steps whose decisions (and Jacobians) fit the workspace at once
+  bool jac = false;
   if (workspace && B > 0) {
     CXL_REQUIRE(((uintptr_t)workspace & 255u) == 0, "workspace must be 256-byte aligned");
-    group = workspace_bytes / (dslot * (int64_t)sizeof(float));
-    CXL_REQUIRE(group >= 1, "workspace smaller than cotix_lunar_adjoint_workspace_bytes(ld, 1)");
+    const int64_t full = adj_dec_bytes(ld) + adj_jac_bytes(ld);
+    if (jacobians) {
+      jac = true;
+      group = (workspace_bytes - 512) / full;
+      CXL_REQUIRE(workspace_bytes >= 512 + full, "workspace smaller than cotix_lunar_adjoint_workspace_bytes(ld, 1)");
+    } else {
+      group = workspace_bytes / adj_dec_bytes(ld);
+      CXL_REQUIRE(group >= 1, "workspace smaller than cotix_lunar_adjoint_decisions_bytes(ld, 1)");
+    }
+    if (group > T) group = T;
+    CXL_REQUIRE(B * group < (1ll << 32), "too many (step, env) items per group");
   }
+  // layout: [group decision tapes][256-byte header: counter][slot list][matrices]
   float* dt = (float*)workspace;
+  uint32_t* jctr = nullptr;
+  uint32_t* jlist = nullptr;
+  float* jM = nullptr;
+  uint32_t jcap = 0;
+  if (jac) {
+    char* base = (char*)workspace + group * adj_dec_bytes(ld);
+    base += (256 - ((uintptr_t)base & 255u)) & 255u;
+    jcap = (uint32_t)(adj_jac_cap(ld) * group);
+    jctr = (uint32_t*)base;
+    jlist = (uint32_t*)(base + 256);
+    jM = (float*)(base + 256 + (int64_t)jcap * 4);
+    // header (256) + its alignment padding (< 256) are the 512 bytes the size function adds
+  }
   int32_t t = T;
   while (t > 0) {
     const int32_t nt = group > 0 ? (int32_t)(t < group ? t : group) : 1;
     const int32_t t0 = t - nt;
     if (group > 0) {
       const int rc = cx_launch_lunar_decide((cudaStream_t)stream, B, nt, tape + t0 * slot, ld,
-                                            actions ? actions + (int64_t)t0 * 2 * ld : nullptr, dt, p);
+                                            actions ? actions + (int64_t)t0 * 2 * ld : nullptr, dt, flags, jctr,
+                                            jlist, jM, jcap, p);
       if (rc != 0) return rc;
     }
     for (int32_t s = t - 1; s >= t0; --s) {
       const float* a = actions ? actions + (int64_t)s * 2 * ld : nullptr;
       float* ga = g_actions ? g_actions + (int64_t)s * 2 * ld : nullptr;
       const int rc = cx_launch_lunar_step_bwd((cudaStream_t)stream, B, tape + s * slot, tape + (s + 1) * slot, ld,
-                                              a, g, g, ga, flags, group > 0 ? dt + (s - t0) * dslot : nullptr, p);
+                                              a, g, g, ga, flags, group > 0 ? dt + (s - t0) * dslot : nullptr, jM, p);
       if (rc != 0) return rc;
     }
     t = t0;

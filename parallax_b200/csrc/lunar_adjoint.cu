@@ -653,16 +653,43 @@ CX_DEV void store_cotangent(const G6 g[4], float* g_in, int64_t ld, int64_t e) {
   }
 }
 
+// Transposed Jacobians of the env-steps with contacts (see lunar_jacobian_kernel)
+constexpr int JAC_ROWS = COTIX_LUNAR_NDYN + 2, JAC_FLOATS = JAC_ROWS * COTIX_LUNAR_NDYN;  // 20 x 18
+constexpr uint32_t DT_HAS_MATRIX = 1u << 23;  // bit of decision word 0; the slot is in word 32
+struct JacWs {
+  uint32_t* ctr;    // [1] env-steps with contacts in this group
+  uint32_t* hlist;  // [cap] item index (step_local * B + env) of slot s
+  float* M;         // [cap][20][18]: (g_state; g_action) = M g_next
+  uint32_t cap;
+};
+
 // One step backwards for every env.  dtape == NULL: the collider's decisions are replayed here
-// (narrowphase of all candidates + coins); else they are read from the decision tape of this step.
+// (narrowphase of all candidates + coins); else they are read from the decision tape of this step,
+// and an env-step whose transposed Jacobian was formed in advance is a matrix-vector product.
 __global__ void __launch_bounds__(TPB)
 lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __restrict__ snext,
                       int64_t ld, const float* __restrict__ action, const float* g_out, float* g_in,
                       float* __restrict__ g_action, uint32_t* __restrict__ flags_out,
-                      const float* __restrict__ dtape, const __grid_constant__ CotixLunarParams P,
-                      const LunarDerived D) {
+                      const float* __restrict__ dtape, const float* __restrict__ jacM,
+                      const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   if (e >= B) return;
+  G6 g[4];
+  load_cotangent(g, g_out, ld, e);
+  if (dtape && jacM && (__float_as_uint(dtape[e]) & DT_HAS_MATRIX)) {
+    const float* M = jacM + (size_t)__float_as_uint(dtape[32 * ld + e]) * JAC_FLOATS;
+    const float gv[COTIX_LUNAR_NDYN] = {g[0].px, g[0].py, g[0].vx, g[0].vy, g[0].ang, g[0].w,
+                                        g[1].px, g[1].py, g[1].vx, g[1].vy, g[1].ang, g[1].w,
+                                        g[2].px, g[2].py, g[2].vx, g[2].vy, g[2].ang, g[2].w};
+    for (int j = 0; j < JAC_ROWS; ++j) {
+      float acc = 0.0f;
+#pragma unroll
+      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) acc += M[j * COTIX_LUNAR_NDYN + k] * gv[k];
+      if (j < COTIX_LUNAR_NDYN) g_in[j * ld + e] = acc;
+      else if (g_action) g_action[(j - COTIX_LUNAR_NDYN) * ld + e] = acc;
+    }
+    return;  // its flags were set when the matrix was formed
+  }
   EnvRegs E;
   load_env(E, sin_, ld, e);
   float am = 0.0f, as = 0.0f;
@@ -670,8 +697,6 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
     am = action[e];
     as = action[ld + e];
   }
-  G6 g[4];
-  load_cotangent(g, g_out, ld, e);
   StepCtx cx;
   Poly wL, wr, wl;
   integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
@@ -695,16 +720,23 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
   if (flags_out) flags_out[e] = flags_out[e] | flags;
 }
 
-// The collider's decisions of nt consecutive steps of a taped rollout in ONE launch: item = (step,
-// env).  The replay of a step depends only on the state before it, which is on the tape, so unlike
-// the reverse sweep it is not sequential in time — this is where the irregular work of the backward
-// pass (narrowphase, coins) runs, at full occupancy instead of one small launch per step.
+// The VJP of an env-step is linear in the cotangent and its coefficients depend only on forward
+// quantities (the state before the step, the action, the collider's decisions).  For the env-steps
+// WITH resolved contacts — whose adjoint is the expensive, divergent one — the 20 x 18 matrix
+// (g_state; g_action) = M g_next is formed here for all steps of a group at once: thread = (env-step
+// with contacts, k) evaluates the VJP of unit cotangent k.  The sequential sweep then spends a
+// matrix-vector product on such an env-step instead of the contact adjoint.
 __global__ void __launch_bounds__(TPB)
-lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t ld,
-                    const float* __restrict__ actions, float* __restrict__ dtape,
-                    const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
-  const int64_t i = (int64_t)blockIdx.x * TPB + threadIdx.x;
-  if (i >= B * nt) return;
+lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
+                      const float* __restrict__ actions, const float* __restrict__ dtape,
+                      uint32_t* __restrict__ flags_out, const JacWs jw,
+                      const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
+  const int64_t idx = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  const uint32_t slot = (uint32_t)(idx / COTIX_LUNAR_NDYN);
+  const int k = (int)(idx - (int64_t)slot * COTIX_LUNAR_NDYN);
+  const uint32_t nh = *jw.ctr < jw.cap ? *jw.ctr : jw.cap;
+  if (slot >= nh) return;
+  const int64_t i = jw.hlist[slot];
   const int64_t t = i / B, e = i - t * B;
   const float* sin_ = tape + t * (int64_t)COTIX_LUNAR_NF * ld;
   EnvRegs E;
@@ -717,15 +749,111 @@ lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t l
   StepCtx cx;
   Poly wL, wr, wl;
   integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
-  float* dt = dtape + t * (int64_t)DT_WORDS * ld;
-  if (cx.cand == 0u) {
-    dt[e] = 0.0f;
-    return;
-  }
   const RegPolys src{wL, wr, wl, E.h, E.kn};
   Decisions d;
-  decide(E, cx.cand, src, P, d);
-  store_decisions(d, dt, ld, e);
+  load_decisions(d, dtape + t * (int64_t)DT_WORDS * ld, ld, e);
+  G6 g[4];
+  g[0] = g[1] = g[2] = g[3] = g6_zero();
+  {
+    G6& gb = g[k / 6];
+    const int l = k % 6;
+    if (l == 0) gb.px = 1.0f;
+    else if (l == 1) gb.py = 1.0f;
+    else if (l == 2) gb.vx = 1.0f;
+    else if (l == 3) gb.vy = 1.0f;
+    else if (l == 4) gb.ang = 1.0f;
+    else gb.w = 1.0f;
+  }
+  uint32_t flags = 0u;
+  float g_am, g_as;
+  step_bwd_core(E, cx, src, am, as, d, P, k == 0 ? sin_ + (int64_t)COTIX_LUNAR_NF * ld : nullptr, ld, e, g, g_am,
+                g_as, flags);
+  // An env that is about to blow up (velocities ~1e20 a step or two before the state goes NaN) has
+  // Jacobian entries that overflow.  Its cotangent was dropped downstream, i.e. is zero, and the
+  // direct sweep then returns zero; 0 x inf would poison the matrix form, so such entries are stored
+  // as 0.
+  float* M = jw.M + (size_t)slot * JAC_FLOATS;
+  auto fin = [](float v) { return (fabsf(v) <= 3.0e38f) ? v : 0.0f; };
+#pragma unroll
+  for (int b = 0; b < 3; ++b) {
+    M[(b * 6 + 0) * COTIX_LUNAR_NDYN + k] = fin(g[b].px);
+    M[(b * 6 + 1) * COTIX_LUNAR_NDYN + k] = fin(g[b].py);
+    M[(b * 6 + 2) * COTIX_LUNAR_NDYN + k] = fin(g[b].vx);
+    M[(b * 6 + 3) * COTIX_LUNAR_NDYN + k] = fin(g[b].vy);
+    M[(b * 6 + 4) * COTIX_LUNAR_NDYN + k] = fin(g[b].ang);
+    M[(b * 6 + 5) * COTIX_LUNAR_NDYN + k] = fin(g[b].w);
+  }
+  M[18 * COTIX_LUNAR_NDYN + k] = fin(g_am);
+  M[19 * COTIX_LUNAR_NDYN + k] = fin(g_as);
+  if (k == 0 && flags_out && flags) atomicOr(&flags_out[e], flags);
+}
+
+// The collider's decisions of nt consecutive steps of a taped rollout in ONE launch: item = (step,
+// env).  The replay of a step depends only on the state before it, which is on the tape, so unlike
+// the reverse sweep it is not sequential in time — this is where the irregular work of the backward
+// pass (narrowphase, coins) runs, at full occupancy instead of one small launch per step.
+constexpr int DECIDE_TILE = TPB * 8;
+__global__ void __launch_bounds__(TPB)
+lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t ld,
+                    const float* __restrict__ actions, float* __restrict__ dtape, const JacWs jw,
+                    const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
+  // Only ~10 % of the items have candidate pairs.  Pass 1 integrates every item of a tile and
+  // collects the ones with candidates in shared memory; pass 2 runs the narrowphase and the
+  // collider's choices on those with consecutive lanes, so the warps of the irregular part are full.
+  __shared__ uint32_t s_list[DECIDE_TILE];
+  __shared__ int s_n;
+  const int64_t N = B * nt;
+  for (int64_t t0 = (int64_t)blockIdx.x * DECIDE_TILE; t0 < N; t0 += (int64_t)gridDim.x * DECIDE_TILE) {
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    for (int j = 0; j < DECIDE_TILE / TPB; ++j) {
+      const int64_t i = t0 + j * TPB + threadIdx.x;
+      if (i >= N) break;
+      const int64_t t = i / B, e = i - t * B;
+      EnvRegs E;
+      load_env(E, tape + t * (int64_t)COTIX_LUNAR_NF * ld, ld, e);
+      float am = 0.0f, as = 0.0f;
+      if (actions) {
+        am = actions[t * 2 * ld + e];
+        as = actions[t * 2 * ld + ld + e];
+      }
+      StepCtx cx;
+      Poly wL, wr, wl;
+      integrate_and_cull<false>(E, am, as, P, D, cx, wL, wr, wl);
+      if (cx.cand == 0u) dtape[t * (int64_t)DT_WORDS * ld + e] = 0.0f;
+      else s_list[atomicAdd(&s_n, 1)] = (uint32_t)(i - t0);
+    }
+    __syncthreads();
+    const int n = s_n;
+    for (int q = threadIdx.x; q < n; q += TPB) {
+      const int64_t i = t0 + s_list[q];
+      const int64_t t = i / B, e = i - t * B;
+      EnvRegs E;
+      load_env(E, tape + t * (int64_t)COTIX_LUNAR_NF * ld, ld, e);
+      float am = 0.0f, as = 0.0f;
+      if (actions) {
+        am = actions[t * 2 * ld + e];
+        as = actions[t * 2 * ld + ld + e];
+      }
+      StepCtx cx;
+      Poly wL, wr, wl;
+      integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
+      const RegPolys src{wL, wr, wl, E.h, E.kn};
+      Decisions d;
+      decide(E, cx.cand, src, P, d);
+      float* dt = dtape + t * (int64_t)DT_WORDS * ld;
+      store_decisions(d, dt, ld, e);
+      if (jw.M && d.pl.n > 0) {  // an env-step with contacts gets a slot for its transposed Jacobian
+        const uint32_t slot = atomicAdd(jw.ctr, 1u);
+        if (slot < jw.cap) {
+          jw.hlist[slot] = (uint32_t)i;
+          dt[e] = __uint_as_float(__float_as_uint(dt[e]) | DT_HAS_MATRIX);
+          dt[32 * ld + e] = __uint_as_float(slot);
+        }
+      }
+    }
+    __syncthreads();
+  }
 }
 
 }  // namespace
@@ -733,24 +861,44 @@ lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t l
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t st, int64_t B, const float* state_in,
                                         const float* state_next, int64_t ld, const float* action,
                                         const float* g_out, float* g_in, float* g_action,
-                                        uint32_t* flags, const float* dtape, const CotixLunarParams* p) {
+                                        uint32_t* flags, const float* dtape, const float* jacM,
+                                        const CotixLunarParams* p) {
   if (B == 0) return 0;
   LunarDerived D;
   cx_lunar_derive(p, &D);
   lunar_step_bwd_kernel<<<(unsigned)((B + TPB - 1) / TPB), TPB, 0, st>>>(
-      B, state_in, state_next, ld, action, g_out, g_in, g_action, flags, dtape, *p, D);
+      B, state_in, state_next, ld, action, g_out, g_in, g_action, flags, dtape, jacM, *p, D);
   cx_count_launch();
   return cx_check_launch("lunar_step_bwd_kernel");
 }
 
-// decisions of steps [t0, t0 + nt) of a taped rollout -> dtape [nt][COTIX_ADJ_TAPE_WORDS][ld]
+// decisions of steps [t0, t0 + nt) of a taped rollout -> dtape [nt][COTIX_ADJ_TAPE_WORDS][ld]; with a
+// Jacobian area (jac_ctr, jac_list, jac_M, jac_cap; or all NULL / 0) also the transposed Jacobians of
+// the env-steps with contacts
 extern "C" int cx_launch_lunar_decide(cudaStream_t st, int64_t B, int nt, const float* tape_t0, int64_t ld,
-                                      const float* actions_t0, float* dtape, const CotixLunarParams* p) {
+                                      const float* actions_t0, float* dtape, uint32_t* flags,
+                                      uint32_t* jac_ctr, uint32_t* jac_list, float* jac_M, uint32_t jac_cap,
+                                      const CotixLunarParams* p) {
   if (B == 0 || nt == 0) return 0;
   LunarDerived D;
   cx_lunar_derive(p, &D);
   const int64_t n = B * nt;
-  lunar_decide_kernel<<<(unsigned)((n + TPB - 1) / TPB), TPB, 0, st>>>(B, nt, tape_t0, ld, actions_t0, dtape, *p, D);
+  JacWs jw;
+  jw.ctr = jac_ctr;
+  jw.hlist = jac_list;
+  jw.M = jac_M;
+  jw.cap = jac_M ? jac_cap : 0u;
+  if (jw.M && cudaMemsetAsync(jw.ctr, 0, 4, st) != cudaSuccess) return cx_check_launch("adjoint memset");
+  int64_t blocks = (n + DECIDE_TILE - 1) / DECIDE_TILE;
+  const int64_t cap = (int64_t)cx_sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  lunar_decide_kernel<<<(unsigned)blocks, TPB, 0, st>>>(B, nt, tape_t0, ld, actions_t0, dtape, jw, *p, D);
   cx_count_launch();
+  if (jw.M) {
+    const int64_t threads = (int64_t)jw.cap * COTIX_LUNAR_NDYN;
+    lunar_jacobian_kernel<<<(unsigned)((threads + TPB - 1) / TPB), TPB, 0, st>>>(B, tape_t0, ld, actions_t0, dtape,
+                                                                                flags, jw, *p, D);
+    cx_count_launch();
+  }
   return cx_check_launch("lunar_decide_kernel");
 }

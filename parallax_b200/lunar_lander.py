@@ -160,6 +160,7 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
 
 
 NDYN = 18
+JACOBIAN_MAX_ENVS = 16384
 ADJ_REPLAY_MISMATCH, ADJ_NONFINITE, ADJ_CONTACT_SHIFT = 0x1, 0x2, 8
 
 
@@ -238,13 +239,20 @@ def rollout(state: LunarState, actions: torch.Tensor | None, n_steps: int,
 
 
 def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None = None,
-                decision_tape: bool | int = True):
+                decision_tape: bool | int = True, jacobians: bool | None = None):
     """Backward pass over a `Rollout` (`cotix_lunar_rollout_bwd`): g_final [18, B] = dL/d(final
     dynamic leaves).  Returns (dL/d(initial dynamic leaves) [18, B], dL/d(actions) [T, 2, B]).
 
-    decision_tape: True = scratch for the collider's decisions of the whole rollout (one batched
-    replay launch + T light reverse launches), an int = scratch for that many steps at a time,
-    False = every reverse step replays its own decisions.  Same results."""
+    decision_tape: True = scratch for the whole rollout, an int = for that many steps at a time:
+    the collider's decisions — and with `jacobians` the transposed Jacobians of the env-steps with
+    contacts — are computed in batched launches over (step, env) and the T reverse launches are
+    light; False = every reverse step replays its own decisions.  Without `jacobians` the results
+    are bit-identical to False; with them they differ at rounding level.  jacobians=None picks them
+    for B <= JACOBIAN_MAX_ENVS: they trade 18 x the contact-adjoint work, done at full occupancy, for
+    short reverse launches — a win while the sweep is latency-bound (B = 4096: 9.0 -> 5.7 ms), a loss
+    once it is throughput-bound (B = 65536: 23.7 -> 43 ms)."""
+    if jacobians is None:
+        jacobians = ro.tape.shape[2] <= JACOBIAN_MAX_ENVS
     tape = ro.tape
     T, B = tape.shape[0] - 1, tape.shape[2]
     g = g_final.to(device=tape.device, dtype=torch.float32).contiguous().clone()
@@ -252,15 +260,17 @@ def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None =
     g_act = torch.zeros((T, 2, B), dtype=torch.float32, device=tape.device)
     wp, wn, ws = None, 0, None
     if decision_tape and T > 0:
+        L = _lib.lib()
         steps = T if decision_tape is True else max(1, min(T, int(decision_tape)))
-        wn = int(_lib.lib().cotix_lunar_adjoint_workspace_bytes(B, steps))
+        size = L.cotix_lunar_adjoint_workspace_bytes if jacobians else L.cotix_lunar_adjoint_decisions_bytes
+        wn = int(size(B, steps))
         ws = torch.empty(wn + 256, dtype=torch.uint8, device=tape.device)
         wp = (ws.data_ptr() + 255) & ~255
     with torch.cuda.device(tape.device):
         _lib.check(_lib.lib().cotix_lunar_rollout_bwd(
             _stream_ptr(tape.device), B, T, tape.data_ptr(), B,
             ro.actions.data_ptr() if ro.actions is not None else None, g.data_ptr(), g_act.data_ptr(),
-            flags.data_ptr() if flags is not None else None, C.byref(ro.params), wp, wn))
+            flags.data_ptr() if flags is not None else None, C.byref(ro.params), wp, wn, 1 if jacobians else 0))
     return g, g_act
 
 
