@@ -659,7 +659,7 @@ constexpr uint32_t DT_HAS_MATRIX = 1u << 23;  // bit of decision word 0; the slo
 struct JacWs {
   uint32_t* ctr;    // [1] env-steps with contacts in this group
   uint32_t* hlist;  // [cap] item index (step_local * B + env) of slot s
-  float* M;         // [cap][20][18]: (g_state; g_action) = M g_next
+  float* M;         // [cap][18][20], column-major: (g_state; g_action) = M g_next, M[k][j] = d out_j / d g_next_k
   uint32_t cap;
 };
 
@@ -673,23 +673,44 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
                       const float* __restrict__ dtape, const float* __restrict__ jacM,
                       const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
-  if (e >= B) return;
+  const bool in = e < B;
   G6 g[4];
-  load_cotangent(g, g_out, ld, e);
-  if (dtape && jacM && (__float_as_uint(dtape[e]) & DT_HAS_MATRIX)) {
-    const float* M = jacM + (size_t)__float_as_uint(dtape[32 * ld + e]) * JAC_FLOATS;
+  g[0] = g[1] = g[2] = g[3] = g6_zero();
+  if (in) load_cotangent(g, g_out, ld, e);
+  bool heavy = false;
+  if (dtape && jacM) {
+    // The matrix-vector products of the warp's env-steps with a Jacobian, one after the other with
+    // the whole warp on each: lane j < 20 owns output row j and reads column-major M[k][j] (18
+    // independent, coalesced loads) while the cotangent comes round by shuffle.  A lane working
+    // through its own 360 entries keeps only a few loads in flight: ~20 rounds of memory latency per
+    // launch, which was most of the sweep's time.
+    uint32_t slot = 0u;
+    if (in && (__float_as_uint(dtape[e]) & DT_HAS_MATRIX)) {
+      heavy = true;
+      slot = __float_as_uint(dtape[32 * ld + e]);
+    }
     const float gv[COTIX_LUNAR_NDYN] = {g[0].px, g[0].py, g[0].vx, g[0].vy, g[0].ang, g[0].w,
                                         g[1].px, g[1].py, g[1].vx, g[1].vy, g[1].ang, g[1].w,
                                         g[2].px, g[2].py, g[2].vx, g[2].vy, g[2].ang, g[2].w};
-    for (int j = 0; j < JAC_ROWS; ++j) {
+    const int j = (int)(threadIdx.x & 31u);
+    uint32_t hm = __ballot_sync(0xFFFFFFFFu, heavy);
+    while (hm) {
+      const int src = __ffs(hm) - 1;
+      hm &= hm - 1u;
+      const uint32_t sl = __shfl_sync(0xFFFFFFFFu, slot, src);
+      const int64_t es = e - j + src;
+      const float* M = jacM + (size_t)sl * JAC_FLOATS;
+      float m[COTIX_LUNAR_NDYN];
+#pragma unroll
+      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) m[k] = (j < JAC_ROWS) ? M[k * JAC_ROWS + j] : 0.0f;
       float acc = 0.0f;
 #pragma unroll
-      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) acc += M[j * COTIX_LUNAR_NDYN + k] * gv[k];
-      if (j < COTIX_LUNAR_NDYN) g_in[j * ld + e] = acc;
-      else if (g_action) g_action[(j - COTIX_LUNAR_NDYN) * ld + e] = acc;
+      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) acc += m[k] * __shfl_sync(0xFFFFFFFFu, gv[k], src);
+      if (j < COTIX_LUNAR_NDYN) g_in[j * ld + es] = acc;
+      else if (j < JAC_ROWS && g_action) g_action[(j - COTIX_LUNAR_NDYN) * ld + es] = acc;
     }
-    return;  // its flags were set when the matrix was formed
   }
+  if (!in || heavy) return;  // a heavy env-step's flags were set when its matrix was formed
   EnvRegs E;
   load_env(E, sin_, ld, e);
   float am = 0.0f, as = 0.0f;
@@ -774,17 +795,19 @@ lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
   // as 0.
   float* M = jw.M + (size_t)slot * JAC_FLOATS;
   auto fin = [](float v) { return (fabsf(v) <= 3.0e38f) ? v : 0.0f; };
+  // column-major: the 20 results of unit cotangent k are contiguous
+  float* Mk = M + k * JAC_ROWS;
 #pragma unroll
   for (int b = 0; b < 3; ++b) {
-    M[(b * 6 + 0) * COTIX_LUNAR_NDYN + k] = fin(g[b].px);
-    M[(b * 6 + 1) * COTIX_LUNAR_NDYN + k] = fin(g[b].py);
-    M[(b * 6 + 2) * COTIX_LUNAR_NDYN + k] = fin(g[b].vx);
-    M[(b * 6 + 3) * COTIX_LUNAR_NDYN + k] = fin(g[b].vy);
-    M[(b * 6 + 4) * COTIX_LUNAR_NDYN + k] = fin(g[b].ang);
-    M[(b * 6 + 5) * COTIX_LUNAR_NDYN + k] = fin(g[b].w);
+    Mk[b * 6 + 0] = fin(g[b].px);
+    Mk[b * 6 + 1] = fin(g[b].py);
+    Mk[b * 6 + 2] = fin(g[b].vx);
+    Mk[b * 6 + 3] = fin(g[b].vy);
+    Mk[b * 6 + 4] = fin(g[b].ang);
+    Mk[b * 6 + 5] = fin(g[b].w);
   }
-  M[18 * COTIX_LUNAR_NDYN + k] = fin(g_am);
-  M[19 * COTIX_LUNAR_NDYN + k] = fin(g_as);
+  Mk[18] = fin(g_am);
+  Mk[19] = fin(g_as);
   if (k == 0 && flags_out && flags) atomicOr(&flags_out[e], flags);
 }
 

@@ -95,7 +95,7 @@ def main():
     for it in range(3):
         flags.zero_()
         ev[0].record()
-        ro = ll.rollout(st0, actions, T, P, mode="fused")
+        ro = ll.rollout(st0, actions, T, P, mode=os.environ.get("MODE", "fused"))
         ev[1].record()
         y = ro.tape[-1, 1]
         g = torch.zeros((18, B), device="cuda")
