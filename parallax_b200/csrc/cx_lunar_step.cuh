@@ -165,9 +165,8 @@ CX_DEV void order_body_poly(int body, Poly& p, const LunarDerived& D) {
 // Updates E (poses, lander velocity, status), fills cx (sin/cos, throttles, candidate mask) and
 // returns the world polygons: with ORDER, in the order part.transform() gives them when there
 // are candidates; without, always in local vertex order (the consumer calls order_body_poly).
-template <bool ORDER>
-CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
-                               const LunarDerived& D, StepCtx& cx, Poly& wL, Poly& wr, Poly& wl) {
+// the first half of integrate_and_cull on its own: Euler, gravity, trig of the three angles, engines
+CX_DEV void integrate_only(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P, StepCtx& cx) {
   // ExplicitEulerPhysics.step (cotix/_physics_solvers.py:17-24); the ground stays at 0
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -196,6 +195,12 @@ CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const Cot
     E.b[0].vy = E.b[0].vy + cx.sn[0] * dv;
     E.b[0].w = E.b[0].w - P.side_engine_dw * cx.thr_side;
   }
+}
+
+template <bool ORDER>
+CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const CotixLunarParams& P,
+                               const LunarDerived& D, StepCtx& cx, Poly& wL, Poly& wr, Poly& wl) {
+  integrate_only(E, a_main, a_side, P, cx);
   // world polygons (local vertex order) and the broadphase — new, exact
   world_poly<6>(P.lander_local, E.b[0], cx.cs[0], cx.sn[0], wL);
   world_poly<4>(P.leg_local[0], E.b[1], cx.cs[1], cx.sn[1], wr);

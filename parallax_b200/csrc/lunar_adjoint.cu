@@ -674,45 +674,57 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
                       const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   const bool in = e < B;
+  bool heavy = false;
+  uint32_t slot = 0u;
+  if (dtape && jacM && in && (__float_as_uint(dtape[e]) & DT_HAS_MATRIX)) {
+    heavy = true;
+    slot = __float_as_uint(dtape[32 * ld + e]);
+    // the warp takes its matrices one after the other below: have them all on their way to L2 now
+    const char* Mb = reinterpret_cast<const char*>(jacM + (size_t)slot * JAC_FLOATS);
+#pragma unroll
+    for (int l = 0; l < JAC_FLOATS * 4; l += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(Mb + l));
+  }
   G6 g[4];
   g[0] = g[1] = g[2] = g[3] = g6_zero();
   if (in) load_cotangent(g, g_out, ld, e);
-  bool heavy = false;
   if (dtape && jacM) {
     // The matrix-vector products of the warp's env-steps with a Jacobian, one after the other with
     // the whole warp on each: lane j < 20 owns output row j and reads column-major M[k][j] (18
-    // independent, coalesced loads) while the cotangent comes round by shuffle.  A lane working
-    // through its own 360 entries keeps only a few loads in flight: ~20 rounds of memory latency per
-    // launch, which was most of the sweep's time.
-    uint32_t slot = 0u;
-    if (in && (__float_as_uint(dtape[e]) & DT_HAS_MATRIX)) {
-      heavy = true;
-      slot = __float_as_uint(dtape[32 * ld + e]);
-    }
+    // independent, coalesced loads; the next matrix is loaded while this one is used) while the
+    // cotangent comes round by shuffle.  A lane working through its own 360 entries keeps only a few
+    // loads in flight: ~20 rounds of memory latency per launch, which was most of the sweep's time.
     const float gv[COTIX_LUNAR_NDYN] = {g[0].px, g[0].py, g[0].vx, g[0].vy, g[0].ang, g[0].w,
                                         g[1].px, g[1].py, g[1].vx, g[1].vy, g[1].ang, g[1].w,
                                         g[2].px, g[2].py, g[2].vx, g[2].vy, g[2].ang, g[2].w};
     const int j = (int)(threadIdx.x & 31u);
     uint32_t hm = __ballot_sync(0xFFFFFFFFu, heavy);
+    float m[COTIX_LUNAR_NDYN];
+    auto fetch = [&](int src_lane) {
+      const uint32_t sl = __shfl_sync(0xFFFFFFFFu, slot, src_lane);
+      const float* M = jacM + (size_t)sl * JAC_FLOATS;
+#pragma unroll
+      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) m[k] = (j < JAC_ROWS) ? M[k * JAC_ROWS + j] : 0.0f;
+    };
+    if (hm) fetch(__ffs(hm) - 1);
     while (hm) {
       const int src = __ffs(hm) - 1;
       hm &= hm - 1u;
-      const uint32_t sl = __shfl_sync(0xFFFFFFFFu, slot, src);
-      const int64_t es = e - j + src;
-      const float* M = jacM + (size_t)sl * JAC_FLOATS;
-      float m[COTIX_LUNAR_NDYN];
+      float mc[COTIX_LUNAR_NDYN];
 #pragma unroll
-      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) m[k] = (j < JAC_ROWS) ? M[k * JAC_ROWS + j] : 0.0f;
+      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) mc[k] = m[k];
+      if (hm) fetch(__ffs(hm) - 1);
+      const int64_t es = e - j + src;
       float acc = 0.0f;
 #pragma unroll
-      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) acc += m[k] * __shfl_sync(0xFFFFFFFFu, gv[k], src);
+      for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) acc += mc[k] * __shfl_sync(0xFFFFFFFFu, gv[k], src);
       if (j < COTIX_LUNAR_NDYN) g_in[j * ld + es] = acc;
       else if (j < JAC_ROWS && g_action) g_action[(j - COTIX_LUNAR_NDYN) * ld + es] = acc;
     }
   }
   if (!in || heavy) return;  // a heavy env-step's flags were set when its matrix was formed
   EnvRegs E;
-  load_env(E, sin_, ld, e);
+  load_dyn(E, sin_, ld, e);
+  E.status = __float_as_uint(sin_[COTIX_F_STATUS * ld + e]);
   float am = 0.0f, as = 0.0f;
   if (action) {
     am = action[e];
@@ -720,15 +732,29 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
   }
   StepCtx cx;
   Poly wL, wr, wl;
-  integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
-  const RegPolys src{wL, wr, wl, E.h, E.kn};
   Decisions d;
-  if (dtape) {
-    load_decisions(d, dtape, ld, e);
-    // integrate_and_cull orders the world polygons only when it found candidates; a taped contact
-    // implies it did
+  // a taped env-step without a resolved contact (most of them) needs neither the terrain, the world
+  // polygons nor the broadphase: Euler, trig and engines only
+  const bool contact_free = dtape && (__float_as_uint(dtape[e]) & 7u) == 0u;
+  if (contact_free) {
+    integrate_only(E, am, as, P, cx);
+    cx.cand = 0u;
+    cx.base = -1;
+    d.pl.n = 0;
   } else {
-    decide(E, cx.cand, src, P, d);
+    load_terrain(E, sin_, ld, e);
+    load_meta(E, sin_, ld, e);
+    integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
+  }
+  const RegPolys src{wL, wr, wl, E.h, E.kn};
+  if (!contact_free) {
+    if (dtape) {
+      load_decisions(d, dtape, ld, e);
+      // integrate_and_cull orders the world polygons only when it found candidates; a taped contact
+      // implies it did
+    } else {
+      decide(E, cx.cand, src, P, d);
+    }
   }
   uint32_t flags = 0u;
   float g_am, g_as;
