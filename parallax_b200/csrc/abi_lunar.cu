@@ -1,4 +1,5 @@
 // abi_lunar.cu — LunarLander entry points of the C-ABI (include/cotix_b200.h).
+#include <mutex>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -25,7 +26,8 @@ extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, con
                                         const float*, const float*, float*, float*, uint32_t*,
                                         const float*, const float*, const CotixLunarParams*);
 extern "C" int cx_launch_lunar_decide(cudaStream_t, int64_t, int, const float*, int64_t, const float*, float*,
-                                      uint32_t*, uint32_t*, uint32_t*, float*, uint32_t, const CotixLunarParams*);
+                                      uint32_t*, uint32_t*, uint32_t*, float*, uint32_t, const CotixLunarParams*,
+                                      int);
 extern "C" int cx_launch_raster_draw(cudaStream_t, int64_t, const int32_t*, const int32_t*, int32_t, uint8_t*);
 extern "C" int cx_launch_lunar_draw(cudaStream_t, int64_t, const float*, int64_t, const int64_t*, uint8_t*,
                                     const CotixLunarParams*);
@@ -322,6 +324,35 @@ int64_t cotix_lunar_adjoint_workspace_bytes(int64_t ld, int32_t T) {
   return 512 + (int64_t)T * (adj_dec_bytes(ld) + adj_jac_bytes(ld));  // header + alignment of the header
 }
 
+// Side stream of the pipelined backward pass (one per device, made on first use): the decisions and
+// Jacobians of the earlier steps are formed there while the sweep of the later steps runs on the
+// caller's stream.  Forked from and joined back into the caller's stream with events, so the call
+// stays stream-ordered (and capturable).
+struct AdjSide {
+  cudaStream_t s;
+  cudaEvent_t fork, done[8];
+  int state;  // 0 not made, 1 ok, -1 failed
+};
+static AdjSide* adj_side() {
+  static AdjSide per_dev[64];
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  AdjSide& a = per_dev[dev];
+  if (a.state == 0) {
+    bool ok = cudaStreamCreateWithFlags(&a.s, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; i < 8 && ok; ++i) ok = cudaEventCreateWithFlags(&a.done[i], cudaEventDisableTiming) == cudaSuccess;
+    a.state = ok ? 1 : -1;
+    if (!ok) cudaGetLastError();
+  }
+  return a.state == 1 ? &a : nullptr;
+}
+// 0: off; n > 0: on, the overlapped launches capped at n blocks per SM; n < 0: on, uncapped
+static int g_adj_pipelined = -1;
+void cx_lunar_adjoint_set_pipelined(int n) { g_adj_pipelined = n; }
+
 int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tape, int64_t ld,
                             const float* actions, float* g, float* g_actions, uint32_t* flags,
                             const CotixLunarParams* p, void* workspace, int64_t workspace_bytes,
@@ -363,6 +394,47 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
     jM = (float*)(base + 256 + (int64_t)jcap * 4);
     // header (256) + its alignment padding (< 256) are the 512 bytes the size function adds
   }
+  // The whole rollout fits: cut it into NG runs of steps.  The decisions + Jacobians of all runs are
+  // enqueued on the side stream, latest run first (the first with the GPU to itself, the others with
+  // capped grids); the sweep of a run starts as soon as its own are done and overlaps the next one's.
+  constexpr int NG = 4;
+  static const char* env_overlap = getenv("COTIX_ADJ_OVERLAP");  // measurement aid: "0" turns the overlap off
+  const bool overlap = g_adj_pipelined != 0 && !(env_overlap && env_overlap[0] == '0');
+  AdjSide* side = (jac && overlap && group >= T && T >= 2 * NG) ? adj_side() : nullptr;
+  if (side) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const int32_t ns = (T + NG - 1) / NG;
+    int32_t b[NG + 1];
+    for (int i = 0; i <= NG; ++i) b[i] = (int32_t)((int64_t)i * ns < T ? (int64_t)i * ns : T);
+    if (cudaEventRecord(side->fork, st) != cudaSuccess || cudaStreamWaitEvent(side->s, side->fork, 0) != cudaSuccess)
+      return cx_check_launch("adjoint fork");
+    const int64_t cap1 = adj_jac_cap(ld);
+    for (int i = NG - 1; i >= 0; --i) {
+      const int32_t nt = b[i + 1] - b[i];
+      if (nt > 0) {
+        const int64_t off = cap1 * b[i];
+        const int rc = cx_launch_lunar_decide(side->s, B, nt, tape + b[i] * slot, ld,
+                                              actions ? actions + (int64_t)b[i] * 2 * ld : nullptr, dt + b[i] * dslot,
+                                              flags, jctr + i, jlist + off, jM + off * 20 * COTIX_LUNAR_NDYN,
+                                              (uint32_t)(cap1 * nt), p,
+                                              (i == NG - 1 || g_adj_pipelined < 0) ? 0 : g_adj_pipelined);
+        if (rc != 0) return rc;
+      }
+      if (cudaEventRecord(side->done[i], side->s) != cudaSuccess) return cx_check_launch("adjoint event");
+    }
+    for (int i = NG - 1; i >= 0; --i) {
+      if (cudaStreamWaitEvent(st, side->done[i], 0) != cudaSuccess) return cx_check_launch("adjoint join");
+      const int64_t off = cap1 * b[i];
+      for (int32_t s = b[i + 1] - 1; s >= b[i]; --s) {
+        const float* a = actions ? actions + (int64_t)s * 2 * ld : nullptr;
+        float* ga = g_actions ? g_actions + (int64_t)s * 2 * ld : nullptr;
+        const int rc = cx_launch_lunar_step_bwd(st, B, tape + s * slot, tape + (s + 1) * slot, ld, a, g, g, ga, flags,
+                                                dt + s * dslot, jM + off * 20 * COTIX_LUNAR_NDYN, p);
+        if (rc != 0) return rc;
+      }
+    }
+    return 0;
+  }
   int32_t t = T;
   while (t > 0) {
     const int32_t nt = group > 0 ? (int32_t)(t < group ? t : group) : 1;
@@ -370,7 +442,7 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
     if (group > 0) {
       const int rc = cx_launch_lunar_decide((cudaStream_t)stream, B, nt, tape + t0 * slot, ld,
                                             actions ? actions + (int64_t)t0 * 2 * ld : nullptr, dt, flags, jctr,
-                                            jlist, jM, jcap, p);
+                                            jlist, jM, jcap, p, 0);
       if (rc != 0) return rc;
     }
     for (int32_t s = t - 1; s >= t0; --s) {

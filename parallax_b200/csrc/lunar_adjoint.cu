@@ -764,7 +764,8 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
     g_action[e] = g_am;
     g_action[ld + e] = g_as;
   }
-  if (flags_out) flags_out[e] = flags_out[e] | flags;
+  // atomic: the Jacobian kernel of an earlier run of steps may be setting flags concurrently
+  if (flags_out && flags) atomicOr(&flags_out[e], flags);
 }
 
 // The VJP of an env-step is linear in the cotangent and its coefficients depend only on forward
@@ -778,11 +779,12 @@ lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
                       const float* __restrict__ actions, const float* __restrict__ dtape,
                       uint32_t* __restrict__ flags_out, const JacWs jw,
                       const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
-  const int64_t idx = (int64_t)blockIdx.x * TPB + threadIdx.x;
+  const uint32_t nh = *jw.ctr < jw.cap ? *jw.ctr : jw.cap;
+  // grid-stride: the launcher may cap the grid so that a concurrent sweep launch finds room on every SM
+  for (int64_t idx = (int64_t)blockIdx.x * TPB + threadIdx.x; idx < (int64_t)nh * COTIX_LUNAR_NDYN;
+       idx += (int64_t)gridDim.x * TPB) {
   const uint32_t slot = (uint32_t)(idx / COTIX_LUNAR_NDYN);
   const int k = (int)(idx - (int64_t)slot * COTIX_LUNAR_NDYN);
-  const uint32_t nh = *jw.ctr < jw.cap ? *jw.ctr : jw.cap;
-  if (slot >= nh) return;
   const int64_t i = jw.hlist[slot];
   const int64_t t = i / B, e = i - t * B;
   const float* sin_ = tape + t * (int64_t)COTIX_LUNAR_NF * ld;
@@ -835,6 +837,7 @@ lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
   Mk[18] = fin(g_am);
   Mk[19] = fin(g_as);
   if (k == 0 && flags_out && flags) atomicOr(&flags_out[e], flags);
+  }
 }
 
 // The collider's decisions of nt consecutive steps of a taped rollout in ONE launch: item = (step,
@@ -927,7 +930,9 @@ extern "C" int cx_launch_lunar_step_bwd(cudaStream_t st, int64_t B, const float*
 extern "C" int cx_launch_lunar_decide(cudaStream_t st, int64_t B, int nt, const float* tape_t0, int64_t ld,
                                       const float* actions_t0, float* dtape, uint32_t* flags,
                                       uint32_t* jac_ctr, uint32_t* jac_list, float* jac_M, uint32_t jac_cap,
-                                      const CotixLunarParams* p) {
+                                      const CotixLunarParams* p, int blocks_per_sm) {
+  // blocks_per_sm > 0: both grids are capped at that many blocks per SM (they loop), which leaves
+  // registers on every SM for sweep launches running concurrently on another stream
   if (B == 0 || nt == 0) return 0;
   LunarDerived D;
   cx_lunar_derive(p, &D);
@@ -939,13 +944,16 @@ extern "C" int cx_launch_lunar_decide(cudaStream_t st, int64_t B, int nt, const 
   jw.cap = jac_M ? jac_cap : 0u;
   if (jw.M && cudaMemsetAsync(jw.ctr, 0, 4, st) != cudaSuccess) return cx_check_launch("adjoint memset");
   int64_t blocks = (n + DECIDE_TILE - 1) / DECIDE_TILE;
-  const int64_t cap = (int64_t)cx_sm_count() * 16;
+  const int64_t cap = (int64_t)cx_sm_count() * (blocks_per_sm > 0 ? blocks_per_sm : 16);
   if (blocks > cap) blocks = cap;
   lunar_decide_kernel<<<(unsigned)blocks, TPB, 0, st>>>(B, nt, tape_t0, ld, actions_t0, dtape, jw, *p, D);
   cx_count_launch();
   if (jw.M) {
     const int64_t threads = (int64_t)jw.cap * COTIX_LUNAR_NDYN;
-    lunar_jacobian_kernel<<<(unsigned)((threads + TPB - 1) / TPB), TPB, 0, st>>>(B, tape_t0, ld, actions_t0, dtape,
+    int64_t jblocks = (threads + TPB - 1) / TPB;
+    if (blocks_per_sm > 0 && jblocks > (int64_t)cx_sm_count() * blocks_per_sm)
+      jblocks = (int64_t)cx_sm_count() * blocks_per_sm;
+    lunar_jacobian_kernel<<<(unsigned)jblocks, TPB, 0, st>>>(B, tape_t0, ld, actions_t0, dtape,
                                                                                 flags, jw, *p, D);
     cx_count_launch();
   }

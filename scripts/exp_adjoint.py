@@ -95,6 +95,9 @@ def main():
     for it in range(3):
         flags.zero_()
         ev[0].record()
+        if os.environ.get("ADJ_PIPE"):
+            from parallax_b200 import _lib
+            _lib.lib().cx_lunar_adjoint_set_pipelined(int(os.environ["ADJ_PIPE"]))
         ro = ll.rollout(st0, actions, T, P, mode=os.environ.get("MODE", "fused"))
         ev[1].record()
         y = ro.tape[-1, 1]
