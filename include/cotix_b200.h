@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define COTIX_ABI_VERSION 1
+#define COTIX_ABI_VERSION 2
 
 /* error codes */
 #define COTIX_OK 0
@@ -235,8 +235,56 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
                         int64_t workspace_bytes);
 
 /*
+ * n_steps consecutive steps IN PLACE on `state` in one enqueue: step t uses the action
+ * actions + (t % n_actions) * 2 * ld (DEVICE [n_actions][2][ld], or NULL), i.e. the loop
+ *   for _ in range(n_steps): env = f(env, key)          examples/test_viz.py:46-48
+ * as one call.  With a workspace (pipeline) the batch is cut into ranges of envs that run their
+ * n_steps on their own streams WITHOUT joining between steps, so the latency-bound sparse stages of
+ * one range execute under the dense stages of the others; the streams are forked from and joined
+ * back into `stream`, so the call is stream-ordered and CUDA-Graph capturable (cotix_graph_*):
+ * capture it once and a rollout of n_steps steps is ONE graph launch.  workspace NULL: n_steps
+ * launches of the fused kernel.  reward / done / obs (or NULL) hold the last step's values.
+ */
+int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, const float* actions,
+                         int32_t n_actions, int32_t n_steps, float* reward, uint8_t* done, float* obs,
+                         const CotixLunarParams* p, void* workspace, int64_t workspace_bytes);
+
+/*
+ * Launch configuration of the pipeline (process-wide; a negative value leaves a setting unchanged):
+ *   split          ranges of envs the batch is cut into, 1..COTIX_MAX_CHUNKS; 0 = automatic
+ *                  (ranges of >= 131072 envs, at most 4).  Results do not depend on it.
+ *   pdl            programmatic dependent launch between the stages of a range (default 1)
+ *   priorities     sparse stages (narrow, contact, reset) at the highest launch priority, dense
+ *                  stages at the lowest (default 1; only with split > 1)
+ *   item_capacity  slots of every range's collision-item queue; 0 = 4 * envs + 4096.  An env whose
+ *                  items do not fit evaluates its pairs inside the contact stage (same results); a
+ *                  small value is how the tests force that branch.
+ * cotix_lunar_pipeline_counters: queue lengths of the last step, summed over the ranges the
+ * workspace is cut into for batch B under the current configuration: out[0..4] = collision items,
+ * live contacts, envs with a candidate, auto-resets, envs that overflowed the item queue
+ * (measurement aid; copies to the host and synchronises `stream`).
+ */
+int cotix_lunar_pipeline_config(int split, int pdl, int priorities, int64_t item_capacity);
+int cotix_lunar_pipeline_counters(void* stream, int64_t B, const void* workspace, int64_t* out /*[5]*/);
+
+/*
+ * CUDA-Graph capture of any sequence of DEVICE entry points of this library (they only enqueue):
+ *   cotix_graph_begin_capture(stream); cotix_lunar_steps_ws(stream, ...); ...;
+ *   cotix_graph_end_capture(stream, &g);   then   cotix_graph_launch(g, stream)  per replay.
+ * This is the single dispatch per rollout that jax.jit gives the reference's loop
+ * (examples/test_viz.py:24,46-48).  Capture is thread-local; one open capture per thread.
+ */
+typedef struct CotixGraph CotixGraph;
+int cotix_graph_begin_capture(void* stream);
+int cotix_graph_end_capture(void* stream, CotixGraph** out);
+int cotix_graph_launch(CotixGraph* g, void* stream);
+int cotix_graph_info(const CotixGraph* g, int32_t* nodes, int64_t* kernel_launches);
+int cotix_graph_destroy(CotixGraph* g);
+
+/*
  * Per-stage timing of the pipeline (measurement aid; not thread-safe): while enabled, every
- * cotix_lunar_step_ws call records CUDA events between its stages on the launching stream.
+ * cotix_lunar_step_ws call runs as ONE range without programmatic dependent launch and records CUDA
+ * events between its stages on the launching stream (serial stage times).
  * cotix_lunar_pipeline_stage_ms writes the average milliseconds of integrate, narrow, contact,
  * finish, reset and the whole step
  * since profiling was enabled, and returns the number of steps averaged.
@@ -261,11 +309,14 @@ int cotix_lunar_env_destroy(CotixLunarEnv* env);
 #define COTIX_MODE_PIPELINE 2
 int cotix_lunar_env_set_mode(CotixLunarEnv* env, int mode);
 /*
- * Host-step chunking: cotix_lunar_env_step_host splits the batch into `chunks` ranges of envs
- * and runs H2D(action) of range c+1, the kernels of range c and D2H(obs, reward, done) of range
- * c-1 concurrently (three streams, PCIe in both directions at once).  Envs are independent, so
- * the results do not depend on `chunks`.  0 = automatic (ranges of >= 256K envs, at most 4:
- * each range pays the fixed latency of the kernels, about 0.1 ms).
+ * Host-step chunking: cotix_lunar_env_step_host splits the batch into `chunks` ranges of envs.
+ * In pipeline mode the ranges are the pipeline's own (cotix_lunar_pipeline_config `split`): H2D(action)
+ * of a range, its kernels and D2H(obs, reward, done) go on the range's stream, so PCIe traffic in both
+ * directions overlaps the kernels of the other ranges.  In fused mode H2D of range c+1, the kernel of
+ * range c and D2H of range c-1 run on three streams.  Envs are independent, so the results do not
+ * depend on `chunks`.  0 = automatic (pipeline: the configured split; fused: ranges of >= 256K envs,
+ * at most 4).  obs / reward / done of cotix_lunar_env_step_host may each be NULL: that output is not
+ * copied to the host (obs stays readable on the device) — obs is 86 % of the D2H bytes of a step.
  */
 #define COTIX_MAX_CHUNKS 16
 int cotix_lunar_env_set_chunks(CotixLunarEnv* env, int chunks);
@@ -468,6 +519,29 @@ int cotix_threefry2x32(void* stream, int64_t n, uint32_t k0, uint32_t k1,
 /* out[i] = philox4x32_10(key, ctr[i]) ; ctr, out are [n][4]                               */
 int cotix_philox4x32(void* stream, int64_t n, uint32_t k0, uint32_t k1,
                      const uint32_t* ctr, uint32_t* out);
+
+/* ------------------------------------------------------------------------------------ */
+/* Device memory, streams and events for hosts that have no CUDA binding of their own      */
+/* (ctypes, cgo, JNI ...): thin wrappers over the CUDA runtime so that the Python mirror    */
+/* runs without torch.  `stream` NULL = the default stream.  cotix_memcpy infers the        */
+/* direction from the pointers (cudaMemcpyDefault) and is asynchronous on `stream` for      */
+/* page-locked host memory.                                                                 */
+/* ------------------------------------------------------------------------------------ */
+int cotix_set_device(int device);
+int cotix_device_count(int* n);
+int cotix_device_malloc(int64_t bytes, void** out);
+int cotix_device_free(void* p);
+int cotix_host_malloc(int64_t bytes, void** out); /* page-locked */
+int cotix_host_free(void* p);
+int cotix_memcpy(void* stream, void* dst, const void* src, int64_t bytes);
+int cotix_memset(void* stream, void* dst, int value, int64_t bytes);
+int cotix_stream_create(void** out);
+int cotix_stream_destroy(void* stream);
+int cotix_stream_synchronize(void* stream);
+int cotix_event_create(void** out);
+int cotix_event_destroy(void* event);
+int cotix_event_record(void* event, void* stream);
+int cotix_event_elapsed_ms(void* start, void* stop, float* ms); /* waits for `stop` */
 
 /* ------------------------------------------------------------------------------------ */
 const char* cotix_last_error(void);

@@ -1966,6 +1966,18 @@ int oracle_num_threads(void) {
   return 1;
 #endif
 }
+// explicit thread count for the timed CPU arm (torchrun exports OMP_NUM_THREADS=1); n <= 0: all
+// logical cores of the box
+int oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n <= 0) n = omp_get_num_procs();
+  omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
 int oracle_sizeof_lunar_params(void) { return (int)sizeof(CotixLunarParams); }
 const char* oracle_last_error(void) { return g_err; }
 

@@ -14,6 +14,23 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
+
+def _timing_lib_path() -> str:
+    """-march=native code must be built by the machine that runs it: the file name carries a hash
+    of this CPU's feature flags, so a library built on another box is never loaded here."""
+    import hashlib
+
+    flags = ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    flags = line
+                    break
+    except OSError:
+        pass
+    return os.path.join(_HERE, "_native", f"liboracle_timing_{hashlib.md5(flags.encode()).hexdigest()[:10]}.so")
+
 NF = 36
 REC = 16
 
@@ -22,8 +39,17 @@ def build(force: bool = False) -> str:
     """Compile liboracle.so with the committed Makefile (g++, -ffp-contract=off)."""
     src = os.path.join(_HERE, "cotix_oracle.cpp")
     if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
-        subprocess.check_call(["make", "-C", _HERE, "-s"])
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
     return _LIB_PATH
+
+
+def build_timing(force: bool = False) -> str:
+    """The -O3 -march=native build for the timed CPU legs of bench.py, compiled on this machine."""
+    src = os.path.join(_HERE, "cotix_oracle.cpp")
+    out = _timing_lib_path()
+    if force or not os.path.exists(out) or os.path.getmtime(out) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s", "timing", f"TIMING_OUT={out}"] + (["-B"] if force else []))
+    return out
 
 
 class NarrowParams(C.Structure):
@@ -83,17 +109,30 @@ class LunarParams(C.Structure):
 
 
 _lib = None
+_libs: dict = {}
+_build_kind = "parity"
+
+
+def select_build(kind: str) -> None:
+    """"parity" (default): liboracle.so, -ffp-contract=off, the checker.  "timing": the same source
+    built -O3 -march=native (liboracle_timing.so) for bench.py's timed CPU legs only."""
+    global _lib, _build_kind
+    assert kind in ("parity", "timing")
+    _build_kind = kind
+    _lib = None
 
 
 def lib():
     global _lib
     if _lib is None:
-        build()
-        _lib = C.CDLL(_LIB_PATH)
-        assert _lib.oracle_sizeof_lunar_params() == C.sizeof(LunarParams), (
-            _lib.oracle_sizeof_lunar_params(),
-            C.sizeof(LunarParams),
-        )
+        if _build_kind not in _libs:
+            L = C.CDLL(build() if _build_kind == "parity" else build_timing())
+            assert L.oracle_sizeof_lunar_params() == C.sizeof(LunarParams), (
+                L.oracle_sizeof_lunar_params(),
+                C.sizeof(LunarParams),
+            )
+            _libs[_build_kind] = L
+        _lib = _libs[_build_kind]
     return _lib
 
 
@@ -109,6 +148,12 @@ def _f32(a):
 
 def num_threads() -> int:
     return int(lib().oracle_num_threads())
+
+
+def set_num_threads(n: int = 0) -> int:
+    """OpenMP threads of the oracle's batched entry points; n <= 0 = every logical core.  Returns the
+    count in effect.  (torchrun exports OMP_NUM_THREADS=1: the timed CPU arm sets this explicitly.)"""
+    return int(lib().oracle_set_num_threads(int(n)))
 
 
 def set_trig_mode(mode: int) -> None:

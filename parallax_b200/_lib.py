@@ -19,7 +19,7 @@ SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu",
            "scene_kernel.cu", "lunar_adjoint.cu", "raster_kernel.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
-    "-lineinfo", "-O3", "-std=c++17",
+    "-lineinfo", "-O3", "-std=c++17", "-t", "8",
     "-fmad=false",            # IEEE-exact fp32: no FMA contraction (see csrc/cx_math.cuh)
     "-Xcompiler", "-fPIC", "-shared",
 ]
@@ -158,6 +158,13 @@ EXPORTS = [
     "cotix_scene_step",
     "cotix_lunar_step_bwd", "cotix_lunar_rollout", "cotix_lunar_rollout_bwd",
     "cotix_lunar_adjoint_workspace_bytes", "cotix_lunar_adjoint_decisions_bytes", "cotix_raster_draw", "cotix_lunar_draw", "cotix_lunar_prims",
+    "cotix_lunar_steps_ws", "cotix_lunar_pipeline_config", "cotix_lunar_pipeline_counters",
+    "cotix_graph_begin_capture", "cotix_graph_end_capture", "cotix_graph_launch", "cotix_graph_info",
+    "cotix_graph_destroy",
+    "cotix_set_device", "cotix_device_count", "cotix_device_malloc", "cotix_device_free", "cotix_host_malloc",
+    "cotix_host_free", "cotix_memcpy", "cotix_memset", "cotix_stream_create", "cotix_stream_destroy",
+    "cotix_stream_synchronize", "cotix_event_create", "cotix_event_destroy", "cotix_event_record",
+    "cotix_event_elapsed_ms",
 ]
 
 _lib = None
@@ -229,7 +236,31 @@ def lib() -> C.CDLL:
     L.cotix_philox4x32.argtypes = [vp, i64, C.c_uint32, C.c_uint32, vp, vp]
     L.cotix_device_info.argtypes = [C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int),
                                     C.POINTER(C.c_int), C.POINTER(C.c_int)]
-    if L.cotix_abi_version() != 1:
+    L.cotix_lunar_steps_ws.argtypes = [vp, i64, vp, i64, vp, C.c_int32, C.c_int32, vp, vp, vp, C.POINTER(LunarParams),
+                                       vp, i64]
+    L.cotix_lunar_pipeline_config.argtypes = [C.c_int, C.c_int, C.c_int, i64]
+    L.cotix_lunar_pipeline_counters.argtypes = [vp, i64, vp, C.POINTER(i64)]
+    L.cotix_graph_begin_capture.argtypes = [vp]
+    L.cotix_graph_end_capture.argtypes = [vp, C.POINTER(vp)]
+    L.cotix_graph_launch.argtypes = [vp, vp]
+    L.cotix_graph_info.argtypes = [vp, C.POINTER(C.c_int32), C.POINTER(i64)]
+    L.cotix_graph_destroy.argtypes = [vp]
+    L.cotix_set_device.argtypes = [C.c_int]
+    L.cotix_device_count.argtypes = [C.POINTER(C.c_int)]
+    L.cotix_device_malloc.argtypes = [i64, C.POINTER(vp)]
+    L.cotix_device_free.argtypes = [vp]
+    L.cotix_host_malloc.argtypes = [i64, C.POINTER(vp)]
+    L.cotix_host_free.argtypes = [vp]
+    L.cotix_memcpy.argtypes = [vp, vp, vp, i64]
+    L.cotix_memset.argtypes = [vp, vp, C.c_int, i64]
+    L.cotix_stream_create.argtypes = [C.POINTER(vp)]
+    L.cotix_stream_destroy.argtypes = [vp]
+    L.cotix_stream_synchronize.argtypes = [vp]
+    L.cotix_event_create.argtypes = [C.POINTER(vp)]
+    L.cotix_event_destroy.argtypes = [vp]
+    L.cotix_event_record.argtypes = [vp, vp]
+    L.cotix_event_elapsed_ms.argtypes = [vp, vp, C.POINTER(C.c_float)]
+    if L.cotix_abi_version() != 2:
         raise CotixError("libcotix_b200.so ABI version mismatch")
     _lib = L
     return L

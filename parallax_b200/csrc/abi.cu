@@ -310,4 +310,87 @@ int cotix_philox4x32(void* stream, int64_t n, uint32_t k0, uint32_t k1, const ui
   return cx_check_launch("philox_kernel");
 }
 
+// ---- device memory, streams and events for hosts without a CUDA binding of their own ----------
+int cotix_set_device(int device) {
+  CX_CUDA(cudaSetDevice(device));
+  return COTIX_OK;
+}
+int cotix_device_count(int* n) {
+  CX_REQUIRE(n != nullptr, "n is null");
+  *n = 0;
+  if (cudaGetDeviceCount(n) != cudaSuccess) {
+    cudaGetLastError();
+    *n = 0;
+  }
+  return COTIX_OK;
+}
+int cotix_device_malloc(int64_t bytes, void** out) {
+  CX_REQUIRE(out != nullptr && bytes >= 0, "bad arguments");
+  *out = nullptr;
+  if (bytes == 0) return COTIX_OK;
+  CX_CUDA(cudaMalloc(out, (size_t)bytes));
+  return COTIX_OK;
+}
+int cotix_device_free(void* p) {
+  if (p) CX_CUDA(cudaFree(p));
+  return COTIX_OK;
+}
+int cotix_host_malloc(int64_t bytes, void** out) {
+  CX_REQUIRE(out != nullptr && bytes >= 0, "bad arguments");
+  *out = nullptr;
+  if (bytes == 0) return COTIX_OK;
+  CX_CUDA(cudaHostAlloc(out, (size_t)bytes, cudaHostAllocDefault));
+  return COTIX_OK;
+}
+int cotix_host_free(void* p) {
+  if (p) CX_CUDA(cudaFreeHost(p));
+  return COTIX_OK;
+}
+int cotix_memcpy(void* stream, void* dst, const void* src, int64_t bytes) {
+  CX_REQUIRE(bytes >= 0 && (bytes == 0 || (dst && src)), "bad arguments");
+  if (bytes) CX_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  return COTIX_OK;
+}
+int cotix_memset(void* stream, void* dst, int value, int64_t bytes) {
+  CX_REQUIRE(bytes >= 0 && (bytes == 0 || dst), "bad arguments");
+  if (bytes) CX_CUDA(cudaMemsetAsync(dst, value, (size_t)bytes, (cudaStream_t)stream));
+  return COTIX_OK;
+}
+int cotix_stream_create(void** out) {
+  CX_REQUIRE(out != nullptr, "out is null");
+  cudaStream_t s;
+  CX_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+  *out = (void*)s;
+  return COTIX_OK;
+}
+int cotix_stream_destroy(void* stream) {
+  if (stream) CX_CUDA(cudaStreamDestroy((cudaStream_t)stream));
+  return COTIX_OK;
+}
+int cotix_stream_synchronize(void* stream) {
+  CX_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return COTIX_OK;
+}
+int cotix_event_create(void** out) {
+  CX_REQUIRE(out != nullptr, "out is null");
+  cudaEvent_t e;
+  CX_CUDA(cudaEventCreate(&e));
+  *out = (void*)e;
+  return COTIX_OK;
+}
+int cotix_event_destroy(void* event) {
+  if (event) CX_CUDA(cudaEventDestroy((cudaEvent_t)event));
+  return COTIX_OK;
+}
+int cotix_event_record(void* event, void* stream) {
+  CX_CUDA(cudaEventRecord((cudaEvent_t)event, (cudaStream_t)stream));
+  return COTIX_OK;
+}
+int cotix_event_elapsed_ms(void* start, void* stop, float* ms) {
+  CX_REQUIRE(ms != nullptr, "ms is null");
+  CX_CUDA(cudaEventSynchronize((cudaEvent_t)stop));
+  CX_CUDA(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+  return COTIX_OK;
+}
+
 }  // extern "C"

@@ -11,6 +11,7 @@
 
 #include "../../include/cotix_b200.h"
 #include "cx_launch.cuh"
+#include "cx_pipeline.h"
 #include "cx_rng.cuh"
 
 extern "C" int cx_launch_lunar_step(cudaStream_t, int64_t, const float*, float*, int64_t,
@@ -18,10 +19,6 @@ extern "C" int cx_launch_lunar_step(cudaStream_t, int64_t, const float*, float*,
 extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, float*, int64_t,
                                      const CotixLunarParams*);
 
-extern "C" int64_t cx_lunar_pipeline_workspace_bytes(int64_t B);
-extern "C" int cx_lunar_pipeline_profile(int enable);
-extern "C" int cx_lunar_pipeline_profiling();
-extern "C" int64_t cx_lunar_pipeline_stage_ms(double* out);
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, const float*, int64_t,
                                         const float*, const float*, float*, float*, uint32_t*,
                                         const float*, const float*, const CotixLunarParams*);
@@ -33,8 +30,6 @@ extern "C" int cx_launch_lunar_draw(cudaStream_t, int64_t, const float*, int64_t
                                     const CotixLunarParams*);
 extern "C" int cx_launch_lunar_prims(cudaStream_t, int64_t, const float*, int64_t, const int64_t*, int32_t*,
                                      const CotixLunarParams*);
-extern "C" int cx_launch_lunar_pipeline(cudaStream_t, int64_t, const float*, float*, int64_t, const float*,
-                                        float*, uint8_t*, float*, const CotixLunarParams*, void*, int64_t);
 
 #define CXL_REQUIRE(cond, msg)               \
   do {                                       \
@@ -278,6 +273,95 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
                                   obs, p, workspace, workspace_bytes);
 }
 
+int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, const float* actions,
+                         int32_t n_actions, int32_t n_steps, float* reward, uint8_t* done, float* obs,
+                         const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
+  CXL_REQUIRE(B >= 0 && ld >= B && n_steps >= 0, "bad batch size / leading dimension / step count");
+  CXL_REQUIRE(check_params(p), "bad params");
+  CXL_REQUIRE(B == 0 || state, "null state");
+  CXL_REQUIRE(!actions || n_actions >= 1, "n_actions must be >= 1 when actions are given");
+  if (workspace)
+    return cx_launch_lunar_pipeline_steps((cudaStream_t)stream, B, state, state, 0, ld, actions, 2 * ld,
+                                          n_actions, n_steps, reward, done, obs, p, workspace, workspace_bytes);
+  for (int32_t t = 0; t < n_steps; ++t) {
+    const float* a = actions ? actions + (int64_t)(t % n_actions) * 2 * ld : nullptr;
+    const int rc = cx_launch_lunar_step((cudaStream_t)stream, B, state, state, ld, a, reward, done, obs, p);
+    if (rc != 0) return rc;
+  }
+  return COTIX_OK;
+}
+
+int cotix_lunar_pipeline_config(int split, int pdl, int priorities, int64_t item_capacity) {
+  const int rc = cx_lunar_pipeline_config(split, pdl, priorities, item_capacity);
+  if (rc != 0) cx_set_error("cotix_lunar_pipeline_config: split must be <= %d", COTIX_MAX_CHUNKS);
+  return rc;
+}
+int cotix_lunar_pipeline_counters(void* stream, int64_t B, const void* workspace, int64_t* out) {
+  CXL_REQUIRE(B > 0 && workspace && out, "null argument");
+  return cx_lunar_pipeline_counters((cudaStream_t)stream, B, workspace, out);
+}
+
+// ---- CUDA-graph capture of any sequence of device entry points ----------------------------------
+struct CotixGraph {
+  cudaGraphExec_t exec;
+  int64_t launches;  // kernels per replay
+  int nodes;
+};
+namespace {
+thread_local int64_t g_capture_base = -1;
+}
+int cotix_graph_begin_capture(void* stream) {
+  CXL_REQUIRE(g_capture_base < 0, "a capture is already open on this thread");
+  CXL_CUDA(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+  g_capture_base = cotix_launch_count();
+  return COTIX_OK;
+}
+int cotix_graph_end_capture(void* stream, CotixGraph** out) {
+  CXL_REQUIRE(g_capture_base >= 0, "no capture open on this thread");
+  cudaGraph_t g = nullptr;
+  const cudaError_t ce = cudaStreamEndCapture((cudaStream_t)stream, &g);
+  const int64_t captured = cotix_launch_count() - g_capture_base;
+  g_capture_base = -1;
+  cx_count_launch_n(-captured);  // captured, not executed
+  CXL_CUDA(ce);
+  CXL_REQUIRE(out != nullptr, "out is null");
+  CotixGraph* cg = new (std::nothrow) CotixGraph();
+  if (!cg) {
+    cudaGraphDestroy(g);
+    CXL_REQUIRE(false, "out of host memory");
+  }
+  size_t nn = 0;
+  cudaGraphGetNodes(g, nullptr, &nn);
+  cg->nodes = (int)nn;
+  cg->launches = captured;
+  const cudaError_t ie = cudaGraphInstantiate(&cg->exec, g, 0);
+  cudaGraphDestroy(g);
+  if (ie != cudaSuccess) {
+    delete cg;
+    CXL_CUDA(ie);
+  }
+  *out = cg;
+  return COTIX_OK;
+}
+int cotix_graph_launch(CotixGraph* g, void* stream) {
+  CXL_REQUIRE(g != nullptr, "graph is null");
+  CXL_CUDA(cudaGraphLaunch(g->exec, (cudaStream_t)stream));
+  cx_count_launch_n(g->launches);
+  return COTIX_OK;
+}
+int cotix_graph_info(const CotixGraph* g, int32_t* nodes, int64_t* kernel_launches) {
+  CXL_REQUIRE(g != nullptr, "graph is null");
+  if (nodes) *nodes = g->nodes;
+  if (kernel_launches) *kernel_launches = g->launches;
+  return COTIX_OK;
+}
+int cotix_graph_destroy(CotixGraph* g) {
+  if (!g) return COTIX_OK;
+  cudaGraphExecDestroy(g->exec);
+  delete g;
+  return COTIX_OK;
+}
+
 // ---- differentiable rollout (K5) ----------------------------------------------------
 int cotix_lunar_step_bwd(void* stream, int64_t B, const float* state_in, const float* state_next,
                          int64_t ld, const float* action, const float* g_out, float* g_in,
@@ -296,15 +380,14 @@ int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t
   CXL_REQUIRE(check_params(p), "bad params");
   CXL_REQUIRE(B == 0 || tape, "null tape");
   const int64_t slot = (int64_t)COTIX_LUNAR_NF * ld;
+  if (workspace)  // the ranges of the pipeline run their T steps without joining
+    return cx_launch_lunar_pipeline_steps((cudaStream_t)stream, B, tape, tape + slot, slot, ld, actions, 2 * ld,
+                                          T > 0 ? T : 1, T, nullptr, nullptr, nullptr, p, workspace,
+                                          workspace_bytes);
   for (int32_t t = 0; t < T; ++t) {
     const float* a = actions ? actions + (int64_t)t * 2 * ld : nullptr;
-    int rc;
-    if (workspace)
-      rc = cx_launch_lunar_pipeline((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot, ld, a,
-                                    nullptr, nullptr, nullptr, p, workspace, workspace_bytes);
-    else
-      rc = cx_launch_lunar_step((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot, ld, a,
-                                nullptr, nullptr, nullptr, p);
+    const int rc = cx_launch_lunar_step((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot, ld, a,
+                                        nullptr, nullptr, nullptr, p);
     if (rc != 0) return rc;
   }
   return 0;
@@ -332,6 +415,7 @@ struct AdjSide {
   cudaStream_t s;
   cudaEvent_t fork, done[8];
   int state;  // 0 not made, 1 ok, -1 failed
+  std::mutex mu;  // held from fork to join: the stream and events are shared by all callers on the device
 };
 static AdjSide* adj_side() {
   static AdjSide per_dev[64];
@@ -402,6 +486,7 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
   const bool overlap = g_adj_pipelined != 0 && !(env_overlap && env_overlap[0] == '0');
   AdjSide* side = (jac && overlap && group >= T && T >= 2 * NG) ? adj_side() : nullptr;
   if (side) {
+    std::lock_guard<std::mutex> lock(side->mu);
     cudaStream_t st = (cudaStream_t)stream;
     const int32_t ns = (T + NG - 1) / NG;
     int32_t b[NG + 1];
@@ -409,31 +494,29 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
     if (cudaEventRecord(side->fork, st) != cudaSuccess || cudaStreamWaitEvent(side->s, side->fork, 0) != cudaSuccess)
       return cx_check_launch("adjoint fork");
     const int64_t cap1 = adj_jac_cap(ld);
+    int rc = 0;  // after the fork every path runs to the joins (an early return would leave a capture unjoined)
     for (int i = NG - 1; i >= 0; --i) {
       const int32_t nt = b[i + 1] - b[i];
-      if (nt > 0) {
+      if (nt > 0 && rc == 0) {
         const int64_t off = cap1 * b[i];
-        const int rc = cx_launch_lunar_decide(side->s, B, nt, tape + b[i] * slot, ld,
-                                              actions ? actions + (int64_t)b[i] * 2 * ld : nullptr, dt + b[i] * dslot,
-                                              flags, jctr + i, jlist + off, jM + off * 20 * COTIX_LUNAR_NDYN,
-                                              (uint32_t)(cap1 * nt), p,
-                                              (i == NG - 1 || g_adj_pipelined < 0) ? 0 : g_adj_pipelined);
-        if (rc != 0) return rc;
+        rc = cx_launch_lunar_decide(side->s, B, nt, tape + b[i] * slot, ld,
+                                    actions ? actions + (int64_t)b[i] * 2 * ld : nullptr, dt + b[i] * dslot, flags,
+                                    jctr + i, jlist + off, jM + off * 20 * COTIX_LUNAR_NDYN, (uint32_t)(cap1 * nt), p,
+                                    (i == NG - 1 || g_adj_pipelined < 0) ? 0 : g_adj_pipelined);
       }
-      if (cudaEventRecord(side->done[i], side->s) != cudaSuccess) return cx_check_launch("adjoint event");
+      if (cudaEventRecord(side->done[i], side->s) != cudaSuccess && rc == 0) rc = cx_check_launch("adjoint event");
     }
     for (int i = NG - 1; i >= 0; --i) {
-      if (cudaStreamWaitEvent(st, side->done[i], 0) != cudaSuccess) return cx_check_launch("adjoint join");
+      if (cudaStreamWaitEvent(st, side->done[i], 0) != cudaSuccess && rc == 0) rc = cx_check_launch("adjoint join");
       const int64_t off = cap1 * b[i];
-      for (int32_t s = b[i + 1] - 1; s >= b[i]; --s) {
+      for (int32_t s = b[i + 1] - 1; s >= b[i] && rc == 0; --s) {
         const float* a = actions ? actions + (int64_t)s * 2 * ld : nullptr;
         float* ga = g_actions ? g_actions + (int64_t)s * 2 * ld : nullptr;
-        const int rc = cx_launch_lunar_step_bwd(st, B, tape + s * slot, tape + (s + 1) * slot, ld, a, g, g, ga, flags,
-                                                dt + s * dslot, jM + off * 20 * COTIX_LUNAR_NDYN, p);
-        if (rc != 0) return rc;
+        rc = cx_launch_lunar_step_bwd(st, B, tape + s * slot, tape + (s + 1) * slot, ld, a, g, g, ga, flags,
+                                      dt + s * dslot, jM + off * 20 * COTIX_LUNAR_NDYN, p);
       }
     }
-    return 0;
+    return rc;
   }
   int32_t t = T;
   while (t > 0) {
@@ -666,35 +749,9 @@ int cotix_lunar_env_reset_host(CotixLunarEnv* e, const uint32_t* keys) {
 // handle's stream computes, s_out copies the results out; [rows][B] host arrays are copied as
 // 2-D blocks of pitch B.  With `forkjoin` the side streams are forked from and joined back into
 // the handle's stream (what stream capture needs).
-// COTIX_TRACE=<step>: print the device timeline of that host step (un-graphed path) to stderr
-static cudaEvent_t g_tr[4][COTIX_MAX_CHUNKS], g_tr_base;
-static int g_tr_state = -1, g_tr_step = 0;  // -1 unknown, 0 off, 1 armed
-static bool trace_armed() {
-  if (g_tr_state < 0) {
-    const char* v = getenv("COTIX_TRACE");
-    g_tr_state = v ? 1 : 0;
-    if (v) {
-      g_tr_step = atoi(v);
-      cudaEventCreate(&g_tr_base);
-      for (int i = 0; i < 4; ++i)
-        for (int c = 0; c < COTIX_MAX_CHUNKS; ++c) cudaEventCreate(&g_tr[i][c]);
-    }
-  }
-  return g_tr_state == 1;
-}
-static void trace_print(int C) {
-  fprintf(stderr, "[cotix trace] range: h2d done | compute start..end | d2h done  (ms)\n");
-  for (int c = 0; c < C; ++c) {
-    float t[4];
-    for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&t[i], g_tr_base, g_tr[i][c]);
-    fprintf(stderr, "[cotix trace] %2d: %.3f | %.3f .. %.3f | %.3f\n", c, t[0], t[1], t[2], t[3]);
-  }
-}
-
 static int enqueue_chunked(CotixLunarEnv* e, int C, int64_t len, const float* action, float* obs,
-                           float* reward, uint8_t* done, bool forkjoin, bool trace = false) {
+                           float* reward, uint8_t* done, bool forkjoin) {
   const size_t pitch = sizeof(float) * (size_t)e->B;
-  if (trace) cudaEventRecord(g_tr_base, e->s_in);
   if (forkjoin) {
     CXL_CUDA(cudaEventRecord(e->ev_fork, e->stream));
     CXL_CUDA(cudaStreamWaitEvent(e->s_in, e->ev_fork, 0));
@@ -709,13 +766,8 @@ static int enqueue_chunked(CotixLunarEnv* e, int C, int64_t len, const float* ac
       CXL_CUDA(cudaEventRecord(e->ev_in[c], e->s_in));
       CXL_CUDA(cudaStreamWaitEvent(e->stream, e->ev_in[c], 0));
     }
-    if (trace) {
-      cudaEventRecord(g_tr[0][c], e->s_in);
-      cudaEventRecord(g_tr[1][c], e->stream);
-    }
     int rc = env_enqueue_range(e, off, n, action ? e->action : nullptr, obs ? e->obs : nullptr);
     if (rc) return rc;
-    if (trace) cudaEventRecord(g_tr[2][c], e->stream);
     CXL_CUDA(cudaEventRecord(e->ev_done[c], e->stream));
     CXL_CUDA(cudaStreamWaitEvent(e->s_out, e->ev_done[c], 0));
     if (obs)
@@ -726,7 +778,6 @@ static int enqueue_chunked(CotixLunarEnv* e, int C, int64_t len, const float* ac
                                cudaMemcpyDeviceToHost, e->s_out));
     if (done)
       CXL_CUDA(cudaMemcpyAsync(done + off, e->done + off, (size_t)n, cudaMemcpyDeviceToHost, e->s_out));
-    if (trace) cudaEventRecord(g_tr[3][c], e->s_out);
   }
   if (forkjoin) {
     CXL_CUDA(cudaEventRecord(e->ev_join[0], e->s_in));
@@ -754,14 +805,41 @@ static void drop_host_graphs(CotixLunarEnv* e) {
   e->hgraphs->clear();
 }
 
+// pipeline mode: the ranges of the wavefront pipeline ARE the chunks of the host step — H2D(action) of
+// a range, its kernels and D2H(obs, reward, done) are enqueued on the range's own stream, so copies in
+// both directions overlap the kernels of the other ranges (and the sparse stages of one range run
+// under the dense stages of another); [rows][B] host arrays are copied as 2-D blocks of pitch B
+static int enqueue_ranges(CotixLunarEnv* e, int split, const float* action, float* obs, float* reward,
+                          uint8_t* done) {
+  const size_t pitch = sizeof(float) * (size_t)e->B;
+  CxRangeHook pre = [&](cudaStream_t cs, int, int64_t off, int64_t n) -> int {
+    if (action)
+      CXL_CUDA(cudaMemcpy2DAsync(e->action + off, pitch, action + off, pitch, sizeof(float) * (size_t)n, 2,
+                                 cudaMemcpyHostToDevice, cs));
+    return COTIX_OK;
+  };
+  CxRangeHook post = [&](cudaStream_t cs, int, int64_t off, int64_t n) -> int {
+    if (obs)
+      CXL_CUDA(cudaMemcpy2DAsync(obs + off, pitch, e->obs + off, pitch, sizeof(float) * (size_t)n,
+                                 COTIX_LUNAR_NOBS, cudaMemcpyDeviceToHost, cs));
+    if (reward)
+      CXL_CUDA(cudaMemcpyAsync(reward + off, e->reward + off, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, cs));
+    if (done) CXL_CUDA(cudaMemcpyAsync(done + off, e->done + off, (size_t)n, cudaMemcpyDeviceToHost, cs));
+    return COTIX_OK;
+  };
+  return cx_launch_lunar_pipeline_hooked(e->stream, e->B, e->state, e->B, action ? e->action : nullptr, e->reward,
+                                         e->done, obs ? e->obs : nullptr, &e->P, e->ws, e->ws_bytes, split, pre, post);
+}
+
 int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs, float* reward,
                               uint8_t* done) {
   CXL_REQUIRE(e != nullptr, "env is null");
   CXL_CUDA(cudaSetDevice(e->device));
   const size_t B = (size_t)e->B;
+  const bool pipe = e->mode == COTIX_MODE_PIPELINE || (e->mode == COTIX_MODE_AUTO && e->B >= 16384);
   int64_t len = 0;
-  const int C = plan_chunks(e, &len);
-  if (C == 1) {
+  const int C = pipe ? e->chunks : plan_chunks(e, &len);
+  if (!pipe && C == 1) {
     if (action)
       CXL_CUDA(cudaMemcpyAsync(e->action, action, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, e->stream));
     int rc = env_enqueue_step(e, action ? e->action : nullptr, obs ? e->obs : nullptr);
@@ -777,12 +855,11 @@ int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs,
   const bool graphable = e->host_graphs && !cx_lunar_pipeline_profiling() && host_pinned(action) &&
                          host_pinned(obs) && host_pinned(reward) && host_pinned(done);
   if (!graphable) {
-    const bool trace = trace_armed() && (g_tr_step-- == 0);
-    int rc = enqueue_chunked(e, C, len, action, obs, reward, done, false, trace);
+    int rc = pipe ? enqueue_ranges(e, C, action, obs, reward, done)
+                  : enqueue_chunked(e, C, len, action, obs, reward, done, false);
     if (rc) return rc;
-    CXL_CUDA(cudaStreamSynchronize(e->s_out));
+    if (!pipe) CXL_CUDA(cudaStreamSynchronize(e->s_out));
     CXL_CUDA(cudaStreamSynchronize(e->stream));
-    if (trace) trace_print(C);
     return COTIX_OK;
   }
   // the whole pipelined step as one replayed CUDA graph, cached per set of host buffers (an RL
@@ -797,7 +874,8 @@ int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs,
     cudaGraph_t g;
     CXL_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
     const int64_t before = cotix_launch_count();
-    int rc = enqueue_chunked(e, C, len, action, obs, reward, done, true);
+    int rc = pipe ? enqueue_ranges(e, C, action, obs, reward, done)
+                  : enqueue_chunked(e, C, len, action, obs, reward, done, true);
     cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
     const int64_t captured = cotix_launch_count() - before;
     cx_count_launch_n(-captured);  // captured, not executed
@@ -855,7 +933,12 @@ int cotix_lunar_env_rollout_graph(CotixLunarEnv* e, int32_t n_steps, const float
     CXL_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
     int rc = COTIX_OK;
     const int64_t before = cotix_launch_count();
-    for (int s = 0; s < n_steps && rc == COTIX_OK; ++s) rc = env_enqueue_step(e, action_dev, nullptr);
+    const bool pipe = e->mode == COTIX_MODE_PIPELINE || (e->mode == COTIX_MODE_AUTO && e->B >= 16384);
+    if (pipe)  // the ranges run their n_steps without joining
+      rc = cx_launch_lunar_pipeline_steps(e->stream, e->B, e->state, e->state, 0, e->B, action_dev, 0, 1, n_steps,
+                                          e->reward, e->done, nullptr, &e->P, e->ws, e->ws_bytes);
+    else
+      for (int s = 0; s < n_steps && rc == COTIX_OK; ++s) rc = env_enqueue_step(e, action_dev, nullptr);
     cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
     const int64_t captured = cotix_launch_count() - before;
     e->graph_launches = captured / n_steps;  // kernels per step under the current strategy

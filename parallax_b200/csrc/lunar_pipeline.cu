@@ -25,8 +25,11 @@
 // is 1 memset + 5 launches with no host synchronisation and is CUDA-Graph capturable.  All
 // stages call the same device functions as the fused kernel (cx_lunar_step.cuh): results are
 // identical bit for bit.
+#include <mutex>
+
 #include "cx_launch.cuh"
 #include "cx_lunar_step.cuh"
+#include "cx_pipeline.h"
 
 namespace {
 
@@ -615,12 +618,11 @@ pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
   }
 }
 
-// optional per-stage timing (bench.py's roofline of the dominant kernel): CUDA events recorded
-// between the stages on the launching stream while profiling is enabled
+// optional per-stage timing (bench.py's per-stage roofline objects): CUDA events recorded between
+// the stages on the launching stream while profiling is enabled (one range, no PDL: serial times)
 // stages: 0 integrate, 1 narrow, 2 contact, 3 finish, 4 reset, 5 whole step
 constexpr int N_STAGES = 6;
 bool g_profile = false;
-bool g_pdl = true;  // programmatic dependent launch between the stages
 cudaEvent_t g_evb[N_STAGES], g_eve[N_STAGES];
 bool g_ev_made = false;
 double g_stage_ms[N_STAGES];
@@ -639,12 +641,34 @@ void profile_collect() {
   g_ev_pending = false;
 }
 
-size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
-uint32_t item_capacity(int64_t B) { return (uint32_t)(4 * B + 4096); }
+// ---- launch configuration (cotix_lunar_pipeline_config) ------------------------------------
+// The two sparse stages (narrow, contact) are bound by the latency of their slowest work item
+// (about 32 us each however short the queue) and leave most of the GPU idle; the two dense stages
+// are issue-bound.  Envs are independent, so the batch is cut into `split` RANGES of envs, each with
+// its own queues and its own stream: the sparse stages of one range run under the dense stages of
+// the others.  The ranges of a multi-step enqueue never join between steps.  Sparse kernels are
+// launched at the highest priority so that they get SM slots as soon as blocks of a dense kernel
+// retire instead of queueing behind its remaining blocks.
+constexpr int MAX_SPLIT = COTIX_MAX_CHUNKS;
+struct PipeCfg {
+  int split;          // 0 = automatic
+  int pdl;            // programmatic dependent launch between the stages of a range
+  int prio;           // sparse stages at high launch priority
+  uint32_t item_cap;  // 0 = 4 B + 4096 per range; tests force the overflow branch with a small value
+  int min_range;      // automatic split: envs per range at least this many
+};
+PipeCfg g_cfg = {0, 1, 1, 0u, 131072};
 
-// carve the workspace; returns the bytes needed
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+// the forced capacity (tests) can only shrink the queue: workspace sizes are those of the default
+uint32_t item_capacity(int64_t B) {
+  const uint32_t full = (uint32_t)(4 * B + 4096);
+  return (g_cfg.item_cap && g_cfg.item_cap < full) ? g_cfg.item_cap : full;
+}
+
+// carve the workspace of one range; returns the bytes needed
 size_t carve(int64_t B, void* base, PipeWs* ws) {
-  const size_t cap = item_capacity(B);
+  const size_t cap = (size_t)(4 * B + 4096);  // layout by the default capacity
   size_t off = 0;
   char* p = static_cast<char*>(base);
   auto take = [&](size_t bytes) {
@@ -667,44 +691,130 @@ size_t carve(int64_t B, void* base, PipeWs* ws) {
     ws->racc = racc;
     ws->latch = latch;
     ws->ctr = ctr; ws->cand = cand; ws->base = bs; ws->rec = rec; ws->item = item; ws->res = res;
-    ws->hit = hit; ws->cenv = cenv; ws->renv = renv; ws->cap = (uint32_t)cap;
+    ws->hit = hit; ws->cenv = cenv; ws->renv = renv; ws->cap = item_capacity(B);
   }
   return off;
 }
+
+// the ranges of a batch: S ranges of ceil(B / S) envs rounded up to a multiple of TPB (so that every
+// range starts on a 512-byte boundary of every state row), the last one takes what is left
+struct RangePlan {
+  int S;
+  int64_t off[MAX_SPLIT + 1];
+  PipeWs ws[MAX_SPLIT];
+};
+size_t plan_ranges(int64_t B, int S, void* workspace, RangePlan* plan) {
+  int64_t len = (B + S - 1) / S;
+  len = (len + TPB - 1) / TPB * TPB;
+  size_t bytes = 0;
+  int n = 0;
+  for (int64_t o = 0; o < B && n < S; o += len, ++n) {
+    const int64_t nb = (o + len <= B) ? len : B - o;
+    char* base = workspace ? static_cast<char*>(workspace) + bytes : nullptr;
+    bytes += carve(nb, base, plan ? &plan->ws[n] : nullptr);
+    if (plan) plan->off[n] = o;
+  }
+  if (plan) {
+    plan->S = n;
+    plan->off[n] = B;
+  }
+  return bytes;
+}
+int choose_split(int64_t B) {
+  int S = g_cfg.split;
+  if (S <= 0) {
+    S = (int)(B / (g_cfg.min_range > 0 ? g_cfg.min_range : 131072));
+    if (S > 4) S = 4;
+  }
+  if (S > MAX_SPLIT) S = MAX_SPLIT;
+  if (S < 1) S = 1;
+  return S;
+}
+
+// side streams of the ranges 1 .. S-1 (range 0 runs on the caller's stream), one set per device, made
+// on first use.  The fork / join events are shared by all callers on a device, so the enqueue of a
+// multi-range step holds the device's mutex from fork to join.
+struct PipeSide {
+  cudaStream_t s[MAX_SPLIT];
+  cudaEvent_t fork, join[MAX_SPLIT];
+  int prio_lo, prio_hi;
+  int state;  // 0 not made, 1 ok, -1 failed
+  std::mutex mu;
+};
+PipeSide* pipe_side() {
+  static PipeSide per_dev[64];
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  PipeSide& a = per_dev[dev];
+  if (a.state == 0) {
+    bool ok = cudaDeviceGetStreamPriorityRange(&a.prio_lo, &a.prio_hi) == cudaSuccess;
+    for (int i = 1; i < MAX_SPLIT && ok; ++i)
+      ok = cudaStreamCreateWithFlags(&a.s[i], cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 1; i < MAX_SPLIT && ok; ++i)
+      ok = cudaEventCreateWithFlags(&a.join[i], cudaEventDisableTiming) == cudaSuccess;
+    a.state = ok ? 1 : -1;
+    if (!ok) cudaGetLastError();
+  }
+  return a.state == 1 ? &a : nullptr;
+}
+
+// which buffers step t of a multi-step enqueue uses
+struct StepSeq {
+  const float* sin0;   // state read by step 0
+  float* sout0;        // state written by step 0
+  int64_t stride;      // floats between the buffers of consecutive steps (0: the same buffers, in place)
+  const float* action; // or NULL
+  int64_t action_stride;
+  int n_actions;       // step t uses action + (t % n_actions) * action_stride
+  int n_steps;
+};
 
 }  // namespace
 
 extern "C" int64_t cx_lunar_pipeline_workspace_bytes(int64_t B) {
   if (B <= 0) return 0;
-  return (int64_t)carve(B, nullptr, nullptr);
+  size_t need = 0;
+  for (int S = 1; S <= MAX_SPLIT; ++S) {
+    const size_t b = plan_ranges(B, S, nullptr, nullptr);
+    if (b > need) need = b;
+  }
+  return (int64_t)need;
 }
 
-extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float* sin_, float* sout,
-                                        int64_t ld, const float* action, float* reward, uint8_t* done,
-                                        float* obs, const CotixLunarParams* p, void* workspace,
-                                        int64_t workspace_bytes) {
-  if (B == 0) return 0;
+static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& q, float* reward, uint8_t* done,
+                         float* obs, const CotixLunarParams* p, void* workspace, int64_t workspace_bytes,
+                         int split = 0, const CxRangeHook* pre = nullptr, const CxRangeHook* post = nullptr) {
+  if (B == 0 || q.n_steps <= 0) return 0;
   if (B >= (1ll << 27)) {
     cx_set_error("lunar pipeline: B must be < 2^27");
     return COTIX_EINVAL;
   }
-  PipeWs ws;
-  const size_t need = carve(B, workspace, &ws);
+  const int K = p->substeps < 1 ? 1 : p->substeps;
+  const bool prof = g_profile && K == 1 && q.n_steps == 1;
+  int S = prof ? 1 : (split > 0 ? split : choose_split(B));
+  if (S > MAX_SPLIT) S = MAX_SPLIT;
+  RangePlan plan;
+  const size_t need = plan_ranges(B, S, workspace, &plan);
   if (!workspace || (size_t)workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 255u)) {
     cx_set_error("lunar pipeline: workspace must be 256-byte aligned and >= %zu bytes", need);
     return COTIX_EINVAL;
   }
+  PipeSide* side = pipe_side();
+  if (!side) {
+    cx_set_error("lunar pipeline: could not create the range streams");
+    return COTIX_ECUDA;
+  }
   LunarDerived D;
   cx_lunar_derive(p, &D);
-  const unsigned env_blocks = (unsigned)((B + TPB - 1) / TPB);
   const int sms = cx_sm_count();
   auto qgrid = [&](int64_t max_items) {
     int64_t b = (max_items + TPB - 1) / TPB;
     const int64_t cap = (int64_t)sms * 8;
     return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
   };
-  const int K = p->substeps < 1 ? 1 : p->substeps;
-  const bool prof = g_profile && K == 1;
   if (prof) {
     profile_collect();
     if (!g_ev_made) {
@@ -719,58 +829,173 @@ extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float*
   if (prof) cudaEventRecord(g_evb[k], stream)
 #define CX_MARK_E(k, stream) \
   if (prof) cudaEventRecord(g_eve[k], stream)
-  // stages 2..5 are launched with programmatic stream serialization: their blocks may be set up
-  // while the previous stage drains, and wait in cudaGridDependencySynchronize() for its results
-  cudaLaunchAttribute pdl_attr[1];
-  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
-  cfg.blockDim = dim3(TPB);
-  cfg.stream = st;
-  cfg.attrs = pdl_attr;
-  cfg.numAttrs = (prof || !g_pdl) ? 0 : 1;
-#define CX_PDL_LAUNCH(kernel, grid, ...) \
-  do {                                   \
-    cfg.gridDim = dim3(grid);            \
-    cudaLaunchKernelEx(&cfg, kernel, __VA_ARGS__); \
-  } while (0)
-  CX_MARK_B(5, st);
-  // K sub-steps with the same action (cotix/_envs.py:72-103: WFE_scale forward steps per control):
-  // the four step stages K times — sub-steps after the first run in place on the output state —
-  // then one reset stage
-  for (int k = 0; k < K; ++k) {
-    if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, st) != cudaSuccess) return cx_check_launch("pipeline memset");
-    CX_MARK_B(0, st);
-    pipe_integrate_kernel<<<env_blocks, TPB, 0, st>>>(B, k == 0 ? sin_ : sout, sout, ld, action, *p, D, ws, k, K);
-    CX_MARK_E(0, st);
-    CX_MARK_B(1, st);
-    CX_PDL_LAUNCH(pipe_narrow_kernel, qgrid((int64_t)ws.cap), *p, D, ws);
-    CX_MARK_E(1, st);
-    CX_MARK_B(2, st);
-    CX_PDL_LAUNCH(pipe_contact_kernel, qgrid(B), sout, ld, *p, D, ws);
-    CX_MARK_E(2, st);
-    CX_MARK_B(3, st);
-    CX_PDL_LAUNCH(pipe_finish_kernel, env_blocks, B, sout, ld, action, reward, done, obs, *p, ws, k, K);
-    CX_MARK_E(3, st);
-  }
-  CX_MARK_B(4, st);
-  if (p->auto_reset) {
-    CX_PDL_LAUNCH(pipe_reset_kernel, qgrid(B), sout, ld, obs, *p, ws);
-    cx_count_launch_n(4 * K + 1);
-  } else {
-    cx_count_launch_n(4 * K);
-  }
-  CX_MARK_E(4, st);
-  CX_MARK_E(5, st);
+  // the chain of one range: per step and sub-step 1 memset + 4 kernels, then the reset stage.
+  // Stages 2..5 are launched with programmatic stream serialization: their blocks may be set up
+  // while the previous stage drains, and wait in cudaGridDependencySynchronize() for its results.
+  auto chain = [&](cudaStream_t cs, int r) -> int {
+    const int64_t off = plan.off[r], n = plan.off[r + 1] - off;
+    const PipeWs& ws = plan.ws[r];
+    const unsigned env_blocks = (unsigned)((n + TPB - 1) / TPB);
+    cudaLaunchAttribute attr[2];
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.blockDim = dim3(TPB);
+    cfg.stream = cs;
+    cfg.attrs = attr;
+    auto set_attrs = [&](bool pdl, bool sparse) {
+      int na = 0;
+      if (pdl && g_cfg.pdl && !prof) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+      }
+      if (g_cfg.prio && S > 1) {
+        attr[na].id = cudaLaunchAttributePriority;
+        attr[na].val.priority = sparse ? side->prio_hi : side->prio_lo;
+        ++na;
+      }
+      cfg.numAttrs = na;
+    };
+    float* rw = reward ? reward + off : nullptr;
+    uint8_t* dn = done ? done + off : nullptr;
+    float* ob = obs ? obs + off : nullptr;
+    if (pre && *pre) {
+      const int hr = (*pre)(cs, r, off, n);
+      if (hr != 0) return hr;
+    }
+    for (int t = 0; t < q.n_steps; ++t) {
+      const float* sin_ = q.sin0 + (int64_t)t * q.stride + off;
+      float* sout = q.sout0 + (int64_t)t * q.stride + off;
+      const float* act = q.action ? q.action + (int64_t)(t % q.n_actions) * q.action_stride + off : nullptr;
+      CX_MARK_B(5, cs);
+      // K sub-steps with the same action (cotix/_envs.py:72-103: WFE_scale forward steps per control):
+      // the four step stages K times — sub-steps after the first run in place on the output state —
+      // then one reset stage
+      for (int k = 0; k < K; ++k) {
+        if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, cs) != cudaSuccess) return cx_check_launch("pipeline memset");
+        CX_MARK_B(0, cs);
+        set_attrs(false, false);
+        cfg.gridDim = dim3(env_blocks);
+        cudaLaunchKernelEx(&cfg, pipe_integrate_kernel, n, k == 0 ? sin_ : (const float*)sout, sout, ld, act, *p, D, ws,
+                           k, K);
+        CX_MARK_E(0, cs);
+        CX_MARK_B(1, cs);
+        set_attrs(true, true);
+        cfg.gridDim = dim3(qgrid((int64_t)ws.cap));
+        cudaLaunchKernelEx(&cfg, pipe_narrow_kernel, *p, D, ws);
+        CX_MARK_E(1, cs);
+        CX_MARK_B(2, cs);
+        cfg.gridDim = dim3(qgrid(n));
+        cudaLaunchKernelEx(&cfg, pipe_contact_kernel, sout, ld, *p, D, ws);
+        CX_MARK_E(2, cs);
+        CX_MARK_B(3, cs);
+        set_attrs(true, false);
+        cfg.gridDim = dim3(env_blocks);
+        cudaLaunchKernelEx(&cfg, pipe_finish_kernel, n, sout, ld, act, rw, dn, ob, *p, ws, k, K);
+        CX_MARK_E(3, cs);
+      }
+      CX_MARK_B(4, cs);
+      if (p->auto_reset) {
+        set_attrs(true, true);
+        cfg.gridDim = dim3(qgrid(n));
+        cudaLaunchKernelEx(&cfg, pipe_reset_kernel, sout, ld, ob, *p, ws);
+      }
+      CX_MARK_E(4, cs);
+      CX_MARK_E(5, cs);
+    }
+    if (post && *post) {
+      const int hr = (*post)(cs, r, off, n);
+      if (hr != 0) return hr;
+    }
+    return cx_check_launch("lunar pipeline");
+  };
 #undef CX_MARK_B
 #undef CX_MARK_E
-#undef CX_PDL_LAUNCH
+  int rc = 0;
+  if (plan.S == 1) {
+    rc = chain(st, 0);
+  } else {
+    std::lock_guard<std::mutex> lock(side->mu);
+    if (cudaEventRecord(side->fork, st) != cudaSuccess) return cx_check_launch("pipeline fork");
+    for (int r = 1; r < plan.S; ++r)
+      if (cudaStreamWaitEvent(side->s[r], side->fork, 0) != cudaSuccess) return cx_check_launch("pipeline fork");
+    // the side ranges first: the caller's stream may already be busy
+    for (int r = 1; r < plan.S; ++r) {
+      const int rr = chain(side->s[r], r);
+      if (rr != 0 && rc == 0) rc = rr;
+    }
+    {
+      const int rr = chain(st, 0);
+      if (rr != 0 && rc == 0) rc = rr;
+    }
+    // every exit path joins (an open fork would leave a stream capture unjoined)
+    for (int r = 1; r < plan.S; ++r) {
+      if (cudaEventRecord(side->join[r], side->s[r]) != cudaSuccess ||
+          cudaStreamWaitEvent(st, side->join[r], 0) != cudaSuccess) {
+        if (rc == 0) rc = cx_check_launch("pipeline join");
+      }
+    }
+  }
+  cx_count_launch_n((int64_t)(4 * K + (p->auto_reset ? 1 : 0)) * plan.S * q.n_steps);
   if (prof) g_ev_pending = true;
-  return cx_check_launch("lunar pipeline");
+  return rc;
 }
 
-extern "C" void cx_lunar_pipeline_set_pdl(int on) { g_pdl = on != 0; }
+extern "C" int cx_launch_lunar_pipeline(cudaStream_t st, int64_t B, const float* sin_, float* sout,
+                                        int64_t ld, const float* action, float* reward, uint8_t* done,
+                                        float* obs, const CotixLunarParams* p, void* workspace,
+                                        int64_t workspace_bytes) {
+  StepSeq q{sin_, sout, 0, action, 0, 1, 1};
+  return enqueue_steps(st, B, ld, q, reward, done, obs, p, workspace, workspace_bytes);
+}
+
+// n_steps steps in one enqueue: step t reads sin0 + t * stride and writes sout0 + t * stride (stride
+// 0 = in place on one buffer; the tape of a rollout: sout0 = sin0 + stride), with action
+// actions + (t % n_actions) * action_stride.  The ranges run their n_steps without joining.
+extern "C" int cx_launch_lunar_pipeline_steps(cudaStream_t st, int64_t B, const float* sin0, float* sout0,
+                                              int64_t stride, int64_t ld, const float* actions,
+                                              int64_t action_stride, int n_actions, int n_steps, float* reward,
+                                              uint8_t* done, float* obs, const CotixLunarParams* p,
+                                              void* workspace, int64_t workspace_bytes) {
+  StepSeq q{sin0, sout0, stride, actions, action_stride, n_actions < 1 ? 1 : n_actions, n_steps};
+  return enqueue_steps(st, B, ld, q, reward, done, obs, p, workspace, workspace_bytes);
+}
+
+int cx_launch_lunar_pipeline_hooked(cudaStream_t st, int64_t B, float* state, int64_t ld, const float* action,
+                                    float* reward, uint8_t* done, float* obs, const CotixLunarParams* p,
+                                    void* workspace, int64_t workspace_bytes, int split, const CxRangeHook& pre,
+                                    const CxRangeHook& post) {
+  StepSeq q{state, state, 0, action, 0, 1, 1};
+  return enqueue_steps(st, B, ld, q, reward, done, obs, p, workspace, workspace_bytes, split, &pre, &post);
+}
+
+// split: 0 automatic, 1..8 ranges; pdl / priorities: 0 off, 1 on; item_capacity: 0 default, > 0 forces
+// the item queue of every range to that many slots (tests of the overflow branch); a negative value
+// leaves a setting unchanged
+extern "C" int cx_lunar_pipeline_config(int split, int pdl, int priorities, int64_t item_capacity) {
+  if (split > MAX_SPLIT) return COTIX_EINVAL;
+  if (split >= 0) g_cfg.split = split;
+  if (pdl >= 0) g_cfg.pdl = pdl != 0;
+  if (priorities >= 0) g_cfg.prio = priorities != 0;
+  if (item_capacity >= 0) g_cfg.item_cap = (uint32_t)item_capacity;
+  return COTIX_OK;
+}
+// queue counters of the last step, summed over the ranges the workspace was cut into for batch B:
+// out[0..4] = items, hits, contact envs, resets, overflowed envs (DEVICE -> host copy, synchronises)
+extern "C" int cx_lunar_pipeline_counters(cudaStream_t st, int64_t B, const void* workspace, int64_t* out) {
+  for (int i = 0; i < 5; ++i) out[i] = 0;
+  if (B <= 0 || !workspace) return COTIX_EINVAL;
+  RangePlan plan;
+  plan_ranges(B, (g_profile ? 1 : choose_split(B)), const_cast<void*>(workspace), &plan);
+  for (int r = 0; r < plan.S; ++r) {
+    uint32_t c[CTR_WORDS];
+    if (cudaMemcpyAsync(c, plan.ws[r].ctr, sizeof(c), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess)
+      return cx_check_launch("pipeline counters");
+    for (int i = 0; i < 5; ++i) out[i] += c[i];
+  }
+  return COTIX_OK;
+}
 
 // ---- per-stage timing (single-threaded use: bench.py) ----------------------------------------
 extern "C" int cx_lunar_pipeline_profiling() { return g_profile ? 1 : 0; }

@@ -105,19 +105,57 @@ def reset(keys, params: LunarParams | None = None, device="cuda") -> LunarState:
 MODE_AUTO, MODE_FUSED, MODE_PIPELINE = 0, 1, 2
 PIPELINE_MIN_ENVS = 16384
 _MODES = {"auto": MODE_AUTO, "fused": MODE_FUSED, "pipeline": MODE_PIPELINE}
-_workspaces: dict = {}
+_workspaces: "dict[tuple, torch.Tensor]" = {}
+_WORKSPACE_CACHE = 4
 
 
 def _workspace(device: torch.device, B: int) -> torch.Tensor:
-    """Device scratch of the wavefront pipeline, cached per (device, batch)."""
-    key = (device.index, B)
-    ws = _workspaces.get(key)
+    """Device scratch of the wavefront pipeline: a small LRU keyed by (device, batch).  A cached
+    block is only ever handed to launches on the caller's current stream of that device (stream order
+    protects it); eviction drops the reference and torch's caching allocator keeps the block alive
+    until the work enqueued on it has drained."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), int(B))
+    ws = _workspaces.pop(key, None)
     if ws is None:
         nbytes = int(_lib.lib().cotix_lunar_workspace_bytes(B))
         ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
-        _workspaces.clear()  # one live batch shape at a time is the common case
-        _workspaces[key] = ws
+        while len(_workspaces) >= _WORKSPACE_CACHE:
+            _workspaces.pop(next(iter(_workspaces)))
+    _workspaces[key] = ws  # most recently used last
     return ws
+
+
+def _ws_args(device: torch.device, B: int):
+    ws = _workspace(device, B)
+    wp = (ws.data_ptr() + 255) & ~255
+    return wp, ws.numel() - (wp - ws.data_ptr())
+
+
+def _row_ld(t: torch.Tensor, what: str) -> int:
+    """Leading dimension of a [rows, B] buffer whose rows are contiguous (stride(1) == 1)."""
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{what}: rows must be contiguous (stride(1) == 1); call .contiguous()")
+    return int(t.stride(0)) if t.shape[0] > 1 else max(int(t.stride(0)), int(t.shape[1]))
+
+
+def _like_ld(rows: int, B: int, ld: int, ref: torch.Tensor, dtype=torch.float32) -> torch.Tensor:
+    """A [rows, B] buffer whose leading dimension is `ld` (the C-ABI takes ONE ld for every [.][ld]
+    buffer of a call, so companions of a sliced state are allocated with the state's row stride)."""
+    if ld == B:
+        return torch.empty((rows, B), dtype=dtype, device=ref.device)
+    return torch.empty_strided((rows, B), (ld, 1), dtype=dtype, device=ref.device)
+
+
+def _with_ld(t: torch.Tensor | None, rows: int, B: int, ld: int, ref: torch.Tensor, what: str):
+    if t is None:
+        return None
+    t = t.to(device=ref.device, dtype=torch.float32)
+    assert tuple(t.shape) == (rows, B), f"{what}: expected shape {(rows, B)}, got {tuple(t.shape)}"
+    if t.stride(1) == 1 and (rows == 1 or t.stride(0) == ld):
+        return t
+    out = _like_ld(rows, B, ld, ref)
+    out.copy_(t)
+    return out
 
 
 def step(state: LunarState, action: torch.Tensor | None = None, params: LunarParams | None = None,
@@ -134,29 +172,169 @@ def step(state: LunarState, action: torch.Tensor | None = None, params: LunarPar
     params = params or default_params()
     d = state.data
     B = d.shape[1]
-    out = d if inplace else torch.empty_like(d)
+    ld = _row_ld(d, "state")  # a column slice of a larger batch keeps the parent's row stride
+    out = d if inplace else _like_ld(NF, B, ld, d)
     reward = torch.empty(B, dtype=torch.float32, device=d.device)
     done = torch.empty(B, dtype=torch.uint8, device=d.device)
-    obs = torch.empty((NOBS, B), dtype=torch.float32, device=d.device) if want_obs else None
-    if action is not None:
-        action = action.to(device=d.device, dtype=torch.float32).contiguous()
-        assert action.shape == (2, B)
+    obs = _like_ld(NOBS, B, ld, d) if want_obs else None
+    action = _with_ld(action, 2, B, ld, d, "action")
     m = _MODES[mode]
     use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and B >= PIPELINE_MIN_ENVS)
     with torch.cuda.device(d.device):
-        args = (_stream_ptr(d.device), B, d.data_ptr(), out.data_ptr(), d.stride(0),
+        args = (_stream_ptr(d.device), B, d.data_ptr(), out.data_ptr(), ld,
                 action.data_ptr() if action is not None else None, reward.data_ptr(), done.data_ptr(),
                 obs.data_ptr() if obs is not None else None, C.byref(params))
         if use_pipe:
-            ws = _workspace(d.device, B)
-            wp = (ws.data_ptr() + 255) & ~255
-            _lib.check(_lib.lib().cotix_lunar_step_ws(*args, wp, ws.numel() - (wp - ws.data_ptr())))
+            _lib.check(_lib.lib().cotix_lunar_step_ws(*args, *_ws_args(d.device, B)))
         else:
             _lib.check(_lib.lib().cotix_lunar_step(*args))
     ns = state if inplace else LunarState(out)
     if want_obs:
         return ns, reward, done, obs
     return ns, reward, done
+
+
+def steps(state: LunarState, actions: torch.Tensor | None, n_steps: int, params: LunarParams | None = None,
+          want_obs: bool = False, mode: str = "auto", out: tuple | None = None):
+    """n_steps steps IN PLACE on `state` in one enqueue (`cotix_lunar_steps_ws`): the loop
+    `for _ in range(n): env = f(env, key)` of examples/test_viz.py:46-48.  actions: [n_actions, 2, B]
+    (step t uses actions[t % n_actions]) or None.  Returns (reward, done[, obs]) of the last step.
+    In pipeline mode the env ranges run their n_steps on their own streams without joining between
+    steps; capture the call in a `Graph` and a whole rollout is one launch."""
+    params = params or default_params()
+    d = state.data
+    B = d.shape[1]
+    ld = _row_ld(d, "state")
+    if out is not None:
+        reward, done, obs = out
+        assert obs is None or _row_ld(obs, "obs") == ld
+    else:
+        reward = torch.empty(B, dtype=torch.float32, device=d.device)
+        done = torch.empty(B, dtype=torch.uint8, device=d.device)
+        obs = _like_ld(NOBS, B, ld, d) if want_obs else None
+    n_act = 0
+    if actions is not None:
+        actions = actions.to(device=d.device, dtype=torch.float32)
+        assert actions.dim() == 3 and tuple(actions.shape[1:]) == (2, B)
+        n_act = actions.shape[0]
+        if not (actions.stride(2) == 1 and actions.stride(1) == ld and actions.stride(0) == 2 * ld):
+            a = torch.empty_strided((n_act, 2, B), (2 * ld, ld, 1), dtype=torch.float32, device=d.device)
+            a.copy_(actions)
+            actions = a
+    m = _MODES[mode]
+    use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and B >= PIPELINE_MIN_ENVS)
+    with torch.cuda.device(d.device):
+        wp, wn = _ws_args(d.device, B) if use_pipe else (None, 0)
+        _lib.check(_lib.lib().cotix_lunar_steps_ws(
+            _stream_ptr(d.device), B, d.data_ptr(), ld, actions.data_ptr() if actions is not None else None,
+            n_act, int(n_steps), reward.data_ptr(), done.data_ptr(), obs.data_ptr() if obs is not None else None,
+            C.byref(params), wp, wn))
+    if want_obs or (out is not None and obs is not None):
+        return reward, done, obs
+    return reward, done
+
+
+class Graph:
+    """CUDA-graph capture of device entry points (`cotix_graph_*`): what is enqueued through this
+    module inside the `with` block becomes one replayable graph — the single dispatch per rollout
+    that `jax.jit` gives the reference's loop (examples/test_viz.py:24,46-48).  Nothing may be
+    allocated while capturing: pass preallocated buffers (`steps(..., out=...)`) and `keep()` every
+    buffer the captured calls touch.  `StepsGraph` does all of that for a rollout."""
+
+    def __init__(self, device="cuda"):
+        self.device = torch.device(device)
+        self._h = C.c_void_p()
+        self._keep = []
+
+    def __enter__(self):
+        torch.cuda.synchronize(self.device)
+        self._stream = torch.cuda.Stream(self.device)
+        self._ctx = torch.cuda.stream(self._stream)
+        self._ctx.__enter__()
+        _lib.check(_lib.lib().cotix_graph_begin_capture(self._stream.cuda_stream))
+        return self
+
+    def __exit__(self, et, ev, tb):
+        rc = _lib.lib().cotix_graph_end_capture(self._stream.cuda_stream, C.byref(self._h))
+        self._ctx.__exit__(et, ev, tb)
+        if et is None:
+            _lib.check(rc)
+        return False
+
+    def keep(self, *objs):
+        """Hold references to buffers a captured call reads or writes."""
+        self._keep.extend(objs)
+
+    def launch(self, stream: int | None = None):
+        with torch.cuda.device(self.device):
+            st = _stream_ptr(self.device) if stream is None else stream
+            _lib.check(_lib.lib().cotix_graph_launch(self._h, st))
+
+    def info(self) -> dict:
+        n, k = C.c_int32(), C.c_int64()
+        _lib.check(_lib.lib().cotix_graph_info(self._h, C.byref(n), C.byref(k)))
+        return {"nodes": n.value, "kernel_launches": k.value}
+
+    def close(self):
+        if self._h:
+            _lib.lib().cotix_graph_destroy(self._h)
+            self._h = C.c_void_p()
+        self._keep.clear()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class StepsGraph:
+    """`steps(state, actions, n_steps)` captured once and replayed: every `launch()` advances
+    `state` by n_steps steps (in place) with ONE graph launch; `reward`, `done` (and `obs`) hold the
+    last step's values.  Owns the buffers the graph touches, including the pipeline workspace."""
+
+    def __init__(self, state: LunarState, actions: torch.Tensor | None, n_steps: int,
+                 params: LunarParams | None = None, want_obs: bool = False, mode: str = "auto"):
+        self.params = (params or default_params()).copy()
+        d = state.data
+        B = d.shape[1]
+        ld = _row_ld(d, "state")
+        self.state, self.n_steps = state, int(n_steps)
+        self.reward = torch.empty(B, dtype=torch.float32, device=d.device)
+        self.done = torch.empty(B, dtype=torch.uint8, device=d.device)
+        self.obs = _like_ld(NOBS, B, ld, d) if want_obs else None
+        if actions is not None:
+            actions = actions.to(device=d.device, dtype=torch.float32)
+            if not (actions.stride(2) == 1 and actions.stride(1) == ld and actions.stride(0) == 2 * ld):
+                a = torch.empty_strided(tuple(actions.shape), (2 * ld, ld, 1), dtype=torch.float32, device=d.device)
+                a.copy_(actions)
+                actions = a
+        self.actions = actions
+        m = _MODES[mode]
+        if m == MODE_PIPELINE or (m == MODE_AUTO and B >= PIPELINE_MIN_ENVS):
+            ws = _workspace(d.device, B)  # allocated before the capture; the graph keeps it
+        else:
+            ws = None
+        self.graph = Graph(d.device)
+        with self.graph:
+            steps(state, actions, self.n_steps, self.params, mode=mode, out=(self.reward, self.done, self.obs))
+        self.graph.keep(d, actions, self.reward, self.done, self.obs, ws)
+
+    def launch(self):
+        self.graph.launch()
+
+    def info(self) -> dict:
+        return self.graph.info()
+
+    def close(self):
+        self.graph.close()
+
+
+def pipeline_config(split: int = -1, pdl: int = -1, priorities: int = -1, item_capacity: int = -1) -> None:
+    """Launch configuration of the wavefront pipeline (`cotix_lunar_pipeline_config`; -1 = unchanged):
+    split = ranges of envs run on their own streams (0 automatic), pdl, priorities, item_capacity
+    (test hook for the item-queue overflow branch)."""
+    _lib.check(_lib.lib().cotix_lunar_pipeline_config(int(split), int(pdl), int(priorities), int(item_capacity)))
 
 
 NDYN = 18
@@ -179,17 +357,19 @@ def step_vjp(state: LunarState, action: torch.Tensor | None, g_next: torch.Tenso
     params = params or default_params()
     d = state.data
     B = d.shape[1]
-    g_next = g_next.to(device=d.device, dtype=torch.float32).contiguous()
-    assert g_next.shape == (NDYN, B)
-    g_in = torch.empty_like(g_next)
-    g_act = torch.zeros((2, B), dtype=torch.float32, device=d.device)
-    if action is not None:
-        action = action.to(device=d.device, dtype=torch.float32).contiguous()
-        assert action.shape == (2, B)
+    ld = _row_ld(d, "state")  # every [.][ld] buffer of the call shares the state's row stride
+    g_next = _with_ld(g_next, NDYN, B, ld, d, "g_next")
+    g_in = _like_ld(NDYN, B, ld, d)
+    g_act = _like_ld(2, B, ld, d)
+    g_act.zero_()
+    action = _with_ld(action, 2, B, ld, d, "action")
+    sn = None
+    if state_next is not None:
+        sn = _with_ld(state_next.data, NF, B, ld, d, "state_next")
     with torch.cuda.device(d.device):
         _lib.check(_lib.lib().cotix_lunar_step_bwd(
-            _stream_ptr(d.device), B, d.data_ptr(), state_next.data.data_ptr() if state_next is not None else None,
-            d.stride(0), action.data_ptr() if action is not None else None, g_next.data_ptr(), g_in.data_ptr(),
+            _stream_ptr(d.device), B, d.data_ptr(), sn.data_ptr() if sn is not None else None,
+            ld, action.data_ptr() if action is not None else None, g_next.data_ptr(), g_in.data_ptr(),
             g_act.data_ptr(), flags.data_ptr() if flags is not None else None, C.byref(params)))
     return g_in, g_act
 
@@ -212,14 +392,17 @@ class Rollout:
 
 
 def rollout(state: LunarState, actions: torch.Tensor | None, n_steps: int,
-            params: LunarParams | None = None, mode: str = "auto") -> Rollout:
+            params: LunarParams | None = None, mode: str = "auto", tape: torch.Tensor | None = None) -> Rollout:
     """n_steps steps of `step`, keeping every intermediate state (`cotix_lunar_rollout`): the
-    forward half of the reference's `jax.value_and_grad` over a rollout."""
+    forward half of the reference's `jax.value_and_grad` over a rollout.  tape: optional
+    preallocated contiguous [n_steps + 1, 36, B] buffer (what a graph capture needs)."""
     params = params or default_params()
     d = state.data
     B = d.shape[1]
     T = int(n_steps)
-    tape = torch.empty((T + 1, NF, B), dtype=torch.float32, device=d.device)
+    if tape is None:
+        tape = torch.empty((T + 1, NF, B), dtype=torch.float32, device=d.device)
+    assert tuple(tape.shape) == (T + 1, NF, B) and tape.is_contiguous()
     tape[0].copy_(d)
     if actions is not None:
         actions = actions.to(device=d.device, dtype=torch.float32).contiguous()
@@ -227,19 +410,29 @@ def rollout(state: LunarState, actions: torch.Tensor | None, n_steps: int,
     m = _MODES[mode]
     use_pipe = m == MODE_PIPELINE or (m == MODE_AUTO and B >= PIPELINE_MIN_ENVS)
     with torch.cuda.device(d.device):
-        wp, wn = None, 0
-        if use_pipe:
-            ws = _workspace(d.device, B)
-            wp = (ws.data_ptr() + 255) & ~255
-            wn = ws.numel() - (wp - ws.data_ptr())
+        wp, wn = _ws_args(d.device, B) if use_pipe else (None, 0)
         _lib.check(_lib.lib().cotix_lunar_rollout(
             _stream_ptr(d.device), B, T, tape.data_ptr(), B, actions.data_ptr() if actions is not None else None,
             C.byref(params), wp, wn))
     return Rollout(tape, actions, params)
 
 
+def adjoint_workspace(B: int, T: int, device, decision_tape: bool | int = True, jacobians: bool | None = None):
+    """Scratch of `rollout_vjp` (decision tapes, and with `jacobians` the transposed Jacobians) for a
+    rollout of T steps of B envs: a uint8 tensor to pass as `workspace=`, or None."""
+    if jacobians is None:
+        jacobians = B <= JACOBIAN_MAX_ENVS
+    if not decision_tape or T <= 0:
+        return None
+    L = _lib.lib()
+    n = T if decision_tape is True else max(1, min(T, int(decision_tape)))
+    size = L.cotix_lunar_adjoint_workspace_bytes if jacobians else L.cotix_lunar_adjoint_decisions_bytes
+    return torch.empty(int(size(B, n)) + 256, dtype=torch.uint8, device=device)
+
+
 def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None = None,
-                decision_tape: bool | int = True, jacobians: bool | None = None):
+                decision_tape: bool | int = True, jacobians: bool | None = None,
+                workspace: torch.Tensor | None = None, out: tuple | None = None):
     """Backward pass over a `Rollout` (`cotix_lunar_rollout_bwd`): g_final [18, B] = dL/d(final
     dynamic leaves).  Returns (dL/d(initial dynamic leaves) [18, B], dL/d(actions) [T, 2, B]).
 
@@ -250,22 +443,30 @@ def rollout_vjp(ro: Rollout, g_final: torch.Tensor, flags: torch.Tensor | None =
     are bit-identical to False; with them they differ at rounding level.  jacobians=None picks them
     for B <= JACOBIAN_MAX_ENVS: they trade 18 x the contact-adjoint work, done at full occupancy, for
     short reverse launches — a win while the sweep is latency-bound (B = 4096: 9.0 -> 5.7 ms), a loss
-    once it is throughput-bound (B = 65536: 23.7 -> 43 ms)."""
+    once it is throughput-bound (B = 65536: 23.7 -> 43 ms).
+    workspace: from `adjoint_workspace` (allocated here when None); out: optional preallocated
+    (g [18, B], g_actions [T, 2, B]) — g is overwritten with g_final first.  With both given the call
+    allocates nothing and can be captured in a `Graph`."""
     if jacobians is None:
         jacobians = ro.tape.shape[2] <= JACOBIAN_MAX_ENVS
     tape = ro.tape
     T, B = tape.shape[0] - 1, tape.shape[2]
-    g = g_final.to(device=tape.device, dtype=torch.float32).contiguous().clone()
+    if out is not None:
+        g, g_act = out
+        assert g.is_contiguous() and g_act.is_contiguous() and tuple(g_act.shape) == (T, 2, B)
+        if g.data_ptr() != g_final.data_ptr():
+            g.copy_(g_final)
+        g_act.zero_()
+    else:
+        g = g_final.to(device=tape.device, dtype=torch.float32).contiguous().clone()
+        g_act = torch.zeros((T, 2, B), dtype=torch.float32, device=tape.device)
     assert g.shape == (NDYN, B)
-    g_act = torch.zeros((T, 2, B), dtype=torch.float32, device=tape.device)
-    wp, wn, ws = None, 0, None
-    if decision_tape and T > 0:
-        L = _lib.lib()
-        steps = T if decision_tape is True else max(1, min(T, int(decision_tape)))
-        size = L.cotix_lunar_adjoint_workspace_bytes if jacobians else L.cotix_lunar_adjoint_decisions_bytes
-        wn = int(size(B, steps))
-        ws = torch.empty(wn + 256, dtype=torch.uint8, device=tape.device)
+    wp, wn, ws = None, 0, workspace
+    if ws is None:
+        ws = adjoint_workspace(B, T, tape.device, decision_tape, jacobians)
+    if ws is not None:
         wp = (ws.data_ptr() + 255) & ~255
+        wn = ws.numel() - (wp - ws.data_ptr())
     with torch.cuda.device(tape.device):
         _lib.check(_lib.lib().cotix_lunar_rollout_bwd(
             _stream_ptr(tape.device), B, T, tape.data_ptr(), B,
@@ -289,14 +490,17 @@ def pipeline_stage_ms() -> tuple[dict, int]:
     return {k: float(out[i]) for i, k in enumerate(PIPELINE_STAGES)}, n
 
 
-def pipeline_counters(device: torch.device | None = None) -> dict | None:
-    """Queue lengths of the last pipeline step on the cached workspace (measurement aid):
-    collision items, live contacts, envs with a candidate contact, auto-resets, overflow."""
-    for (idx, _B), ws in _workspaces.items():
-        if device is None or device.index in (None, idx):
-            off = ((ws.data_ptr() + 255) & ~255) - ws.data_ptr()
-            c = ws[off:off + 32].view(torch.int32).cpu().tolist()
-            return {"items": c[0], "hits": c[1], "contact_envs": c[2], "resets": c[3], "overflow": c[4]}
+def pipeline_counters(device: torch.device | None = None, B: int | None = None) -> dict | None:
+    """Queue lengths of the last pipeline step on the cached workspace of (device, B) — the most
+    recently used one when B is None — summed over the env ranges (measurement aid): collision
+    items, live contacts, envs with a candidate contact, auto-resets, envs that overflowed the queue."""
+    for (idx, b), ws in reversed(list(_workspaces.items())):
+        if (device is None or device.index in (None, idx)) and (B is None or B == b):
+            wp = (ws.data_ptr() + 255) & ~255
+            out = (C.c_int64 * 5)()
+            with torch.cuda.device(ws.device):
+                _lib.check(_lib.lib().cotix_lunar_pipeline_counters(_stream_ptr(ws.device), b, wp, out))
+            return {"items": out[0], "hits": out[1], "contact_envs": out[2], "resets": out[3], "overflow": out[4]}
     return None
 
 
@@ -345,17 +549,18 @@ class LunarLanderEnv:
         k = np.ascontiguousarray(np.asarray(keys).astype(np.uint32)).reshape(self.B, 2)
         _lib.check(_lib.lib().cotix_lunar_env_reset_host(self._h, k.ctypes.data))
 
-    def step(self, action_host: torch.Tensor | np.ndarray | None):
-        """action_host: [2, B] float32 host tensor (pinned for best speed)."""
+    def step(self, action_host: torch.Tensor | np.ndarray | None, want_obs: bool = True):
+        """action_host: [2, B] float32 host tensor (pinned for best speed).  want_obs=False leaves the
+        observation on the device (86 % of the step's D2H bytes): (None, reward, done)."""
         ptr = None
         if action_host is not None:
             if isinstance(action_host, np.ndarray):
                 action_host = torch.from_numpy(np.ascontiguousarray(action_host, np.float32))
             assert action_host.shape == (2, self.B) and action_host.dtype == torch.float32
             ptr = action_host.data_ptr()
-        _lib.check(_lib.lib().cotix_lunar_env_step_host(self._h, ptr, self.obs.data_ptr(),
+        _lib.check(_lib.lib().cotix_lunar_env_step_host(self._h, ptr, self.obs.data_ptr() if want_obs else None,
                                                         self.reward.data_ptr(), self.done.data_ptr()))
-        return self.obs, self.reward, self.done
+        return (self.obs if want_obs else None), self.reward, self.done
 
     def get_state(self) -> np.ndarray:
         out = np.empty((NF, self.B), np.float32)

@@ -41,7 +41,7 @@ def test_every_declared_symbol_is_exported(lib):
 def test_abi_version_and_struct_layout(lib, oracle):
     import parallax_b200
 
-    assert lib.cotix_abi_version() == 1
+    assert lib.cotix_abi_version() == 2
     # the ctypes mirror, the oracle's mirror and the C struct agree on the size
     assert C.sizeof(parallax_b200.LunarParams) == oracle.lib().oracle_sizeof_lunar_params()
     assert C.sizeof(parallax_b200.LunarParams) == C.sizeof(oracle.LunarParams)

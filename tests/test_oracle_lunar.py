@@ -162,3 +162,28 @@ def test_scene_step_two_circles_head_on(oracle):
         else:
             assert np.array_equal(out[:, 4], bodies[:, 4])
     assert 8 <= hit <= 32  # the coin flip (p = 0.5, cotix/_colliders.py:220) decides
+
+
+def test_horizon_100_steps_trig_definitions(oracle):
+    """The 100-step-horizon tolerance of north_star, on the CPU: the oracle with the engine's trig
+    (cx_trig.h — what the CUDA path computes bit for bit) against the oracle with libm trig, from
+    identical contact-rich states.  tests/horizon.py states and asserts the tolerance."""
+    from gen_inputs import lunar_keys, perturbed_lunar_state
+    from horizon import HORIZON_STEPS, check_horizon
+
+    P = oracle.default_lunar_params()
+    P.judge_enabled = 1
+    B = 2048
+    s0 = perturbed_lunar_state(oracle.lunar_reset(lunar_keys(B), P), np.random.default_rng(161), P)
+    a, b = s0.copy(), s0.copy()
+    same = np.ones(B, bool)
+    try:
+        for _ in range(HORIZON_STEPS):
+            oracle.set_trig_mode(1)
+            a, _, da, oa = oracle.lunar_step(a, None, P, want_obs=True)
+            oracle.set_trig_mode(0)
+            b, _, db, ob = oracle.lunar_step(b, None, P, want_obs=True)
+            same &= (oa[6:8] == ob[6:8]).all(axis=0) & (da == db)
+    finally:
+        oracle.set_trig_mode(0)
+    check_horizon(a, b, same)
