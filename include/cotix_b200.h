@@ -190,6 +190,9 @@ typedef struct CotixLunarParams {
   float reset_x[2], reset_y[2], reset_angle[2]; /* uniform ranges (reset_perturb)           */
   float reset_v, reset_w;     /* uniform half-ranges for velocity / angular velocity        */
   uint32_t philox_seed[2];    /* stream seed for COTIX_RNG_PHILOX                           */
+  int32_t solver_loops;       /* SimpleConstraintSolver(loops) (cotix/_constraint_solvers.py:4-17):  */
+                              /* sequential passes over the four joint constraints per step; 1 =     */
+                              /* LunarLander.step as written (cotix/_lunar_lander.py:193-204)        */
 } CotixLunarParams;
 
 /* Fill *p with the reference literals (leaving the new env logic disabled). */

@@ -1189,6 +1189,7 @@ void lunar_default_params(CotixLunarParams* p) {
   p->reset_w = 0.8660254f;
   p->philox_seed[0] = 0x243F6A88u;
   p->philox_seed[1] = 0x85A308D3u;
+  p->solver_loops = 1;
 }
 
 // ---- the engine's env-logic spec (new; the reference has none): RNG streams ----------
@@ -1380,10 +1381,13 @@ void lunar_joints(std::vector<Body>& bodies, const CotixLunarParams& P) {
     apply_impulse(b1, -impulse, c1);
     apply_impulse(b2, impulse, c2);
   };
-  constraint(lander, lj[0], left_leg, left_leg_joint_1);
-  constraint(lander, lj[1], left_leg, left_leg_joint_2);
-  constraint(lander, lj[2], right_leg, right_leg_joint_1);
-  constraint(lander, lj[3], right_leg, right_leg_joint_2);
+  // SimpleConstraintSolver.solve (_constraint_solvers.py:13-17): `loops` passes over the list
+  for (int it = 0; it < (P.solver_loops < 1 ? 1 : P.solver_loops); ++it) {
+    constraint(lander, lj[0], left_leg, left_leg_joint_1);
+    constraint(lander, lj[1], left_leg, left_leg_joint_2);
+    constraint(lander, lj[2], right_leg, right_leg_joint_1);
+    constraint(lander, lj[3], right_leg, right_leg_joint_2);
+  }
   right_leg.angvel = right_leg.angvel * P.leg_damping;
   left_leg.angvel = left_leg.angvel * P.leg_damping;
 }

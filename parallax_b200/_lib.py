@@ -133,6 +133,7 @@ class LunarParams(C.Structure):
         ("reset_v", C.c_float),
         ("reset_w", C.c_float),
         ("philox_seed", C.c_uint32 * 2),
+        ("solver_loops", C.c_int32),
     ]
 
     def copy(self) -> "LunarParams":

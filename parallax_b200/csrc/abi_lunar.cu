@@ -226,6 +226,7 @@ int cotix_lunar_default_params(CotixLunarParams* p) {
   p->reset_w = 0.8660254f;
   p->philox_seed[0] = 0x243F6A88u;
   p->philox_seed[1] = 0x85A308D3u;
+  p->solver_loops = 1;
   return COTIX_OK;
 }
 
@@ -234,6 +235,7 @@ static int check_params(const CotixLunarParams* p) {
   if (p->rng_mode != COTIX_RNG_THREEFRY && p->rng_mode != COTIX_RNG_PHILOX) return 0;
   if (p->substeps < 1 || p->substeps > 1024) return 0;
   if (p->gjk_max_iters < 0) return 0;
+  if (p->solver_loops < 1 || p->solver_loops > 64) return 0;
   return 1;
 }
 
@@ -368,7 +370,8 @@ int cotix_lunar_step_bwd(void* stream, int64_t B, const float* state_in, const f
                          float* g_action, uint32_t* flags, const CotixLunarParams* p) {
   CXL_REQUIRE(B >= 0 && ld >= B, "bad batch size / leading dimension");
   CXL_REQUIRE(check_params(p), "bad params");
-  CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
+  CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0 && p->solver_loops == 1,
+              "the adjoint needs substeps == 1, auto_reset == 0 and solver_loops == 1");
   CXL_REQUIRE(B == 0 || (state_in && g_out && g_in), "null state / cotangent");
   return cx_launch_lunar_step_bwd((cudaStream_t)stream, B, state_in, state_next, ld, action, g_out, g_in,
                                   g_action, flags, nullptr, nullptr, p);
@@ -443,7 +446,8 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
                             int32_t jacobians) {
   CXL_REQUIRE(B >= 0 && ld >= B && T >= 0, "bad batch size / leading dimension / step count");
   CXL_REQUIRE(check_params(p), "bad params");
-  CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0, "the adjoint needs substeps == 1 and auto_reset == 0");
+  CXL_REQUIRE(p->substeps <= 1 && p->auto_reset == 0 && p->solver_loops == 1,
+              "the adjoint needs substeps == 1, auto_reset == 0 and solver_loops == 1");
   CXL_REQUIRE(B == 0 || (tape && g), "null tape / cotangent");
   const int64_t slot = (int64_t)COTIX_LUNAR_NF * ld;
   const int64_t dslot = (int64_t)COTIX_ADJ_TAPE_WORDS * ld;

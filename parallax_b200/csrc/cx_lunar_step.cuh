@@ -495,10 +495,15 @@ CX_DEV void finish_step(EnvRegs& E, const CotixLunarParams& P, const float cs[3]
     V2 ll2 = ll1 + rot_cs(j2l, cs[2], sn[2]);
     V2 rl1 = mk2(E.b[1].px, E.b[1].py);
     V2 rl2 = rl1 + rot_cs(j2l, cs[1], sn[1]);
-    joint_constraint(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
-    joint_constraint(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
-    joint_constraint(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
-    joint_constraint(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
+    // SimpleConstraintSolver.solve (cotix/_constraint_solvers.py:13-17): `loops` sequential passes
+    // over the constraint list; the anchors are those of the step (positions do not move here)
+    const int loops = P.solver_loops < 1 ? 1 : P.solver_loops;
+    for (int it = 0; it < loops; ++it) {
+      joint_constraint(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
+      joint_constraint(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
+      joint_constraint(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
+      joint_constraint(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
+    }
     E.b[1].w = E.b[1].w * P.leg_damping;
     E.b[2].w = E.b[2].w * P.leg_damping;
   }

@@ -641,6 +641,14 @@ void profile_collect() {
   g_ev_pending = false;
 }
 
+// ---- timeline of a multi-range enqueue (measurement aid, eager launches only): an event after every
+// kernel of every range; read back as milliseconds since the fork (cx_lunar_pipeline_trace_read)
+constexpr int TR_STEPS = 8, TR_STAGES = 5;
+bool g_trace = false;
+cudaEvent_t g_tr_base = nullptr;
+cudaEvent_t g_tr_ev[COTIX_MAX_CHUNKS][TR_STEPS][TR_STAGES];
+int g_tr_S = 0, g_tr_T = 0;
+
 // ---- launch configuration (cotix_lunar_pipeline_config) ------------------------------------
 // The two sparse stages (narrow, contact) are bound by the latency of their slowest work item
 // (about 32 us each however short the queue) and leave most of the GPU idle; the two dense stages
@@ -832,6 +840,20 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
   // the chain of one range: per step and sub-step 1 memset + 4 kernels, then the reset stage.
   // Stages 2..5 are launched with programmatic stream serialization: their blocks may be set up
   // while the previous stage drains, and wait in cudaGridDependencySynchronize() for its results.
+  const bool trace = g_trace && !prof && K == 1 && q.n_steps <= TR_STEPS;
+  if (trace) {
+    if (!g_tr_base) {
+      cudaEventCreate(&g_tr_base);
+      for (auto& a : g_tr_ev)
+        for (auto& b : a)
+          for (auto& e : b) cudaEventCreate(&e);
+    }
+    g_tr_S = plan.S;
+    g_tr_T = q.n_steps;
+    cudaEventRecord(g_tr_base, st);
+  }
+#define CX_TRACE(stage, stream) \
+  if (trace) cudaEventRecord(g_tr_ev[r][t][stage], stream)
   auto chain = [&](cudaStream_t cs, int r) -> int {
     const int64_t off = plan.off[r], n = plan.off[r + 1] - off;
     const PipeWs& ws = plan.ws[r];
@@ -879,20 +901,24 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         cudaLaunchKernelEx(&cfg, pipe_integrate_kernel, n, k == 0 ? sin_ : (const float*)sout, sout, ld, act, *p, D, ws,
                            k, K);
         CX_MARK_E(0, cs);
+        CX_TRACE(0, cs);
         CX_MARK_B(1, cs);
         set_attrs(true, true);
         cfg.gridDim = dim3(qgrid((int64_t)ws.cap));
         cudaLaunchKernelEx(&cfg, pipe_narrow_kernel, *p, D, ws);
         CX_MARK_E(1, cs);
+        CX_TRACE(1, cs);
         CX_MARK_B(2, cs);
         cfg.gridDim = dim3(qgrid(n));
         cudaLaunchKernelEx(&cfg, pipe_contact_kernel, sout, ld, *p, D, ws);
         CX_MARK_E(2, cs);
+        CX_TRACE(2, cs);
         CX_MARK_B(3, cs);
         set_attrs(true, false);
         cfg.gridDim = dim3(env_blocks);
         cudaLaunchKernelEx(&cfg, pipe_finish_kernel, n, sout, ld, act, rw, dn, ob, *p, ws, k, K);
         CX_MARK_E(3, cs);
+        CX_TRACE(3, cs);
       }
       CX_MARK_B(4, cs);
       if (p->auto_reset) {
@@ -901,6 +927,7 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         cudaLaunchKernelEx(&cfg, pipe_reset_kernel, sout, ld, ob, *p, ws);
       }
       CX_MARK_E(4, cs);
+      CX_TRACE(4, cs);
       CX_MARK_E(5, cs);
     }
     if (post && *post) {
@@ -911,6 +938,7 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
   };
 #undef CX_MARK_B
 #undef CX_MARK_E
+#undef CX_TRACE
   int rc = 0;
   if (plan.S == 1) {
     rc = chain(st, 0);
@@ -995,6 +1023,30 @@ extern "C" int cx_lunar_pipeline_counters(cudaStream_t st, int64_t B, const void
     for (int i = 0; i < 5; ++i) out[i] += c[i];
   }
   return COTIX_OK;
+}
+
+// timeline of the last traced enqueue: out[(r * T + t) * 5 + stage] = ms from the fork to the END of
+// that kernel; returns S * T (0 when nothing was traced).  Synchronises.
+extern "C" int cx_lunar_pipeline_trace(int enable) {
+  g_trace = enable != 0;
+  return COTIX_OK;
+}
+extern "C" int cx_lunar_pipeline_trace_read(float* out, int* S, int* T) {
+  *S = g_tr_S;
+  *T = g_tr_T;
+  if (!g_tr_base || g_tr_S == 0) return 0;
+  cudaDeviceSynchronize();
+  for (int r = 0; r < g_tr_S; ++r)
+    for (int t = 0; t < g_tr_T; ++t)
+      for (int k = 0; k < TR_STAGES; ++k) {
+        float ms = -1.0f;
+        if (cudaEventElapsedTime(&ms, g_tr_base, g_tr_ev[r][t][k]) != cudaSuccess) {
+          cudaGetLastError();
+          ms = -1.0f;
+        }
+        out[(r * g_tr_T + t) * TR_STAGES + k] = ms;
+      }
+  return g_tr_S * g_tr_T;
 }
 
 // ---- per-stage timing (single-threaded use: bench.py) ----------------------------------------

@@ -22,8 +22,8 @@ from __future__ import annotations
 from dataclasses import dataclass, replace
 
 import numpy as np
-import torch
 
+from . import _xp
 from . import lunar_lander as ll
 from ._lib import LunarParams
 
@@ -137,7 +137,7 @@ class LunarWorldState:
 class ThrottleSignal:
     """A control signal: the [2, B] (main, side) throttle applied during a forward step."""
 
-    def __init__(self, action: torch.Tensor | None):
+    def __init__(self, action):
         self.action = action
 
 
@@ -162,8 +162,8 @@ class LunarJudge:
 
     CODES = {0: "running", 1: "crash", 2: "out_of_bounds", 3: "landed", 4: "timeout", 5: "nan"}
 
-    def is_done(self, done: torch.Tensor) -> torch.Tensor:
-        return done != 0
+    def is_done(self, done):
+        return (done.numpy() != 0) if hasattr(done, "is_native") else (done != 0)
 
 
 class LunarWorld:
@@ -202,15 +202,29 @@ class LunarEnvironment:
         dt = time_per_nfe / float(WFE_scale)
         st, control = self.state, self.control
         B = st.state.batch
-        dev = st.state.data.device
-        total = torch.zeros(B, dtype=torch.float32, device=dev)
-        finished = torch.zeros(B, dtype=torch.bool, device=dev)
+        xp = _xp.backend_of(st.state.data)
+        if xp.name == "torch":
+            torch = xp.torch
+            total = torch.zeros(B, dtype=torch.float32, device=xp.device)
+            finished = torch.zeros(B, dtype=torch.bool, device=xp.device)
+        else:  # torch-free: the two per-env selects of the carry run on the host
+            total = np.zeros(B, np.float32)
+            finished = np.zeros(B, bool)
         for _ in range(int(num_NFEs)):
-            dense_fn, _new_control = control(st)
+            # one NFE: `dense_control_approximation_fn, new_control = control(state)`; the new
+            # control is what the next NFE calls (the carry of cotix/_envs.py:40,43,117)
+            dense_fn, new_control = control(st)
             nxt, reward, done = self.world.forward(st, dense_fn(st), dt, substeps=WFE_scale)
             keep = finished
-            total = total + torch.where(keep, torch.zeros_like(reward), reward)
-            data = torch.where(keep[None, :], st.state.data, nxt.state.data)
+            if xp.name == "torch":
+                total = total + torch.where(keep, torch.zeros_like(reward), reward)
+                data = torch.where(keep[None, :], st.state.data, nxt.state.data)
+            else:
+                total = total + np.where(keep, np.float32(0), reward.numpy())
+                data = xp.asarray(np.where(keep[None, :], st.state.numpy(), nxt.state.numpy()), np.float32)
             st = LunarWorldState(nxt.time, ll.LunarState(data), st.params)
             finished = finished | self.judge.is_done(done)
+            control = new_control
+        # like the reference, only the state is written back: "we don't update control, since it
+        # could have 'jumps' between evals" (cotix/_envs.py:126-131)
         return replace(self, state=st), total

@@ -15,9 +15,8 @@ import ctypes as C
 from dataclasses import dataclass, field
 
 import numpy as np
-import torch
 
-from . import _lib
+from . import _lib, _xp
 from ._lib import SceneParams
 
 REC = 16
@@ -156,8 +155,8 @@ def robocup_scene(n_robots: int = 0, areas_collide: bool = True, robot_radius: f
 
 class Scene:
     """Device-resident static scene + the batched step.  `state` is a [nb * 6, B] float32 device
-    tensor (rows 6b..6b+5 = px, py, vx, vy, angle, angular_velocity of body b), `keys` a [2, B]
-    int32 device tensor holding the uint32 key words."""
+    array (rows 6b..6b+5 = px, py, vx, vy, angle, angular_velocity of body b), `keys` a [2, B]
+    int32 / uint32 device array holding the key words; torch tensors or `devmem.DeviceArray`."""
 
     def __init__(self, spec: SceneSpec, device: int = 0):
         self.spec = spec
@@ -187,27 +186,28 @@ class Scene:
         return {"groups": ng.value, "group_sizes": list(sizes)[:ng.value], "distinct_pairs": npairs.value,
                 "reference_evaluations": ev.value}
 
-    def initial_state(self, B: int) -> torch.Tensor:
-        s = torch.from_numpy(np.ascontiguousarray(self.spec.init_state.reshape(-1, 1).repeat(B, axis=1)))
-        return s.to(f"cuda:{self.device}")
+    def initial_state(self, B: int, backend: str = "cuda"):
+        """[nb * 6, B] initial state on this scene's device (backend "cuda" = torch, "native")."""
+        s = np.ascontiguousarray(self.spec.init_state.reshape(-1, 1).repeat(B, axis=1), np.float32)
+        return _xp.backend_for(f"{backend}:{self.device}").asarray(s, np.float32)
 
-    def step(self, state: torch.Tensor, keys: torch.Tensor, params: SceneParams | None = None,
-             want_cells: bool = False):
+    def step(self, state, keys, params: SceneParams | None = None, want_cells: bool = False):
         """In place on `state` and (with `advance_key`) `keys`.  Returns (cell [nb*nb, B] uint8,
         chosen [nb, B] int32, status [B] int32) when `want_cells`, else None."""
         params = params or default_params()
         nb = self.spec.nb
-        assert state.dtype == torch.float32 and state.shape[0] == nb * 6 and state.is_contiguous()
+        xp = _xp.backend_of(state)
+        assert state.shape[0] == nb * 6 and state.is_contiguous()
         B = state.shape[1]
-        assert keys.shape == (2, B) and keys.dtype == torch.int32 and keys.is_contiguous()
+        assert tuple(keys.shape) == (2, B) and keys.is_contiguous()
         cell = chosen = status = None
         if want_cells:
-            cell = torch.empty((nb * nb, B), dtype=torch.uint8, device=state.device)
-            chosen = torch.empty((nb, B), dtype=torch.int32, device=state.device)
-            status = torch.empty(B, dtype=torch.int32, device=state.device)
-        with torch.cuda.device(state.device):
+            cell = xp.empty((nb * nb, B), np.uint8)
+            chosen = xp.empty((nb, B), np.int32)
+            status = xp.empty((B,), np.int32)
+        with xp.device_ctx():
             _lib.check(_lib.lib().cotix_scene_step(
-                torch.cuda.current_stream(state.device).cuda_stream, self._h, B, state.data_ptr(), B,
+                xp.stream_ptr(), self._h, B, state.data_ptr(), B,
                 keys.data_ptr(), C.byref(params), cell.data_ptr() if want_cells else None,
                 chosen.data_ptr() if want_cells else None, status.data_ptr() if want_cells else None))
         return (cell, chosen, status) if want_cells else None

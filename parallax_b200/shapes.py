@@ -4,30 +4,37 @@ Same names and argument meaning as the reference (`cotix/_convex_shapes.py` Circ
 AABB :50-133, Polygon :197-229; `cotix/_contacts.py` ContactInfo :11-27 and the six
 `*_vs_*` functions :30-315), but every object is a BATCH of N shapes stored as [N, 16] float32
 shape records on the GPU (layout: include/cotix_b200.h), and every contact function is one
-launch of the narrowphase kernel through the C-ABI.  torch is used only to own device memory
-and streams.
+launch of the narrowphase kernel through the C-ABI.  Device memory is a torch tensor or a
+`devmem.DeviceArray` (`device="native"`, no torch needed — `_xp`); records are assembled on the host
+from numpy inputs, on the device from torch inputs.
 """
 from __future__ import annotations
 
 import ctypes as C
 
 import numpy as np
-import torch
 
-from . import _lib
+from . import _lib, _xp
 
 REC = 16
 CIRCLE, AABB_T, POLYGON = 0, 1, 2
 
 
-def _dev_f32(x, device):
-    if isinstance(x, torch.Tensor):
-        return x.to(device=device, dtype=torch.float32)
-    return torch.as_tensor(np.asarray(x, dtype=np.float32), device=device)
+def _np_f32(x) -> np.ndarray:
+    if _xp.is_torch(x):
+        x = x.detach().cpu().numpy()
+    elif hasattr(x, "is_native"):
+        x = x.numpy()
+    return np.asarray(x, dtype=np.float32)
 
 
-def _stream_ptr(device) -> int:
-    return torch.cuda.current_stream(device).cuda_stream
+def _device_of(x, device):
+    """Inputs that already live on a device keep it; otherwise the `device=` argument decides."""
+    if _xp.is_torch(x) and x.is_cuda:
+        return x.device
+    if hasattr(x, "is_native"):
+        return int(x.device)
+    return device
 
 
 class ShapeBatch:
@@ -35,9 +42,10 @@ class ShapeBatch:
 
     type_id = -1
 
-    def __init__(self, recs: torch.Tensor):
-        assert recs.is_cuda and recs.dtype == torch.float32 and recs.shape[-1] == REC
+    def __init__(self, recs):
+        assert recs.shape[-1] == REC and recs.dim() == 2
         self.recs = recs.contiguous()
+        self.xp = _xp.backend_of(self.recs)
 
     def __len__(self):
         return self.recs.shape[0]
@@ -46,14 +54,32 @@ class ShapeBatch:
     def device(self):
         return self.recs.device
 
+    def numpy(self) -> np.ndarray:
+        return self.xp.to_numpy(self.recs)
+
     def get_support(self, direction):
         """get_support for one direction per shape -> [N, 2] (reference: get_support)."""
-        d = _dev_f32(direction, self.device).reshape(-1, 2).contiguous()
-        out = torch.empty_like(d)
-        with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().cotix_support(_stream_ptr(self.device), len(self), self.recs.data_ptr(),
+        xp = self.xp
+        d = xp.asarray(_np_f32(direction).reshape(-1, 2) if not _same_backend(direction, xp) else direction,
+                       np.float32).reshape(-1, 2).contiguous()
+        out = xp.empty((d.shape[0], 2), np.float32)
+        with xp.device_ctx():
+            _lib.check(_lib.lib().cotix_support(xp.stream_ptr(), len(self), self.recs.data_ptr(),
                                                 d.data_ptr(), out.data_ptr()))
         return out
+
+    def _rebuilt(self, recs_host: np.ndarray):
+        out = type(self).__new__(type(self))
+        ShapeBatch.__init__(out, self.xp.asarray(recs_host, np.float32))
+        return out
+
+
+def _same_backend(x, xp) -> bool:
+    return (xp.name == "torch" and _xp.is_torch(x)) or (xp.name == "native" and hasattr(x, "is_native"))
+
+
+def _upload(recs_host: np.ndarray, device):
+    return _xp.backend_for(device).asarray(np.ascontiguousarray(recs_host, np.float32), np.float32)
 
 
 class Circle(ShapeBatch):
@@ -62,28 +88,27 @@ class Circle(ShapeBatch):
     type_id = CIRCLE
 
     def __init__(self, radius, position, device="cuda"):
-        radius = _dev_f32(radius, device).reshape(-1)
-        position = _dev_f32(position, device).reshape(-1, 2)
-        r = torch.zeros((radius.shape[0], REC), dtype=torch.float32, device=radius.device)
+        device = _device_of(radius, device)
+        radius = _np_f32(radius).reshape(-1)
+        position = _np_f32(position).reshape(-1, 2)
+        r = np.zeros((radius.shape[0], REC), np.float32)
         r[:, 0] = CIRCLE
         r[:, 2] = radius
         r[:, 4:6] = position
-        super().__init__(r)
+        super().__init__(_upload(r, device))
 
     @property
     def radius(self):
-        return self.recs[:, 2]
+        return self.recs[:, 2] if self.xp.name == "torch" else self.numpy()[:, 2]
 
     @property
     def position(self):
-        return self.recs[:, 4:6]
+        return self.recs[:, 4:6] if self.xp.name == "torch" else self.numpy()[:, 4:6]
 
     def move(self, delta):
-        out = Circle.__new__(Circle)
-        r = self.recs.clone()
-        r[:, 4:6] += _dev_f32(delta, self.device).reshape(-1, 2)
-        ShapeBatch.__init__(out, r)
-        return out
+        r = self.numpy().copy()
+        r[:, 4:6] += _np_f32(delta).reshape(-1, 2)
+        return self._rebuilt(r)
 
 
 class AABB(ShapeBatch):
@@ -92,30 +117,29 @@ class AABB(ShapeBatch):
     type_id = AABB_T
 
     def __init__(self, lower, upper, device="cuda"):
-        lower = _dev_f32(lower, device).reshape(-1, 2)
-        upper = _dev_f32(upper, device).reshape(-1, 2)
-        r = torch.zeros((lower.shape[0], REC), dtype=torch.float32, device=lower.device)
+        device = _device_of(lower, device)
+        lower = _np_f32(lower).reshape(-1, 2)
+        upper = _np_f32(upper).reshape(-1, 2)
+        r = np.zeros((lower.shape[0], REC), np.float32)
         r[:, 0] = AABB_T
         r[:, 4:6] = lower
         r[:, 6:8] = upper
-        super().__init__(r)
+        super().__init__(_upload(r, device))
 
     @property
     def lower(self):
-        return self.recs[:, 4:6]
+        return self.recs[:, 4:6] if self.xp.name == "torch" else self.numpy()[:, 4:6]
 
     @property
     def upper(self):
-        return self.recs[:, 6:8]
+        return self.recs[:, 6:8] if self.xp.name == "torch" else self.numpy()[:, 6:8]
 
     def move(self, delta):
-        out = AABB.__new__(AABB)
-        r = self.recs.clone()
-        d = _dev_f32(delta, self.device).reshape(-1, 2)
+        r = self.numpy().copy()
+        d = _np_f32(delta).reshape(-1, 2)
         r[:, 4:6] += d
         r[:, 6:8] += d
-        ShapeBatch.__init__(out, r)
-        return out
+        return self._rebuilt(r)
 
 
 class Polygon(ShapeBatch):
@@ -128,33 +152,45 @@ class Polygon(ShapeBatch):
     type_id = POLYGON
 
     def __init__(self, vertices, device="cuda", n=None):
-        v = _dev_f32(vertices, device)
-        if v.dim() == 2:
+        device = _device_of(vertices, device)
+        v = _np_f32(vertices)
+        if v.ndim == 2:
             v = v[None]
         N, nv = v.shape[0], v.shape[1]
         if not 1 <= nv <= 6:
             raise ValueError("Polygon supports up to 6 vertices")
-        r = torch.zeros((N, REC), dtype=torch.float32, device=v.device)
+        r = np.zeros((N, REC), np.float32)
         r[:, 0] = POLYGON
-        r[:, 1] = float(nv) if n is None else _dev_f32(n, device)
+        r[:, 1] = float(nv) if n is None else _np_f32(n)
         r[:, 4:4 + 2 * nv] = v.reshape(N, -1)
-        with torch.cuda.device(r.device):
-            _lib.check(_lib.lib().cotix_order_clockwise(_stream_ptr(r.device), N, r.data_ptr()))
-        super().__init__(r)
+        recs = _upload(r, device)
+        xp = _xp.backend_of(recs)
+        with xp.device_ctx():
+            _lib.check(_lib.lib().cotix_order_clockwise(xp.stream_ptr(), N, recs.data_ptr()))
+        super().__init__(recs)
 
     @property
     def vertices(self):
-        n = int(self.recs[0, 1].item()) if len(self) else 0
-        return self.recs[:, 4:4 + 2 * n].reshape(len(self), n, 2)
+        if not len(self):
+            return self.recs[:, 4:4].reshape(0, 0, 2) if self.xp.name == "torch" else np.zeros((0, 0, 2), np.float32)
+        if self.xp.name == "torch":
+            n = int(self.recs[0, 1].item())
+            return self.recs[:, 4:4 + 2 * n].reshape(len(self), n, 2)
+        h = self.numpy()
+        n = int(h[0, 1])
+        return h[:, 4:4 + 2 * n].reshape(len(self), n, 2)
 
     def move(self, delta):
-        d = _dev_f32(delta, self.device).reshape(-1, 1, 2)
-        return Polygon(self.vertices + d, device=self.device)
+        d = _np_f32(delta).reshape(-1, 1, 2)
+        return Polygon(_np_f32(self.vertices) + d, device=_device_of(self.recs, "cuda"))
 
 
 def from_records(recs, device="cuda") -> ShapeBatch:
-    """Wrap raw [N, 16] records (polygons must already be in order_clockwise order)."""
-    return ShapeBatch(_dev_f32(recs, device).reshape(-1, REC))
+    """Wrap raw [N, 16] records (polygons must already be in order_clockwise order): a numpy array
+    is uploaded to `device`; a device array (torch / DeviceArray) is used as it is."""
+    if _xp.is_torch(recs) and recs.is_cuda or hasattr(recs, "is_native"):
+        return ShapeBatch(recs.reshape(-1, REC))
+    return ShapeBatch(_upload(_np_f32(recs).reshape(-1, REC), device))
 
 
 class ContactInfo:
@@ -166,27 +202,51 @@ class ContactInfo:
     def __init__(self, penetration_vector, contact_point, exists=None, status=None):
         self.penetration_vector = penetration_vector
         self.contact_point = contact_point
-        self.exists = exists if exists is not None else ~torch.isnan(contact_point).any(-1)
+        self.exists = exists if exists is not None else ~self._isnan(contact_point)
         self.status = status
 
+    @staticmethod
+    def _isnan(cp):
+        if _xp.is_torch(cp):
+            import torch
+
+            return torch.isnan(cp).any(-1)
+        return np.isnan(cp.numpy() if hasattr(cp, "is_native") else np.asarray(cp)).any(-1)
+
     def isnan(self):
-        return torch.isnan(self.contact_point).any(-1)
+        return self._isnan(self.contact_point)
 
     def invert(self):
-        return ContactInfo(-self.penetration_vector, self.contact_point, self.exists, self.status)
+        pv = self.penetration_vector
+        if hasattr(pv, "is_native"):
+            pv = _xp.backend_of(pv).asarray(-pv.numpy(), np.float32)
+        else:
+            pv = -pv
+        return ContactInfo(pv, self.contact_point, self.exists, self.status)
+
+    def numpy(self):
+        """(exists, penetration_vector, contact_point, status) as host numpy arrays."""
+        def h(x):
+            if x is None:
+                return None
+            return x.numpy() if hasattr(x, "is_native") else (x.detach().cpu().numpy() if _xp.is_torch(x) else np.asarray(x))
+        return h(self.exists), h(self.penetration_vector), h(self.contact_point), h(self.status)
 
 
 SWEEP_PIPELINE_MIN_PAIRS = 65536
 _sweep_ws: dict = {}
 
 
-def _sweep_workspace(device, n: int) -> torch.Tensor:
-    key = (device.index, n)
+def _sweep_workspace(xp, n: int):
+    key = (xp.name, xp.device_index(), n)
     ws = _sweep_ws.get(key)
     if ws is None:
         nbytes = int(_lib.lib().cotix_narrowphase_workspace_bytes(n))
+        if any(k[0] == "native" for k in _sweep_ws):
+            xp.synchronize()
         _sweep_ws.clear()
-        ws = torch.empty(nbytes + 256, dtype=torch.uint8, device=device)
+        with xp.device_ctx():
+            ws = xp.empty((nbytes + 256,), np.uint8)
         _sweep_ws[key] = ws
     return ws
 
@@ -199,24 +259,24 @@ def narrowphase(a: ShapeBatch, b: ShapeBatch, params: _lib.NarrowParams | None =
     Identical results."""
     if len(a) != len(b):
         raise ValueError("shape batches differ in length")
-    dev = a.device
+    xp = a.xp
     n = len(a)
     params = params or _lib.default_narrow_params()
-    exists = torch.empty(n, dtype=torch.uint8, device=dev)
-    pen = torch.empty((n, 2), dtype=torch.float32, device=dev)
-    cp = torch.empty((n, 2), dtype=torch.float32, device=dev)
-    status = torch.empty(n, dtype=torch.uint8, device=dev)
+    exists = xp.empty((n,), np.uint8)
+    pen = xp.empty((n, 2), np.float32)
+    cp = xp.empty((n, 2), np.float32)
+    status = xp.empty((n,), np.uint8)
     use_pipe = mode == "pipeline" or (mode == "auto" and n >= SWEEP_PIPELINE_MIN_PAIRS)
-    with torch.cuda.device(dev):
-        args = (_stream_ptr(dev), n, a.recs.data_ptr(), b.recs.data_ptr(), exists.data_ptr(), pen.data_ptr(),
+    with xp.device_ctx():
+        args = (xp.stream_ptr(), n, a.recs.data_ptr(), b.recs.data_ptr(), exists.data_ptr(), pen.data_ptr(),
                 cp.data_ptr(), status.data_ptr(), C.byref(params))
         if use_pipe and n > 0:
-            ws = _sweep_workspace(dev, n)
+            ws = _sweep_workspace(xp, n)
             wp = (ws.data_ptr() + 255) & ~255
             _lib.check(_lib.lib().cotix_narrowphase_ws(*args, wp, ws.numel() - (wp - ws.data_ptr())))
         else:
             _lib.check(_lib.lib().cotix_narrowphase(*args))
-    return ContactInfo(pen, cp, exists.bool(), status)
+    return ContactInfo(pen, cp, exists.bool() if xp.name == "torch" else exists, status)
 
 
 def _typed(fn_name, ta, tb):

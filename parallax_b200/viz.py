@@ -13,9 +13,8 @@ from __future__ import annotations
 import ctypes as C
 
 import numpy as np
-import torch
 
-from . import _lib
+from . import _lib, _xp
 from ._lib import LunarParams
 
 IMG_W, IMG_H, PRIM_WORDS = 800, 600, 16
@@ -53,7 +52,7 @@ class Painter:
     the GPU onto a black frame and returns it ([600, 800, 3] uint8 device tensor)."""
 
     def __init__(self, device="cuda"):
-        self.device = torch.device(device)
+        self.device = device
         self._prims: list[list[int]] = []
 
     def setup(self) -> None:  # PyPainter.setup: nothing to open
@@ -79,7 +78,7 @@ class Painter:
         """the queued draw calls as records, int32 [n, 16] (include/cotix_b200.h)"""
         return np.asarray(self._prims, dtype=np.int32).reshape(-1, PRIM_WORDS)
 
-    def next(self) -> torch.Tensor:
+    def next(self):
         """PyPainter.next (cotix/_viz.py:43-49): present the frame, start the next one black."""
         prims = self.primitives()
         self._prims = []
@@ -89,70 +88,91 @@ class Painter:
         env.draw(self)
 
 
-def raster_draw(prims, counts=None, device="cuda") -> torch.Tensor:
-    """prims int32 [n_img, max_prims, 16] (numpy or device tensor) -> uint8 [n_img, 600, 800, 3] on
+def _to_host(x):
+    if _xp.is_torch(x):
+        return x.detach().cpu().numpy()
+    if hasattr(x, "is_native"):
+        return x.numpy()
+    return np.asarray(x)
+
+
+def _on_device(x, dtype, xp):
+    """numpy / torch / DeviceArray -> contiguous array of `dtype` on backend xp's device"""
+    if (xp.name == "torch" and _xp.is_torch(x)) or (xp.name == "native" and hasattr(x, "is_native")):
+        return xp.asarray(x, dtype).contiguous()
+    return xp.asarray(np.ascontiguousarray(_to_host(x), dtype=dtype), dtype)
+
+
+def raster_draw(prims, counts=None, device="cuda"):
+    """prims int32 [n_img, max_prims, 16] (numpy or device array) -> uint8 [n_img, 600, 800, 3] on
     the device: every image painted in list order onto black (`cotix_raster_draw`)."""
-    if not isinstance(prims, torch.Tensor):
-        prims = torch.from_numpy(np.ascontiguousarray(prims, dtype=np.int32))
-    prims = prims.to(device=device, dtype=torch.int32).contiguous()
+    if _xp.is_torch(prims) and prims.is_cuda or hasattr(prims, "is_native"):
+        xp = _xp.backend_of(prims)
+    else:
+        xp = _xp.backend_for(device)
+    prims = _on_device(prims, np.int32, xp)
     n, mp = int(prims.shape[0]), int(prims.shape[1])
     assert prims.dim() == 3 and prims.shape[2] == PRIM_WORDS
     if counts is not None:
-        if not isinstance(counts, torch.Tensor):
-            counts = torch.from_numpy(np.ascontiguousarray(counts, dtype=np.int32))
-        counts = counts.to(device=prims.device, dtype=torch.int32).contiguous()
-    img = torch.empty((n, IMG_H, IMG_W, 3), dtype=torch.uint8, device=prims.device)
-    with torch.cuda.device(prims.device):
+        counts = _on_device(counts, np.int32, xp)
+    img = xp.empty((n, IMG_H, IMG_W, 3), np.uint8)
+    with xp.device_ctx():
         _lib.check(_lib.lib().cotix_raster_draw(
-            torch.cuda.current_stream(prims.device).cuda_stream, n, prims.data_ptr() if mp else None,
+            xp.stream_ptr(), n, prims.data_ptr() if mp else None,
             counts.data_ptr() if counts is not None else None, mp, img.data_ptr()))
+        if xp.name == "native":
+            xp.synchronize()  # temporaries are dropped on return
     return img
 
 
-def _index(env_index, device):
+def _index(env_index, xp):
     if env_index is None:
         return None
-    if not isinstance(env_index, torch.Tensor):
-        env_index = torch.from_numpy(np.ascontiguousarray(env_index, dtype=np.int64))
-    return env_index.to(device=device, dtype=torch.int64).contiguous()
+    return _on_device(env_index, np.int64, xp)
 
 
-def render_lunar(state, env_index=None, params: LunarParams | None = None) -> torch.Tensor:
+def render_lunar(state, env_index=None, params: LunarParams | None = None):
     """`env.draw(painter); painter.next()` for LunarLander envs (cotix/_lunar_lander.py:220-225):
     uint8 [n_img, 600, 800, 3]; image i shows env env_index[i] (default: every env of `state`)."""
     from . import lunar_lander as ll
 
     params = params or ll.default_params()
     d = state.data
-    idx = _index(env_index, d.device)
+    xp = _xp.backend_of(d)
+    idx = _index(env_index, xp)
     n = int(idx.numel()) if idx is not None else int(d.shape[1])
-    img = torch.empty((n, IMG_H, IMG_W, 3), dtype=torch.uint8, device=d.device)
-    with torch.cuda.device(d.device):
+    img = xp.empty((n, IMG_H, IMG_W, 3), np.uint8)
+    with xp.device_ctx():
         _lib.check(_lib.lib().cotix_lunar_draw(
-            torch.cuda.current_stream(d.device).cuda_stream, n, d.data_ptr(), d.stride(0),
+            xp.stream_ptr(), n, d.data_ptr(), d.stride(0),
             idx.data_ptr() if idx is not None else None, img.data_ptr(), C.byref(params)))
+        if xp.name == "native":
+            xp.synchronize()
     return img
 
 
-def lunar_primitives(state, env_index=None, params: LunarParams | None = None) -> torch.Tensor:
+def lunar_primitives(state, env_index=None, params: LunarParams | None = None):
     """the 44 draw calls of LunarLander.draw per env as primitive records, int32 [n_img, 44, 16]"""
     from . import lunar_lander as ll
 
     params = params or ll.default_params()
     d = state.data
-    idx = _index(env_index, d.device)
+    xp = _xp.backend_of(d)
+    idx = _index(env_index, xp)
     n = int(idx.numel()) if idx is not None else int(d.shape[1])
-    prims = torch.empty((n, LUNAR_PRIMS, PRIM_WORDS), dtype=torch.int32, device=d.device)
-    with torch.cuda.device(d.device):
+    prims = xp.empty((n, LUNAR_PRIMS, PRIM_WORDS), np.int32)
+    with xp.device_ctx():
         _lib.check(_lib.lib().cotix_lunar_prims(
-            torch.cuda.current_stream(d.device).cuda_stream, n, d.data_ptr(), d.stride(0),
+            xp.stream_ptr(), n, d.data_ptr(), d.stride(0),
             idx.data_ptr() if idx is not None else None, prims.data_ptr(), C.byref(params)))
+        if xp.name == "native":
+            xp.synchronize()
     return prims
 
 
 def write_ppm(path: str, image) -> None:
     """one frame ([600, 800, 3] uint8, tensor or array) as a binary PPM file"""
-    a = image.detach().cpu().numpy() if isinstance(image, torch.Tensor) else np.asarray(image)
+    a = _to_host(image)
     assert a.dtype == np.uint8 and a.ndim == 3 and a.shape[2] == 3
     with open(path, "wb") as f:
         f.write(b"P6\n%d %d\n255\n" % (a.shape[1], a.shape[0]))
@@ -166,7 +186,7 @@ def scene_primitives(spec, state, env_index=None) -> np.ndarray:
     four edges (`AABB.draw` -> `drawEdges`, cotix/_convex_shapes.py:119-133; translated by the body
     position only, :113-117), a circle part a filled circle (:43-44).  `state` is the scene state
     [nb * 6, B] (tensor or array), `spec.draw_list` says what each body paints."""
-    s = state.detach().cpu().numpy() if isinstance(state, torch.Tensor) else np.asarray(state, np.float32)
+    s = np.asarray(_to_host(state), np.float32)
     idx = np.arange(s.shape[1]) if env_index is None else np.asarray(env_index, np.int64)
     f = np.float32
 
@@ -203,6 +223,6 @@ def scene_primitives(spec, state, env_index=None) -> np.ndarray:
     return np.stack(cols, 1)
 
 
-def render_scene(spec, state, env_index=None, device="cuda") -> torch.Tensor:
+def render_scene(spec, state, env_index=None, device="cuda"):
     """frames of a generic scene (e.g. RoboCup), uint8 [n_img, 600, 800, 3] on the device"""
     return raster_draw(scene_primitives(spec, state, env_index), device=device)
