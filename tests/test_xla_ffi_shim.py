@@ -129,15 +129,15 @@ def test_shim_handlers_execute_and_match_ctypes_path(cuda_lib, tmp_path):
     ro = ll.rollout(ll.LunarState(sd), ad, T, P0, mode="fused")
     eq(tape, ro.tape, "tape")
     gf = torch.from_numpy(rng.normal(size=(18, Bd)).astype(np.float32)).cuda()
-    aws = ll.adjoint_workspace(Bd, T, sd.device)
+    aws = ll.adjoint_workspace(Bd, T, sd.device, jacobians=False)  # decisions only: deterministic bits
     awp = (aws.data_ptr() + 255) & ~255
     g0, ga, fl = torch.empty((18, Bd), device="cuda"), torch.full((T, 2, Bd), 7.0, device="cuda"), torch.full((Bd,), 9, dtype=torch.int32, device="cuda")
     ok(so.shim_rollout_bwd(C.c_void_p(st), C.c_int64(Bd), C.c_int64(T), C.c_void_p(tape.data_ptr()), C.c_void_p(ad.data_ptr()),
                            C.c_void_p(gf.data_ptr()), C.c_void_p(awp), C.c_int64(aws.numel() - (awp - aws.data_ptr())),
                            C.c_void_p(g0.data_ptr()), C.c_void_p(ga.data_ptr()), C.c_void_p(fl.data_ptr()), w0p, int(w0.size),
-                           C.c_int32(1), err, 512))
+                           C.c_int32(0), err, 512))
     flags = torch.zeros(Bd, dtype=torch.int32, device="cuda")
-    g0r, gar = ll.rollout_vjp(ro, gf, flags)
+    g0r, gar = ll.rollout_vjp(ro, gf, flags, jacobians=False)
     eq(g0, g0r, "g0"); eq(ga, gar, "g_actions"); eq(fl, flags, "flags")
     # a bad params attribute is an error, not a crash
     assert so.shim_reset(C.c_void_p(st), C.c_int64(B), C.c_void_p(kd.data_ptr()), C.c_void_p(state.data_ptr()), wp, nw - 1, err, 512) != 0
