@@ -100,6 +100,25 @@ int cotix_narrowphase_ws(void* stream, int64_t n, const float* a, const float* b
                          uint8_t* exists, float* pen, float* cp, uint8_t* status,
                          const CotixNarrowParams* params, void* workspace, int64_t workspace_bytes);
 
+/*
+ * The wavefront sweep WITHOUT any allocation, for callers that cannot call cudaMalloc (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the
+ * reference.  Same arguments and bit-identical results
+ * as cotix_narrowphase_ws, but the scratch is a file-scope `static __device__` array inside the
+ * library (99 B per pair, about 13 MB; every GPU that loads the library holds it until exit), so
+ * n is limited: n > COTIX_NARROWPHASE_STATIC_MAX_PAIRS fails with COTIX_EINVAL and a message that
+ * names the limit.  The call issues no cudaMalloc / cudaFree / allocating routine; it only enqueues
+ * on `stream` (the first call on a device also looks the array's address up with
+ * cudaGetSymbolAddress: make that call outside a capture).  ALL calls on a device share the array
+ * and it keeps the last call's contents: each call zeroes the queue counters it needs first, and
+ * two calls that overlap on the GPU (different streams, no ordering between them) race — order
+ * them on one stream or with events.
+ */
+#define COTIX_NARROWPHASE_STATIC_MAX_PAIRS 131072
+int cotix_narrowphase_static(void* stream, int64_t n, const float* a, const float* b,
+                             uint8_t* exists, float* pen, float* cp, uint8_t* status,
+                             const CotixNarrowParams* params);
+
 /* Same query with HOST buffers: copies in, runs, copies out, synchronises. */
 int cotix_narrowphase_host(int device, int64_t n, const float* a, const float* b,
                            uint8_t* exists, float* pen, float* cp, uint8_t* status,

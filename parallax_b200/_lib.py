@@ -145,7 +145,7 @@ class LunarParams(C.Structure):
 # every symbol include/cotix_b200.h declares
 EXPORTS = [
     "cotix_narrowphase", "cotix_narrowphase_host", "cotix_order_clockwise",
-    "cotix_narrowphase_workspace_bytes", "cotix_narrowphase_ws",
+    "cotix_narrowphase_workspace_bytes", "cotix_narrowphase_ws", "cotix_narrowphase_static",
     "cotix_lunar_default_params", "cotix_lunar_reset", "cotix_lunar_step",
     "cotix_lunar_workspace_bytes", "cotix_lunar_step_ws", "cotix_lunar_env_set_mode", "cotix_lunar_env_set_chunks", "cotix_lunar_env_set_host_graphs",
     "cotix_lunar_pipeline_profile", "cotix_lunar_pipeline_stage_ms",
@@ -191,6 +191,7 @@ def lib() -> C.CDLL:
     L.cotix_narrowphase_workspace_bytes.restype = C.c_int64
     L.cotix_narrowphase_workspace_bytes.argtypes = [i64]
     L.cotix_narrowphase_ws.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, C.POINTER(NarrowParams), vp, i64]
+    L.cotix_narrowphase_static.argtypes = [vp, i64, vp, vp, vp, vp, vp, vp, C.POINTER(NarrowParams)]
     L.cotix_order_clockwise.argtypes = [vp, i64, vp]
     L.cotix_support.argtypes = [vp, i64, vp, vp, vp]
     L.cotix_lunar_default_params.argtypes = [C.POINTER(LunarParams)]

@@ -18,6 +18,8 @@ extern "C" int cx_launch_narrowphase(cudaStream_t, int64_t, const float*, const 
 extern "C" int64_t cx_narrowphase_workspace_bytes(int64_t);
 extern "C" int cx_launch_narrowphase_ws(cudaStream_t, int64_t, const float*, const float*, uint8_t*, float*,
                                         float*, uint8_t*, const CotixNarrowParams*, void*, int64_t);
+extern "C" int cx_launch_narrowphase_static(cudaStream_t, int64_t, const float*, const float*, uint8_t*, float*,
+                                            float*, uint8_t*, const CotixNarrowParams*);
 extern "C" int cx_launch_order_clockwise(cudaStream_t, int64_t, float*);
 extern "C" int cx_launch_support(cudaStream_t, int64_t, const float*, const float*, float*);
 extern "C" int cx_launch_lunar_step(cudaStream_t, int64_t, const float*, float*, int64_t,
@@ -201,6 +203,17 @@ int cotix_narrowphase_ws(void* stream, int64_t n, const float* a, const float* b
   if (rc) return rc;
   return cx_launch_narrowphase_ws((cudaStream_t)stream, n, a, b, exists, pen, cp, status, params, workspace,
                                   workspace_bytes);
+}
+
+int cotix_narrowphase_static(void* stream, int64_t n, const float* a, const float* b, uint8_t* exists,
+                             float* pen, float* cp, uint8_t* status, const CotixNarrowParams* params) {
+  CX_REQUIRE(n >= 0, "n < 0");
+  CX_REQUIRE(params != nullptr, "params is null");
+  CX_REQUIRE(n == 0 || (a && b), "null shape records");
+  CX_REQUIRE(params->gjk_max_iters >= 0 && params->epa_iters_circle_poly >= 3, "bad iteration caps");
+  int rc = require_device();
+  if (rc) return rc;
+  return cx_launch_narrowphase_static((cudaStream_t)stream, n, a, b, exists, pen, cp, status, params);
 }
 
 int cotix_narrowphase_host(int device, int64_t n, const float* a, const float* b, uint8_t* exists,

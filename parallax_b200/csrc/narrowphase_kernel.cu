@@ -4,6 +4,8 @@
 // HBM traffic per pair: 2 x 64 B records in, 1 + 8 + 8 (+1) B out (148 B).
 // Records are read as four 16-byte vector loads per shape (a warp covers 2 KB of
 // contiguous records per array); outputs are written as float2 / bytes, coalesced.
+#include <mutex>
+
 #include "../../include/cotix_b200.h"
 #include "cx_launch.cuh"
 #include "cx_narrow.cuh"
@@ -467,4 +469,71 @@ extern "C" int cx_launch_narrowphase_ws(cudaStream_t st, int64_t n, const float*
   sweep_epa_kernel<2><<<g, 128, 0, st>>>(n, a, b, exists, pen, cp, status, *p, ws);
   cx_count_launch_n(8);
   return cx_check_launch("narrowphase sweep");
+}
+
+// ---- no-allocation variant of the wavefront sweep (cotix_narrowphase_static) --------------------
+// For callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops,
+// harnesses that forbid it): the sweep's scratch (queues, hit lists, GJK simplices; 99 B per pair)
+// lives in a file-scope __device__ array of a fixed, modest size, so the call allocates nothing.
+// Every GPU that loads the library holds the array (about 13 MB) until the process exits.
+// In HOST code the array's name is only a host-side stand-in, not a device address, so the address
+// is taken once per device with cudaGetSymbolAddress (that device current) and handed to the same
+// launcher the caller-workspace entry point uses.  All calls on a device share the array: the
+// launcher zeroes the queue counters at the start of every call (everything else is written before
+// it is read), and two calls that overlap on the GPU (different streams) race.
+namespace {
+constexpr int64_t SW_STATIC_MAX_PAIRS = COTIX_NARROWPHASE_STATIC_MAX_PAIRS;
+// sweep_carve(n) for n a multiple of 256: 256 B of counters + (3*4 + 3*4 + 3*24 + 3*1) B per pair
+constexpr size_t SW_STATIC_BYTES = 256 + (size_t)SW_STATIC_MAX_PAIRS * 99;
+static_assert(SW_STATIC_MAX_PAIRS % 256 == 0, "the static scratch is sized for a multiple of 256 pairs");
+static __device__ __align__(256) unsigned char g_sweep_static_scratch[SW_STATIC_BYTES];
+
+std::mutex g_sweep_static_mu;
+void* g_sweep_static_ptr[64];  // device address of the array, per device ordinal
+bool g_sweep_static_known[64];
+
+// device address of the static scratch on the CURRENT device (taken on first use per device)
+int sweep_static_address(void** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    cx_set_error("cotix_narrowphase_static: cannot tell the current device");
+    (void)cudaGetLastError();
+    return COTIX_ECUDA;
+  }
+  std::lock_guard<std::mutex> lock(g_sweep_static_mu);
+  if (!g_sweep_static_known[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_sweep_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      cx_set_error("cotix_narrowphase_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                   cudaGetErrorString(e));
+      (void)cudaGetLastError();
+      return COTIX_ECUDA;
+    }
+    g_sweep_static_ptr[dev] = p;
+    g_sweep_static_known[dev] = true;
+  }
+  *out = g_sweep_static_ptr[dev];
+  return COTIX_OK;
+}
+}  // namespace
+
+extern "C" int cx_launch_narrowphase_static(cudaStream_t st, int64_t n, const float* a, const float* b,
+                                            uint8_t* exists, float* pen, float* cp, uint8_t* status,
+                                            const CotixNarrowParams* p) {
+  if (n > SW_STATIC_MAX_PAIRS) {
+    cx_set_error("cotix_narrowphase_static: n = %lld exceeds COTIX_NARROWPHASE_STATIC_MAX_PAIRS = %lld; "
+                 "use cotix_narrowphase_ws with a caller-provided workspace",
+                 (long long)n, (long long)SW_STATIC_MAX_PAIRS);
+    return COTIX_EINVAL;
+  }
+  if (n == 0) return 0;
+  if (sweep_carve(n, nullptr, nullptr) > SW_STATIC_BYTES) {  // cannot happen for n <= the maximum
+    cx_set_error("cotix_narrowphase_static: internal scratch too small");
+    return COTIX_EINVAL;
+  }
+  void* scratch = nullptr;
+  const int rc = sweep_static_address(&scratch);
+  if (rc != 0) return rc;
+  return cx_launch_narrowphase_ws(st, n, a, b, exists, pen, cp, status, p, scratch, (int64_t)SW_STATIC_BYTES);
 }
