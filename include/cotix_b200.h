@@ -273,8 +273,8 @@ int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, cons
 
 /*
  * Launch configuration of the pipeline (process-wide; a negative value leaves a setting unchanged):
- *   split          ranges of envs the batch is cut into, 1..COTIX_MAX_CHUNKS; 0 = automatic
- *                  (ranges of >= 131072 envs, at most 4).  Results do not depend on it.
+ *   split          ranges of envs the batch is cut into, 1..COTIX_MAX_CHUNKS; 0 = automatic = 1
+ *                  (measured best for device-resident stepping).  Results do not depend on it.
  *   pdl            programmatic dependent launch between the stages of a range (default 1)
  *   priorities     sparse stages (narrow, contact, reset) at the highest launch priority, dense
  *                  stages at the lowest (default 1; only with split > 1)
@@ -336,8 +336,7 @@ int cotix_lunar_env_set_mode(CotixLunarEnv* env, int mode);
  * of a range, its kernels and D2H(obs, reward, done) go on the range's stream, so PCIe traffic in both
  * directions overlaps the kernels of the other ranges.  In fused mode H2D of range c+1, the kernel of
  * range c and D2H of range c-1 run on three streams.  Envs are independent, so the results do not
- * depend on `chunks`.  0 = automatic (pipeline: the configured split; fused: ranges of >= 256K envs,
- * at most 4).  obs / reward / done of cotix_lunar_env_step_host may each be NULL: that output is not
+ * depend on `chunks`.  0 = automatic (ranges of >= 256K envs, at most 4).  obs / reward / done of cotix_lunar_env_step_host may each be NULL: that output is not
  * copied to the host (obs stays readable on the device) — obs is 86 % of the D2H bytes of a step.
  */
 #define COTIX_MAX_CHUNKS 16

@@ -842,7 +842,8 @@ int cotix_lunar_env_step_host(CotixLunarEnv* e, const float* action, float* obs,
   const size_t B = (size_t)e->B;
   const bool pipe = e->mode == COTIX_MODE_PIPELINE || (e->mode == COTIX_MODE_AUTO && e->B >= 16384);
   int64_t len = 0;
-  const int C = pipe ? e->chunks : plan_chunks(e, &len);
+  // pipeline mode, automatic: ranges of >= 256 K envs, at most 4 (copy / compute overlap)
+  const int C = pipe ? (e->chunks > 0 ? e->chunks : plan_chunks(e, &len)) : plan_chunks(e, &len);
   if (!pipe && C == 1) {
     if (action)
       CXL_CUDA(cudaMemcpyAsync(e->action, action, sizeof(float) * 2 * B, cudaMemcpyHostToDevice, e->stream));

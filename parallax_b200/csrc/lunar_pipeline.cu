@@ -665,7 +665,7 @@ struct PipeCfg {
   uint32_t item_cap;  // 0 = 4 B + 4096 per range; tests force the overflow branch with a small value
   int min_range;      // automatic split: envs per range at least this many
 };
-PipeCfg g_cfg = {0, 1, 1, 0u, 131072};
+PipeCfg g_cfg = {0, 1, 1, 0u, 131072};  // split 0 = automatic (see choose_split)
 
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 // the forced capacity (tests) can only shrink the queue: workspace sizes are those of the default
@@ -729,11 +729,12 @@ size_t plan_ranges(int64_t B, int S, void* workspace, RangePlan* plan) {
   return bytes;
 }
 int choose_split(int64_t B) {
+  // automatic = ONE range: measured on B200 at 1 M envs (profiles/r2e_split_sweep.jsonl), 1 / 2 / 4 / 8
+  // ranges take 245 / 245 / 258 / 268 us per step -- co-running the stages of different ranges does not
+  // raise the issue rate (profiles/r2e_timeline.txt), it only adds launches.  Ranges pay off for the
+  // host-facing step, where they overlap PCIe copies with kernels (cotix_lunar_env_step_host).
+  (void)B;
   int S = g_cfg.split;
-  if (S <= 0) {
-    S = (int)(B / (g_cfg.min_range > 0 ? g_cfg.min_range : 131072));
-    if (S > 4) S = 4;
-  }
   if (S > MAX_SPLIT) S = MAX_SPLIT;
   if (S < 1) S = 1;
   return S;
