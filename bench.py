@@ -350,6 +350,19 @@ def run_ours(args):
 
     e2e_value, e2e_launches = e2e_run(True)
     e2e_lean, e2e_lean_launches = e2e_run(False)
+    # the ceiling of a synchronous host step: the D2H copy of one step's results alone (same bytes,
+    # same pinned buffers, nothing else running) -- what the PCIe link / host memory allow
+    barrier()
+    dsrc = torch.empty((8 * 4 + 4 + 1) * B, dtype=torch.uint8, device=dev)
+    hdst = torch.empty((8 * 4 + 4 + 1) * B, dtype=torch.uint8).pin_memory()
+    hdst.copy_(dsrc, non_blocking=True)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(10):
+        hdst.copy_(dsrc, non_blocking=True)
+    torch.cuda.synchronize(dev)
+    d2h_ms = allmax(time.perf_counter() - t0) * 100.0
+    del dsrc, hdst
     env.close()
 
     peak, peak_src, sm_max_mhz = _peaks()
@@ -404,11 +417,19 @@ def run_ours(args):
                      # the step is issue-bound, not HBM-bound: issue-slot and FP32-pipe utilisation from the
                      # committed ncu --set full capture (static evidence; see profiles/)
                      "issue_slot": whole.get("issue_slot_pct"), "fp32_pipe": whole.get("fp32_pipe_pct"),
-                     "alu_pipe": whole.get("alu_pipe_pct"), "ncu_source": ncu.get("_source"),
+                     "alu_pipe": whole.get("alu_pipe_pct"), "occupancy": whole.get("occupancy_pct"),
+                     "warp_instructions_per_step": whole.get("warp_instr"),
+                     # what the step would take at 100 % issue-slot use: the bound that matters here
+                     "issue_bound_ms": (whole["warp_instr"] / (148 * 4 * sm_max_mhz * 1e3)) if whole.get("warp_instr") else None,
+                     "issue_frac": (whole["warp_instr"] / (148 * 4 * sm_max_mhz * 1e3) / step_ms) if whole.get("warp_instr") else None,
+                     "ncu_source": ncu.get("_source"),
                      "stages": stages, "queue_counts": counters},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * 4 * B,
                 "d2h_bytes_per_step": (8 * 4 + 4 + 1) * B, "steps": e2e_steps,
                 "overlap": "env ranges on their own streams: H2D(action) | kernels | D2H(obs, reward, done)",
+                "d2h_only_ms": d2h_ms, "d2h_gbs": (8 * 4 + 4 + 1) * B / (d2h_ms * 1e-3) / 1e9,
+                "copy_bound_value": world * B / (d2h_ms * 1e-3),
+                "note": "copy_bound_value = env-steps/s if a step cost only its D2H copy (measured, all ranks at once)",
                 "reward_done_only": {"value": e2e_lean, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * 4 * B,
                                      "d2h_bytes_per_step": (4 + 1) * B,
                                      "note": "obs left on the device (want_obs=False): 86 % of the D2H bytes"}},
