@@ -328,6 +328,12 @@ def run_ours(args):
     value = total_env_steps / (ms_max * 1e-3)
     g_warm.close()
     g_time.close()
+    if args.value_only:  # the fast-math leg of the main run (child process, COTIX_FLAVOUR=fast)
+        if rank == 0:
+            print(json.dumps({"value": value, "ms_per_step": ms_max / args.steps, "unit": "env-steps/s",
+                              "flavour": parallax_b200._lib.FLAVOUR,
+                              "math_flavour": int(parallax_b200._lib.lib().cotix_math_flavour())}), flush=True)
+        return
 
     # ---- end-to-end through the host-facing env handle ("e2e") ---------------------------
     env = ll.LunarLanderEnv(B, P, device=dev.index)
@@ -447,11 +453,36 @@ def run_ours(args):
         line["render"] = render(args, dev, peak)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_baseline(args)
+    line["math_flavour"] = "exact (-fmad=false, IEEE division / sqrt: bit-identical to the oracle)" \
+        if parallax_b200._lib.lib().cotix_math_flavour() == 0 else "fast"
+    if rank == 0 and world == 1 and not args.no_sweep and parallax_b200._lib.FLAVOUR == "exact":
+        line["fast_math"] = fast_math_leg(args)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def fast_math_leg(args):
+    """The same device-resident measurement with libcotix_b200_fast.so (-fmad=true -prec-div=false
+    -prec-sqrt=false; within 1e-5 relative per step of the exact build, tests/test_fast_flavour.py) in a
+    child process.  Reported beside the headline, never as it: the exact flavour is the parity build."""
+    import subprocess
+
+    env = dict(os.environ, COTIX_FLAVOUR="fast")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    cmd = [sys.executable, os.path.abspath(__file__), "--value-only", "--steps", str(args.steps), "--warmup",
+           str(args.warmup), "--envs", str(args.envs), "--rng", args.rng, "--max-episode-steps",
+           str(args.max_episode_steps), "--substeps", str(args.substeps)]
+    try:
+        res = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
+        out = json.loads([l for l in res.stdout.splitlines() if l.startswith("{")][-1])
+        out["build"] = "-fmad=true -prec-div=false -prec-sqrt=false (COTIX_FLAVOUR=fast); not bit-exact"
+        return out
+    except Exception as e:  # the leg is informative: never take the main line down
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 def config1(args, dev):
@@ -772,6 +803,7 @@ def main():
     ap.add_argument("--ref-threads", dest="ref_threads", type=int, default=0, help="0 = every logical core")
     ap.add_argument("--ref-literal", dest="ref_literal", action="store_true")
     ap.add_argument("--split", type=int, default=-1, help="env ranges of the pipeline (-1 = library default)")
+    ap.add_argument("--value-only", dest="value_only", action="store_true", help="device-resident leg only")
     ap.add_argument("--no-sweep", dest="no_sweep", action="store_true")
     ap.add_argument("--no-cpu", dest="no_cpu", action="store_true")
     args = ap.parse_args()

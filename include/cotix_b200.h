@@ -567,6 +567,10 @@ int cotix_event_elapsed_ms(void* start, void* stop, float* ms); /* waits for `st
 /* ------------------------------------------------------------------------------------ */
 const char* cotix_last_error(void);
 int cotix_abi_version(void);
+/* 0: the exact build (-fmad=false, IEEE division / sqrt: bit-identical to the CPU oracle);          */
+/* 1: libcotix_b200_fast.so, the same sources built -fmad=true -prec-div=false -prec-sqrt=false:   */
+/*    within 1e-5 relative per step of the exact build, not bit-exact         */
+int cotix_math_flavour(void);
 /* number of kernels this library has launched in this process (all streams) */
 int64_t cotix_launch_count(void);
 /* name, SM count and compute capability of `device`; returns 0 or COTIX_E*           */

@@ -14,7 +14,18 @@ import subprocess
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 _CSRC = os.path.join(_PKG, "csrc")
-LIB_PATH = os.path.join(_PKG, "libcotix_b200.so")
+# Two flavours of the same sources (COTIX_FLAVOUR = "exact" (default) | "fast"):
+#   exact  libcotix_b200.so       -fmad=false, IEEE division / sqrt: bit-identical to the oracle (the parity build)
+#   fast   libcotix_b200_fast.so  -fmad=true -prec-div=false -prec-sqrt=false -DCOTIX_MATH_FAST: FMA contraction
+#          and 2-ulp division / sqrt; validated at north_star's 1e-5 relative per step
+#          (tests/test_fast_flavour.py), NOT bit-exact; ~16 % faster on the issue-bound step
+# COTIX_LIB_PATH: load another build of the library (kernel-tuning experiments)
+FLAVOUR = os.environ.get("COTIX_FLAVOUR", "exact")
+if FLAVOUR not in ("exact", "fast"):
+    raise ValueError(f"COTIX_FLAVOUR must be 'exact' or 'fast', not {FLAVOUR!r}")
+FLAVOUR_LIBS = {"exact": os.path.join(_PKG, "libcotix_b200.so"), "fast": os.path.join(_PKG, "libcotix_b200_fast.so")}
+FAST_FLAGS = ["-fmad=true", "-prec-div=false", "-prec-sqrt=false", "-DCOTIX_MATH_FAST=1"]
+LIB_PATH = os.environ.get("COTIX_LIB_PATH") or FLAVOUR_LIBS[FLAVOUR]
 SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu",
            "scene_kernel.cu", "lunar_adjoint.cu", "raster_kernel.cu"]
 NVCC_FLAGS = [
@@ -36,21 +47,30 @@ def _nvcc() -> str:
     raise CotixError("nvcc not found; cannot build libcotix_b200.so")
 
 
-def _stale() -> bool:
-    if not os.path.exists(LIB_PATH):
+def _stale(path=None) -> bool:
+    path = path or LIB_PATH
+    if not os.path.exists(path):
         return True
-    t = os.path.getmtime(LIB_PATH)
+    t = os.path.getmtime(path)
     deps = [os.path.join(_CSRC, f) for f in os.listdir(_CSRC)]
     deps.append(os.path.join(_PKG, "..", "include", "cotix_b200.h"))
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every CUDA translation unit into parallax_b200/libcotix_b200.so."""
-    if not force and not _stale():
-        return LIB_PATH
+def build(force: bool = False, verbose: bool = False, flavour: str | None = None) -> str:
+    """Compile every CUDA translation unit into the flavour's shared library (default: the flavour
+    this process loads; `build_all` makes both)."""
+    out = LIB_PATH if flavour is None else FLAVOUR_LIBS[flavour]
+    fast = (FLAVOUR if flavour is None else flavour) == "fast" and not os.environ.get("COTIX_LIB_PATH")
+    if not force and not _stale(out):
+        return out
     extra = os.environ.get("COTIX_NVCC_EXTRA", "").split()  # experiments, e.g. -DCX_BAND_ROWS=12
-    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-o", LIB_PATH, *[os.path.join(_CSRC, s) for s in SOURCES]]
+    if fast:
+        extra = FAST_FLAGS + extra
+    flags = list(NVCC_FLAGS)
+    if any(x.startswith("-fmad=") for x in extra):  # the fast flavour / an experiment overrides the contraction flag
+        flags = [f for f in flags if not f.startswith("-fmad=")]
+    cmd = [_nvcc(), *flags, *extra, "-o", out, *[os.path.join(_CSRC, s) for s in SOURCES]]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
@@ -61,7 +81,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise CotixError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
-    return LIB_PATH
+    return out
+
+
+def build_all(force: bool = False) -> list:
+    """Both flavours (what __graft_entry__.build() does)."""
+    return [build(force=force, flavour="exact"), build(force=force, flavour="fast")]
 
 
 class NarrowParams(C.Structure):
@@ -154,7 +179,7 @@ EXPORTS = [
     "cotix_lunar_env_set_state_host", "cotix_lunar_env_state_ptr", "cotix_lunar_env_stream",
     "cotix_lunar_env_rollout_graph", "cotix_euler_step", "cotix_resolve_collision",
     "cotix_support", "cotix_threefry2x32", "cotix_philox4x32", "cotix_last_error",
-    "cotix_abi_version", "cotix_launch_count", "cotix_device_info",
+    "cotix_abi_version", "cotix_math_flavour", "cotix_launch_count", "cotix_device_info",
     "cotix_scene_default_params", "cotix_scene_create", "cotix_scene_destroy", "cotix_scene_info",
     "cotix_scene_step",
     "cotix_lunar_step_bwd", "cotix_lunar_rollout", "cotix_lunar_rollout_bwd",
@@ -262,6 +287,9 @@ def lib() -> C.CDLL:
     L.cotix_event_destroy.argtypes = [vp]
     L.cotix_event_record.argtypes = [vp, vp]
     L.cotix_event_elapsed_ms.argtypes = [vp, vp, C.POINTER(C.c_float)]
+    want = 1 if (FLAVOUR == "fast" and not os.environ.get("COTIX_LIB_PATH")) else None
+    if want is not None and L.cotix_math_flavour() != want:
+        raise CotixError(f"{LIB_PATH} is not the fast-math build")
     if L.cotix_abi_version() != 2:
         raise CotixError("libcotix_b200.so ABI version mismatch")
     _lib = L

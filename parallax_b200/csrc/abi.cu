@@ -126,6 +126,7 @@ __global__ void resolve_kernel(int64_t n, float* body1, float* body2, const floa
     b[q].ang = src[q][6];
     b[q].w = src[q][7];
     m[q].e = src[q][8];
+    m[q].inv_mass = 1.0f / src[q][0];
     m[q].mu = src[q][9];
   }
   resolve_collision(b[0], m[0], b[1], m[1], mk2(pen[2 * k], pen[2 * k + 1]),
@@ -163,6 +164,13 @@ extern "C" {
 
 const char* cotix_last_error(void) { return g_err; }
 int cotix_abi_version(void) { return COTIX_ABI_VERSION; }
+int cotix_math_flavour(void) {
+#ifdef COTIX_MATH_FAST
+  return 1;
+#else
+  return 0;
+#endif
+}
 int64_t cotix_launch_count(void) { return g_launches.load(); }
 
 int cotix_device_info(int device, char* name, int name_len, int* sm_count, int* cc_major,

@@ -29,7 +29,18 @@ struct BodyS {
 };
 struct MassP {
   float mass, inertia, e, mu;
+  float inv_mass;  // 1.0f / mass, IEEE: the same bits whether the host or a thread divides
 };
+CX_DEV MassP mk_massp(const float props[4], float inv_mass) {
+  MassP m;
+  m.mass = props[0];
+  m.inertia = props[1];
+  m.e = props[2];
+  m.mu = props[3];
+  m.inv_mass = inv_mass;
+  return m;
+}
+CX_DEV MassP mk_massp(const float props[4]) { return mk_massp(props, 1.0f / props[0]); }
 
 // ---- order_clockwise on a register polygon of N vertices (cotix/_geometry_utils.py:60-67) ----
 template <int N>
@@ -89,6 +100,7 @@ struct LunarDerived {
                     // local vertex order (convex, centroid strictly inside, angular gaps > 1e-3)
   int orient[3];    // +1: local order is counter-clockwise (ascending angle), -1: clockwise
   float lext[4];    // lander local extents: min x, min y, max x, max y
+  float inv_mass[4];  // 1.0f / body_props[i][0] (launch constants: divided once on the host, not per thread)
 };
 
 // order_clockwise of a RIGIDLY transformed convex polygon without computing any angle.
@@ -171,14 +183,14 @@ static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1
   float lever1 = sumsq2(r1), lever2 = sumsq2(r2);
   float ang = lever1 / m1.inertia + lever2 / m2.inertia;
   float nim = -(1.0f + el) * vn - baumgarte * norm2(pen) / baumgarte_dt;
-  float kden = 1.0f / m1.mass + 1.0f / m2.mass + ang;
+  float kden = m1.inv_mass + m2.inv_mass + ang;  // 1.0f / m1.mass + 1.0f / m2.mass + ang
   float nimp = nim / kden;
   V2 ivec = nimp * nd;
   float fr = (m1.mu + m2.mu) / 2.0f;
   V2 vdrag = vrel + vn * nd;
   float vdn = norm2(vdrag);
   V2 vdu = vdrag / vdn;
-  float idrag = -norm2(vdrag) / (1.0f / m1.mass + 1.0f / m2.mass + ang);
+  float idrag = -norm2(vdrag) / (m1.inv_mass + m2.inv_mass + ang);
   idrag = jclip(idrag, 0.0f, nimp * fr);
   V2 idv = idrag * vdu;
   ivec = ivec + idv;

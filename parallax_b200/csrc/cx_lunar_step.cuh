@@ -379,16 +379,11 @@ CX_DEV void make_coin_ctx(const EnvRegs& E, const CotixLunarParams& P, CoinCtx& 
 // choose_random_contact (:274-295) + the sequential resolution scan (:310-336), given the winner
 // of every cell (win[c] = winning q or -1).  Updates E (velocities, status).
 template <class CS>
-CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const CS& cs, const CoinCtx& cc,
-                          const int win[7]) {
+CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const LunarDerived& D, const CS& cs,
+                          const CoinCtx& cc, const int win[7]) {
   MassP mp[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    mp[i].mass = P.body_props[i][0];
-    mp[i].inertia = P.body_props[i][1];
-    mp[i].e = P.body_props[i][2];
-    mp[i].mu = P.body_props[i][3];
-  }
+  for (int i = 0; i < 4; ++i) mp[i] = mk_massp(P.body_props[i], D.inv_mass[i]);
   const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
   BodyS G;  // the static ground body (mass = inertia = inf); NaN once poisoned
   G.px = G.py = G.vx = G.vy = G.ang = G.w = poisoned ? CX_NAN : 0.0f;
@@ -448,7 +443,7 @@ CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const CS& cs, c
 
 // one thread does everything for its env (the fused kernel)
 template <class CS>
-CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, uint32_t cand, const CS& cs,
+CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, const LunarDerived& D, uint32_t cand, const CS& cs,
                     bool& crash, bool& rc, bool& lc) {
   uint32_t m[7];
   if (!collide_masks(cand, cs, false, m, crash, rc, lc)) return;
@@ -465,7 +460,7 @@ CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, uint32_t cand, const 
     const CellDesc d = cell_desc(6);
     win[6] = cell_winner(cc, d.g, d.N1, d.N2, d.b_lo, d.b_hi, d.a0, d.nq, d.reps, cs.live(10) ? 1u : 0u);
   }
-  collide_apply(E, P, cs, cc, win);
+  collide_apply(E, P, D, cs, cc, win);
 }
 
 // ---- key split, joints, judge --------------------------------------------------------------------
@@ -474,12 +469,7 @@ CX_DEV void finish_step(EnvRegs& E, const CotixLunarParams& P, const float cs[3]
                         float thr_main, float thr_side, bool crash, bool rc, bool lc, SubInfo& info) {
   MassP mp[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    mp[i].mass = P.body_props[i][0];
-    mp[i].inertia = P.body_props[i][1];
-    mp[i].e = P.body_props[i][2];
-    mp[i].mu = P.body_props[i][3];
-  }
+  for (int i = 0; i < 3; ++i) mp[i] = mk_massp(P.body_props[i], 0.0f);  // the joints never read inv_mass
   // key, next_key = jr.split(key) (examples/test_viz.py:39)
   if (P.rng_mode == COTIX_RNG_THREEFRY) E.key = tf_split(E.key, 2u, 0u);
 

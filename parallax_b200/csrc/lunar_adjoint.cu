@@ -521,6 +521,7 @@ static __device__ __noinline__ void step_bwd_core(const EnvRegs& E, const StepCt
     mp[i].inertia = P.body_props[i][1];
     mp[i].e = P.body_props[i][2];
     mp[i].mu = P.body_props[i][3];
+    mp[i].inv_mass = 1.0f / P.body_props[i][0];
   }
   const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
   BodyS bd[4];

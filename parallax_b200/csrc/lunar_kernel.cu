@@ -152,11 +152,11 @@ struct SmemContacts {
 };
 
 // ---- phase C: contact selection, resolution, joints, judge --------------------------------
-__device__ void phase_c(EnvRegs& E, const CotixLunarParams& P, const SharedBlock& S,
+__device__ void phase_c(EnvRegs& E, const CotixLunarParams& P, const LunarDerived& D, const SharedBlock& S,
                         const StepCtx& cx, SubInfo& info) {
   bool crash, rc, lc;
   SmemContacts cs{S, cx, P};
-  collide(E, P, cx.cand, cs, crash, rc, lc);
+  collide(E, P, D, cx.cand, cs, crash, rc, lc);
   finish_step(E, P, cx.cs, cx.sn, cx.thr_main, cx.thr_side, crash, rc, lc, info);
 }
 
@@ -194,7 +194,7 @@ lunar_step_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__
     __syncthreads();
     if (running) {
       SubInfo si;
-      phase_c(E, P, S, cx, si);
+      phase_c(E, P, D, S, cx, si);
       rsum = rsum + si.reward;
       rc = si.rc;
       lc = si.lc;
@@ -272,6 +272,7 @@ extern "C" void cx_lunar_derive(const CotixLunarParams* p, LunarDerived* out) {
     D.lext[2] = fmaxf(D.lext[2], p->lander_local[k][0]);
     D.lext[3] = fmaxf(D.lext[3], p->lander_local[k][1]);
   }
+  for (int i = 0; i < 4; ++i) D.inv_mass[i] = 1.0f / p->body_props[i][0];
 }
 
 extern "C" int cx_launch_lunar_step(cudaStream_t st, int64_t B, const float* sin_, float* sout,

@@ -46,7 +46,7 @@ enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 
 #define CX_INTEGRATE_MINB 6
 #endif
 #ifndef CX_FINISH_MINB
-#define CX_FINISH_MINB 6
+#define CX_FINISH_MINB 8  // 64 registers: 72.5 -> 64 us (profiles/r2h_variants.jsonl); integrate is unchanged by 5..8
 #endif
 
 struct PipeWs {
@@ -535,7 +535,7 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
 #pragma unroll
         for (int k = 0; k < 7; ++k) win[k] = W.win[lane][k];
         load_dyn(E, s, ld, e);  // only envs with a live contact need their bodies
-        collide_apply(E, P, qc, cc, win);
+        collide_apply(E, P, D, qc, cc, win);
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           s[(i * 6 + 2) * ld + e] = E.b[i].vx;

@@ -23,21 +23,28 @@ MEDIAN_MAX, P90_MAX, P99_MAX = 5e-6, 5e-5, 5e-4
 DIVERGED_AT, DIVERGED_MAX = 1e-2, 5e-3
 
 
-def check_horizon(got, ref, same_flags):
+def horizon_stats(got, ref, same_flags):
     """got / ref: [36, B] states after HORIZON_STEPS steps; same_flags: [B] bool, the reported flags
-    agreed at every step.  Asserts the stated tolerance and returns the measured figures."""
+    agreed at every step.  The measured figures, no assertion."""
     fa, fb = np.isfinite(got[:18]).all(axis=0), np.isfinite(ref[:18]).all(axis=0)
-    assert (fa == fb).all(), f"{int((fa != fb).sum())} envs are non-finite in one run only"
     fin = fa & fb
     with np.errstate(invalid="ignore"):
         d = np.abs(got[:18] - ref[:18]) / np.maximum(np.abs(ref[:18]), 1.0)
     d = np.where(fin[None], d, 0.0).max(axis=0)
-    flips = float((~same_flags & fin).sum() / max(1, fin.sum()))
-    assert flips <= FLAG_FLIP_MAX, f"flag flips in {flips:.4f} of the finite envs"
     ok = same_flags & fin
     med, p90, p99 = (float(np.percentile(d[ok], q)) for q in (50, 90, 99))
-    diverged = float((d[ok] > DIVERGED_AT).mean())
-    assert med <= MEDIAN_MAX and p90 <= P90_MAX and p99 <= P99_MAX, (med, p90, p99)
-    assert diverged <= DIVERGED_MAX, f"{diverged:.4f} of the envs beyond {DIVERGED_AT}"
-    return {"nonfinite": float(1.0 - fin.mean()), "flag_flips": flips, "median": med, "p90": p90, "p99": p99,
-            "diverged": diverged, "max": float(d[ok].max())}
+    return {"nonfinite": float(1.0 - fin.mean()), "nonfinite_in_one_run_only": float((fa != fb).mean()),
+            "flag_flips": float((~same_flags & fin).sum() / max(1, fin.sum())), "median": med, "p90": p90, "p99": p99,
+            "diverged": float((d[ok] > DIVERGED_AT).mean()), "max": float(d[ok].max())}
+
+
+def check_horizon(got, ref, same_flags, flag_flip_max=FLAG_FLIP_MAX, median_max=MEDIAN_MAX, p90_max=P90_MAX,
+                  p99_max=P99_MAX, diverged_max=DIVERGED_MAX, nonfinite_mismatch_max=0.0):
+    """Asserts the stated tolerance (defaults: the exact flavour's, module docstring) and returns the
+    measured figures."""
+    st = horizon_stats(got, ref, same_flags)
+    assert st["nonfinite_in_one_run_only"] <= nonfinite_mismatch_max, st
+    assert st["flag_flips"] <= flag_flip_max, f"flag flips in {st['flag_flips']:.4f} of the finite envs: {st}"
+    assert st["median"] <= median_max and st["p90"] <= p90_max and st["p99"] <= p99_max, st
+    assert st["diverged"] <= diverged_max, f"{st['diverged']:.4f} of the envs beyond {DIVERGED_AT}: {st}"
+    return st
