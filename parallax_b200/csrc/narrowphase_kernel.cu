@@ -333,6 +333,12 @@ sweep_epa_cp_short_kernel(int64_t n, const float* __restrict__ a, const float* _
   const int budget = prm.epa_iters_circle_poly < CX_EPA_SHORT ? prm.epa_iters_circle_poly : CX_EPA_SHORT;
   const bool whole = prm.epa_iters_circle_poly <= CX_EPA_SHORT;  // the short budget is the full one
   const float* sx = ws.simplex[1];
+  // the EPA edge ring of every thread in shared memory, [entry][thread] (cx_narrow.cuh, EpaRing): 44.9 KB
+  // per block, 5 blocks per SM, no local memory
+  constexpr int RE = CX_EPA_SHORT + 3;
+  __shared__ float s_ax[RE][128], s_ay[RE][128], s_d[RE][128];
+  __shared__ uint8_t s_nx[RE][128];
+  const EpaRing<128> ring{&s_ax[0][threadIdx.x], &s_ay[0][threadIdx.x], &s_d[0][threadIdx.x], &s_nx[0][threadIdx.x]};
   // (appends per warp, not per block: only ~10 % of the hits are deferred, and a block barrier per
   // iteration would make every warp wait for the slowest of the block's four)
   for (uint32_t i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < cnt; i0 += stride) {
@@ -347,7 +353,7 @@ sweep_epa_cp_short_kernel(int64_t n, const float* __restrict__ a, const float* _
       const V2 s2 = mk2(sx[4 * n + i], sx[5 * n + i]);
       bool ecap;
       V2 ea, eb;
-      epa_edge<CX_EPA_SHORT + 3>(circle, B, s0, s1, s2, budget, ecap, ea, eb);
+      epa_edge_ring<128>(circle, B, s0, s1, s2, budget, ecap, ea, eb, ring);
       defer = ecap && !whole;
       if (!defer) {
         Contact c = contact_none();
