@@ -34,6 +34,19 @@
 namespace {
 
 constexpr int TPB = 128;
+// lanes of a warp that take work in the two single-wave sparse stages = 32 / SPREAD (see pipe_narrow_kernel)
+#ifndef CX_NARROW_SPREAD
+#define CX_NARROW_SPREAD 1
+#endif
+// block size of the narrow stage: the items a block takes are binned by pair class, so a bigger block
+// has fewer warps that straddle a class boundary (3 boundaries per block)
+#ifndef CX_NARROW_TPB
+#define CX_NARROW_TPB 128
+#endif
+constexpr int NTPB = CX_NARROW_TPB;
+#ifndef CX_CONTACT_SPREAD
+#define CX_CONTACT_SPREAD 1
+#endif
 constexpr int REC_FLOATS = 48;  // 192 B per env: polys 0..27, heights 28..35, knots 36..39
 constexpr uint32_t BASE_INLINE = 0xFFFFFFFFu;
 constexpr uint32_t F_QUEUED = 0x80000000u;
@@ -56,12 +69,13 @@ struct PipeWs {
   float* rec;      // [B][REC_FLOATS]
   uint32_t* item;  // [cap] (env << 5) | pair id
   float* res;      // [6][cap] simplex after K_B1; pen.xy, cp.xy after K_B2
-  uint32_t* hit;   // [cap] item slots whose GJK said yes
+  uint32_t* hit;   // [cap >= B] envs whose items overflowed the item queue (list of CTR_OVERFLOW entries)
   uint32_t* cenv;  // [B] envs with at least one GJK hit
   uint32_t* renv;  // [B] envs to reset
   float* racc;     // [B] reward accumulated over the sub-steps of this call (K > 1)
   uint32_t* latch; // [B] done code | rc << 8 | lc << 9 of an env that finished in an earlier sub-step
   uint32_t cap;
+  uint32_t nenv;   // envs of this range
 };
 
 CX_DEV uint32_t lanemask_lt() {
@@ -239,32 +253,37 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
       ws.item[slot] = 0xFFFFFFFFu;
     ws.cand[e] = cand;
     ws.base[e] = BASE_INLINE;
-    atomicAdd(&ws.ctr[CTR_OVERFLOW], 1u);
+    ws.hit[atomicAdd(&ws.ctr[CTR_OVERFLOW], 1u)] = (uint32_t)e;  // pipe_contact_kernel<true> takes these
   }
 }
 
 // ---- K_B -----------------------------------------------------------------------------------
 // GJK, and for hits (82 % of the candidate pairs on the bench state: resting leg/lander and
 // leg/ground contacts persist) EPA + contact point, in one pass over the item queue.
-__global__ void __launch_bounds__(TPB)
+__global__ void __launch_bounds__(NTPB)
 pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const uint32_t n = min(ws.ctr[CTR_ITEMS], ws.cap);
-  const uint32_t stride = gridDim.x * TPB;
+  // The stage is ONE wave that fills a third of the thread slots, so its time is the longest warp's
+  // instruction chain, and a warp serialises the divergent paths of its lanes: a block takes only
+  // IPB = TPB / CX_NARROW_SPREAD items and gives every warp 32 / CX_NARROW_SPREAD of them (the other
+  // lanes idle) -- more, shorter warps on SM slots that would otherwise be empty.
+  constexpr uint32_t LPW = 32u / CX_NARROW_SPREAD, IPB = NTPB / CX_NARROW_SPREAD;
+  const uint32_t stride = gridDim.x * IPB;
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
   uint32_t hits = 0u;
-  // The 128 items a block takes are binned by pair class (leg-lander, ground-lander, ground-leg,
+  // The NTPB items a block takes are binned by pair class (leg-lander, ground-lander, ground-leg,
   // leg-leg) through a counting sort in shared memory before they are handed to the threads, so
   // that a warp mostly runs one kind of pair: same polygon sizes, same EPA trip bound, ground
   // polygon built or not.  Results go to the item's own slot, so nothing downstream changes.
-  __shared__ uint32_t s_slot[TPB];
+  __shared__ uint32_t s_slot[NTPB];
   __shared__ uint32_t s_cnt[4];
-  for (uint32_t base = blockIdx.x * TPB; base < n; base += stride) {
+  for (uint32_t base = blockIdx.x * IPB; base < n; base += stride) {
     if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0u;
     __syncthreads();
     const uint32_t i0 = base + threadIdx.x;
     uint32_t it0 = 0xFFFFFFFFu;
-    if (i0 < n) it0 = ws.item[i0];
+    if (threadIdx.x < IPB && i0 < n) it0 = ws.item[i0];
     int cls = -1;
     uint32_t rank = 0u;
     if (it0 != 0xFFFFFFFFu) {
@@ -279,8 +298,9 @@ pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerive
       s_slot[off + rank] = i0;
     }
     __syncthreads();
-    if (threadIdx.x < c0 + c1 + c2 + c3) {
-      const uint32_t i = s_slot[threadIdx.x];
+    const uint32_t lane_ = threadIdx.x & 31u, j = (threadIdx.x >> 5) * LPW + lane_;
+    if (lane_ < LPW && j < c0 + c1 + c2 + c3) {
+      const uint32_t i = s_slot[j];
       const uint32_t it = ws.item[i];
       const uint32_t e = it >> 5;
       Poly A, Bp;
@@ -299,7 +319,11 @@ pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerive
   if ((threadIdx.x & 31u) == 0u && hits) atomicAdd(&ws.ctr[CTR_HITS], hits);
 }
 
-// contact source of one env: the queue results in HBM (or inline after a queue overflow)
+// contact source of one env: the queue results in HBM (INLINE = false), or, for an env whose items
+// overflowed the queue, its pairs evaluated on the spot (INLINE = true).  Two instantiations of the
+// contact kernel: the narrowphase code (90 KB of SASS) costs the common one 12 us per step when it is
+// compiled in, although it never runs there (the stage is instruction-fetch bound).
+template <bool INLINE>
 struct QueueContacts {
   const PipeWs& ws;
   const CotixLunarParams& P;
@@ -312,7 +336,7 @@ struct QueueContacts {
     return poly_pair(A, Bp, mk2(P.init_dir[0], P.init_dir[1]), P.gjk_max_iters);
   }
   CX_DEV Contact get(int bit) const {
-    if (base != BASE_INLINE) {
+    if (!INLINE) {
       const size_t i = base + (uint32_t)__popc(cand & ((1u << bit) - 1u));
       Contact c;
       c.pen = mk2(ws.res[0 * (size_t)ws.cap + i], ws.res[1 * (size_t)ws.cap + i]);
@@ -325,7 +349,7 @@ struct QueueContacts {
   // pairs with a non-NaN contact; the env's items sit in consecutive queue slots
   CX_DEV uint32_t live_bits() const {
     uint32_t live = 0u;
-    if (base != BASE_INLINE) {
+    if (!INLINE) {
       const float* cpx = ws.res + 2 * (size_t)ws.cap + base;
       const float* cpy = ws.res + 3 * (size_t)ws.cap + base;
       uint32_t todo = cand;
@@ -349,7 +373,7 @@ struct QueueContacts {
   }
   CX_DEV bool live(int bit) const {
     if (!((cand >> bit) & 1u)) return false;
-    if (base != BASE_INLINE) {
+    if (!INLINE) {
       const size_t i = base + (uint32_t)__popc(cand & ((1u << bit) - 1u));
       const float x = ws.res[2 * (size_t)ws.cap + i], y = ws.res[3 * (size_t)ws.cap + i];
       return !((x != x) || (y != y));
@@ -484,6 +508,7 @@ CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParam
   }
 }
 
+template <bool INLINE>
 __global__ void __launch_bounds__(TPB)
 pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
                     const LunarDerived D, const PipeWs ws) {
@@ -491,18 +516,27 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
   __shared__ WarpColl Wall[TPB / 32];
   WarpColl& W = Wall[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
-  const uint32_t n = ws.ctr[CTR_CENV];
-  const uint32_t stride = gridDim.x * TPB;
-  for (uint32_t c0 = blockIdx.x * TPB + (threadIdx.x & ~31u); c0 < n; c0 += stride) {
+  // INLINE: the (rare) envs of the overflow list; otherwise the contact-env queue minus those envs
+  const uint32_t n = INLINE ? min(ws.ctr[CTR_OVERFLOW], (uint32_t)ws.nenv) : ws.ctr[CTR_CENV];
+  if (INLINE && n == 0u) return;
+  const uint32_t* __restrict__ list = INLINE ? ws.hit : ws.cenv;
+  constexpr uint32_t CLPW = 32u / CX_CONTACT_SPREAD;  // envs per warp (the other lanes only help flipping coins)
+  const uint32_t stride = gridDim.x * (TPB / 32u) * CLPW;
+  for (uint32_t c0 = (blockIdx.x * (TPB / 32u) + (threadIdx.x >> 5)) * CLPW; c0 < n; c0 += stride) {
     const uint32_t c = c0 + (uint32_t)lane;
-    const bool valid = c < n;
+    bool valid = (uint32_t)lane < CLPW && c < n;
     uint32_t e = 0u, cand = 0u, status0 = 0u;
     EnvRegs E;
     uint32_t m[7] = {0u, 0u, 0u, 0u, 0u, 0u, 0u};
     bool crash = false, rc = false, lc = false, any = false;
     CoinCtx cc;
+    uint32_t base = 0u;
     if (valid) {
-      e = ws.cenv[c];
+      e = list[c];
+      base = ws.base[e];
+      if (!INLINE && base == BASE_INLINE) valid = false;  // left to the INLINE instantiation
+    }
+    if (valid) {
       cand = ws.cand[e] & CX_PAIR_BITS;
       E.key.a = __float_as_uint(s[COTIX_F_KEY0 * ld + e]);
       E.key.b = __float_as_uint(s[COTIX_F_KEY1 * ld + e]);
@@ -510,7 +544,7 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
       E.status = __float_as_uint(s[COTIX_F_STATUS * ld + e]);
       status0 = E.status;
     }
-    QueueContacts qc{ws, P, D, e, cand, valid ? ws.base[e] : 0u};
+    QueueContacts<INLINE> qc{ws, P, D, e, cand, base};
     if (valid) any = cell_masks(qc.live_bits(), true, m, crash, rc, lc);
     if (any) {
       make_coin_ctx(E, P, cc);
@@ -700,6 +734,7 @@ size_t carve(int64_t B, void* base, PipeWs* ws) {
     ws->latch = latch;
     ws->ctr = ctr; ws->cand = cand; ws->base = bs; ws->rec = rec; ws->item = item; ws->res = res;
     ws->hit = hit; ws->cenv = cenv; ws->renv = renv; ws->cap = item_capacity(B);
+    ws->nenv = (uint32_t)B;
   }
   return off;
 }
@@ -824,6 +859,11 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
     const int64_t cap = (int64_t)sms * 8;
     return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
   };
+  auto qgrid_sparse = [&](int64_t max_items, int spread) {
+    int64_t b = (max_items + TPB - 1) / TPB;
+    const int64_t cap = (int64_t)sms * 8 * spread;
+    return (unsigned)(b < 1 ? 1 : (b > cap ? cap : b));
+  };
   if (prof) {
     profile_collect();
     if (!g_ev_made) {
@@ -905,13 +945,18 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         CX_TRACE(0, cs);
         CX_MARK_B(1, cs);
         set_attrs(true, true);
-        cfg.gridDim = dim3(qgrid((int64_t)ws.cap));
+        cfg.gridDim = dim3(qgrid_sparse((int64_t)ws.cap * CX_NARROW_SPREAD * TPB / NTPB, CX_NARROW_SPREAD));
+        cfg.blockDim = dim3(NTPB);
         cudaLaunchKernelEx(&cfg, pipe_narrow_kernel, *p, D, ws);
+        cfg.blockDim = dim3(TPB);
         CX_MARK_E(1, cs);
         CX_TRACE(1, cs);
         CX_MARK_B(2, cs);
-        cfg.gridDim = dim3(qgrid(n));
-        cudaLaunchKernelEx(&cfg, pipe_contact_kernel, sout, ld, *p, D, ws);
+        cfg.gridDim = dim3(qgrid_sparse(n * CX_CONTACT_SPREAD, CX_CONTACT_SPREAD));
+        cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false>, sout, ld, *p, D, ws);
+        // the envs that overflowed the item queue (normally none: the kernel reads the count and exits)
+        cfg.gridDim = dim3((unsigned)(env_blocks < (unsigned)sms ? env_blocks : (unsigned)sms));
+        cudaLaunchKernelEx(&cfg, pipe_contact_kernel<true>, sout, ld, *p, D, ws);
         CX_MARK_E(2, cs);
         CX_TRACE(2, cs);
         CX_MARK_B(3, cs);
@@ -965,7 +1010,7 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
       }
     }
   }
-  cx_count_launch_n((int64_t)(4 * K + (p->auto_reset ? 1 : 0)) * plan.S * q.n_steps);
+  cx_count_launch_n((int64_t)(5 * K + (p->auto_reset ? 1 : 0)) * plan.S * q.n_steps);
   if (prof) g_ev_pending = true;
   return rc;
 }

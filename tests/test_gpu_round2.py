@@ -78,7 +78,7 @@ def test_steps_graph_replay(cuda_lib, oracle, exact_trig, pipe_cfg, mode):
     g = ll.StepsGraph(st, torch.from_numpy(acts).cuda(), T, P, want_obs=True, mode=mode)
     info = g.info()
     if mode == "pipeline":
-        assert info["kernel_launches"] == 3 * T * 5 and info["nodes"] >= 3 * T * 6
+        assert info["kernel_launches"] == 3 * T * 6 and info["nodes"] >= 3 * T * 7
     else:
         assert info["kernel_launches"] == T
     import parallax_b200
