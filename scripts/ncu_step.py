@@ -1,8 +1,8 @@
 """One steady-state step of the bench workload for Nsight Compute (eager launches, ONE env range):
-40 warm-up steps, then 2 more.  With split = 1 a step is 5 kernels, so
-  ncu --set full --clock-control none --import-source on -k regex:pipe_ --launch-skip 200 --launch-count 5 \
+40 warm-up steps, then 2 more.  With split = 1 a step is 6 kernels, so
+  ncu --set full --clock-control none --import-source on -k regex:pipe_ --launch-skip 240 --launch-count 6 \
       -o gpurun_out/r2_step python scripts/ncu_step.py
-captures exactly the 5 kernels of step 41.  usage: python scripts/ncu_step.py [envs]"""
+captures exactly the 6 kernels of step 41.  usage: python scripts/ncu_step.py [envs]"""
 import os
 import sys
 
