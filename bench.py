@@ -432,7 +432,7 @@ def run_ours(args):
                      "stages": stages, "queue_counts": counters},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": 2 * 4 * B,
                 "d2h_bytes_per_step": (8 * 4 + 4 + 1) * B, "steps": e2e_steps,
-                "overlap": "env ranges on their own streams: H2D(action) | kernels | D2H(obs, reward, done)",
+                "overlap": "4 env ranges on their own streams, H2D(action) -> kernels -> D2H(obs, reward, done); compute range after range, so D2H of range r runs under the kernels of r+1..",
                 "d2h_only_ms": d2h_ms, "d2h_gbs": (8 * 4 + 4 + 1) * B / (d2h_ms * 1e-3) / 1e9,
                 "copy_bound_value": world * B / (d2h_ms * 1e-3),
                 "note": "copy_bound_value = env-steps/s if a step cost only its D2H copy (measured, all ranks at once)",

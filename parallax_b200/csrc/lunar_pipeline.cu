@@ -993,12 +993,19 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
     if (cudaEventRecord(side->fork, st) != cudaSuccess) return cx_check_launch("pipeline fork");
     for (int r = 1; r < plan.S; ++r)
       if (cudaStreamWaitEvent(side->s[r], side->fork, 0) != cudaSuccess) return cx_check_launch("pipeline fork");
-    // the side ranges first: the caller's stream may already be busy
-    for (int r = 1; r < plan.S; ++r) {
-      const int rr = chain(side->s[r], r);
-      if (rr != 0 && rc == 0) rc = rr;
-    }
-    {
+    if (pre || post) {
+      // hooked (host-facing) step: ranges in natural order, so that a hook of range r may wait for an
+      // event a hook of range r - 1 recorded
+      for (int r = 0; r < plan.S; ++r) {
+        const int rr = chain(r == 0 ? st : side->s[r], r);
+        if (rr != 0 && rc == 0) rc = rr;
+      }
+    } else {
+      // the side ranges first: the caller's stream may already be busy
+      for (int r = 1; r < plan.S; ++r) {
+        const int rr = chain(side->s[r], r);
+        if (rr != 0 && rc == 0) rc = rr;
+      }
       const int rr = chain(st, 0);
       if (rr != 0 && rc == 0) rc = rr;
     }
