@@ -127,6 +127,8 @@ __global__ void resolve_kernel(int64_t n, float* body1, float* body2, const floa
     b[q].w = src[q][7];
     m[q].e = src[q][8];
     m[q].inv_mass = 1.0f / src[q][0];
+    m[q].dmass = divc_plain(src[q][0]);
+    m[q].dinertia = divc_plain(src[q][1]);
     m[q].mu = src[q][9];
   }
   resolve_collision(b[0], m[0], b[1], m[1], mk2(pen[2 * k], pen[2 * k + 1]),

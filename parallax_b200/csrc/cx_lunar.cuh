@@ -27,9 +27,40 @@
 struct BodyS {
   float px, py, vx, vy, ang, w;
 };
+// Exact division by a launch constant c in three operations instead of the ~22 of an IEEE division:
+//   q = x * r;  rem = fma(-q, c, x);  x / c == fma(rem, r, q)        with r = RN(1 / c)
+// (the remainder is exact, the correction lands on the correctly rounded quotient).  Whether that holds
+// for EVERY x is a property of c: the host checks it exhaustively over one binade of x (2^23 values; the
+// result is scale-invariant while nothing under- or overflows) the first time a constant is seen
+// (cx_divc_make, lunar_kernel.cu) and sets `ok`; x outside [1e-20, 1e20], x = 0 and non-finite x take
+// the plain division, as does every constant that fails the check.  The results are the bits of x / c.
+struct DivC {
+  float c, r;
+  int ok;
+};
+CX_DEV DivC divc_plain(float c) {
+  DivC d;
+  d.c = c;
+  d.r = 0.0f;
+  d.ok = 0;
+  return d;
+}
+CX_DEV float div_c(float x, const DivC& d) {
+  if (d.c == 1.0f) return x;  // x / 1 == x bit for bit (the legs' mass and inertia); uniform branch
+  if (d.ok) {
+    const float ax = fabsf(x);
+    if (ax >= 1e-20f && ax <= 1e20f) {  // false for NaN
+      const float q = x * d.r;
+      const float rem = __fmaf_rn(-q, d.c, x);
+      return __fmaf_rn(rem, d.r, q);
+    }
+  }
+  return x / d.c;
+}
 struct MassP {
   float mass, inertia, e, mu;
   float inv_mass;  // 1.0f / mass, IEEE: the same bits whether the host or a thread divides
+  DivC dmass, dinertia;
 };
 CX_DEV MassP mk_massp(const float props[4], float inv_mass) {
   MassP m;
@@ -38,6 +69,8 @@ CX_DEV MassP mk_massp(const float props[4], float inv_mass) {
   m.e = props[2];
   m.mu = props[3];
   m.inv_mass = inv_mass;
+  m.dmass = divc_plain(props[0]);
+  m.dinertia = divc_plain(props[1]);
   return m;
 }
 CX_DEV MassP mk_massp(const float props[4]) { return mk_massp(props, 1.0f / props[0]); }
@@ -101,7 +134,14 @@ struct LunarDerived {
   int orient[3];    // +1: local order is counter-clockwise (ascending angle), -1: clockwise
   float lext[4];    // lander local extents: min x, min y, max x, max y
   float inv_mass[4];  // 1.0f / body_props[i][0] (launch constants: divided once on the host, not per thread)
+  DivC dmass[4], dinertia[4];  // exact division by the bodies' mass / inertia (div_c)
 };
+CX_DEV MassP mk_massp(const float props[4], const LunarDerived& D, int i) {
+  MassP m = mk_massp(props, D.inv_mass[i]);
+  m.dmass = D.dmass[i];
+  m.dinertia = D.dinertia[i];
+  return m;
+}
 
 // order_clockwise of a RIGIDLY transformed convex polygon without computing any angle.
 // The vertices keep their cyclic order under rotation + translation, so the ascending-atan2
@@ -156,8 +196,18 @@ CX_DEV bool poly_order_rigid(Poly& p, int orient) {
 // ---- resolution — cotix/_collision_resolution.py:52-151 -------------------------------
 // x / m; a divisor of exactly 1 (the legs' mass and inertia) is skipped — x / 1 == x bit for bit —
 // and since m is a launch constant the branch is uniform
-CX_DEV float div_m(float x, float m) { return (m == 1.0f) ? x : x / m; }
 CX_DEV void apply_impulse(BodyS& b, const MassP& m, V2 imp, V2 point) {  // :68-73
+  V2 arm = point - mk2(b.px, b.py);
+  float torque = cross2(arm, imp);
+  b.vx = b.vx + div_c(imp.x, m.dmass);
+  b.vy = b.vy + div_c(imp.y, m.dmass);
+  b.w = b.w + div_c(torque, m.dinertia);
+}
+// the same with plain IEEE divisions: resolve_collision is out of line and gets its MassP by reference,
+// i.e. from local memory, where the three extra loads per division of div_c cost more than they save
+// (contact stage 64.8 -> 70.2 us); the inlined joints of the finish stage are where div_c pays (64 -> 53.5)
+CX_DEV float div_m(float x, float m) { return (m == 1.0f) ? x : x / m; }
+CX_DEV void apply_impulse_plain(BodyS& b, const MassP& m, V2 imp, V2 point) {
   V2 arm = point - mk2(b.px, b.py);
   float torque = cross2(arm, imp);
   b.vx = b.vx + div_m(imp.x, m.mass);
@@ -195,18 +245,24 @@ static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1
   V2 idv = idrag * vdu;
   ivec = ivec + idv;
   if (dot2(pen, vrel) < 0) return;
-  apply_impulse(b1, m1, -ivec, cp);
-  apply_impulse(b2, m2, ivec, cp);
+  apply_impulse_plain(b1, m1, -ivec, cp);
+  apply_impulse_plain(b2, m2, ivec, cp);
 }
 
 // ---- joints — cotix/_lunar_lander.py:145-218 -------------------------------------------
-static __device__ __noinline__ void joint_constraint(BodyS& b1, const MassP& m1, V2 c1, BodyS& b2, const MassP& m2, V2 c2,
-                             const CotixLunarParams& P) {
+CX_DEV void joint_constraint_inl(BodyS& b1, const MassP& m1, V2 c1, BodyS& b2, const MassP& m2, V2 c2,
+                                 const CotixLunarParams& P) {
   V2 dp = c1 - c2;
   V2 dv = velocity_at(b1, c1) - velocity_at(b2, c2);
   V2 imp = dp * P.spring_kp + dv * (norm2(dv) + P.spring_kv0) * P.spring_kv;
   apply_impulse(b1, m1, -imp, c1);
   apply_impulse(b2, m2, imp, c2);
+}
+// out of line (the fused kernel and the adjoint: code size); the pipeline's finish stage inlines it so that
+// the masses and their DivC fold into constant-bank operands instead of local-memory loads
+static __device__ __noinline__ void joint_constraint(BodyS& b1, const MassP& m1, V2 c1, BodyS& b2, const MassP& m2, V2 c2,
+                                                     const CotixLunarParams& P) {
+  joint_constraint_inl(b1, m1, c1, b2, m2, c2, P);
 }
 CX_DEV V2 rot_cs(V2 v, float c, float s) {  // rotate(): [[c,-s],[s,c]] @ v
   return mk2(c * v.x + (-s) * v.y, s * v.x + c * v.y);

@@ -383,7 +383,7 @@ CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const LunarDeri
                           const CoinCtx& cc, const int win[7]) {
   MassP mp[4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) mp[i] = mk_massp(P.body_props[i], D.inv_mass[i]);
+  for (int i = 0; i < 4; ++i) mp[i] = mk_massp(P.body_props[i], D, i);
   const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
   BodyS G;  // the static ground body (mass = inertia = inf); NaN once poisoned
   G.px = G.py = G.vx = G.vy = G.ang = G.w = poisoned ? CX_NAN : 0.0f;
@@ -465,11 +465,12 @@ CX_DEV void collide(EnvRegs& E, const CotixLunarParams& P, const LunarDerived& D
 
 // ---- key split, joints, judge --------------------------------------------------------------------
 // cs/sn: sin/cos of the three body angles of THIS step (after integration).
-CX_DEV void finish_step(EnvRegs& E, const CotixLunarParams& P, const float cs[3], const float sn[3],
+template <bool INLINE_JOINTS = false>
+CX_DEV void finish_step(EnvRegs& E, const CotixLunarParams& P, const LunarDerived& D, const float cs[3], const float sn[3],
                         float thr_main, float thr_side, bool crash, bool rc, bool lc, SubInfo& info) {
   MassP mp[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) mp[i] = mk_massp(P.body_props[i], 0.0f);  // the joints never read inv_mass
+  for (int i = 0; i < 3; ++i) mp[i] = mk_massp(P.body_props[i], D, i);
   // key, next_key = jr.split(key) (examples/test_viz.py:39)
   if (P.rng_mode == COTIX_RNG_THREEFRY) E.key = tf_split(E.key, 2u, 0u);
 
@@ -489,10 +490,17 @@ CX_DEV void finish_step(EnvRegs& E, const CotixLunarParams& P, const float cs[3]
     // over the constraint list; the anchors are those of the step (positions do not move here)
     const int loops = P.solver_loops < 1 ? 1 : P.solver_loops;
     for (int it = 0; it < loops; ++it) {
-      joint_constraint(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
-      joint_constraint(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
-      joint_constraint(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
-      joint_constraint(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
+      if (INLINE_JOINTS) {
+        joint_constraint_inl(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
+        joint_constraint_inl(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
+        joint_constraint_inl(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
+        joint_constraint_inl(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
+      } else {
+        joint_constraint(E.b[0], mp[0], lj0, E.b[2], mp[2], ll1, P);
+        joint_constraint(E.b[0], mp[0], lj1, E.b[2], mp[2], ll2, P);
+        joint_constraint(E.b[0], mp[0], lj2, E.b[1], mp[1], rl1, P);
+        joint_constraint(E.b[0], mp[0], lj3, E.b[1], mp[1], rl2, P);
+      }
     }
     E.b[1].w = E.b[1].w * P.leg_damping;
     E.b[2].w = E.b[2].w * P.leg_damping;

@@ -522,6 +522,8 @@ static __device__ __noinline__ void step_bwd_core(const EnvRegs& E, const StepCt
     mp[i].e = P.body_props[i][2];
     mp[i].mu = P.body_props[i][3];
     mp[i].inv_mass = 1.0f / P.body_props[i][0];
+    mp[i].dmass = divc_plain(P.body_props[i][0]);
+    mp[i].dinertia = divc_plain(P.body_props[i][1]);
   }
   const bool poisoned = (E.status & COTIX_ST_GROUND_NAN) != 0u;
   BodyS bd[4];

@@ -14,6 +14,11 @@
 // State is struct-of-arrays over the env axis (include/cotix_b200.h): every field access of a
 // warp is one coalesced 128-byte transaction.  This kernel keeps the state in registers across
 // K sub-steps; for large batches at K = 1 the wavefront pipeline (lunar_pipeline.cu) is faster.
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <mutex>
+
 #include "cx_launch.cuh"
 #include "cx_lunar_step.cuh"
 
@@ -157,7 +162,7 @@ __device__ void phase_c(EnvRegs& E, const CotixLunarParams& P, const LunarDerive
   bool crash, rc, lc;
   SmemContacts cs{S, cx, P};
   collide(E, P, D, cx.cand, cs, crash, rc, lc);
-  finish_step(E, P, cx.cs, cx.sn, cx.thr_main, cx.thr_side, crash, rc, lc, info);
+  finish_step(E, P, D, cx.cs, cx.sn, cx.thr_main, cx.thr_side, crash, rc, lc, info);
 }
 
 __global__ void __launch_bounds__(TPB)
@@ -259,6 +264,40 @@ static void derive_body(const float (*v)[2], int n, int* ok, int* orient) {
   }
   *ok = good ? 1 : 0;
 }
+// DivC for constant c (see cx_lunar.cuh): r = RN(1 / c) and the exhaustive check that
+// fma(fma(-x r, c, x), r, x r) == x / c for all 2^23 floats x of one binade (the property is invariant
+// under scaling x by powers of two while nothing under- or overflows, which div_c's range test excludes).
+// One check per distinct constant and process (a few tens of milliseconds), cached.
+static DivC cx_divc_make(float c) {
+  DivC d;
+  d.c = c;
+  d.r = 0.0f;
+  d.ok = 0;
+  const float ac = fabsf(c);
+  if (!(ac >= 1e-6f && ac <= 1e6f) || c == 1.0f) return d;  // inf (static bodies), NaN, extreme: plain division
+  static std::mutex mu;
+  static std::map<uint32_t, int> cache;
+  uint32_t bits;
+  memcpy(&bits, &c, 4);
+  d.r = 1.0f / c;
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(bits);
+  if (it == cache.end()) {
+    int ok = 1;
+    for (uint32_t m = 0; m < (1u << 23) && ok; ++m) {
+      const uint32_t xb = 0x3F800000u | m;  // x in [1, 2)
+      float x;
+      memcpy(&x, &xb, 4);
+      const float q = x * d.r;
+      const float rem = fmaf(-q, c, x);
+      if (fmaf(rem, d.r, q) != x / c) ok = 0;
+    }
+    it = cache.emplace(bits, ok).first;
+  }
+  d.ok = it->second;
+  return d;
+}
+
 extern "C" void cx_lunar_derive(const CotixLunarParams* p, LunarDerived* out) {
   LunarDerived& D = *out;
   derive_body(p->lander_local, 6, &D.rigid_ok[0], &D.orient[0]);
@@ -272,7 +311,11 @@ extern "C" void cx_lunar_derive(const CotixLunarParams* p, LunarDerived* out) {
     D.lext[2] = fmaxf(D.lext[2], p->lander_local[k][0]);
     D.lext[3] = fmaxf(D.lext[3], p->lander_local[k][1]);
   }
-  for (int i = 0; i < 4; ++i) D.inv_mass[i] = 1.0f / p->body_props[i][0];
+  for (int i = 0; i < 4; ++i) {
+    D.inv_mass[i] = 1.0f / p->body_props[i][0];
+    D.dmass[i] = cx_divc_make(p->body_props[i][0]);
+    D.dinertia[i] = cx_divc_make(p->body_props[i][1]);
+  }
 }
 
 extern "C" int cx_launch_lunar_step(cudaStream_t st, int64_t B, const float* sin_, float* sout,

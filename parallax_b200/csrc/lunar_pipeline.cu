@@ -389,8 +389,8 @@ struct QueueContacts {
 CX_DEV bool finish_and_store(EnvRegs& E, int64_t e, float* __restrict__ s, int64_t ld,
                              const float* __restrict__ action, float* __restrict__ reward,
                              uint8_t* __restrict__ done, float* __restrict__ obs,
-                             const CotixLunarParams& P, bool crash, bool rc, bool lc, const PipeWs& ws, int k,
-                             int K) {
+                             const CotixLunarParams& P, const LunarDerived& D, bool crash, bool rc, bool lc,
+                             const PipeWs& ws, int k, int K) {
   float am = 0.0f, as = 0.0f;
   if (action) {
     am = action[e];
@@ -400,7 +400,7 @@ CX_DEV bool finish_and_store(EnvRegs& E, int64_t e, float* __restrict__ s, int64
 #pragma unroll
   for (int i = 0; i < 3; ++i) cx_sincosf(E.b[i].ang, &sn[i], &cs[i]);
   SubInfo si;
-  finish_step(E, P, cs, sn, jclip(am, 0.0f, 1.0f), jclip(as, -1.0f, 1.0f), crash, rc, lc, si);
+  finish_step<true>(E, P, D, cs, sn, jclip(am, 0.0f, 1.0f), jclip(as, -1.0f, 1.0f), crash, rc, lc, si);
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     s[(i * 6 + 2) * ld + e] = E.b[i].vx;
@@ -590,7 +590,8 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
 __global__ void __launch_bounds__(TPB, CX_FINISH_MINB)
 pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __restrict__ action,
                    float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
-                   const __grid_constant__ CotixLunarParams P, const PipeWs ws, int k, int K) {
+                   const __grid_constant__ CotixLunarParams P, const __grid_constant__ LunarDerived D, const PipeWs ws,
+                   int k, int K) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   bool want_reset = false;
@@ -613,7 +614,7 @@ pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __
       load_dyn(E, s, ld, e);
       load_meta(E, s, ld, e);
       const uint32_t cw = ws.cand[e];
-      want_reset = finish_and_store(E, e, s, ld, action, reward, done, obs, P, (cw >> F_CRASH_SHIFT) & 1u,
+      want_reset = finish_and_store(E, e, s, ld, action, reward, done, obs, P, D, (cw >> F_CRASH_SHIFT) & 1u,
                                     (cw >> F_RC_SHIFT) & 1u, (cw >> F_LC_SHIFT) & 1u, ws, k, K);
     }
   }
@@ -962,7 +963,7 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         CX_MARK_B(3, cs);
         set_attrs(true, false);
         cfg.gridDim = dim3(env_blocks);
-        cudaLaunchKernelEx(&cfg, pipe_finish_kernel, n, sout, ld, act, rw, dn, ob, *p, ws, k, K);
+        cudaLaunchKernelEx(&cfg, pipe_finish_kernel, n, sout, ld, act, rw, dn, ob, *p, D, ws, k, K);
         CX_MARK_E(3, cs);
         CX_TRACE(3, cs);
       }
