@@ -217,9 +217,9 @@ CX_DEV void apply_impulse_plain(BodyS& b, const MassP& m, V2 imp, V2 point) {
 CX_DEV V2 velocity_at(const BodyS& b, V2 point) {  // cotix/_bodies.py:50-55
   return mk2(b.vx, b.vy) + perp(point - mk2(b.px, b.py)) * b.w;
 }
-static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1, BodyS& b2,
-                                               const MassP& m2, V2 pen, V2 cp, float baumgarte,
-                                               float baumgarte_dt) {
+template <bool DIVC>
+CX_DEV void resolve_collision_inl(BodyS& b1, const MassP& m1, BodyS& b2, const MassP& m2, V2 pen, V2 cp,
+                                  float baumgarte, float baumgarte_dt) {
   if (isnan2(cp)) return;
   V2 p1 = mk2(b1.px, b1.py), p2 = mk2(b2.px, b2.py);
   V2 v1 = mk2(b1.vx, b1.vy) + perp(cp - p1) * b1.w;
@@ -231,7 +231,8 @@ static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1
   float el = jmin(m1.e, m2.e);
   V2 r1 = cp - p1, r2 = cp - p2;
   float lever1 = sumsq2(r1), lever2 = sumsq2(r2);
-  float ang = lever1 / m1.inertia + lever2 / m2.inertia;
+  float ang = DIVC ? div_c(lever1, m1.dinertia) + div_c(lever2, m2.dinertia)
+                   : lever1 / m1.inertia + lever2 / m2.inertia;
   float nim = -(1.0f + el) * vn - baumgarte * norm2(pen) / baumgarte_dt;
   float kden = m1.inv_mass + m2.inv_mass + ang;  // 1.0f / m1.mass + 1.0f / m2.mass + ang
   float nimp = nim / kden;
@@ -245,8 +246,18 @@ static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1
   V2 idv = idrag * vdu;
   ivec = ivec + idv;
   if (dot2(pen, vrel) < 0) return;
-  apply_impulse_plain(b1, m1, -ivec, cp);
-  apply_impulse_plain(b2, m2, ivec, cp);
+  if (DIVC) {
+    apply_impulse(b1, m1, -ivec, cp);
+    apply_impulse(b2, m2, ivec, cp);
+  } else {
+    apply_impulse_plain(b1, m1, -ivec, cp);
+    apply_impulse_plain(b2, m2, ivec, cp);
+  }
+}
+static __device__ __noinline__ void resolve_collision(BodyS& b1, const MassP& m1, BodyS& b2,
+                                               const MassP& m2, V2 pen, V2 cp, float baumgarte,
+                                               float baumgarte_dt) {
+  resolve_collision_inl<false>(b1, m1, b2, m2, pen, cp, baumgarte, baumgarte_dt);
 }
 
 // ---- joints — cotix/_lunar_lander.py:145-218 -------------------------------------------

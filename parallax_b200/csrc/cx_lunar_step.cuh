@@ -378,9 +378,14 @@ CX_DEV void make_coin_ctx(const EnvRegs& E, const CotixLunarParams& P, CoinCtx& 
 
 // choose_random_contact (:274-295) + the sequential resolution scan (:310-336), given the winner
 // of every cell (win[c] = winning q or -1).  Updates E (velocities, status).
-template <class CS>
+template <class CS, bool INLINE_RESOLVE = false>
 CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const LunarDerived& D, const CS& cs,
                           const CoinCtx& cc, const int win[7]) {
+#define CX_RESOLVE(...)                                        \
+  do {                                                         \
+    if (INLINE_RESOLVE) resolve_collision_inl<true>(__VA_ARGS__); \
+    else resolve_collision(__VA_ARGS__);                       \
+  } while (0)
   MassP mp[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) mp[i] = mk_massp(P.body_props[i], D, i);
@@ -418,27 +423,28 @@ CX_DEV void collide_apply(EnvRegs& E, const CotixLunarParams& P, const LunarDeri
   // sequential resolution scan i = 0..3 (:310-336); row 0 is always empty
   if (v10) {
     const Contact c = cs.get(0);
-    resolve_collision(E.b[1], mp[1], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+    CX_RESOLVE(E.b[1], mp[1], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
   }
   if (j2 == 0 && v20) {
     const Contact c = cs.get(1);
-    resolve_collision(E.b[2], mp[2], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+    CX_RESOLVE(E.b[2], mp[2], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
   }
   if (j2 == 1 && v21) {
     const Contact c = cs.get(9);
-    resolve_collision(E.b[2], mp[2], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+    CX_RESOLVE(E.b[2], mp[2], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
   }
   if (j3 >= 0 && j3 <= 2) {
     const int w = j3 == 0 ? w30 : (j3 == 1 ? w31 : w32);
     if (w >= 0) {
       const Contact c = cs.get((j3 == 0 ? 2 : (j3 == 1 ? 11 : 18)) + w);
-      if (j3 == 0) resolve_collision(G, mp[3], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      else if (j3 == 1) resolve_collision(G, mp[3], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
-      else resolve_collision(G, mp[3], E.b[2], mp[2], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      if (j3 == 0) CX_RESOLVE(G, mp[3], E.b[0], mp[0], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      else if (j3 == 1) CX_RESOLVE(G, mp[3], E.b[1], mp[1], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
+      else CX_RESOLVE(G, mp[3], E.b[2], mp[2], c.pen, c.cp, P.baumgarte, P.baumgarte_dt);
     }
   }
   if ((G.vx != 0.0f) || (G.vy != 0.0f) || (G.w != 0.0f) || (G.px != 0.0f) || (G.py != 0.0f) || (G.ang != 0.0f))
     E.status |= COTIX_ST_GROUND_NAN;
+#undef CX_RESOLVE
 }
 
 // one thread does everything for its env (the fused kernel)

@@ -332,13 +332,9 @@ scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict_
     const int q = allq[i][j];
     MassP mi, mj;
     mi.mass = S->props[i][0]; mi.inertia = S->props[i][1]; mi.e = S->props[i][2]; mi.mu = S->props[i][3];
-    mi.inv_mass = 1.0f / mi.mass;
-    mi.dmass = divc_plain(mi.mass);
-    mi.dinertia = divc_plain(mi.inertia);
+    mi.inv_mass = 1.0f / mi.mass;  // (dmass / dinertia: not read by the out-of-line resolve_collision)
     mj.mass = S->props[j][0]; mj.inertia = S->props[j][1]; mj.e = S->props[j][2]; mj.mu = S->props[j][3];
     mj.inv_mass = 1.0f / mj.mass;
-    mj.dmass = divc_plain(mj.mass);
-    mj.dinertia = divc_plain(mj.inertia);
     resolve_collision(body[i], mi, body[j], mj, mk2(cpen[q][0], cpen[q][1]),
                       mk2(ccp[q][0], ccp[q][1]), P.baumgarte, P.baumgarte_dt);
   }
