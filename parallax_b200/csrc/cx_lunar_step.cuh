@@ -216,6 +216,7 @@ CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const Cot
     // of such segments (1-3) rather than 7, so the lanes of a warp stay together
     const float m = CX_CULL_MARGIN;
     const float ulx = fminf(bL.lx, fminf(br.lx, bl.lx)), uhx = fmaxf(bL.hx, fmaxf(br.hx, bl.hx));
+    const float uly = fminf(bL.ly, fminf(br.ly, bl.ly));
     float X[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) X[k] = terrain_x(E.kn, P, k);
@@ -223,8 +224,12 @@ CX_DEV void integrate_and_cull(EnvRegs& E, float a_main, float a_side, const Cot
 #pragma unroll
     for (int k = 0; k < 7; ++k) {
       const float glx = fminf(X[k], X[k + 1]), ghx = fmaxf(X[k], X[k + 1]);
-      // negated form so that NaN bounds keep the segment (aabb_near decides below)
-      if (!(uhx + m < glx || ghx + m < ulx)) segs |= 1u << k;
+      // the segment's box against the box of the whole assembly, in x AND in y (its top is the higher of its
+      // two heights and the floor): what the per-polygon aabb_near below would reject anyway, decided here
+      // with static indices so that an env in flight enters the loop with no segment at all -- the loop's
+      // trip count is the maximum over the warp.  Negated form: NaN bounds keep the segment.
+      const float ghy = fmaxf(fmaxf(E.h[k], E.h[k + 1]), P.ground_floor);
+      if (!(uhx + m < glx || ghx + m < ulx || ghy + m < uly)) segs |= 1u << k;
     }
     while (segs) {
       const int k = __ffs(segs) - 1;
