@@ -34,22 +34,19 @@
 namespace {
 
 constexpr int TPB = 128;
-// lanes of a warp that take work in the two single-wave sparse stages = 32 / SPREAD (see pipe_narrow_kernel)
-#ifndef CX_NARROW_SPREAD
-#define CX_NARROW_SPREAD 1
-#endif
+// Lanes of a warp that take work in the two sparse stages = 32 / SPREAD (template parameter, chosen per
+// launch by sparse_spread()).  At 1 M envs these stages are bound by warp-instruction throughput and
+// SPREAD = 1 is best (2 / 4: 61 -> 117 -> 251 us); at a few thousand envs they are ONE thin wave whose time
+// is the longest warp's chain, a warp serialises the divergent paths of its lanes, and the SMs are empty:
+// fewer items per warp make the chain shorter.
 // block size of the narrow stage: the items a block takes are binned by pair class, so a bigger block
 // has fewer warps that straddle a class boundary (3 boundaries per block)
 #ifndef CX_NARROW_TPB
 #define CX_NARROW_TPB 128
 #endif
 constexpr int NTPB = CX_NARROW_TPB;
-#ifndef CX_CONTACT_SPREAD
-#define CX_CONTACT_SPREAD 1
-#endif
 constexpr int REC_FLOATS = 48;  // 192 B per env: polys 0..27, heights 28..35, knots 36..39
 constexpr uint32_t BASE_INLINE = 0xFFFFFFFFu;
-constexpr uint32_t F_QUEUED = 0x80000000u;
 constexpr int F_CRASH_SHIFT = 25, F_RC_SHIFT = 26, F_LC_SHIFT = 27;
 
 enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 4, CTR_WORDS = 16 };
@@ -260,15 +257,16 @@ pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restri
 // ---- K_B -----------------------------------------------------------------------------------
 // GJK, and for hits (82 % of the candidate pairs on the bench state: resting leg/lander and
 // leg/ground contacts persist) EPA + contact point, in one pass over the item queue.
+template <int SPREAD>
 __global__ void __launch_bounds__(NTPB)
 pipe_narrow_kernel(const __grid_constant__ CotixLunarParams P, const LunarDerived D, const PipeWs ws) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   const uint32_t n = min(ws.ctr[CTR_ITEMS], ws.cap);
   // The stage is ONE wave that fills a third of the thread slots, so its time is the longest warp's
   // instruction chain, and a warp serialises the divergent paths of its lanes: a block takes only
-  // IPB = TPB / CX_NARROW_SPREAD items and gives every warp 32 / CX_NARROW_SPREAD of them (the other
+  // IPB = NTPB / SPREAD items and gives every warp 32 / SPREAD of them (the other
   // lanes idle) -- more, shorter warps on SM slots that would otherwise be empty.
-  constexpr uint32_t LPW = 32u / CX_NARROW_SPREAD, IPB = NTPB / CX_NARROW_SPREAD;
+  constexpr uint32_t LPW = 32u / SPREAD, IPB = NTPB / SPREAD;
   const uint32_t stride = gridDim.x * IPB;
   const V2 start = mk2(P.init_dir[0], P.init_dir[1]);
   uint32_t hits = 0u;
@@ -508,7 +506,7 @@ CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParam
   }
 }
 
-template <bool INLINE>
+template <bool INLINE, int SPREAD>
 __global__ void __launch_bounds__(TPB)
 pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
                     const LunarDerived D, const PipeWs ws) {
@@ -520,7 +518,7 @@ pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ C
   const uint32_t n = INLINE ? min(ws.ctr[CTR_OVERFLOW], (uint32_t)ws.nenv) : ws.ctr[CTR_CENV];
   if (INLINE && n == 0u) return;
   const uint32_t* __restrict__ list = INLINE ? ws.hit : ws.cenv;
-  constexpr uint32_t CLPW = 32u / CX_CONTACT_SPREAD;  // envs per warp (the other lanes only help flipping coins)
+  constexpr uint32_t CLPW = 32u / SPREAD;  // envs per warp (the other lanes only help flipping coins)
   const uint32_t stride = gridDim.x * (TPB / 32u) * CLPW;
   for (uint32_t c0 = (blockIdx.x * (TPB / 32u) + (threadIdx.x >> 5)) * CLPW; c0 < n; c0 += stride) {
     const uint32_t c = c0 + (uint32_t)lane;
@@ -741,6 +739,16 @@ size_t carve(int64_t B, void* base, PipeWs* ws) {
   return off;
 }
 
+// lanes-per-warp divisor of the sparse stages for a range of n envs (see the note at the top);
+// COTIX_SPARSE_SPREAD = 1 | 2 | 4 overrides (measurement aid)
+int sparse_spread(int64_t n) {
+  static const char* env = getenv("COTIX_SPARSE_SPREAD");
+  if (env && (env[0] == '1' || env[0] == '2' || env[0] == '4')) return env[0] - '0';
+  // measured (100-step contact-rich rollouts / steps, spread 1 -> 2 -> 4): 4096 envs 6.65 -> 6.24 -> 5.87 ms,
+  // 16384: 7.02 -> 6.58 -> 6.28 ms, 65536: 67.8 -> 64.9 -> 63.6 us per step, 262144: 90.7 -> 94.6 -> 113.6 us
+  return n <= 65536 ? 4 : 1;
+}
+
 // the ranges of a batch: S ranges of ceil(B / S) envs rounded up to a multiple of TPB (so that every
 // range starts on a 512-byte boundary of every state row), the last one takes what is left
 struct RangePlan {
@@ -900,6 +908,7 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
   auto chain = [&](cudaStream_t cs, int r) -> int {
     const int64_t off = plan.off[r], n = plan.off[r + 1] - off;
     const PipeWs& ws = plan.ws[r];
+    const int spread = sparse_spread(n);
     const unsigned env_blocks = (unsigned)((n + TPB - 1) / TPB);
     cudaLaunchAttribute attr[2];
     cudaLaunchConfig_t cfg;
@@ -947,18 +956,22 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         CX_TRACE(0, cs);
         CX_MARK_B(1, cs);
         set_attrs(true, true);
-        cfg.gridDim = dim3(qgrid_sparse((int64_t)ws.cap * CX_NARROW_SPREAD * TPB / NTPB, CX_NARROW_SPREAD));
+        cfg.gridDim = dim3(qgrid_sparse((int64_t)ws.cap * spread * TPB / NTPB, spread));
         cfg.blockDim = dim3(NTPB);
-        cudaLaunchKernelEx(&cfg, pipe_narrow_kernel, *p, D, ws);
+        if (spread == 1) cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<1>, *p, D, ws);
+        else if (spread == 2) cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<2>, *p, D, ws);
+        else cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<4>, *p, D, ws);
         cfg.blockDim = dim3(TPB);
         CX_MARK_E(1, cs);
         CX_TRACE(1, cs);
         CX_MARK_B(2, cs);
-        cfg.gridDim = dim3(qgrid_sparse(n * CX_CONTACT_SPREAD, CX_CONTACT_SPREAD));
-        cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false>, sout, ld, *p, D, ws);
+        cfg.gridDim = dim3(qgrid_sparse(n * spread, spread));
+        if (spread == 1) cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 1>, sout, ld, *p, D, ws);
+        else if (spread == 2) cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 2>, sout, ld, *p, D, ws);
+        else cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 4>, sout, ld, *p, D, ws);
         // the envs that overflowed the item queue (normally none: the kernel reads the count and exits)
         cfg.gridDim = dim3((unsigned)(env_blocks < (unsigned)sms ? env_blocks : (unsigned)sms));
-        cudaLaunchKernelEx(&cfg, pipe_contact_kernel<true>, sout, ld, *p, D, ws);
+        cudaLaunchKernelEx(&cfg, pipe_contact_kernel<true, 1>, sout, ld, *p, D, ws);
         CX_MARK_E(2, cs);
         CX_TRACE(2, cs);
         CX_MARK_B(3, cs);
