@@ -264,9 +264,13 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
  * n_steps on their own streams WITHOUT joining between steps, so the latency-bound sparse stages of
  * one range execute under the dense stages of the others; the streams are forked from and joined
  * back into `stream`, so the call is stream-ordered and CUDA-Graph capturable (cotix_graph_*):
- * capture it once and a rollout of n_steps steps is ONE graph launch.  workspace NULL: n_steps
- * launches of the fused kernel.  reward / done / obs (or NULL) hold the last step's values.
+ * capture it once and a rollout of n_steps steps is ONE graph launch.  workspace NULL: up to
+ * COTIX_ROLLOUT_MAX_ENVS envs (and substeps <= 1) run all n_steps inside ONE launch with the envs
+ * resident in their thread block (csrc/lunar_rollout.cu: no launch gaps, no queue counters -- the
+ * small-batch, latency-bound case); larger batches n_steps launches of the fused kernel.  Same results
+ * bit for bit on every route.  reward / done / obs (or NULL) hold the last step's values.
  */
+#define COTIX_ROLLOUT_MAX_ENVS 32768
 int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, const float* actions,
                          int32_t n_actions, int32_t n_steps, float* reward, uint8_t* done, float* obs,
                          const CotixLunarParams* p, void* workspace, int64_t workspace_bytes);

@@ -26,7 +26,7 @@ if FLAVOUR not in ("exact", "fast"):
 FLAVOUR_LIBS = {"exact": os.path.join(_PKG, "libcotix_b200.so"), "fast": os.path.join(_PKG, "libcotix_b200_fast.so")}
 FAST_FLAGS = ["-fmad=true", "-prec-div=false", "-prec-sqrt=false", "-DCOTIX_MATH_FAST=1"]
 LIB_PATH = os.environ.get("COTIX_LIB_PATH") or FLAVOUR_LIBS[FLAVOUR]
-SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu",
+SOURCES = ["abi.cu", "abi_lunar.cu", "narrowphase_kernel.cu", "lunar_kernel.cu", "lunar_pipeline.cu", "lunar_rollout.cu",
            "scene_kernel.cu", "lunar_adjoint.cu", "raster_kernel.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

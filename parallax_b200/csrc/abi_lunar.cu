@@ -16,6 +16,8 @@
 
 extern "C" int cx_launch_lunar_step(cudaStream_t, int64_t, const float*, float*, int64_t,
                                     const float*, float*, uint8_t*, float*, const CotixLunarParams*);
+extern "C" int cx_launch_lunar_rollout_kernel(cudaStream_t, int64_t, const float*, float*, int64_t, int64_t, const float*,
+                                              int64_t, int, int, float*, uint8_t*, float*, const CotixLunarParams*);
 extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, float*, int64_t,
                                      const CotixLunarParams*);
 
@@ -275,6 +277,15 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
                                   obs, p, workspace, workspace_bytes);
 }
 
+// Multi-step calls without a workspace: up to COTIX_ROLLOUT_MAX_ENVS envs run all their steps inside one launch of
+// the block-resident rollout kernel (csrc/lunar_rollout.cu; K = 1 sub-step per step only), larger batches one
+// fused launch per step.  COTIX_ROLLOUT_KERNEL=0 keeps the per-step launches (A/B measurements, tests).
+static bool use_rollout_kernel(int64_t B, int64_t n_steps, const CotixLunarParams* p) {
+  static const char* env = getenv("COTIX_ROLLOUT_KERNEL");
+  if (env && env[0] == '0') return false;
+  return n_steps > 1 && p->substeps <= 1 && B <= COTIX_ROLLOUT_MAX_ENVS;
+}
+
 int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, const float* actions,
                          int32_t n_actions, int32_t n_steps, float* reward, uint8_t* done, float* obs,
                          const CotixLunarParams* p, void* workspace, int64_t workspace_bytes) {
@@ -285,6 +296,9 @@ int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, cons
   if (workspace)
     return cx_launch_lunar_pipeline_steps((cudaStream_t)stream, B, state, state, 0, ld, actions, 2 * ld,
                                           n_actions, n_steps, reward, done, obs, p, workspace, workspace_bytes);
+  if (use_rollout_kernel(B, n_steps, p))  // small batch: all steps in one launch, envs resident in their block
+    return cx_launch_lunar_rollout_kernel((cudaStream_t)stream, B, state, state, 0, ld, actions, 2 * ld, n_actions,
+                                          n_steps, reward, done, obs, p);
   for (int32_t t = 0; t < n_steps; ++t) {
     const float* a = actions ? actions + (int64_t)(t % n_actions) * 2 * ld : nullptr;
     const int rc = cx_launch_lunar_step((cudaStream_t)stream, B, state, state, ld, a, reward, done, obs, p);
@@ -387,6 +401,9 @@ int cotix_lunar_rollout(void* stream, int64_t B, int32_t T, float* tape, int64_t
     return cx_launch_lunar_pipeline_steps((cudaStream_t)stream, B, tape, tape + slot, slot, ld, actions, 2 * ld,
                                           T > 0 ? T : 1, T, nullptr, nullptr, nullptr, p, workspace,
                                           workspace_bytes);
+  if (use_rollout_kernel(B, T, p))
+    return cx_launch_lunar_rollout_kernel((cudaStream_t)stream, B, tape, tape + slot, slot, ld, actions, 2 * ld, T, T,
+                                          nullptr, nullptr, nullptr, p);
   for (int32_t t = 0; t < T; ++t) {
     const float* a = actions ? actions + (int64_t)t * 2 * ld : nullptr;
     const int rc = cx_launch_lunar_step((cudaStream_t)stream, B, tape + t * slot, tape + (t + 1) * slot, ld, a,

@@ -280,13 +280,138 @@ CX_DEV void pair_bodies(int pid, int& wa, int& wb, int& gk) {
 }
 // ground part k as the collider sees it: Polygon4.__init__ sort (cotix/_lunar_lander.py:132)
 // followed by the identity transform + re-sort of part.transform (cotix/_colliders.py:92-94)
+#ifndef CX_GROUND_FAST
+#define CX_GROUND_FAST 1
+#endif
+// One order_clockwise pass over a quadrilateral given in COUNTER-CLOCKWISE cyclic order, without computing an
+// angle: the ascending-atan2 order about the centroid is the same cycle started at the one vertex below the
+// centroid whose predecessor is not (cx_atan2f's branch cut: dy < 0 gives a negative angle, dy = -0 gives +pi).
+// The centroid and the differences are computed with exactly the operations of poly_sort_cw (running sums
+// from 0 in vertex order, / 4), so the sign of every dy is the sign poly_sort_cw's atan2 argument has.
+// check_gaps: also require every angular gap between neighbours to exceed 0.05 rad (atan2 errors are 1e-6),
+// which makes the cyclic order the sorted order.  Returns false (c untouched) when the pattern is not found.
+CX_DEV bool quad_order_pass(float cxv[4], float cyv[4], bool check_gaps) {
+  float sx = 0.0f, sy = 0.0f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    sx = sx + cxv[k];
+    sy = sy + cyv[k];
+  }
+  const float mx = sx / 4.0f, my = sy / 4.0f;
+  float dx[4], dy[4];
+  bool neg[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    dy[k] = cyv[k] - my;
+    dx[k] = cxv[k] - mx;
+    neg[k] = dy[k] < 0.0f;
+  }
+  bool ok = true;
+  if (check_gaps) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int j = (k + 1) & 3;
+      const float cr = dx[k] * dy[j] - dy[k] * dx[j];
+      const float dt = dx[k] * dx[j] + dy[k] * dy[j];
+      ok = ok && (cr > 0.0f) && (cr > 0.05f * dt);
+    }
+  }
+  int start = 0, nstart = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (neg[k] && !neg[(k + 3) & 3]) {
+      start = k;
+      ++nstart;
+    }
+  }
+  if (!ok || nstart != 1) return false;
+  float ox[4], oy[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    ox[t] = cxv[0];
+    oy[t] = cyv[0];
+#pragma unroll
+    for (int k = 1; k < 4; ++k)
+      if (((start + t) & 3) == k) {
+        ox[t] = cxv[k];
+        oy[t] = cyv[k];
+      }
+  }
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    cxv[t] = ox[t];
+    cyv[t] = oy[t];
+  }
+  return true;
+}
 CX_DEV void ground_poly(float x0, float h0, float x1, float h1, const CotixLunarParams& P, Poly& g) {
   g.n = 4;
-  g.x[0] = x0; g.y[0] = h0;
-  g.x[1] = x0; g.y[1] = P.ground_floor;
-  g.x[2] = x1; g.y[2] = h1;
-  g.x[3] = x1; g.y[3] = P.ground_floor;
   g.x[4] = g.y[4] = g.x[5] = g.y[5] = 0.0f;
+  const float f = P.ground_floor;
+#if CX_GROUND_FAST
+  // A regular trapezoid (left of right, tops above the floor) of ordinary size: its two order_clockwise passes
+  // (8 atan2 + 2 sorts, a tenth of the narrowphase's instructions) reduce to two rotations of the cycle
+  // bottom-left -> bottom-right -> top-right -> top-left.  The bounds keep the rounding of the second pass's
+  // centroid (a different summation order) three orders of magnitude below the gap that was checked.
+  const float lim = 1024.0f;
+  if ((x1 - x0 >= 0.5f) && (h0 > f) && (h1 > f) && (fabsf(x0) <= lim) && (fabsf(x1) <= lim) && (fabsf(h0) <= lim) &&
+      (fabsf(h1) <= lim) && (fabsf(f) <= lim)) {
+    // poly_sort_cw's centroid sums the vertices in the order they are stored: raw order first
+    const float sx = ((0.0f + x0) + x0 + x1) + x1, sy = ((0.0f + h0) + f + h1) + f;
+    const float mx = sx / 4.0f, my = sy / 4.0f;
+    // counter-clockwise cycle of the raw vertices: (x0, f), (x1, f), (x1, h1), (x0, h0)
+    float cxv[4] = {x0, x1, x1, x0}, cyv[4] = {f, f, h1, h0};
+    float dx[4], dy[4];
+    bool neg[4], ok = true;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      dy[k] = cyv[k] - my;
+      dx[k] = cxv[k] - mx;
+      neg[k] = dy[k] < 0.0f;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int j = (k + 1) & 3;
+      const float cr = dx[k] * dy[j] - dy[k] * dx[j];
+      const float dt = dx[k] * dx[j] + dy[k] * dy[j];
+      ok = ok && (cr > 0.0f) && (cr > 0.05f * dt);
+    }
+    int start = 0, nstart = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (neg[k] && !neg[(k + 3) & 3]) {
+        start = k;
+        ++nstart;
+      }
+    }
+    if (ok && nstart == 1) {
+      float px[4], py[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        px[t] = cxv[0];
+        py[t] = cyv[0];
+#pragma unroll
+        for (int k = 1; k < 4; ++k)
+          if (((start + t) & 3) == k) {
+            px[t] = cxv[k];
+            py[t] = cyv[k];
+          }
+      }
+      if (quad_order_pass(px, py, false)) {  // the second pass, on the stored order of the first
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          g.x[t] = px[t];
+          g.y[t] = py[t];
+        }
+        return;
+      }
+    }
+  }
+#endif
+  g.x[0] = x0; g.y[0] = h0;
+  g.x[1] = x0; g.y[1] = f;
+  g.x[2] = x1; g.y[2] = h1;
+  g.x[3] = x1; g.y[3] = f;
   poly_sort_cw<4>(g);
   poly_sort_cw<4>(g);
 }
@@ -304,8 +429,12 @@ CX_DEV void make_item_polys(const PS& src, int pid, const CotixLunarParams& P, P
   src.body(wb, B);
 }
 
+// polygon_vs_polygon of one candidate pair.  The first polygon is a leg or a ground trapezoid — always 4
+// vertices (pair_bodies) — and is compiled with a static vertex count; the second (a leg, 4, or the lander,
+// 6) keeps its dynamic count so that the lanes of a warp run ONE instruction stream whatever their pair
+// (two static instantiations were measured slower: narrow stage 56 -> 61 us).
 static __device__ __noinline__ Contact poly_pair(const Poly& a, const Poly& b, V2 start, int gjk_max) {
-  return convex_vs_polygon(a, b, start, gjk_max);
+  return convex_vs_polygon(poly_fixed<4>(a), b, start, gjk_max);
 }
 
 // ---- collider given the contacts — cotix/_colliders.py:137-351 ------------------------------------

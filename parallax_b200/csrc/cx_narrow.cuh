@@ -39,18 +39,37 @@ CX_DEV V2 support(const Box& s, V2 d) {
   return mk2(d.x >= 0.0f ? s.hi.x : s.lo.x, d.y >= 0.0f ? s.hi.y : s.lo.y);
 }
 CX_DEV V2 support(const Poly& s, V2 d) {
+  // first maximum of the dot products, the first NaN winning (jnp.argmax).  The sum of the products is
+  // NaN exactly when one of them is (or +inf meets -inf): only then the NaN-aware scan is needed
+  float dd[CX_MAXV];
+  dd[0] = s.x[0] * d.x + s.y[0] * d.y;
+  float acc = dd[0];
+#pragma unroll
+  for (int k = 1; k < CX_MAXV; ++k) {
+    dd[k] = s.x[k] * d.x + s.y[k] * d.y;
+    if (k < s.n) acc = acc + dd[k];
+  }
+  float best = dd[0], bx = s.x[0], by = s.y[0];
+  if (acc == acc) {
+#pragma unroll
+    for (int k = 1; k < CX_MAXV; ++k) {
+      if (k < s.n && dd[k] > best) {
+        best = dd[k];
+        bx = s.x[k];
+        by = s.y[k];
+      }
+    }
+    return mk2(bx, by);
+  }
   if (isnan2(d)) return nan2();
-  float best = s.x[0] * d.x + s.y[0] * d.y;
-  float bx = s.x[0], by = s.y[0];
   bool bnan = best != best;
 #pragma unroll
   for (int k = 1; k < CX_MAXV; ++k) {
     if (k < s.n) {
-      float dd = s.x[k] * d.x + s.y[k] * d.y;
-      bool dnan = dd != dd;
-      bool take = !bnan && (dnan || dd > best);
+      const bool dnan = dd[k] != dd[k];
+      const bool take = !bnan && (dnan || dd[k] > best);
       if (take) {
-        best = dd;
+        best = dd[k];
         bx = s.x[k];
         by = s.y[k];
         bnan = dnan;
@@ -58,6 +77,60 @@ CX_DEV V2 support(const Poly& s, V2 d) {
     }
   }
   return mk2(bx, by);
+}
+// A polygon whose vertex count is a compile-time constant (the LunarLander bodies: 4 or 6): no per-vertex
+// `k < n` predicate, and — the support function is half of all instructions the narrowphase executes — a
+// support that takes the plain first-maximum scan whenever no dot product is NaN.  The sum of the products
+// is NaN exactly when one of them is (or when +inf and -inf meet); then, and only then, the NaN-aware scan
+// of support(Poly) decides, so the result is the same vertex in every case.
+template <int N>
+struct PolyN {
+  float x[N], y[N];
+};
+template <int N>
+CX_DEV V2 support(const PolyN<N>& s, V2 d) {
+  float dd[N];
+#pragma unroll
+  for (int k = 0; k < N; ++k) dd[k] = s.x[k] * d.x + s.y[k] * d.y;
+  float acc = dd[0];
+#pragma unroll
+  for (int k = 1; k < N; ++k) acc = acc + dd[k];
+  float best = dd[0], bx = s.x[0], by = s.y[0];
+  if (acc == acc) {
+#pragma unroll
+    for (int k = 1; k < N; ++k) {
+      if (dd[k] > best) {
+        best = dd[k];
+        bx = s.x[k];
+        by = s.y[k];
+      }
+    }
+    return mk2(bx, by);
+  }
+  if (isnan2(d)) return nan2();
+  bool bnan = best != best;
+#pragma unroll
+  for (int k = 1; k < N; ++k) {
+    const bool dnan = dd[k] != dd[k];
+    const bool take = !bnan && (dnan || dd[k] > best);
+    if (take) {
+      best = dd[k];
+      bx = s.x[k];
+      by = s.y[k];
+      bnan = dnan;
+    }
+  }
+  return mk2(bx, by);
+}
+template <int N>
+CX_DEV PolyN<N> poly_fixed(const Poly& p) {
+  PolyN<N> q;
+#pragma unroll
+  for (int k = 0; k < N; ++k) {
+    q.x[k] = p.x[k];
+    q.y[k] = p.y[k];
+  }
+  return q;
 }
 template <class SA, class SB>
 CX_DEV V2 mdiff(const SA& a, const SB& b, V2 d) {  // minkowski_diff, _geometry_utils.py:49-57
@@ -101,6 +174,22 @@ CX_DEV void edges_of(const Box& s, EdgeList& e) {  // AABB.get_edges, :82-93
   e.ax[5] = e.ay[5] = e.bx[5] = e.by[5] = 0.0f;
 }
 
+template <int N>
+CX_DEV void edges_of(const PolyN<N>& s, EdgeList& e) {
+  e.n = N;
+#pragma unroll
+  for (int k = 0; k < CX_MAXV; ++k) {
+    if (k < N) {
+      e.ax[k] = s.x[k];
+      e.ay[k] = s.y[k];
+      e.bx[k] = s.x[k == 0 ? N - 1 : k - 1];
+      e.by[k] = s.y[k == 0 ? N - 1 : k - 1];
+    } else {
+      e.ax[k] = e.ay[k] = e.bx[k] = e.by[k] = 0.0f;
+    }
+  }
+}
+
 // ---- contains ------------------------------------------------------------------------
 CX_DEV bool contains(const Circ& s, V2 p) {
   float re = s.r + 1e-6f;
@@ -124,16 +213,12 @@ CX_DEV bool poly_contains(const EdgeList& e, V2 p) {
   }
   return ok;
 }
-template <class S>
-CX_DEV bool contains_el(const S& s, const EdgeList& e, V2 p);
-template <>
-CX_DEV bool contains_el<Poly>(const Poly&, const EdgeList& e, V2 p) {
+CX_DEV bool contains_el(const Poly&, const EdgeList& e, V2 p) { return poly_contains(e, p); }
+template <int N>
+CX_DEV bool contains_el(const PolyN<N>&, const EdgeList& e, V2 p) {
   return poly_contains(e, p);
 }
-template <>
-CX_DEV bool contains_el<Box>(const Box& s, const EdgeList&, V2 p) {
-  return contains(s, p);
-}
+CX_DEV bool contains_el(const Box& s, const EdgeList&, V2 p) { return contains(s, p); }
 
 // ---- GJK — cotix/_collisions.py:20-112, 277-310 --------------------------------------
 CX_DEV bool point_in_triangle0(V2 v1, V2 v2, V2 v3) {  // is_point_in_triangle(0, ...)
@@ -578,14 +663,14 @@ CX_DEV V2 contact_from_edges(const SA& A, const SB& B) {
   V2 avg = mk2(0.0f, 0.0f);
   for (int k = 0; k < ea.n; ++k) {
     V2 v = mk2(ea.ax[k], ea.ay[k]);
-    if (contains_el<SB>(B, eb, v)) {
+    if (contains_el(B, eb, v)) {
       avg = avg + v;
       n = n + 1.0f;
     }
   }
   for (int k = 0; k < eb.n; ++k) {
     V2 v = mk2(eb.ax[k], eb.ay[k]);
-    if (contains_el<SA>(A, ea, v)) {
+    if (contains_el(A, ea, v)) {
       avg = avg + v;
       n = n + 1.0f;
     }
@@ -615,11 +700,13 @@ CX_DEV V2 contact_from_edges(const SA& A, const SB& B) {
 
 CX_DEV int nverts(const Poly& p) { return p.n; }
 CX_DEV int nverts(const Box&) { return 4; }
+template <int N>
+CX_DEV int nverts(const PolyN<N>&) { return N; }
 
 // aabb_vs_polygon :270-291 / polygon_vs_polygon :294-315
-template <class SA>
-CX_DEV Contact convex_vs_polygon(const SA& A, const Poly& B, V2 start, int gjk_max) {
-  int iters = nverts(A) + B.n + 1;
+template <class SA, class SB>
+CX_DEV Contact convex_vs_polygon(const SA& A, const SB& B, V2 start, int gjk_max) {
+  int iters = nverts(A) + nverts(B) + 1;
   if (iters > 13) iters = 13;  // min(48, .) never binds for <= 6 vertices
   V2 s0, s1, s2;
   bool gcap, ecap;

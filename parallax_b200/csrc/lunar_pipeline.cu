@@ -28,6 +28,7 @@
 #include <mutex>
 
 #include "cx_launch.cuh"
+#include "cx_lunar_coll.cuh"
 #include "cx_lunar_step.cuh"
 #include "cx_pipeline.h"
 
@@ -75,11 +76,6 @@ struct PipeWs {
   uint32_t nenv;   // envs of this range
 };
 
-CX_DEV uint32_t lanemask_lt() {
-  uint32_t m;
-  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
-  return m;
-}
 // warp-aggregated queue append; must be reached by all 32 lanes.  Returns the slot of this
 // lane (valid only where pred).
 CX_DEV uint32_t queue_push(uint32_t* counter, bool pred) {
@@ -422,90 +418,7 @@ CX_DEV bool finish_and_store(EnvRegs& E, int64_t e, float* __restrict__ s, int64
   return want_reset;
 }
 
-// ---- K_C1 ----------------------------------------------------------------------------------
-// The coin flips dominate this stage in threefry mode (a coin = 7 threefry-2x32 calls down the
-// key chain split(gkey, N2)[ind2] -> split(., N1)[ind1] -> split(.)[0] -> bernoulli), and which
-// cells are live differs from env to env.  Per-thread loops over 7 cells ran at 6 of 32 lanes
-// (profiles/r1d_pipeline_v1.txt), so the warp pools the live cells of its 32 envs in a task
-// ring in shared memory and flips ONE coin per lane per round: a tails re-queues the task at
-// its next entry, a heads (or the end of the entries) retires it.  Every round is dense.
-struct WarpColl {
-  uint32_t gk[32][4];   // gkey[0], gkey[1] of lane's env
-  uint32_t pk[32][2];   // philox key
-  uint32_t st[32][2];   // steps, episode
-  uint32_t tmask[256];  // task ring: live mask of the cell
-  uint16_t tdesc[256];  //            env lane | cell << 5
-  uint16_t tidx[256];   //            next entry, in the scan order of cell_winner
-  int8_t win[32][8];
-};
-
-CX_DEV void coll_push(WarpColl& W, int& tail, bool pred, uint32_t desc, uint32_t mask, uint32_t t) {
-  const uint32_t m = __ballot_sync(0xFFFFFFFFu, pred);
-  if (pred) {
-    const int slot = (tail + __popc(m & lanemask_lt())) & 255;
-    W.tdesc[slot] = (uint16_t)desc;
-    W.tmask[slot] = mask;
-    W.tidx[slot] = (uint16_t)t;
-  }
-  tail += __popc(m);
-}
-
-// One round: the first T = min(32, pending) tasks of the ring, m = 32 / T consecutive entries of
-// each (m = 1 while the ring is full).  The extra entries are flipped speculatively: a task takes
-// the FIRST heads among its m entries, exactly what flipping them one per round would find, so the
-// thin rounds at the end of a warp's work (16, 8, 4, ... tasks left) collapse into one or two.
-CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParams& P) {
-  const int lane = threadIdx.x & 31;
-  __syncwarp();
-  while (head < tail) {
-    const int T = min(tail - head, 32);
-    const int m = 32 / T;
-    const int task = lane / m, off = lane - task * m;
-    const bool has = task < T;
-    bool heads = false;
-    uint32_t desc = 0u, mask = 0u, t0 = 0u;
-    int el = 0, c = 0, q = 0, total = 0;
-    if (has) {
-      const int slot = (head + task) & 255;
-      desc = W.tdesc[slot];
-      mask = W.tmask[slot];
-      t0 = W.tidx[slot];
-      el = (int)(desc & 31u);
-      c = (int)(desc >> 5);
-      const CellDesc d = cell_desc(c);
-      const int L = __popc(mask), per2 = d.reps * L;
-      total = (d.b_hi - d.b_lo + 1) * per2;
-      const int t = (int)t0 + off;
-      if (t < total) {
-        const int ind2 = d.b_hi - t / per2, rem = t % per2;
-        const int r = d.reps - 1 - rem / L, j = rem % L;
-        q = (int)__fns(mask, 0u, L - j);  // live entries from the highest q down
-        const int ind1 = d.a0 + q + d.nq * r;
-        CoinCtx cc;
-        cc.mode = P.rng_mode;
-        cc.p = P.coin_p;
-        cc.gkey[0].a = W.gk[el][0]; cc.gkey[0].b = W.gk[el][1];
-        cc.gkey[1].a = W.gk[el][2]; cc.gkey[1].b = W.gk[el][3];
-        cc.pkey.a = W.pk[el][0]; cc.pkey.b = W.pk[el][1];
-        cc.steps = W.st[el][0]; cc.episode = W.st[el][1];
-        Key2 k2;
-        k2.a = k2.b = 0u;
-        if (cc.mode == COTIX_RNG_THREEFRY) k2 = tf_split(cc.gkey[d.g], (uint32_t)d.N2, (uint32_t)ind2);
-        heads = coin_heads(cc, d.g, d.N1, k2, ind2, ind1);
-      }
-    }
-    const uint32_t hb = __ballot_sync(0xFFFFFFFFu, heads);
-    const uint32_t seg = (m >= 32 ? 0xFFFFFFFFu : ((1u << m) - 1u)) << (has ? task * m : 0);
-    const uint32_t mine = has ? (hb & seg) : 0u;
-    if (mine != 0u && lane == __ffs(mine) - 1) W.win[el][c] = (int8_t)q;
-    const bool requeue = has && off == 0 && mine == 0u && (int)t0 + m < total;
-    __syncwarp();
-    head += T;
-    coll_push(W, tail, requeue, desc, mask, t0 + (uint32_t)m);
-    __syncwarp();
-  }
-}
-
+// ---- K_C1 (the warp-pooled coin flips: cx_lunar_coll.cuh) ------------------------------------
 template <bool INLINE, int SPREAD>
 __global__ void __launch_bounds__(TPB)
 pipe_contact_kernel(float* __restrict__ s, int64_t ld, const __grid_constant__ CotixLunarParams P,
@@ -743,7 +656,10 @@ size_t carve(int64_t B, void* base, PipeWs* ws) {
 // COTIX_SPARSE_SPREAD = 1 | 2 | 4 overrides (measurement aid)
 int sparse_spread(int64_t n) {
   static const char* env = getenv("COTIX_SPARSE_SPREAD");
-  if (env && (env[0] == '1' || env[0] == '2' || env[0] == '4')) return env[0] - '0';
+  if (env) {
+    const int v = atoi(env);
+    if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) return v;
+  }
   // measured (100-step contact-rich rollouts / steps, spread 1 -> 2 -> 4): 4096 envs 6.65 -> 6.24 -> 5.87 ms,
   // 16384: 7.02 -> 6.58 -> 6.28 ms, 65536: 67.8 -> 64.9 -> 63.6 us per step, 262144: 90.7 -> 94.6 -> 113.6 us
   return n <= 65536 ? 4 : 1;
@@ -958,17 +874,27 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         set_attrs(true, true);
         cfg.gridDim = dim3(qgrid_sparse((int64_t)ws.cap * spread * TPB / NTPB, spread));
         cfg.blockDim = dim3(NTPB);
-        if (spread == 1) cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<1>, *p, D, ws);
-        else if (spread == 2) cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<2>, *p, D, ws);
-        else cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<4>, *p, D, ws);
+        switch (spread) {
+          case 1: cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<1>, *p, D, ws); break;
+          case 2: cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<2>, *p, D, ws); break;
+          case 4: cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<4>, *p, D, ws); break;
+          case 8: cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<8>, *p, D, ws); break;
+          case 16: cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<16>, *p, D, ws); break;
+          default: cudaLaunchKernelEx(&cfg, pipe_narrow_kernel<32>, *p, D, ws); break;
+        }
         cfg.blockDim = dim3(TPB);
         CX_MARK_E(1, cs);
         CX_TRACE(1, cs);
         CX_MARK_B(2, cs);
         cfg.gridDim = dim3(qgrid_sparse(n * spread, spread));
-        if (spread == 1) cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 1>, sout, ld, *p, D, ws);
-        else if (spread == 2) cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 2>, sout, ld, *p, D, ws);
-        else cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 4>, sout, ld, *p, D, ws);
+        switch (spread) {
+          case 1: cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 1>, sout, ld, *p, D, ws); break;
+          case 2: cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 2>, sout, ld, *p, D, ws); break;
+          case 4: cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 4>, sout, ld, *p, D, ws); break;
+          case 8: cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 8>, sout, ld, *p, D, ws); break;
+          case 16: cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 16>, sout, ld, *p, D, ws); break;
+          default: cudaLaunchKernelEx(&cfg, pipe_contact_kernel<false, 32>, sout, ld, *p, D, ws); break;
+        }
         // the envs that overflowed the item queue (normally none: the kernel reads the count and exits)
         cfg.gridDim = dim3((unsigned)(env_blocks < (unsigned)sms ? env_blocks : (unsigned)sms));
         cudaLaunchKernelEx(&cfg, pipe_contact_kernel<true, 1>, sout, ld, *p, D, ws);
