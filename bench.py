@@ -487,7 +487,8 @@ def fast_math_leg(args):
 
 def config1(args, dev):
     """BASELINE config 1 as stated (B = 1024 envs x 1000 steps from reset(key), zero action, no judge:
-    the loop of examples/test_viz.py:46-48) on one B200: one graph of 1000 fused-kernel steps."""
+    the loop of examples/test_viz.py:46-48) on one B200: `steps(state, None, 1000)` = one launch of the
+    block-resident rollout kernel (a graph of 1000 fused-kernel launches took 11.9 us per step)."""
     import torch
 
     from gen_inputs import lunar_keys
@@ -511,7 +512,9 @@ def config1(args, dev):
     g.close()
     return {"workload": f"BASELINE config 1: 1024 envs x {T} steps from reset, zero action", "value": B * T / (ms * 1e-3),
             "unit": "env-steps/s", "ms": ms, "us_per_step": 1e3 * ms / T, "graph_nodes": info["nodes"],
-            "note": "latency-bound: 8 blocks of 128 threads per step; the number to compare with the CPU arm's config1"}
+            "kernel_launches": info["kernel_launches"],
+            "note": "latency-bound: 128 blocks of 8 envs, every env resident in its block for the 1000 steps; the number "
+                    "to compare with the CPU arm's config1"}
 
 
 def sweep(args, dev, peak):
@@ -648,9 +651,8 @@ def differentiable(args, dev):
     g = torch.zeros((18, B), device=dev)
     g_act = torch.zeros((T, 2, B), device=dev)
     ws = ll.adjoint_workspace(B, T, dev)
-    # contact-rich rollouts: the pipeline (sparse stages at 8 lanes per warp for small batches) beats the
-    # fused kernel from a few thousand envs (4096 envs x 100 steps: 5.87 against 6.83 ms)
-    mode = "pipeline" if B >= 2048 else "fused"
+    # small batch: the block-resident rollout kernel (one launch for the T steps), else the pipeline
+    mode = "pipeline" if B > ll.ROLLOUT_MAX_ENVS else "fused"
     if mode == "pipeline":
         ll._workspace(dev, B)
 
@@ -696,8 +698,9 @@ def differentiable(args, dev):
            "forward_ms": fwd_ms, "backward_ms": bwd_ms, "kernels_per_rollout": int(eager_launches),
            "graph_launches_per_rollout": 2, "graph_nodes": [gf.info()["nodes"], gb.info()["nodes"]],
            "forward_mode": mode,
-           "kernel": "forward: wavefront pipeline x T (fused lunar_step_kernel below 2048 envs); backward: lunar_decide + "
-                     "lunar_jacobian + lunar_step_bwd_kernel x T (recompute-and-reverse)",
+           "kernel": "forward: lunar_rollout_kernel, T steps in one launch with the envs resident in their block (the "
+                     "wavefront pipeline above %d envs); backward: lunar_decide + lunar_jacobian on a side stream, "
+                     "lunar_sweep_bwd_kernel per run of steps (recompute-and-reverse)" % ll.ROLLOUT_MAX_ENVS,
            "tape_bytes": int(tape.numel() * 4), "replay_mismatch_envs": int((f & 1).sum()),
            "nonfinite_envs": int(((f >> 1) & 1).sum()), "envs_with_contact": int((((f >> 8) & 7) > 0).sum()),
            "grad_finite": bool(torch.isfinite(g).all() and torch.isfinite(g_act).all())}

@@ -270,7 +270,7 @@ int cotix_lunar_step_ws(void* stream, int64_t B, const float* state_in, float* s
  * small-batch, latency-bound case); larger batches n_steps launches of the fused kernel.  Same results
  * bit for bit on every route.  reward / done / obs (or NULL) hold the last step's values.
  */
-#define COTIX_ROLLOUT_MAX_ENVS 32768
+#define COTIX_ROLLOUT_MAX_ENVS 4736 /* 148 SMs x 32 envs per block: one block per SM */
 int cotix_lunar_steps_ws(void* stream, int64_t B, float* state, int64_t ld, const float* actions,
                          int32_t n_actions, int32_t n_steps, float* reward, uint8_t* done, float* obs,
                          const CotixLunarParams* p, void* workspace, int64_t workspace_bytes);

@@ -24,6 +24,8 @@ extern "C" int cx_launch_lunar_reset(cudaStream_t, int64_t, const uint32_t*, flo
 extern "C" int cx_launch_lunar_step_bwd(cudaStream_t, int64_t, const float*, const float*, int64_t,
                                         const float*, const float*, float*, float*, uint32_t*,
                                         const float*, const float*, const CotixLunarParams*);
+extern "C" int cx_launch_lunar_sweep_bwd(cudaStream_t, int64_t, int, int, const float*, int64_t, const float*, float*,
+                                         float*, uint32_t*, const float*, const float*, const CotixLunarParams*);
 extern "C" int cx_launch_lunar_decide(cudaStream_t, int64_t, int, const float*, int64_t, const float*, float*,
                                       uint32_t*, uint32_t*, uint32_t*, float*, uint32_t, const CotixLunarParams*,
                                       int);
@@ -453,6 +455,13 @@ static AdjSide* adj_side() {
   }
   return a.state == 1 ? &a : nullptr;
 }
+// the reverse sweep of a run of steps as ONE launch (lunar_sweep_bwd_kernel) up to this many envs;
+// COTIX_SWEEP_KERNEL=0 keeps one launch per step (A/B measurements, tests)
+static bool use_sweep_kernel(int64_t B) {
+  static const char* env = getenv("COTIX_SWEEP_KERNEL");
+  if (env && env[0] == '0') return false;
+  return B <= 16384;
+}
 // 0: off; n > 0: on, the overlapped launches capped at n blocks per SM; n < 0: on, uncapped
 static int g_adj_pipelined = -1;
 void cx_lunar_adjoint_set_pipelined(int n) { g_adj_pipelined = n; }
@@ -505,6 +514,14 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
   constexpr int NG = 4;
   static const char* env_overlap = getenv("COTIX_ADJ_OVERLAP");  // measurement aid: "0" turns the overlap off
   const bool overlap = g_adj_pipelined != 0 && !(env_overlap && env_overlap[0] == '0');
+  static const char* env_runs = getenv("COTIX_ADJ_RUNS");  // measurement aid: "1" = no runs for small batches
+  if (jac && group >= T && T >= 1 && use_sweep_kernel(B) && env_runs && env_runs[0] == '1') {
+    // small batch: decisions + Jacobians of the whole rollout at full grid, then the sweep in one launch
+    int rc = cx_launch_lunar_decide((cudaStream_t)stream, B, T, tape, ld, actions, dt, flags, jctr, jlist, jM, jcap, p, 0);
+    if (rc == 0)
+      rc = cx_launch_lunar_sweep_bwd((cudaStream_t)stream, B, 0, T, tape, ld, actions, g, g_actions, flags, dt, jM, p);
+    return rc;
+  }
   AdjSide* side = (jac && overlap && group >= T && T >= 2 * NG) ? adj_side() : nullptr;
   if (side) {
     std::lock_guard<std::mutex> lock(side->mu);
@@ -530,6 +547,11 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
     for (int i = NG - 1; i >= 0; --i) {
       if (cudaStreamWaitEvent(st, side->done[i], 0) != cudaSuccess && rc == 0) rc = cx_check_launch("adjoint join");
       const int64_t off = cap1 * b[i];
+      if (use_sweep_kernel(B) && rc == 0) {  // small batch: the steps of the run in one launch
+        rc = cx_launch_lunar_sweep_bwd(st, B, b[i], b[i + 1], tape, ld, actions, g, g_actions, flags, dt,
+                                       jM + off * 20 * COTIX_LUNAR_NDYN, p);
+        continue;
+      }
       for (int32_t s = b[i + 1] - 1; s >= b[i] && rc == 0; --s) {
         const float* a = actions ? actions + (int64_t)s * 2 * ld : nullptr;
         float* ga = g_actions ? g_actions + (int64_t)s * 2 * ld : nullptr;

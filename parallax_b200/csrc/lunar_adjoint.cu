@@ -771,6 +771,130 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
   if (flags_out && flags) atomicOr(&flags_out[e], flags);
 }
 
+// Steps s_hi-1 .. s_lo backwards in ONE launch for a small batch: the reverse sweep is sequential in time,
+// and launched step by step a batch of a few thousand envs spends its time in launch gaps and in warps that
+// work through the Jacobians of eight heavy env-steps one after the other.  Envs never interact, so a warp
+// keeps the cotangents of its `epw` envs (lanes 0 .. epw-1; few, so that few matrices queue up per step) in
+// registers for the whole run of steps.  Needs the decision tape and the Jacobians of the run (taped mode).
+// The arithmetic is that of lunar_step_bwd_kernel, operation for operation: identical gradients.
+__global__ void __launch_bounds__(TPB)
+lunar_sweep_bwd_kernel(int64_t B, int s_lo, int s_hi, const float* __restrict__ tape, int64_t ld,
+                       const float* __restrict__ actions, float* g_io, float* __restrict__ g_actions,
+                       uint32_t* __restrict__ flags_out, const float* __restrict__ dtape0,
+                       const float* __restrict__ jacM, const __grid_constant__ CotixLunarParams P, const LunarDerived D,
+                       int epw) {
+  __shared__ float s_row[TPB / 32][JAC_ROWS][32];  // matrix-vector results: [output row][env lane]
+  const int j = (int)(threadIdx.x & 31u), wib = (int)(threadIdx.x >> 5);
+  const int64_t e = ((int64_t)blockIdx.x * (TPB / 32) + wib) * epw + j;
+  const bool in = j < epw && e < B;
+  G6 g[4];
+  g[0] = g[1] = g[2] = g[3] = g6_zero();
+  if (in) load_cotangent(g, g_io, ld, e);
+  uint32_t flags = 0u;
+  const int64_t slot_f = (int64_t)COTIX_LUNAR_NF * ld, dslot = (int64_t)DT_WORDS * ld;
+  for (int s = s_hi - 1; s >= s_lo; --s) {
+    const float* sin_ = tape + (int64_t)s * slot_f;
+    const float* snext = sin_ + slot_f;
+    const float* dtape = dtape0 + (int64_t)s * dslot;
+    const float* action = actions ? actions + (int64_t)s * 2 * ld : nullptr;
+    float* g_action = g_actions ? g_actions + (int64_t)s * 2 * ld : nullptr;
+    bool heavy = false;
+    uint32_t slot = 0u;
+    uint32_t w0 = 0u;
+    if (in) {
+      w0 = __float_as_uint(dtape[e]);
+      if (w0 & DT_HAS_MATRIX) {
+        heavy = true;
+        slot = __float_as_uint(dtape[32 * ld + e]);
+      }
+      if (s > s_lo) {  // next iteration's matrix on its way to L2 while this step is worked on
+        const float* dn = dtape - dslot;
+        if (__float_as_uint(dn[e]) & DT_HAS_MATRIX) {
+          const char* Mb = reinterpret_cast<const char*>(jacM + (size_t)__float_as_uint(dn[32 * ld + e]) * JAC_FLOATS);
+#pragma unroll
+          for (int l = 0; l < JAC_FLOATS * 4; l += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(Mb + l));
+        }
+      }
+    }
+    uint32_t hm = __ballot_sync(0xFFFFFFFFu, heavy);
+    if (hm) {
+      const float gv[COTIX_LUNAR_NDYN] = {g[0].px, g[0].py, g[0].vx, g[0].vy, g[0].ang, g[0].w,
+                                          g[1].px, g[1].py, g[1].vx, g[1].vy, g[1].ang, g[1].w,
+                                          g[2].px, g[2].py, g[2].vx, g[2].vy, g[2].ang, g[2].w};
+      float m[COTIX_LUNAR_NDYN];
+      auto fetch = [&](int src_lane) {
+        const uint32_t sl = __shfl_sync(0xFFFFFFFFu, slot, src_lane);
+        const float* M = jacM + (size_t)sl * JAC_FLOATS;
+#pragma unroll
+        for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) m[k] = (j < JAC_ROWS) ? M[k * JAC_ROWS + j] : 0.0f;
+      };
+      fetch(__ffs(hm) - 1);
+      while (hm) {
+        const int src = __ffs(hm) - 1;
+        hm &= hm - 1u;
+        float mc[COTIX_LUNAR_NDYN];
+#pragma unroll
+        for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) mc[k] = m[k];
+        if (hm) fetch(__ffs(hm) - 1);
+        float acc = 0.0f;
+#pragma unroll
+        for (int k = 0; k < COTIX_LUNAR_NDYN; ++k) acc += mc[k] * __shfl_sync(0xFFFFFFFFu, gv[k], src);
+        if (j < JAC_ROWS) s_row[wib][j][src] = acc;
+      }
+      __syncwarp();
+      if (heavy) {
+        g[0].px = s_row[wib][0][j]; g[0].py = s_row[wib][1][j]; g[0].vx = s_row[wib][2][j];
+        g[0].vy = s_row[wib][3][j]; g[0].ang = s_row[wib][4][j]; g[0].w = s_row[wib][5][j];
+        g[1].px = s_row[wib][6][j]; g[1].py = s_row[wib][7][j]; g[1].vx = s_row[wib][8][j];
+        g[1].vy = s_row[wib][9][j]; g[1].ang = s_row[wib][10][j]; g[1].w = s_row[wib][11][j];
+        g[2].px = s_row[wib][12][j]; g[2].py = s_row[wib][13][j]; g[2].vx = s_row[wib][14][j];
+        g[2].vy = s_row[wib][15][j]; g[2].ang = s_row[wib][16][j]; g[2].w = s_row[wib][17][j];
+        if (g_action) {
+          g_action[e] = s_row[wib][18][j];
+          g_action[ld + e] = s_row[wib][19][j];
+        }
+      }
+      __syncwarp();
+    }
+    if (in && !heavy) {
+      EnvRegs E;
+      load_dyn(E, sin_, ld, e);
+      E.status = __float_as_uint(sin_[COTIX_F_STATUS * ld + e]);
+      float am = 0.0f, as = 0.0f;
+      if (action) {
+        am = action[e];
+        as = action[ld + e];
+      }
+      StepCtx cx;
+      Poly wL, wr, wl;
+      Decisions d;
+      const bool contact_free = (w0 & 7u) == 0u;
+      if (contact_free) {
+        integrate_only(E, am, as, P, cx);
+        cx.cand = 0u;
+        cx.base = -1;
+        d.pl.n = 0;
+      } else {
+        load_terrain(E, sin_, ld, e);
+        load_meta(E, sin_, ld, e);
+        integrate_and_cull<true>(E, am, as, P, D, cx, wL, wr, wl);
+        load_decisions(d, dtape, ld, e);
+      }
+      const RegPolys src{wL, wr, wl, E.h, E.kn};
+      float g_am, g_as;
+      step_bwd_core(E, cx, src, am, as, d, P, snext, ld, e, g, g_am, g_as, flags);
+      if (g_action) {
+        g_action[e] = g_am;
+        g_action[ld + e] = g_as;
+      }
+    }
+  }
+  if (in) {
+    store_cotangent(g, g_io, ld, e);
+    if (flags_out && flags) atomicOr(&flags_out[e], flags);
+  }
+}
+
 // The VJP of an env-step is linear in the cotangent and its coefficients depend only on forward
 // quantities (the state before the step, the action, the collider's decisions).  For the env-steps
 // WITH resolved contacts — whose adjoint is the expensive, divergent one — the 20 x 18 matrix
@@ -925,6 +1049,21 @@ extern "C" int cx_launch_lunar_step_bwd(cudaStream_t st, int64_t B, const float*
       B, state_in, state_next, ld, action, g_out, g_in, g_action, flags, dtape, jacM, *p, D);
   cx_count_launch();
   return cx_check_launch("lunar_step_bwd_kernel");
+}
+
+// steps [s_lo, s_hi) backwards in one launch (small batches, taped mode with Jacobians; see the kernel)
+extern "C" int cx_launch_lunar_sweep_bwd(cudaStream_t st, int64_t B, int s_lo, int s_hi, const float* tape, int64_t ld,
+                                         const float* actions, float* g, float* g_actions, uint32_t* flags,
+                                         const float* dtape0, const float* jacM, const CotixLunarParams* p) {
+  if (B == 0 || s_hi <= s_lo) return 0;
+  LunarDerived D;
+  cx_lunar_derive(p, &D);
+  const int epw = B <= 8192 ? 8 : 16;
+  const int64_t warps = (B + epw - 1) / epw;
+  lunar_sweep_bwd_kernel<<<(unsigned)((warps + TPB / 32 - 1) / (TPB / 32)), TPB, 0, st>>>(
+      B, s_lo, s_hi, tape, ld, actions, g, g_actions, flags, dtape0, jacM, *p, D, epw);
+  cx_count_launch();
+  return cx_check_launch("lunar_sweep_bwd_kernel");
 }
 
 // decisions of steps [t0, t0 + nt) of a taped rollout -> dtape [nt][COTIX_ADJ_TAPE_WORDS][ld]; with a

@@ -287,7 +287,7 @@ extern "C" int cx_launch_lunar_rollout_kernel(cudaStream_t st, int64_t B, const 
   // envs per block: 32 once that fills the SMs, fewer (down to 8) for tiny batches so that every SM has work
   const int sms = cx_sm_count();
   int epb = REPB;
-  while (epb > RWARPS && (B + epb - 1) / epb < sms) epb >>= 1;
+  while (epb > RWARPS && (B + epb - 1) / epb < (sms * 2) / 3) epb >>= 1;  // 4096 envs: 128 blocks of 32 beat 256 of 16
   if (const char* env = getenv("COTIX_ROLLOUT_EPB")) {  // measurement aid
     const int v = atoi(env);
     if (v == 8 || v == 16 || v == 32) epb = v;

@@ -121,12 +121,13 @@ def workspace_bytes(B: int) -> int:
     return int(_lib.lib().cotix_lunar_workspace_bytes(int(B)))
 
 
-def _workspace(B: int, pipeline: bool | None):
+def _workspace(B: int, pipeline: bool | None, multi_step: bool = False):
     """The pipeline's scratch as an XLA-owned u8 operand (the handlers never allocate); a zero-sized
-    operand selects the fused kernel.  XLA materialises the zeros once under jit."""
+    operand selects the fused kernel (one step) or the block-resident rollout kernel (several steps, small
+    batch).  XLA materialises the zeros once under jit."""
     import jax.numpy as jnp
 
-    use = (B >= 16384) if pipeline is None else pipeline
+    use = (B > 4736 if multi_step else B >= 16384) if pipeline is None else pipeline
     return jnp.zeros((workspace_bytes(B) + 256 if use else 0,), jnp.uint8)
 
 
@@ -172,7 +173,7 @@ def steps(state, actions, n_steps: int, P: LunarParams | None = None, pipeline: 
     out = (jax.ShapeDtypeStruct((NF, B), jnp.float32), jax.ShapeDtypeStruct((B,), jnp.float32),
            jax.ShapeDtypeStruct((B,), jnp.uint8), jax.ShapeDtypeStruct((NOBS, B), jnp.float32))
     return jax.ffi.ffi_call("cotix_lunar_steps", out, input_output_aliases={0: 0})(
-        state, actions, _workspace(B, pipeline), params=params_words(P), n_steps=np.int32(n_steps))
+        state, actions, _workspace(B, pipeline, True), params=params_words(P), n_steps=np.int32(n_steps))
 
 
 def narrowphase(a, b, wavefront: bool | None = None):
@@ -215,7 +216,7 @@ def make_rollout(P: LunarParams | None = None, pipeline: bool | None = None, jac
     def fwd(state0, actions):
         T, _, B = actions.shape
         tape = jax.ffi.ffi_call("cotix_lunar_rollout", jax.ShapeDtypeStruct((T + 1, NF, B), jnp.float32))(
-            state0, actions, _workspace(B, pipeline), params=words)
+            state0, actions, _workspace(B, pipeline, True), params=words)
         return tape[-1], (tape, actions)
 
     def bwd(res, g_final):  # g_final f32[36, B]: rows 0..17 (the dynamic leaves) carry a cotangent

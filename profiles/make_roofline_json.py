@@ -20,12 +20,15 @@ KEYS = {"gpu__time_duration.sum": "duration_us", "dram__bytes_read.sum": "rd", "
 UNIT = {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1.0}
 kern, cur = {}, None
 for line in open(src):
-    m = re.match(r"== (?:void )?(?:<unnamed>::)?(\w+)(<\d+>)?", line)
+    m = re.match(r"== (?:void )?(?:<unnamed>::)?(\w+)(<[\d, ]+>)?", line)
     if m:
-        name = m.group(1) + (m.group(2) or "")
+        name = m.group(1) + (m.group(2) or "").replace(" ", "")
         cur = kern.setdefault(name, {})
-        if name == "pipe_contact_kernel<0>":  # bench.py looks the stages up by their plain names
+        # bench.py looks the stages up by their plain names: the common instantiations (INLINE = 0, any SPREAD)
+        if name.startswith("pipe_contact_kernel<0"):
             kern["pipe_contact_kernel"] = cur
+        if name.startswith("pipe_narrow_kernel<"):
+            kern["pipe_narrow_kernel"] = cur
         continue
     p = line.split()
     if cur is not None and len(p) >= 2 and p[0] in KEYS and KEYS[p[0]] not in cur:
@@ -40,7 +43,7 @@ for k, v in kern.items():
     if "dram_bytes" not in v:
         v["dram_bytes"] = int(v.pop("rd", 0) + v.pop("wr", 0))
     out[k] = v
-pipe = [v for k, v in kern.items() if k.startswith("pipe_") and k != "pipe_contact_kernel"]
+pipe = [v for k, v in kern.items() if k.startswith("pipe_") and k not in ("pipe_contact_kernel", "pipe_narrow_kernel")]
 if pipe:
     T = sum(v["duration_us"] for v in pipe)
     w = lambda f: sum(v[f] * v["duration_us"] for v in pipe) / T
