@@ -608,7 +608,12 @@ def robocup(args, dev, dist, rank, world, peak):
                         "achieved": algo * Bg / (ms * 1e-3) / 1e9 / world, "peak": peak, "unit": "GB/s",
                         "frac": algo * Bg / (ms * 1e-3) / 1e9 / world / peak,
                         "traffic": _traffic("scene_step_kernel"),
-                        "note": "per GPU; the kernel is instruction / latency bound (GJK + EPA + coin chains per env)"}}
+                        "issue_slot": (_ncu().get("scene_step_kernel") or {}).get("issue_slot_pct"),
+                        "alu_pipe": (_ncu().get("scene_step_kernel") or {}).get("alu_pipe_pct"),
+                        "fp32_pipe": (_ncu().get("scene_step_kernel") or {}).get("fp32_pipe_pct"),
+                        "ncu_source": (_ncu().get("scene_step_kernel") or {}).get("source"),
+                        "note": "per GPU; bound by the integer ALU pipe (65 % busy): half of the 4.5e8 warp instructions of "
+                                "a step are threefry-2x32 rounds of the collider's coin flips (jax.random parity)"}}
     if rank == 0 and world == 1 and not args.no_cpu:
         # CPU: the oracle's generic collider (memoised duplicate pairs), one core, 64 envs x 2 steps
         from oracle import oracle as o

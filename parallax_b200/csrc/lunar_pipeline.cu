@@ -653,16 +653,17 @@ size_t carve(int64_t B, void* base, PipeWs* ws) {
 }
 
 // lanes-per-warp divisor of the sparse stages for a range of n envs (see the note at the top);
-// COTIX_SPARSE_SPREAD = 1 | 2 | 4 overrides (measurement aid)
+// COTIX_SPARSE_SPREAD = 1 | 2 | 4 | 8 | 16 | 32 overrides (measurement aid)
 int sparse_spread(int64_t n) {
   static const char* env = getenv("COTIX_SPARSE_SPREAD");
   if (env) {
     const int v = atoi(env);
     if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) return v;
   }
-  // measured (100-step contact-rich rollouts / steps, spread 1 -> 2 -> 4): 4096 envs 6.65 -> 6.24 -> 5.87 ms,
-  // 16384: 7.02 -> 6.58 -> 6.28 ms, 65536: 67.8 -> 64.9 -> 63.6 us per step, 262144: 90.7 -> 94.6 -> 113.6 us
-  return n <= 65536 ? 4 : 1;
+  // measured, 100-step contact-rich rollouts, spread 1 / 2 / 4 / 8 / 16 / 32: 1024 envs . / . / 5.56 / 5.26 / 4.93 / 4.55 ms,
+  // 4096 envs 6.65 / 6.24 / 5.89 / 5.61 / 5.32 / 5.08, 16384 envs 7.02 / 6.58 / 6.30 / 6.20 / 6.24 / 7.18; steps of 65536
+  // envs 67.8 / 64.9 / 63.0 / 63.8 / 69.8 us; 262144 envs 90.7 / 94.6 / 113.6 us
+  return n <= 4096 ? 32 : (n <= 8192 ? 16 : (n <= 16384 ? 8 : (n <= 65536 ? 4 : 1)));
 }
 
 // the ranges of a batch: S ranges of ceil(B / S) envs rounded up to a multiple of TPB (so that every
