@@ -30,7 +30,10 @@
 
 namespace {
 
-constexpr int RTPB = 256;   // threads per block
+#ifndef CX_ROLLOUT_TPB
+#define CX_ROLLOUT_TPB 256
+#endif
+constexpr int RTPB = CX_ROLLOUT_TPB;   // threads per block
 constexpr int RWARPS = RTPB / 32;
 constexpr int REPB = 32;    // most envs per block (four per warp)
 constexpr int RQCAP = 256;  // items per block and step; beyond, the owning lane evaluates its own pairs
@@ -117,14 +120,15 @@ struct BlockContacts {
 };
 
 #ifndef CX_ROLLOUT_MINB
-#define CX_ROLLOUT_MINB 2
+#define CX_ROLLOUT_MINB (512 / CX_ROLLOUT_TPB)
 #endif
 __global__ void __launch_bounds__(RTPB, CX_ROLLOUT_MINB)
 lunar_rollout_kernel(int64_t B, const float* __restrict__ sin0, float* __restrict__ sout0, int64_t stride, int64_t ld,
                      const float* __restrict__ actions, int64_t action_stride, int n_actions, int n_steps,
                      float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
                      const __grid_constant__ CotixLunarParams P, const __grid_constant__ LunarDerived D, int epb) {
-  __shared__ RolloutShared S;
+  extern __shared__ __align__(16) unsigned char rollout_smem[];  // dynamic: 16 warps need more than the 48 KB static limit
+  RolloutShared& S = *reinterpret_cast<RolloutShared*>(rollout_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // the block's epb envs are dealt to its warps, epb / 8 each (lanes 0 .. epw-1): a warp is as fast with one
   // env as with thirty-two, and the fewer envs share a warp the fewer divergent branches it serialises
@@ -290,10 +294,18 @@ extern "C" int cx_launch_lunar_rollout_kernel(cudaStream_t st, int64_t B, const 
   while (epb > RWARPS && (B + epb - 1) / epb < (sms * 2) / 3) epb >>= 1;  // 4096 envs: 128 blocks of 32 beat 256 of 16
   if (const char* env = getenv("COTIX_ROLLOUT_EPB")) {  // measurement aid
     const int v = atoi(env);
-    if (v == 8 || v == 16 || v == 32) epb = v;
+    if ((v == 8 || v == 16 || v == 32) && v >= RWARPS) epb = v;
   }
   const unsigned blocks = (unsigned)((B + epb - 1) / epb);
-  lunar_rollout_kernel<<<blocks, RTPB, 0, st>>>(B, sin0, sout0, stride, ld, actions, action_stride,
+  static bool attr_set[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < 64 && !attr_set[dev]) {
+    if (cudaFuncSetAttribute(lunar_rollout_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sizeof(RolloutShared)) != cudaSuccess)
+      return cx_check_launch("lunar_rollout_kernel shared-memory attribute");
+    attr_set[dev] = true;
+  }
+  lunar_rollout_kernel<<<blocks, RTPB, sizeof(RolloutShared), st>>>(B, sin0, sout0, stride, ld, actions, action_stride,
                                                 n_actions > 0 ? n_actions : 1, n_steps, reward, done, obs, *p, D, epb);
   cx_count_launch();
   return cx_check_launch("lunar_rollout_kernel");
