@@ -34,10 +34,16 @@ struct BodyS {
 // result is scale-invariant while nothing under- or overflows) the first time a constant is seen
 // (cx_divc_make, lunar_kernel.cu) and sets `ok`; x outside [1e-20, 1e20], x = 0 and non-finite x take
 // the plain division, as does every constant that fails the check.  The results are the bits of x / c.
+// ok == 2: c is +-inf (the static ground's mass and inertia), where x / c == x * (+-0) for EVERY x — a
+// finite x gives the zero of the right sign, an infinite or NaN x gives NaN — so r = +-0 and one multiply
+// replaces the division, whose special-operand path was 4 % of the contact stage's instructions.
 struct DivC {
   float c, r;
   int ok;
 };
+// the IEEE division out of line: after the shortcuts below it runs for out-of-range operands only, and its
+// ~70 inlined instructions per call site were a seventh of the contact stage's code
+static __device__ __noinline__ float div_ieee(float x, float c) { return x / c; }
 CX_DEV DivC divc_plain(float c) {
   DivC d;
   d.c = c;
@@ -47,6 +53,7 @@ CX_DEV DivC divc_plain(float c) {
 }
 CX_DEV float div_c(float x, const DivC& d) {
   if (d.c == 1.0f) return x;  // x / 1 == x bit for bit (the legs' mass and inertia); uniform branch
+  if (d.ok == 2) return x * d.r;
   if (d.ok) {
     const float ax = fabsf(x);
     if (ax >= 1e-20f && ax <= 1e20f) {  // false for NaN
@@ -55,7 +62,7 @@ CX_DEV float div_c(float x, const DivC& d) {
       return __fmaf_rn(rem, d.r, q);
     }
   }
-  return x / d.c;
+  return div_ieee(x, d.c);
 }
 struct MassP {
   float mass, inertia, e, mu;

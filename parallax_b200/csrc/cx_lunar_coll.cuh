@@ -66,7 +66,11 @@ CX_DEV void coll_rounds(WarpColl& W, int& head, int& tail, const CotixLunarParam
       if (t < total) {
         const int ind2 = d.b_hi - t / per2, rem = t % per2;
         const int r = d.reps - 1 - rem / L, j = rem % L;
-        q = (int)__fns(mask, 0u, L - j);  // live entries from the highest q down
+        // the (L - j)-th set bit of the (at most 7-bit) live mask: live entries from the highest q down.
+        // Clearing the lowest set bit L - j - 1 times is a handful of instructions; __fns was 6 % of the stage
+        uint32_t mq = mask;
+        for (int c2 = L - j - 1; c2 > 0; --c2) mq &= mq - 1u;
+        q = __ffs(mq) - 1;
         const int ind1 = d.a0 + q + d.nq * r;
         CoinCtx cc;
         cc.mode = P.rng_mode;

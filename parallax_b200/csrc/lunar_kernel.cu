@@ -274,7 +274,12 @@ static DivC cx_divc_make(float c) {
   d.r = 0.0f;
   d.ok = 0;
   const float ac = fabsf(c);
-  if (!(ac >= 1e-6f && ac <= 1e6f) || c == 1.0f) return d;  // inf (static bodies), NaN, extreme: plain division
+  if (std::isinf(c)) {  // static bodies: x / +-inf == x * +-0 for every x (finite -> signed zero, inf / NaN -> NaN)
+    d.r = c > 0 ? 0.0f : -0.0f;
+    d.ok = 2;
+    return d;
+  }
+  if (!(ac >= 1e-6f && ac <= 1e6f) || c == 1.0f) return d;  // NaN, extreme: plain division
   static std::mutex mu;
   static std::map<uint32_t, int> cache;
   uint32_t bits;
