@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(RTPB, CX_ROLLOUT_MINB)
 lunar_rollout_kernel(int64_t B, const float* __restrict__ sin0, float* __restrict__ sout0, int64_t stride, int64_t ld,
                      const float* __restrict__ actions, int64_t action_stride, int n_actions, int n_steps,
                      float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
-                     const __grid_constant__ CotixLunarParams P, const __grid_constant__ LunarDerived D, int epb) {
+                     const __grid_constant__ CotixLunarParams P, const __grid_constant__ LunarDerived D, int epb, int qcap) {
   extern __shared__ __align__(16) unsigned char rollout_smem[];  // dynamic: 16 warps need more than the 48 KB static limit
   RolloutShared& S = *reinterpret_cast<RolloutShared*>(rollout_smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -183,7 +183,7 @@ lunar_rollout_kernel(int64_t B, const float* __restrict__ sin0, float* __restric
         for (int k = 0; k < 4; ++k) S.terr[8 + k][el] = E.kn[k];
         const int cnt = __popc(cx.cand);
         const int base = atomicAdd(&S.qcount, cnt);
-        if (base + cnt <= RQCAP) {
+        if (base + cnt <= qcap) {
           cx.base = base;
           uint32_t m = cx.cand;
           int slot = base;
@@ -193,7 +193,7 @@ lunar_rollout_kernel(int64_t B, const float* __restrict__ sin0, float* __restric
             S.item[slot++] = ((uint32_t)el << 8) | (uint32_t)bit;
           }
         } else {
-          for (int slot = base; slot < RQCAP && slot < base + cnt; ++slot) S.item[slot] = ITEM_SKIP;
+          for (int slot = base; slot < qcap && slot < base + cnt; ++slot) S.item[slot] = ITEM_SKIP;
         }
       }
     }
@@ -204,7 +204,7 @@ lunar_rollout_kernel(int64_t B, const float* __restrict__ sin0, float* __restric
 #endif
     // ---- phase B: items across the warps first ---------------------------------------------------
     {
-      const int n = S.qcount < RQCAP ? S.qcount : RQCAP;
+      const int n = S.qcount < qcap ? S.qcount : qcap;
       for (int i = lane * RWARPS + warp; i < n; i += RTPB) {
         const uint32_t it = S.item[i];
         if (it == ITEM_SKIP) continue;
@@ -296,6 +296,11 @@ extern "C" int cx_launch_lunar_rollout_kernel(cudaStream_t st, int64_t B, const 
     const int v = atoi(env);
     if ((v == 8 || v == 16 || v == 32) && v >= RWARPS) epb = v;
   }
+  int qcap = RQCAP;
+  if (const char* env = getenv("COTIX_ROLLOUT_QCAP")) {  // tests force the queue-overflow branch with a small value
+    const int v = atoi(env);
+    if (v >= 0 && v < RQCAP) qcap = v;
+  }
   const unsigned blocks = (unsigned)((B + epb - 1) / epb);
   static bool attr_set[64];
   int dev = 0;
@@ -306,7 +311,7 @@ extern "C" int cx_launch_lunar_rollout_kernel(cudaStream_t st, int64_t B, const 
     attr_set[dev] = true;
   }
   lunar_rollout_kernel<<<blocks, RTPB, sizeof(RolloutShared), st>>>(B, sin0, sout0, stride, ld, actions, action_stride,
-                                                n_actions > 0 ? n_actions : 1, n_steps, reward, done, obs, *p, D, epb);
+                                                n_actions > 0 ? n_actions : 1, n_steps, reward, done, obs, *p, D, epb, qcap);
   cx_count_launch();
   return cx_check_launch("lunar_rollout_kernel");
 }

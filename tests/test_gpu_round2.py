@@ -449,3 +449,24 @@ def test_rollout_kernel_tape(cuda_lib, oracle, exact_trig):
         ll.step(st, acts[t], P, inplace=True, mode="fused")
         if t in (0, 17, T - 1):
             _eq(ro.tape[t + 1].cpu().numpy(), st.numpy(), f"tape slot {t + 1}")
+
+
+def test_rollout_kernel_queue_overflow(cuda_lib, oracle, exact_trig, monkeypatch):
+    """The rollout kernel's per-block item queue overflowing (COTIX_ROLLOUT_QCAP = 3 slots for up to 32 envs):
+    envs whose items do not fit evaluate their own pairs in phase C — same tape as with the full queue."""
+    import torch
+    from parallax_b200 import lunar_lander as ll
+
+    P = ll.default_params()
+    B, T = 300, 30
+    rng = np.random.default_rng(78)
+    s0 = perturbed_lunar_state(oracle.lunar_reset(lunar_keys(B, offset=2), P), rng, P)
+    acts = torch.from_numpy(rng.uniform(-1, 1, size=(T, 2, B)).astype(np.float32)).cuda()
+    st0 = ll.LunarState.from_numpy(s0)
+    full = ll.rollout(st0, acts, T, P, mode="fused").tape.cpu().numpy()
+    monkeypatch.setenv("COTIX_ROLLOUT_QCAP", "3")
+    small = ll.rollout(st0, acts, T, P, mode="fused").tape.cpu().numpy()
+    monkeypatch.setenv("COTIX_ROLLOUT_QCAP", "0")
+    none = ll.rollout(st0, acts, T, P, mode="fused").tape.cpu().numpy()
+    _eq(small, full, "tape with a 3-slot queue"); _eq(none, full, "tape with no queue at all")
+    assert not np.array_equal(full[1, :18], full[-1, :18])
