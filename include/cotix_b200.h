@@ -241,7 +241,7 @@ int cotix_lunar_step(void* stream, int64_t B, const float* state_in, float* stat
                      float* obs, const CotixLunarParams* p);
 
 /*
- * The same step run as a WAVEFRONT PIPELINE (csrc/lunar_pipeline.cu): 1 memset + 5 small dense
+ * The same step run as a WAVEFRONT PIPELINE (csrc/lunar_pipeline.cu): 1 memset per call + 6 small dense
  * kernels with stream-compacted work queues in a caller-provided DEVICE workspace, instead of
  * one fused kernel.  Results are identical bit for bit; it is several times faster for large,
  * contact-rich batches.  K = params->substeps sub-steps run the four step stages K times (an env

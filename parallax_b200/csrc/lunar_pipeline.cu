@@ -8,7 +8,7 @@
 // at the points where it becomes irregular, stream-compact the irregular work into queues in
 // HBM, and run every stage as a dense kernel over its queue.
 //
-//   memset   counters
+//   memset   counters (once per enqueue; between steps the finish stage zeroes them)
 //   K_A  integrate  (thread = env)        Euler + gravity + engines + exact broadphase; envs with
 //                                         candidate pairs write their world polygons + terrain to
 //                                         a 192-byte record, append (env, pair) items and join
@@ -22,7 +22,7 @@
 //
 // Queue counters live in device memory; the queue kernels are launched with a fixed grid (a
 // multiple of the SM count) and loop over the count they read on the device, so the whole step
-// is 1 memset + 5 launches with no host synchronisation and is CUDA-Graph capturable.  All
+// is 6 launches (+ 1 memset per enqueue) with no host synchronisation and is CUDA-Graph capturable.  All
 // stages call the same device functions as the fused kernel (cx_lunar_step.cuh): results are
 // identical bit for bit.
 #include <mutex>
@@ -50,7 +50,13 @@ constexpr int REC_FLOATS = 48;  // 192 B per env: polys 0..27, heights 28..35, k
 constexpr uint32_t BASE_INLINE = 0xFFFFFFFFu;
 constexpr int F_CRASH_SHIFT = 25, F_RC_SHIFT = 26, F_LC_SHIFT = 27;
 
-enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 4, CTR_WORDS = 16 };
+// Queue counters.  They are zeroed by a memset once per enqueue; between the steps of a multi-step enqueue the
+// FINISH stage zeroes them for the next step (after copying them to CTR_SNAP.. for cx_lunar_pipeline_counters),
+// so that a step is kernels only and every stage can be a programmatic dependent launch of the one before.  The
+// reset queue's counter is written by finish and read by the reset stage that follows it, so it alternates
+// between two words with the parity of the step: finish(t) zeroes the one reset(t - 1) has long finished with.
+enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 4, CTR_RESET_ODD = 5, CTR_SNAP = 8,
+       CTR_WORDS = 16 };
 
 // minimum resident blocks per SM asked of ptxas for the two dense kernels (register caps)
 #ifndef CX_INTEGRATE_MINB
@@ -128,6 +134,7 @@ __global__ void __launch_bounds__(TPB, CX_INTEGRATE_MINB)
 pipe_integrate_kernel(int64_t B, const float* __restrict__ sin_, float* __restrict__ sout, int64_t ld,
                       const float* __restrict__ action, const __grid_constant__ CotixLunarParams P,
                       const LunarDerived D, const PipeWs ws, int k, int K) {
+  cudaGridDependencySynchronize();  // after the first step of an enqueue this stage follows reset / finish as a PDL
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   // sub-step k of K: an env that finished in an earlier sub-step of this call is frozen
   // (cotix/_envs.py:81-103) — nothing of it is read, written or queued
@@ -503,8 +510,19 @@ __global__ void __launch_bounds__(TPB, CX_FINISH_MINB)
 pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __restrict__ action,
                    float* __restrict__ reward, uint8_t* __restrict__ done, float* __restrict__ obs,
                    const __grid_constant__ CotixLunarParams P, const __grid_constant__ LunarDerived D, const PipeWs ws,
-                   int k, int K) {
+                   int k, int K, int par) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    // the narrow / contact stages are done with their counters: keep a copy for the host, zero them for the next
+    // step's integrate stage (no memset node between the steps)
+    ws.ctr[CTR_SNAP + 0] = ws.ctr[CTR_ITEMS];
+    ws.ctr[CTR_SNAP + 1] = ws.ctr[CTR_HITS];
+    ws.ctr[CTR_SNAP + 2] = ws.ctr[CTR_CENV];
+    ws.ctr[CTR_SNAP + 3] = 0u;  // the reset stage, when there is one, puts its count here
+    ws.ctr[CTR_SNAP + 4] = ws.ctr[CTR_OVERFLOW];
+    ws.ctr[CTR_ITEMS] = ws.ctr[CTR_HITS] = ws.ctr[CTR_CENV] = ws.ctr[CTR_OVERFLOW] = 0u;
+    ws.ctr[par ? CTR_RESET : CTR_RESET_ODD] = 0u;  // the OTHER step parity's reset counter
+  }
   const int64_t e = (int64_t)blockIdx.x * TPB + threadIdx.x;
   bool want_reset = false;
   if (e < B) {
@@ -530,18 +548,19 @@ pipe_finish_kernel(int64_t B, float* __restrict__ s, int64_t ld, const float* __
                                     (cw >> F_RC_SHIFT) & 1u, (cw >> F_LC_SHIFT) & 1u, ws, k, K);
     }
   }
-  const uint32_t slot = queue_push(&ws.ctr[CTR_RESET], want_reset);
+  const uint32_t slot = queue_push(&ws.ctr[par ? CTR_RESET_ODD : CTR_RESET], want_reset);
   if (want_reset) ws.renv[slot] = (uint32_t)e;
 }
 
 // ---- K_R -----------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB)
 pipe_reset_kernel(float* __restrict__ s, int64_t ld, float* __restrict__ obs,
-                  const __grid_constant__ CotixLunarParams P, const PipeWs ws) {
+                  const __grid_constant__ CotixLunarParams P, const PipeWs ws, int par) {
   cudaGridDependencySynchronize();  // programmatic dependent launch: the previous stage is complete past here
   // eight lanes per finished env (lunar_auto_reset_coop): a reset is a chain of ~30 threefry calls,
   // and this stage is pure latency (a few hundred envs per step)
-  const uint32_t n = ws.ctr[CTR_RESET];
+  const uint32_t n = ws.ctr[par ? CTR_RESET_ODD : CTR_RESET];
+  if (blockIdx.x == 0 && threadIdx.x == 0) ws.ctr[CTR_SNAP + 3] = n;
   const uint32_t warp = (blockIdx.x * TPB + threadIdx.x) >> 5, nwarps = (gridDim.x * TPB) >> 5;
   const uint32_t grp = (threadIdx.x & 31u) >> 3, sub = threadIdx.x & 7u;
   for (uint32_t r0 = warp * 4u; r0 < n; r0 += nwarps * 4u) {
@@ -805,7 +824,7 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
   if (prof) cudaEventRecord(g_evb[k], stream)
 #define CX_MARK_E(k, stream) \
   if (prof) cudaEventRecord(g_eve[k], stream)
-  // the chain of one range: per step and sub-step 1 memset + 4 kernels, then the reset stage.
+  // the chain of one range: one memset, then per step and sub-step 5 kernels, then the reset stage.
   // Stages 2..5 are launched with programmatic stream serialization: their blocks may be set up
   // while the previous stage drains, and wait in cudaGridDependencySynchronize() for its results.
   const bool trace = g_trace && !prof && K == 1 && q.n_steps <= TR_STEPS;
@@ -854,6 +873,10 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
       const int hr = (*pre)(cs, r, off, n);
       if (hr != 0) return hr;
     }
+    // counters: zeroed here once; from then on by the finish stage of every (sub-)step
+    if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, cs) != cudaSuccess) return cx_check_launch("pipeline memset");
+    int par = 0;       // parity of the (sub-)step: which of the two reset counters finish / reset use
+    bool first = true;  // the first kernel of the chain follows a memset, not a kernel: no PDL
     for (int t = 0; t < q.n_steps; ++t) {
       const float* sin_ = q.sin0 + (int64_t)t * q.stride + off;
       float* sout = q.sout0 + (int64_t)t * q.stride + off;
@@ -863,9 +886,9 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
       // the four step stages K times — sub-steps after the first run in place on the output state —
       // then one reset stage
       for (int k = 0; k < K; ++k) {
-        if (cudaMemsetAsync(ws.ctr, 0, CTR_WORDS * 4, cs) != cudaSuccess) return cx_check_launch("pipeline memset");
         CX_MARK_B(0, cs);
-        set_attrs(false, false);
+        set_attrs(!first, false);
+        first = false;
         cfg.gridDim = dim3(env_blocks);
         cudaLaunchKernelEx(&cfg, pipe_integrate_kernel, n, k == 0 ? sin_ : (const float*)sout, sout, ld, act, *p, D, ws,
                            k, K);
@@ -904,7 +927,8 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
         CX_MARK_B(3, cs);
         set_attrs(true, false);
         cfg.gridDim = dim3(env_blocks);
-        cudaLaunchKernelEx(&cfg, pipe_finish_kernel, n, sout, ld, act, rw, dn, ob, *p, D, ws, k, K);
+        cudaLaunchKernelEx(&cfg, pipe_finish_kernel, n, sout, ld, act, rw, dn, ob, *p, D, ws, k, K, par);
+        if (k + 1 < K) par ^= 1;  // the last sub-step's parity is the reset stage's
         CX_MARK_E(3, cs);
         CX_TRACE(3, cs);
       }
@@ -912,8 +936,9 @@ static int enqueue_steps(cudaStream_t st, int64_t B, int64_t ld, const StepSeq& 
       if (p->auto_reset) {
         set_attrs(true, true);
         cfg.gridDim = dim3(qgrid(n));
-        cudaLaunchKernelEx(&cfg, pipe_reset_kernel, sout, ld, ob, *p, ws);
+        cudaLaunchKernelEx(&cfg, pipe_reset_kernel, sout, ld, ob, *p, ws, par);
       }
+      par ^= 1;
       CX_MARK_E(4, cs);
       CX_TRACE(4, cs);
       CX_MARK_E(5, cs);
@@ -1015,7 +1040,7 @@ extern "C" int cx_lunar_pipeline_counters(cudaStream_t st, int64_t B, const void
     if (cudaMemcpyAsync(c, plan.ws[r].ctr, sizeof(c), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
         cudaStreamSynchronize(st) != cudaSuccess)
       return cx_check_launch("pipeline counters");
-    for (int i = 0; i < 5; ++i) out[i] += c[i];
+    for (int i = 0; i < 5; ++i) out[i] += c[CTR_SNAP + i];  // the finish stage's copy (the live counters are zeroed)
   }
   return COTIX_OK;
 }

@@ -78,7 +78,7 @@ def test_steps_graph_replay(cuda_lib, oracle, exact_trig, pipe_cfg, mode):
     g = ll.StepsGraph(st, torch.from_numpy(acts).cuda(), T, P, want_obs=True, mode=mode)
     info = g.info()
     if mode == "pipeline":
-        assert info["kernel_launches"] == 3 * T * 6 and info["nodes"] >= 3 * T * 7
+        assert info["kernel_launches"] == 3 * T * 6 and info["nodes"] >= 3 * T * 6 + 3  # + one memset per range
     else:
         assert info["kernel_launches"] == 1  # small batch, no workspace: all T steps in one launch (lunar_rollout.cu)
     import parallax_b200
