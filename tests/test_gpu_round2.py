@@ -470,3 +470,27 @@ def test_rollout_kernel_queue_overflow(cuda_lib, oracle, exact_trig, monkeypatch
     none = ll.rollout(st0, acts, T, P, mode="fused").tape.cpu().numpy()
     _eq(small, full, "tape with a 3-slot queue"); _eq(none, full, "tape with no queue at all")
     assert not np.array_equal(full[1, :18], full[-1, :18])
+
+
+def test_rollout_kernel_long_horizon_config1(cuda_lib, oracle, exact_trig):
+    """BASELINE config 1 shape through the rollout kernel: 1000 steps from reset(key), zero action, in ONE launch,
+    against the same 1000 steps through the wavefront pipeline (one launch per stage and step) and, for a few envs,
+    the oracle: free fall, touchdown, resting contact — state identical bit for bit at the end."""
+    import torch
+    from parallax_b200 import lunar_lander as ll
+
+    P = ll.default_params()
+    B, T = 320, 1000
+    keys = lunar_keys(B, offset=21)
+    s0 = oracle.lunar_reset(keys, P)
+    st = ll.LunarState.from_numpy(s0)
+    ll.steps(st, None, T, P, mode="fused")  # no workspace: lunar_rollout_kernel
+    sp = ll.LunarState.from_numpy(s0)
+    ll.steps(sp, None, T, P, mode="pipeline")
+    _eq(st.numpy(), sp.numpy(), "rollout kernel vs pipeline after 1000 steps")
+    n = 6
+    ref = s0[:, :n].copy()
+    for _ in range(T):
+        ref = oracle.lunar_step(np.ascontiguousarray(ref), None, P)[0]
+    _eq(st.numpy()[:, :n], ref, "vs oracle")
+    assert np.abs(st.numpy()[1] - s0[1]).max() > 1.0  # the landers did come down
