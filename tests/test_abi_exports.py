@@ -111,3 +111,20 @@ def test_product_package_does_not_touch_the_oracle():
         src = open(path, errors="ignore").read()
         for needle in ("import oracle", "from oracle", "liboracle", "oracle/", "oracle_", "cotix_oracle"):
             assert needle not in src, (path, needle)
+
+
+def test_header_constants_match_the_python_mirror():
+    """Routing constants the Python mirror repeats: multi-step calls up to COTIX_ROLLOUT_MAX_ENVS envs go to the
+    block-resident rollout kernel (no workspace), larger ones to the pipeline."""
+    import re
+
+    from parallax_b200 import jax_ffi
+    from parallax_b200 import lunar_lander as ll
+
+    hdr = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "cotix_b200.h")).read()
+    m = re.search(r"#define\s+COTIX_ROLLOUT_MAX_ENVS\s+(\d+)", hdr)
+    assert m and int(m.group(1)) == ll.ROLLOUT_MAX_ENVS
+    assert not ll._use_pipe("auto", ll.ROLLOUT_MAX_ENVS, n_steps=100) and ll._use_pipe("auto", ll.ROLLOUT_MAX_ENVS + 1, n_steps=100)
+    assert not ll._use_pipe("auto", ll.PIPELINE_MIN_ENVS - 1) and ll._use_pipe("auto", ll.PIPELINE_MIN_ENVS)
+    assert ll._use_pipe("auto", 8192, n_steps=10, substeps=4) is False  # sub-steps: the per-step routing
+    assert "4736" in open(jax_ffi.__file__).read()
