@@ -34,7 +34,13 @@
 
 namespace {
 
-constexpr int TPB = 128;
+// threads per block of the env-indexed stages.  64, not 128: the integrate stage has two block barriers (queue
+// allocation), and with two warps per block instead of four fewer warps wait for the block's slowest one
+// (1 M envs: 196.4 -> 192.1 us per step; 32: the contact stage loses 12 us; 256: integrate 72 -> 112 us)
+#ifndef CX_PIPE_TPB
+#define CX_PIPE_TPB 64
+#endif
+constexpr int TPB = CX_PIPE_TPB;
 // Lanes of a warp that take work in the two sparse stages = 32 / SPREAD (template parameter, chosen per
 // launch by sparse_spread()).  At 1 M envs these stages are bound by warp-instruction throughput and
 // SPREAD = 1 is best (2 / 4: 61 -> 117 -> 251 us); at a few thousand envs they are ONE thin wave whose time
@@ -60,10 +66,10 @@ enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 
 
 // minimum resident blocks per SM asked of ptxas for the two dense kernels (register caps)
 #ifndef CX_INTEGRATE_MINB
-#define CX_INTEGRATE_MINB 6
+#define CX_INTEGRATE_MINB (768 / CX_PIPE_TPB)
 #endif
 #ifndef CX_FINISH_MINB
-#define CX_FINISH_MINB 8  // 64 registers: 72.5 -> 64 us (profiles/r2h_variants.jsonl); integrate is unchanged by 5..8
+#define CX_FINISH_MINB (1024 / CX_PIPE_TPB)  // 64 registers: 72.5 -> 64 us (profiles/r2h_variants.jsonl); integrate is unchanged by 5..8 blocks of 128
 #endif
 
 struct PipeWs {
