@@ -514,9 +514,12 @@ int cotix_lunar_rollout_bwd(void* stream, int64_t B, int32_t T, const float* tap
   constexpr int NG = 4;
   static const char* env_overlap = getenv("COTIX_ADJ_OVERLAP");  // measurement aid: "0" turns the overlap off
   const bool overlap = g_adj_pipelined != 0 && !(env_overlap && env_overlap[0] == '0');
-  static const char* env_runs = getenv("COTIX_ADJ_RUNS");  // measurement aid: "1" = no runs for small batches
-  if (jac && group >= T && T >= 1 && use_sweep_kernel(B) && env_runs && env_runs[0] == '1') {
-    // small batch: decisions + Jacobians of the whole rollout at full grid, then the sweep in one launch
+  static const char* env_runs = getenv("COTIX_ADJ_RUNS");  // measurement aid: "4" = the four overlapped runs
+  if (jac && group >= T && T >= 1 && use_sweep_kernel(B) && !(env_runs && env_runs[0] == '4')) {
+    // small batch: decisions + Jacobians of the whole rollout at full grid, then the sweep in ONE launch on the
+    // caller's stream.  Measured (4096 envs x 100 steps): 3.74 ms against 3.87-4.02 with the runs overlapped on
+    // the side stream -- the latency-bound sweep stretches when the Jacobian kernel shares its SMs -- and the
+    // slot order of the Jacobians, hence the gradient's rounding, is the same from call to call
     int rc = cx_launch_lunar_decide((cudaStream_t)stream, B, T, tape, ld, actions, dt, flags, jctr, jlist, jM, jcap, p, 0);
     if (rc == 0)
       rc = cx_launch_lunar_sweep_bwd((cudaStream_t)stream, B, 0, T, tape, ld, actions, g, g_actions, flags, dt, jM, p);

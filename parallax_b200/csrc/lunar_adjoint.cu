@@ -25,6 +25,8 @@
 // SAME device functions the forward kernels use (so every decision is reproduced bit for bit —
 // checked against state_{t+1} when the caller passes it), keeps the few intermediates the
 // adjoint needs in registers / local memory and walks the step backwards.  One env per thread.
+#include <cstdlib>
+
 #include "cx_launch.cuh"
 #include "cx_lunar_step.cuh"
 
@@ -1058,7 +1060,11 @@ extern "C" int cx_launch_lunar_sweep_bwd(cudaStream_t st, int64_t B, int s_lo, i
   if (B == 0 || s_hi <= s_lo) return 0;
   LunarDerived D;
   cx_lunar_derive(p, &D);
-  const int epw = B <= 8192 ? 8 : 16;
+  int epw = 16;  // measured, 4096 envs x 100 steps, 2 / 4 / 8 / 16 / 32 envs per warp: 5.08 / 4.57 / 4.02 / 3.74 / 4.05 ms
+  if (const char* env = getenv("COTIX_SWEEP_EPW")) {  // measurement aid
+    const int v = atoi(env);
+    if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) epw = v;
+  }
   const int64_t warps = (B + epw - 1) / epw;
   lunar_sweep_bwd_kernel<<<(unsigned)((warps + TPB / 32 - 1) / (TPB / 32)), TPB, 0, st>>>(
       B, s_lo, s_hi, tape, ld, actions, g, g_actions, flags, dtape0, jacM, *p, D, epw);
