@@ -32,7 +32,10 @@
 
 namespace {
 
-constexpr int TPB = 64;
+#ifndef CX_ADJ_TPB
+#define CX_ADJ_TPB 64
+#endif
+constexpr int TPB = CX_ADJ_TPB;
 
 struct G6 {  // cotangent of a BodyS
   float px, py, vx, vy, ang, w;
@@ -973,7 +976,10 @@ lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
 // env).  The replay of a step depends only on the state before it, which is on the tape, so unlike
 // the reverse sweep it is not sequential in time — this is where the irregular work of the backward
 // pass (narrowphase, coins) runs, at full occupancy instead of one small launch per step.
-constexpr int DECIDE_TILE = TPB * 8;
+#ifndef CX_DECIDE_MUL
+#define CX_DECIDE_MUL 8
+#endif
+constexpr int DECIDE_TILE = TPB * CX_DECIDE_MUL;
 __global__ void __launch_bounds__(TPB)
 lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t ld,
                     const float* __restrict__ actions, float* __restrict__ dtape, const JacWs jw,

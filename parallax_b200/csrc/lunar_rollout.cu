@@ -295,7 +295,7 @@ extern "C" int cx_launch_lunar_rollout_kernel(cudaStream_t st, int64_t B, const 
   while (epb > RWARPS && (B + epb - 1) / epb < (sms * 2) / 3) epb >>= 1;  // 4096 envs: 128 blocks of 32 beat 256 of 16
   if (const char* env = getenv("COTIX_ROLLOUT_EPB")) {  // measurement aid
     const int v = atoi(env);
-    if ((v == 8 || v == 16 || v == 32) && v >= RWARPS) epb = v;
+    if (v >= RWARPS && v <= REPB && v % RWARPS == 0) epb = v;
   }
   int qcap = RQCAP;
   if (const char* env = getenv("COTIX_ROLLOUT_QCAP")) {  // tests force the queue-overflow branch with a small value
