@@ -66,7 +66,9 @@ enum { CTR_ITEMS = 0, CTR_HITS = 1, CTR_CENV = 2, CTR_RESET = 3, CTR_OVERFLOW = 
 
 // minimum resident blocks per SM asked of ptxas for the two dense kernels (register caps)
 #ifndef CX_INTEGRATE_MINB
-#define CX_INTEGRATE_MINB (768 / CX_PIPE_TPB)
+// 640 threads per SM = 96 registers per thread: the kernel keeps its 28 polygon floats next to the state without
+// squeezing (80 registers at 768 threads: 70.0 us; 96 at 576 - 640: 65.2 - 65.9; 119 at 512: 71.2)
+#define CX_INTEGRATE_MINB (640 / CX_PIPE_TPB)
 #endif
 #ifndef CX_FINISH_MINB
 #define CX_FINISH_MINB (1024 / CX_PIPE_TPB)  // 64 registers: 72.5 -> 64 us (profiles/r2h_variants.jsonl); integrate is unchanged by 5..8 blocks of 128
