@@ -782,7 +782,10 @@ lunar_step_bwd_kernel(int64_t B, const float* __restrict__ sin_, const float* __
 // keeps the cotangents of its `epw` envs (lanes 0 .. epw-1; few, so that few matrices queue up per step) in
 // registers for the whole run of steps.  Needs the decision tape and the Jacobians of the run (taped mode).
 // The arithmetic is that of lunar_step_bwd_kernel, operation for operation: identical gradients.
-__global__ void __launch_bounds__(TPB)
+#ifndef CX_SWEEP_MINB
+#define CX_SWEEP_MINB 1
+#endif
+__global__ void __launch_bounds__(TPB, CX_SWEEP_MINB)
 lunar_sweep_bwd_kernel(int64_t B, int s_lo, int s_hi, const float* __restrict__ tape, int64_t ld,
                        const float* __restrict__ actions, float* g_io, float* __restrict__ g_actions,
                        uint32_t* __restrict__ flags_out, const float* __restrict__ dtape0,
@@ -906,7 +909,13 @@ lunar_sweep_bwd_kernel(int64_t B, int s_lo, int s_hi, const float* __restrict__ 
 // (g_state; g_action) = M g_next is formed here for all steps of a group at once: thread = (env-step
 // with contacts, k) evaluates the VJP of unit cotangent k.  The sequential sweep then spends a
 // matrix-vector product on such an env-step instead of the contact adjoint.
-__global__ void __launch_bounds__(TPB)
+// 20 blocks of 64 threads per SM (51 registers; unconstrained: 96 registers, 10 blocks): the kernel is throughput
+// work over (contact env-step, unit cotangent) and gains from occupancy what it loses to spills --
+// backward pass of 4096 envs x 100 steps 3.72 -> 3.51 ms (12 / 16 / 20 / 24 blocks: 3.63 / 3.59 / 3.51 / 3.51)
+#ifndef CX_JAC_MINB
+#define CX_JAC_MINB 20
+#endif
+__global__ void __launch_bounds__(TPB, CX_JAC_MINB)
 lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
                       const float* __restrict__ actions, const float* __restrict__ dtape,
                       uint32_t* __restrict__ flags_out, const JacWs jw,
@@ -980,7 +989,10 @@ lunar_jacobian_kernel(int64_t B, const float* __restrict__ tape, int64_t ld,
 #define CX_DECIDE_MUL 8
 #endif
 constexpr int DECIDE_TILE = TPB * CX_DECIDE_MUL;
-__global__ void __launch_bounds__(TPB)
+#ifndef CX_DEC_MINB
+#define CX_DEC_MINB 1
+#endif
+__global__ void __launch_bounds__(TPB, CX_DEC_MINB)
 lunar_decide_kernel(int64_t B, int nt, const float* __restrict__ tape, int64_t ld,
                     const float* __restrict__ actions, float* __restrict__ dtape, const JacWs jw,
                     const __grid_constant__ CotixLunarParams P, const LunarDerived D) {
