@@ -189,7 +189,7 @@ CX_DEV int choose_generic(uint32_t live, int nb, float u) {
 }
 
 #ifndef CXS_MINB
-#define CXS_MINB 8
+#define CXS_MINB 6  // 4 / 5 / 6 / 8 / 10 / 12 blocks per SM: 0.728 / 0.690 / 0.614 / 0.627 / 0.662 / 0.705 ms per RoboCup step of 262144 envs
 #endif
 __global__ void __launch_bounds__(128, CXS_MINB)
 scene_step_kernel(const SceneDesc* __restrict__ S, int64_t B, float* __restrict__ state, int64_t ld,
